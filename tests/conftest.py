@@ -1,0 +1,35 @@
+import os
+import sys
+import numpy as np
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+GOLDEN = os.path.join(ROOT, "tests", "golden")
+
+
+def pytest_configure(config):
+    config.addinivalue_line("markers", "gpu: needs a CUDA device (run on the B200 box)")
+
+
+def load_golden(name):
+    return np.load(os.path.join(GOLDEN, name + ".npz"))
+
+
+GOLDEN_CASES = ["g_tiny", "g_small", "g_loops", "g_outliers", "g_odom_only", "c1"]
+
+
+def wrap(a):
+    return np.arctan2(np.sin(a), np.cos(a))
+
+
+def state_diff(pose_a, lm_a, pose_b, lm_b):
+    """max abs difference of two states, theta compared modulo 2*pi, relative to max(1, |ref|)."""
+    d = pose_a - pose_b
+    d[:, 2] = wrap(d[:, 2])
+    scale_p = np.maximum(1.0, np.abs(pose_b))
+    out = float(np.max(np.abs(d) / scale_p)) if len(d) else 0.0
+    if len(lm_a):
+        out = max(out, float(np.max(np.abs(lm_a - lm_b) / np.maximum(1.0, np.abs(lm_b)))))
+    return out
