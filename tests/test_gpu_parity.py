@@ -1,0 +1,191 @@
+"""GPU parity tests (run on the B200 box): the CUDA path, called through the C ABI, against the
+CPU oracle on the same wire payloads.  Tolerances are the north star's: state 1e-9 relative,
+chi2 trajectory 1e-8 relative (fp64)."""
+import numpy as np
+import pytest
+from conftest import load_golden, GOLDEN_CASES, state_diff
+
+pytestmark = pytest.mark.gpu
+
+STATE_TOL = 1e-9
+CHI2_TOL = 1e-8
+
+
+@pytest.fixture(scope="module")
+def gpu():
+    from toyslam_b200.capi import GraphOptimizerGpu
+    import torch
+    assert torch.cuda.is_available(), "GPU tests need a CUDA device"
+    return GraphOptimizerGpu
+
+
+def dense_from_blocks(sysd, od_i, od_j, lm_i, lm_l, P, L):
+    n = 3 * P + 2 * L
+    H = np.zeros((n, n)); b = np.zeros(n)
+    tri = [(0, 0), (0, 1), (0, 2), (1, 1), (1, 2), (2, 2)]
+    for p in range(P):
+        for v, (r, c) in zip(sysd["hpp_diag"][p], tri):
+            H[3 * p + r, 3 * p + c] = v; H[3 * p + c, 3 * p + r] = v
+    b[:3 * P] = sysd["b_pose"].reshape(-1)
+    for k, (i, j) in enumerate(zip(od_i, od_j)):
+        for q in range(3):
+            H[3 * i + q, 3 * j + q] += sysd["hpp_off"][k, q]; H[3 * j + q, 3 * i + q] += sysd["hpp_off"][k, q]
+    for k, (i, l) in enumerate(zip(lm_i, lm_l)):
+        H[3 * i:3 * i + 3, 3 * P + 2 * l:3 * P + 2 * l + 2] += sysd["hpl"][k]
+        H[3 * P + 2 * l:3 * P + 2 * l + 2, 3 * i:3 * i + 3] += sysd["hpl"][k].T
+    for l in range(L):
+        o = 3 * P + 2 * l
+        H[o, o], H[o, o + 1], H[o + 1, o], H[o + 1, o + 1] = sysd["hll"][l, 0], sysd["hll"][l, 1], sysd["hll"][l, 1], sysd["hll"][l, 2]
+    b[3 * P:] = sysd["b_lm"].reshape(-1)
+    return H, b
+
+
+@pytest.mark.parametrize("name", GOLDEN_CASES)
+def test_linearize_and_solve_match_oracle(gpu, name):
+    from oracle.oracle import OracleGraph
+    d = load_golden(name)
+    payload = d["request"].tobytes()
+    o = OracleGraph(payload)
+    Ho, bo, chi2o = o.assemble_dense()
+    g = gpu(pcg_tol=1e-14, pcg_max_iters=5000)
+    c = g.load_wire(payload)
+    assert (c.n_pose, c.n_lm, c.n_odom, c.n_lmedge) == (o.P, o.Lm, o.Eo, o.El)
+    pi, li = g.ids(); opi, oli = o.ids()
+    assert np.array_equal(pi, opi) and np.array_equal(li, oli)
+    st = g.linearize()
+    assert abs(st.chi2 - chi2o) <= 1e-12 * chi2o
+    H, b = dense_from_blocks(g.system(), *o.edge_index(), o.P, o.Lm)
+    assert np.max(np.abs(H - Ho)) <= 1e-12 * np.max(np.abs(Ho))
+    assert np.max(np.abs(b - bo)) <= 1e-11 * np.max(np.abs(bo))
+    # solve: landmark Schur + PCG against a dense LAPACK solve of the oracle's system
+    s2 = g.solve()
+    dp, dl = g.delta()
+    x = np.linalg.solve(Ho, bo)
+    got = np.r_[dp.reshape(-1), dl.reshape(-1)]
+    assert np.max(np.abs(got - x)) <= 1e-9 * max(1.0, np.max(np.abs(x))), (s2.pcg_iters, s2.pcg_rel_residual)
+
+
+@pytest.mark.parametrize("name", GOLDEN_CASES)
+def test_optimize_matches_oracle(gpu, name):
+    from oracle.oracle import OracleGraph
+    d = load_golden(name)
+    payload = d["request"].tobytes()
+    iters, exits = int(d["iterations"]), bool(d["exits"])
+    o = OracleGraph(payload)
+    traj, code = o.optimize_dense(iters, exits)
+    g = gpu(iterations=iters, pcg_tol=1e-14, pcg_max_iters=5000, enable_exits=exits)
+    g.load_wire(payload)
+    rep, per = g.optimize()
+    got = np.array([p.chi2 for p in per])
+    assert rep.iterations_run == len(traj) and rep.exit_code == code
+    assert np.max(np.abs(got - traj) / np.abs(traj)) < CHI2_TOL
+    assert state_diff(*g.state(), *o.state()) < STATE_TOL
+    # and against the golden trajectory produced from the reference's Python linearisation
+    assert len(d["traj"]) == len(got)
+    assert np.max(np.abs(got - d["traj"]) / np.abs(d["traj"])) < (1e-9 if name == "c1" else 5e-6)
+
+
+def test_structure_is_bit_exact(gpu):
+    """The integer edge -> block index map held on the device equals an independent numpy derivation."""
+    from oracle.oracle import OracleGraph
+    from toyslam_b200 import synth
+    for payload in (load_golden("c1")["request"].tobytes(), synth.to_payload(synth.make_config("c2", scale=0.05))):
+        o = OracleGraph(payload)
+        _, _, lm_i, lm_l = o.edge_index()
+        g = gpu(); c = g.load_wire(payload); s = g.structure()
+        order = np.lexsort((np.arange(len(lm_i)), lm_l, lm_i)).astype(np.uint32)
+        assert np.array_equal(s["lm_perm"], order)
+        ptr = np.r_[0, np.cumsum(np.bincount(lm_i, minlength=o.P))].astype(np.uint32)
+        assert np.array_equal(s["pose_ptr"], ptr)
+        slot_lm_expect = []
+        for (e0, e1, p0, p1, s0, s1, blk, _) in s["chunk_desc"]:
+            assert e1 - e0 <= 512 or p1 - p0 == 1
+            assert ptr[p0] <= e0 and e1 <= ptr[p1]
+            lms = lm_l[order[e0:e1]]; uniq = np.unique(lms)
+            assert s1 - s0 == len(uniq); slot_lm_expect.append(uniq)
+            pose_local = lm_i[order[e0:e1]] - p0
+            packed = (pose_local.astype(np.uint32) << 16) | np.searchsorted(uniq, lms).astype(np.uint32)
+            assert np.array_equal(s["lm_packed"][e0:e1], packed)
+        slot_lm = np.concatenate(slot_lm_expect) if slot_lm_expect else np.zeros(0, np.uint32)
+        assert np.array_equal(s["slot_lm"], slot_lm)
+        assert np.array_equal(s["lm_part_ptr"], np.r_[0, np.cumsum(np.bincount(slot_lm, minlength=o.Lm))])
+        assert np.array_equal(s["lm_part_idx"], np.argsort(slot_lm, kind="stable"))
+        # chunks tile the edge range and the blocks tile the pose range
+        cd = s["chunk_desc"]
+        assert cd[0, 0] == 0 and cd[-1, 1] == c.n_lmedge and np.array_equal(cd[1:, 0], cd[:-1, 1])
+
+
+def test_runs_are_bit_reproducible(gpu):
+    from toyslam_b200 import synth
+    payload = synth.to_payload(synth.make_config("c2", scale=0.2, seed=3))
+    outs = []
+    for _ in range(2):
+        g = gpu(iterations=4, enable_exits=False); g.load_wire(payload)
+        rep, per = g.optimize()
+        outs.append((np.array([p.chi2 for p in per]), *g.state(), [p.pcg_iters for p in per]))
+    assert np.array_equal(outs[0][0], outs[1][0]) and np.array_equal(outs[0][1], outs[1][1])
+    assert np.array_equal(outs[0][2], outs[1][2]) and outs[0][3] == outs[1][3]
+
+
+@pytest.mark.parametrize("cfg,scale", [("c2", 0.1), ("c3", 0.01), ("c5", 0.002)])
+def test_synthetic_matches_sparse_oracle(gpu, cfg, scale):
+    from oracle.oracle import OracleGraph
+    from toyslam_b200 import synth
+    payload = synth.to_payload(synth.make_config(cfg, scale=scale, seed=1))
+    o = OracleGraph(payload)
+    traj, its, code = o.optimize_sparse(8, False, tol=1e-14, max_pcg=20000, threads=0)
+    g = gpu(iterations=8, pcg_tol=1e-14, pcg_max_iters=20000, enable_exits=False); g.load_wire(payload)
+    rep, per = g.optimize()
+    got = np.array([p.chi2 for p in per])
+    assert np.max(np.abs(got - traj) / np.abs(traj)) < CHI2_TOL
+    assert state_diff(*g.state(), *o.state()) < STATE_TOL
+
+
+def test_reply_matches_oracle_reply(gpu):
+    from oracle.oracle import OracleGraph
+    from toyslam_b200 import wire
+    d = load_golden("g_loops"); payload = d["request"].tobytes()
+    o = OracleGraph(payload); o.optimize_dense(5, True)
+    g = gpu(iterations=5, pcg_tol=1e-14); g.load_wire(payload); g.optimize()
+    a, b = wire.decode_reply(g.reply()), wire.decode_reply(o.reply())
+    assert set(a["vertices"]) == set(b["vertices"]) and a["fixed"] == b["fixed"] and len(a["edges"]) == len(b["edges"])
+    for vid, (t, v) in a["vertices"].items():
+        assert t == b["vertices"][vid][0] and np.allclose(v, b["vertices"][vid][1], rtol=0, atol=2e-6)
+    key = lambda e: (e[0], e[1], e[2], e[3].tobytes(), e[4].tobytes())
+    assert sorted(map(key, a["edges"])) == sorted(map(key, b["edges"]))
+
+
+def test_load_soa_equals_load_wire(gpu):
+    from toyslam_b200 import synth
+    gr = synth.make_config("c2", scale=0.03, seed=5)
+    g1 = gpu(iterations=3, enable_exits=False); g1.load_wire(synth.to_payload(gr)); g1.optimize()
+    g2 = gpu(iterations=3, enable_exits=False); g2.load_soa(gr); g2.optimize()
+    assert np.array_equal(g1.state()[0], g2.state()[0]) and np.array_equal(g1.state()[1], g2.state()[1])
+
+
+def test_malformed_payload_returns_parse_error(gpu):
+    from toyslam_b200.capi import TsbError
+    buf = load_golden("g_small")["request"].tobytes()
+    g = gpu()
+    for cut in (0, 3, 17, len(buf) // 2, len(buf) - 1):
+        with pytest.raises(TsbError) as ei:
+            g.load_wire(buf[:cut])
+        assert ei.value.code == 2
+    g.load_wire(buf)                      # the context survives a rejected payload
+    assert g.linearize().chi2 > 0
+
+
+def test_full_size_c2_properties(gpu):
+    """BASELINE config 2 at full size: chi2 falls monotonically over the first iterations, the PCG
+    reaches its tolerance, and the whole run agrees with the sparse oracle on chi2."""
+    from oracle.oracle import OracleGraph
+    from toyslam_b200 import synth
+    payload = synth.to_payload(synth.make_config("c2"))
+    g = gpu(iterations=6, pcg_tol=1e-12, pcg_max_iters=20000, enable_exits=False); g.load_wire(payload)
+    rep, per = g.optimize()
+    chi = np.array([p.chi2 for p in per])
+    assert np.all(np.diff(chi) < 0)
+    assert all(p.pcg_rel_residual <= 1e-12 for p in per)
+    o = OracleGraph(payload)
+    traj, _, _ = o.optimize_sparse(6, False, tol=1e-12, max_pcg=20000, threads=0)
+    assert np.max(np.abs(chi - traj) / traj) < CHI2_TOL

@@ -1,0 +1,435 @@
+// api.cu -- C ABI (include/toyslam_b200.h): context, upload, Gauss-Newton driver.
+// The driver restates the control flow of OptimizerCpu<T>::Optimize (remote/optimizer/OptimizerCpu.h:70-182):
+// linearize -> "getting worse" test -> solve -> damped update (0.2) -> plateau / convergence tests.
+#include "../../include/toyslam_b200.h"
+#include "device_graph.h"
+
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+
+using namespace tsb;
+
+static std::string g_create_error;
+
+struct tsb_ctx {
+    tsb_config cfg{};
+    std::string err;
+    cudaStream_t stream = nullptr;
+    cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
+    HostGraph g;
+    Structure st;
+    Dev d{};
+    std::vector<void*> allocs;
+    double4* pose0 = nullptr; double2* lm0 = nullptr;     // state as loaded (tsb_reset_state)
+    double* tmp_xyt = nullptr;                            // 3 * (nP + nG) scratch
+    double* h_scal = nullptr; int* h_flags = nullptr;     // pinned
+    bool loaded = false, linearized = false, solved = false;
+    uint32_t part_cap = 0;
+};
+
+namespace {
+
+#define CU(call)                                                                                   \
+    do { cudaError_t e_ = (call); if (e_ != cudaSuccess) {                                         \
+        c->err = std::string(#call) + ": " + cudaGetErrorString(e_); return TSB_ECUDA; } } while (0)
+
+void free_graph(tsb_ctx* c) {
+    for (void* p : c->allocs) cudaFree(p);
+    c->allocs.clear(); c->d = Dev{}; c->loaded = c->linearized = c->solved = false;
+    c->pose0 = nullptr; c->lm0 = nullptr; c->tmp_xyt = nullptr;
+}
+
+template <typename T> int dalloc(tsb_ctx* c, T*& out, size_t n) {
+    void* p = nullptr;
+    if (cudaMalloc(&p, std::max<size_t>(n, 1) * sizeof(T)) != cudaSuccess) {
+        cudaGetLastError(); c->err = "cudaMalloc failed (" + std::to_string(n * sizeof(T)) + " bytes)"; return TSB_ENOMEM; }
+    c->allocs.push_back(p); out = (T*)p; return TSB_OK;
+}
+template <typename T, typename U> int upload(tsb_ctx* c, const U*& out, const std::vector<T>& v) {
+    static_assert(sizeof(T) == sizeof(U) || sizeof(U) % sizeof(T) == 0, "layout");
+    T* p = nullptr;
+    if (int rc = dalloc(c, p, v.size())) return rc;
+    if (!v.empty()) CU(cudaMemcpyAsync(p, v.data(), v.size() * sizeof(T), cudaMemcpyHostToDevice, c->stream));
+    out = reinterpret_cast<const U*>(p); return TSB_OK;
+}
+#define TRY(x) do { if (int rc_ = (x)) return rc_; } while (0)
+
+int upload_graph(tsb_ctx* c) {
+    const HostGraph& g = c->g; const Structure& s = c->st; Dev& d = c->d;
+    d.nP = s.nP; d.nG = s.nG; d.L = g.L; d.nE = (uint32_t)s.lm_perm.size(); d.nO = (uint32_t)s.od_local.size();
+    d.nOwned = s.n_od_owned; d.nChunks = (uint32_t)s.chunks.size(); d.nBlocks = (uint32_t)s.blk_chunk_ptr.size() - 1;
+    d.nSlots = (uint32_t)s.slot_lm.size();
+    // per-edge data gathered into assembly order
+    std::vector<double> z(2ull * d.nE), w(2ull * d.nE);
+    for (uint32_t k = 0; k < d.nE; ++k) {
+        const uint32_t e = s.le_local[s.lm_perm[k]];
+        z[2ull * k] = g.le_z[2ull * e]; z[2ull * k + 1] = g.le_z[2ull * e + 1];
+        w[2ull * k] = g.le_w[2ull * e]; w[2ull * k + 1] = g.le_w[2ull * e + 1];
+    }
+    std::vector<double> oz(6ull * d.nO), ow(3ull * d.nO);
+    for (uint32_t k = 0; k < d.nO; ++k) {
+        const uint32_t e = s.od_local[k];
+        std::memcpy(&oz[6ull * k], &g.od_zinv[6ull * e], 48); std::memcpy(&ow[3ull * k], &g.od_w[3ull * e], 24);
+    }
+    TRY(upload(c, d.lm_packed, s.lm_packed)); TRY(upload(c, d.le_z, z)); TRY(upload(c, d.le_w, w));
+    TRY(upload(c, d.pose_ptr, s.pose_ptr)); TRY(upload(c, d.blk_chunk_ptr, s.blk_chunk_ptr));
+    { std::vector<uint32_t> raw(8ull * s.chunks.size());
+      if (!s.chunks.empty()) std::memcpy(raw.data(), s.chunks.data(), raw.size() * 4);
+      TRY(upload(c, d.chunks, raw)); }
+    TRY(upload(c, d.slot_lm, s.slot_lm)); TRY(upload(c, d.slot_ptr, s.slot_ptr)); TRY(upload(c, d.slot_edge, s.slot_edge));
+    TRY(upload(c, d.lm_part_ptr, s.lm_part_ptr)); TRY(upload(c, d.lm_part_idx, s.lm_part_idx));
+    TRY(upload(c, d.od_a, s.od_a)); TRY(upload(c, d.od_b, s.od_b)); TRY(upload(c, d.od_zinv, oz)); TRY(upload(c, d.od_w, ow));
+    TRY(upload(c, d.od_out_ptr, s.od_out_ptr)); TRY(upload(c, d.od_in_ptr, s.od_in_ptr)); TRY(upload(c, d.od_in_edge, s.od_in_edge));
+    TRY(upload(c, d.fixed_pose_count, s.fixed_pose_count)); TRY(upload(c, d.fixed_lm_count, s.fixed_lm_count));
+    // state: local poses then ghosts
+    const uint32_t nPG = d.nP + d.nG;
+    std::vector<double> xyt(3ull * nPG);
+    if (d.nP) std::memcpy(xyt.data(), &g.pose_xyt[3ull * s.pose_begin], 24ull * d.nP);
+    for (uint32_t q = 0; q < d.nG; ++q) std::memcpy(&xyt[3ull * (d.nP + q)], &g.pose_xyt[3ull * s.ghost_pose[q]], 24);
+    TRY(dalloc(c, c->tmp_xyt, 3ull * std::max(nPG, g.P)));
+    TRY(dalloc(c, d.pose, nPG)); TRY(dalloc(c, c->pose0, nPG)); TRY(dalloc(c, d.lm, g.L)); TRY(dalloc(c, c->lm0, g.L));
+    if (nPG) CU(cudaMemcpyAsync(c->tmp_xyt, xyt.data(), 24ull * nPG, cudaMemcpyHostToDevice, c->stream));
+    launch_init_pose(c->tmp_xyt, nPG, c->pose0, c->stream);
+    if (g.L) CU(cudaMemcpyAsync(c->lm0, g.lm_xy.data(), 16ull * g.L, cudaMemcpyHostToDevice, c->stream));
+    // system and solver vectors
+    TRY(dalloc(c, d.hpl, 6ull * d.nE)); TRY(dalloc(c, d.hoo, 3ull * d.nO));
+    TRY(dalloc(c, d.hpp, 6ull * d.nP)); TRY(dalloc(c, d.bp, 3ull * d.nP));
+    TRY(dalloc(c, d.lm_part, 5ull * d.nSlots)); TRY(dalloc(c, d.lm_sum, 5ull * g.L));
+    TRY(dalloc(c, d.hll, 3ull * g.L)); TRY(dalloc(c, d.hinv, 3ull * g.L)); TRY(dalloc(c, d.bl, 2ull * g.L));
+    TRY(dalloc(c, d.minv, 6ull * d.nP)); TRY(dalloc(c, d.rhs, 3ull * d.nP));
+    TRY(dalloc(c, d.x, 3ull * d.nP)); TRY(dalloc(c, d.r, 3ull * d.nP)); TRY(dalloc(c, d.z, 3ull * d.nP));
+    TRY(dalloc(c, d.p, 3ull * nPG)); TRY(dalloc(c, d.sp, 3ull * d.nP));
+    TRY(dalloc(c, d.w_part, 2ull * d.nSlots)); TRY(dalloc(c, d.w_sum, 2ull * g.L + 64)); TRY(dalloc(c, d.dl, 2ull * g.L));
+    c->part_cap = std::max<uint32_t>(d.nBlocks, (std::max(d.nP, g.L) + kThreads - 1) / kThreads) + 1;
+    TRY(dalloc(c, d.part, c->part_cap)); TRY(dalloc(c, d.part2, c->part_cap));
+    TRY(dalloc(c, d.scal, (size_t)S_COUNT)); TRY(dalloc(c, d.flags, (size_t)F_COUNT));
+    CU(cudaMemsetAsync(d.scal, 0, sizeof(double) * S_COUNT, c->stream));
+    CU(cudaMemsetAsync(d.flags, 0, sizeof(int) * F_COUNT, c->stream));
+    CU(cudaMemsetAsync(d.p, 0, 24ull * nPG, c->stream));
+    CU(cudaMemsetAsync(d.x, 0, 24ull * d.nP, c->stream));
+    CU(cudaMemsetAsync(d.dl, 0, 16ull * g.L, c->stream));
+    const double tol = c->cfg.pcg_tol > 0 ? c->cfg.pcg_tol : 1e-12;
+    const double tol2 = tol * tol; const int maxit = c->cfg.pcg_max_iters > 0 ? c->cfg.pcg_max_iters : 4000;
+    CU(cudaMemcpyAsync(d.scal + S_TOL2, &tol2, 8, cudaMemcpyHostToDevice, c->stream));
+    CU(cudaMemcpyAsync(d.flags + F_MAXIT, &maxit, 4, cudaMemcpyHostToDevice, c->stream));
+    CU(cudaMemcpyAsync(d.pose, c->pose0, sizeof(double4) * nPG, cudaMemcpyDeviceToDevice, c->stream));
+    CU(cudaMemcpyAsync(d.lm, c->lm0, sizeof(double2) * g.L, cudaMemcpyDeviceToDevice, c->stream));
+    CU(cudaStreamSynchronize(c->stream));
+    c->loaded = true; c->linearized = c->solved = false;
+    return TSB_OK;
+}
+
+int fetch_scalars(tsb_ctx* c) {
+    CU(cudaMemcpyAsync(c->h_scal, c->d.scal, sizeof(double) * S_COUNT, cudaMemcpyDeviceToHost, c->stream));
+    CU(cudaMemcpyAsync(c->h_flags, c->d.flags, sizeof(int) * F_COUNT, cudaMemcpyDeviceToHost, c->stream));
+    CU(cudaStreamSynchronize(c->stream));
+    return TSB_OK;
+}
+
+void enqueue_linearize(tsb_ctx* c) {
+    launch_linearize(c->d, c->stream);
+    launch_lm_sum(c->d, c->stream);
+    launch_lm_finalize(c->d, c->stream);
+}
+
+// Schur preparation + PCG + landmark back-substitution; leaves delta in d.x / d.dl
+int run_solve(tsb_ctx* c) {
+    const Dev& d = c->d;
+    launch_schur_prep(d, c->stream);
+    launch_pcg_init(d, c->stream);
+    const int maxit = c->cfg.pcg_max_iters > 0 ? c->cfg.pcg_max_iters : 4000;
+    const int batch = 16;
+    for (int it = 0; it < maxit + batch; it += batch) {
+        for (int b = 0; b < batch; ++b) {
+            launch_pcg_pass_a(d, 0, c->stream);
+            launch_pcg_w_sum(d, 1, c->stream);
+            launch_pcg_pass_b(d, c->stream);
+            launch_pcg_alpha(d, c->stream);
+            launch_pcg_update(d, c->stream);
+            launch_pcg_beta(d, c->stream);
+        }
+        CU(cudaMemcpyAsync(c->h_flags, d.flags, sizeof(int) * F_COUNT, cudaMemcpyDeviceToHost, c->stream));
+        CU(cudaStreamSynchronize(c->stream));
+        if (c->h_flags[F_DONE]) break;
+    }
+    launch_pcg_pass_a(d, 1, c->stream);
+    launch_pcg_w_sum(d, 0, c->stream);
+    launch_backsub(d, c->stream);
+    return TSB_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+const char* tsb_last_error(const tsb_ctx* c) { return c ? c->err.c_str() : g_create_error.c_str(); }
+
+int tsb_create(const tsb_config* cfg, tsb_ctx** out) {
+    if (!cfg || !out) { g_create_error = "tsb_create: null argument"; return TSB_EINVAL; }
+    *out = nullptr;
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) {
+        cudaGetLastError();
+        g_create_error = "no CUDA device: the PIPELINE=gpu path has no CPU fallback"; return TSB_ECUDA; }
+    if (cfg->device < 0 || cfg->device >= ndev) { g_create_error = "tsb_create: bad device ordinal"; return TSB_EINVAL; }
+    if (cfg->world > 1) { g_create_error = "tsb_create: world > 1 not available in this build"; return TSB_EINVAL; }
+    tsb_ctx* c = new tsb_ctx();
+    c->cfg = *cfg; if (c->cfg.world < 1) { c->cfg.world = 1; c->cfg.rank = 0; }
+    auto fail = [&](const char* what, cudaError_t e) { g_create_error = std::string(what) + ": " + cudaGetErrorString(e); delete c; return TSB_ECUDA; };
+    cudaError_t e;
+    if ((e = cudaSetDevice(cfg->device)) != cudaSuccess) return fail("cudaSetDevice", e);
+    if ((e = cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking)) != cudaSuccess) return fail("cudaStreamCreate", e);
+    for (auto& ev : c->ev) if ((e = cudaEventCreate(&ev)) != cudaSuccess) return fail("cudaEventCreate", e);
+    if ((e = cudaMallocHost((void**)&c->h_scal, sizeof(double) * S_COUNT)) != cudaSuccess) return fail("cudaMallocHost", e);
+    if ((e = cudaMallocHost((void**)&c->h_flags, sizeof(int) * F_COUNT)) != cudaSuccess) return fail("cudaMallocHost", e);
+    *out = c;
+    return TSB_OK;
+}
+
+void tsb_destroy(tsb_ctx* c) {
+    if (!c) return;
+    cudaSetDevice(c->cfg.device);
+    free_graph(c);
+    if (c->h_scal) cudaFreeHost(c->h_scal);
+    if (c->h_flags) cudaFreeHost(c->h_flags);
+    for (auto& ev : c->ev) if (ev) cudaEventDestroy(ev);
+    if (c->stream) cudaStreamDestroy(c->stream);
+    delete c;
+}
+
+int tsb_load_wire(tsb_ctx* c, const void* payload, uint32_t nbytes) {
+    if (!c || (!payload && nbytes)) return TSB_EINVAL;
+    CU(cudaSetDevice(c->cfg.device));
+    free_graph(c);
+    if (!parse_wire((const uint8_t*)payload, nbytes, c->g, c->err)) return TSB_EPARSE;
+    build_structure(c->g, (uint32_t)c->cfg.rank, (uint32_t)c->cfg.world, c->st);
+    return upload_graph(c);
+}
+
+int tsb_load_soa(tsb_ctx* c, const tsb_graph_soa* s) {
+    if (!c || !s) return TSB_EINVAL;
+    // encode exactly what the reference client would send (graph_to_bytes.py:32-67), then take the wire path
+    std::vector<uint8_t> buf;
+    auto pu = [&](uint32_t v) { const uint8_t* p = (const uint8_t*)&v; buf.insert(buf.end(), p, p + 4); };
+    auto pf = [&](float v) { const uint8_t* p = (const uint8_t*)&v; buf.insert(buf.end(), p, p + 4); };
+    buf.reserve(16 + 20ull * s->n_pose + 16ull * s->n_lm + 76ull * s->n_odom + 44ull * s->n_lmedge + 4ull * s->n_fixed);
+    pu(s->n_pose + s->n_lm);
+    for (uint32_t i = 0; i < s->n_pose; ++i) { pu(s->pose_id[i]); pu(0); for (int q = 0; q < 3; ++q) pf(s->pose_xyt[3ull * i + q]); }
+    for (uint32_t i = 0; i < s->n_lm; ++i) { pu(s->lm_id[i]); pu(1); pf(s->lm_xy[2ull * i]); pf(s->lm_xy[2ull * i + 1]); }
+    pu(s->n_odom + s->n_lmedge);
+    for (uint32_t i = 0; i < s->n_odom; ++i) {
+        pu(0); pu(s->odom_ij[2ull * i]); pu(s->odom_ij[2ull * i + 1]); pu(3); pu(3);
+        for (int q = 0; q < 9; ++q) pf(s->odom_Z[9ull * i + q]);
+        pu(0); pu(3); for (int q = 0; q < 3; ++q) pf(s->odom_w[3ull * i + q]);
+    }
+    for (uint32_t i = 0; i < s->n_lmedge; ++i) {
+        pu(1); pu(s->lmedge_ij[2ull * i]); pu(s->lmedge_ij[2ull * i + 1]); pu(0); pu(2);
+        pf(s->lmedge_meas[2ull * i]); pf(s->lmedge_meas[2ull * i + 1]);
+        pu(0); pu(2); pf(s->lmedge_w[2ull * i]); pf(s->lmedge_w[2ull * i + 1]);
+    }
+    pu(s->n_fixed);
+    for (uint32_t i = 0; i < s->n_fixed; ++i) pu(s->fixed_id[i]);
+    return tsb_load_wire(c, buf.data(), (uint32_t)buf.size());
+}
+
+int tsb_get_counts(const tsb_ctx* c, tsb_counts* o) {
+    if (!c || !o || !c->loaded) return TSB_EINVAL;
+    o->n_pose = c->g.P; o->n_lm = c->g.L; o->n_odom = c->g.Eo; o->n_lmedge = c->g.El; o->n_fixed = (uint32_t)c->g.fixed.size();
+    o->dim = 3 * c->g.P + 2 * c->g.L; o->pose_begin = c->st.pose_begin; o->pose_end = c->st.pose_end;
+    o->n_lmedge_local = c->d.nE; o->n_odom_local = c->d.nOwned;
+    o->n_chunks = c->d.nChunks; o->n_blocks = c->d.nBlocks; o->n_slots = c->d.nSlots;
+    return TSB_OK;
+}
+
+int tsb_reset_state(tsb_ctx* c) {
+    if (!c || !c->loaded) return TSB_EINVAL;
+    CU(cudaSetDevice(c->cfg.device));
+    CU(cudaMemcpyAsync(c->d.pose, c->pose0, sizeof(double4) * (c->d.nP + c->d.nG), cudaMemcpyDeviceToDevice, c->stream));
+    CU(cudaMemcpyAsync(c->d.lm, c->lm0, sizeof(double2) * c->g.L, cudaMemcpyDeviceToDevice, c->stream));
+    c->linearized = c->solved = false;
+    return TSB_OK;
+}
+
+int tsb_set_state(tsb_ctx* c, const double* pose_xyt, const double* lm_xy) {
+    if (!c || !c->loaded || !pose_xyt || (!lm_xy && c->g.L)) return TSB_EINVAL;
+    CU(cudaSetDevice(c->cfg.device));
+    const Structure& s = c->st; const uint32_t nPG = c->d.nP + c->d.nG;
+    std::vector<double> xyt(3ull * nPG);
+    if (c->d.nP) std::memcpy(xyt.data(), pose_xyt + 3ull * s.pose_begin, 24ull * c->d.nP);
+    for (uint32_t q = 0; q < c->d.nG; ++q) std::memcpy(&xyt[3ull * (c->d.nP + q)], pose_xyt + 3ull * s.ghost_pose[q], 24);
+    if (nPG) CU(cudaMemcpyAsync(c->tmp_xyt, xyt.data(), 24ull * nPG, cudaMemcpyHostToDevice, c->stream));
+    launch_init_pose(c->tmp_xyt, nPG, c->d.pose, c->stream);
+    if (c->g.L) CU(cudaMemcpyAsync(c->d.lm, lm_xy, 16ull * c->g.L, cudaMemcpyHostToDevice, c->stream));
+    CU(cudaStreamSynchronize(c->stream));
+    c->linearized = c->solved = false;
+    return TSB_OK;
+}
+
+int tsb_linearize(tsb_ctx* c, tsb_iter_stats* st) {
+    if (!c || !c->loaded) return TSB_EINVAL;
+    CU(cudaSetDevice(c->cfg.device));
+    CU(cudaEventRecord(c->ev[0], c->stream));
+    enqueue_linearize(c);
+    CU(cudaEventRecord(c->ev[1], c->stream));
+    TRY(fetch_scalars(c));
+    CU(cudaGetLastError());
+    c->linearized = true; c->solved = false;
+    if (st) { std::memset(st, 0, sizeof(*st)); st->chi2 = c->h_scal[S_CHI2]; CU(cudaEventElapsedTime(&st->ms_linearize, c->ev[0], c->ev[1])); }
+    return TSB_OK;
+}
+
+int tsb_solve(tsb_ctx* c, tsb_iter_stats* st) {
+    if (!c || !c->loaded || !c->linearized) { if (c) c->err = "tsb_solve needs a preceding tsb_linearize"; return TSB_EINVAL; }
+    CU(cudaSetDevice(c->cfg.device));
+    CU(cudaEventRecord(c->ev[1], c->stream));
+    TRY(run_solve(c));
+    CU(cudaEventRecord(c->ev[2], c->stream));
+    TRY(fetch_scalars(c));
+    CU(cudaGetLastError());
+    c->solved = true;
+    if (st) { st->pcg_iters = c->h_flags[F_ITERS];
+        st->pcg_rel_residual = c->h_scal[S_RZ0] > 0 ? std::sqrt(c->h_scal[S_RZ] / c->h_scal[S_RZ0]) : 0;
+        CU(cudaEventElapsedTime(&st->ms_solve, c->ev[1], c->ev[2])); }
+    return TSB_OK;
+}
+
+int tsb_optimize(tsb_ctx* c, uint32_t iterations, tsb_report* rep, tsb_iter_stats* per_iter) {
+    if (!c || !c->loaded) return TSB_EINVAL;
+    CU(cudaSetDevice(c->cfg.device));
+    const uint64_t launches0 = g_launches;
+    const bool exits = c->cfg.enable_exits != 0;
+    double prevErr = -1, err = 0; int penalty = 0, code = 0; uint32_t done = 0;
+    int64_t pcg_total = 0; float ms_lin = 0, ms_sol = 0;
+    CU(cudaEventRecord(c->ev[3], c->stream));
+    for (uint32_t it = 0; it < iterations; ++it) {
+        CU(cudaEventRecord(c->ev[0], c->stream));
+        enqueue_linearize(c);
+        CU(cudaEventRecord(c->ev[1], c->stream));
+        if (exits) {                                     // OptimizerCpu.h:140-153 needs err before the solve
+            TRY(fetch_scalars(c)); err = c->h_scal[S_CHI2];
+            if (prevErr > 0 && err > prevErr) {
+                if (++penalty > 2) {
+                    code = 1;
+                    if (per_iter) { std::memset(&per_iter[it], 0, sizeof(tsb_iter_stats)); per_iter[it].chi2 = err; }
+                    ++done;
+                    if (c->cfg.verbose) std::printf("Error is getting worse\n");
+                    break;
+                }
+            } else penalty = 0;
+        }
+        TRY(run_solve(c));
+        CU(cudaEventRecord(c->ev[2], c->stream));
+        launch_update_state(c->d, 0.2, c->stream);       // OptimizerCpu.h:159-165
+        TRY(fetch_scalars(c));
+        CU(cudaGetLastError());
+        err = c->h_scal[S_CHI2];
+        const double dnorm = std::sqrt(c->h_scal[S_DELTA2] + c->h_scal[S_DELTA2L]);
+        float a = 0, b = 0;
+        CU(cudaEventElapsedTime(&a, c->ev[0], c->ev[1])); CU(cudaEventElapsedTime(&b, c->ev[1], c->ev[2]));
+        ms_lin += a; ms_sol += b; pcg_total += c->h_flags[F_ITERS]; ++done;
+        if (per_iter) { tsb_iter_stats& s = per_iter[it]; s.chi2 = err; s.delta_norm = dnorm; s.pcg_iters = c->h_flags[F_ITERS];
+            s.pcg_rel_residual = c->h_scal[S_RZ0] > 0 ? std::sqrt(c->h_scal[S_RZ] / c->h_scal[S_RZ0]) : 0; s.ms_linearize = a; s.ms_solve = b; }
+        if (exits && std::fabs(err - prevErr) < 0.001) { code = 2; if (c->cfg.verbose) std::printf("Plateau: NO MORE OPT\n"); break; }
+        if (exits && dnorm < 0.001) { code = 3; if (c->cfg.verbose) std::printf("CONVERGED\n"); break; }
+        prevErr = err;
+    }
+    CU(cudaEventRecord(c->ev[2], c->stream));
+    CU(cudaEventSynchronize(c->ev[2]));
+    if (c->cfg.verbose) std::printf("Summary() error = %g\n", err);
+    c->linearized = c->solved = false;
+    if (rep) { rep->iterations_run = (int32_t)done; rep->exit_code = code; rep->final_chi2 = err; rep->pcg_iters_total = pcg_total;
+        rep->kernel_launches = (int64_t)(g_launches - launches0); rep->ms_linearize_total = ms_lin; rep->ms_solve_total = ms_sol;
+        CU(cudaEventElapsedTime(&rep->ms_total, c->ev[3], c->ev[2])); }
+    return TSB_OK;
+}
+
+}  // extern "C"
+
+namespace {
+template <typename T> int download(tsb_ctx* c, std::vector<T>& out, const void* dev, size_t n) {
+    out.resize(n);
+    if (n) CU(cudaMemcpyAsync(out.data(), dev, n * sizeof(T), cudaMemcpyDeviceToHost, c->stream));
+    CU(cudaStreamSynchronize(c->stream));
+    return TSB_OK;
+}
+}  // namespace
+
+extern "C" {
+
+int tsb_read_ids(const tsb_ctx* c, uint32_t* pose_id, uint32_t* lm_id) {
+    if (!c || !c->loaded) return TSB_EINVAL;
+    if (pose_id) std::memcpy(pose_id, c->g.pose_id.data(), 4ull * c->g.P);
+    if (lm_id) std::memcpy(lm_id, c->g.lm_id.data(), 4ull * c->g.L);
+    return TSB_OK;
+}
+
+int tsb_read_state(tsb_ctx* c, double* pose_xyt, double* lm_xy) {
+    if (!c || !c->loaded) return TSB_EINVAL;
+    CU(cudaSetDevice(c->cfg.device));
+    if (pose_xyt) {
+        launch_read_pose(c->d.pose, c->d.nP, c->tmp_xyt, c->stream);
+        if (c->d.nP) CU(cudaMemcpyAsync(pose_xyt + 3ull * c->st.pose_begin, c->tmp_xyt, 24ull * c->d.nP, cudaMemcpyDeviceToHost, c->stream));
+    }
+    if (lm_xy && c->g.L) CU(cudaMemcpyAsync(lm_xy, c->d.lm, 16ull * c->g.L, cudaMemcpyDeviceToHost, c->stream));
+    CU(cudaStreamSynchronize(c->stream));
+    return TSB_OK;
+}
+
+int tsb_read_delta(tsb_ctx* c, double* delta_pose, double* delta_lm) {
+    if (!c || !c->loaded || !c->solved) { if (c) c->err = "tsb_read_delta needs a preceding tsb_solve"; return TSB_EINVAL; }
+    CU(cudaSetDevice(c->cfg.device));
+    if (delta_pose && c->d.nP) CU(cudaMemcpyAsync(delta_pose, c->d.x, 24ull * c->d.nP, cudaMemcpyDeviceToHost, c->stream));
+    if (delta_lm && c->g.L) CU(cudaMemcpyAsync(delta_lm, c->d.dl, 16ull * c->g.L, cudaMemcpyDeviceToHost, c->stream));
+    CU(cudaStreamSynchronize(c->stream));
+    return TSB_OK;
+}
+
+int tsb_read_system(tsb_ctx* c, double* hpp_diag, double* b_pose, double* hpl, double* hpp_off, double* hll, double* b_lm) {
+    if (!c || !c->loaded || !c->linearized) { if (c) c->err = "tsb_read_system needs a preceding tsb_linearize"; return TSB_EINVAL; }
+    CU(cudaSetDevice(c->cfg.device));
+    const Dev& d = c->d; const Structure& s = c->st;
+    if (hpp_diag && d.nP) CU(cudaMemcpyAsync(hpp_diag + 6ull * s.pose_begin, d.hpp, 48ull * d.nP, cudaMemcpyDeviceToHost, c->stream));
+    if (b_pose && d.nP) CU(cudaMemcpyAsync(b_pose + 3ull * s.pose_begin, d.bp, 24ull * d.nP, cudaMemcpyDeviceToHost, c->stream));
+    if (hll && d.L) CU(cudaMemcpyAsync(hll, d.hll, 24ull * d.L, cudaMemcpyDeviceToHost, c->stream));
+    if (b_lm && d.L) CU(cudaMemcpyAsync(b_lm, d.bl, 16ull * d.L, cudaMemcpyDeviceToHost, c->stream));
+    CU(cudaStreamSynchronize(c->stream));
+    if (hpl) { std::vector<double> t; TRY(download(c, t, d.hpl, 6ull * d.nE));
+        for (uint32_t k = 0; k < d.nE; ++k) std::memcpy(hpl + 6ull * s.le_local[s.lm_perm[k]], &t[6ull * k], 48); }
+    if (hpp_off) { std::vector<double> t; TRY(download(c, t, d.hoo, 3ull * d.nOwned));
+        for (uint32_t k = 0; k < d.nOwned; ++k) std::memcpy(hpp_off + 3ull * s.od_local[k], &t[3ull * k], 24); }
+    return TSB_OK;
+}
+
+int tsb_read_structure(tsb_ctx* c, uint32_t* lm_perm, uint32_t* lm_packed, uint32_t* chunk_desc, uint32_t* slot_lm,
+                       uint32_t* pose_ptr, uint32_t* lm_part_ptr, uint32_t* lm_part_idx) {
+    if (!c || !c->loaded) return TSB_EINVAL;
+    CU(cudaSetDevice(c->cfg.device));
+    const Dev& d = c->d; const Structure& s = c->st;
+    // lm_perm is host-side knowledge (request index of each assembly position); the rest comes back from the device
+    if (lm_perm) for (uint32_t k = 0; k < d.nE; ++k) lm_perm[k] = s.le_local[s.lm_perm[k]];
+    auto get = [&](uint32_t* out, const void* dev, size_t n) -> int {
+        if (out && n) CU(cudaMemcpyAsync(out, dev, 4 * n, cudaMemcpyDeviceToHost, c->stream)); return TSB_OK; };
+    TRY(get(lm_packed, d.lm_packed, d.nE)); TRY(get(chunk_desc, d.chunks, 8ull * d.nChunks)); TRY(get(slot_lm, d.slot_lm, d.nSlots));
+    TRY(get(pose_ptr, d.pose_ptr, d.nP + 1ull)); TRY(get(lm_part_ptr, d.lm_part_ptr, d.L + 1ull)); TRY(get(lm_part_idx, d.lm_part_idx, d.nSlots));
+    CU(cudaStreamSynchronize(c->stream));
+    return TSB_OK;
+}
+
+int tsb_reply_size(tsb_ctx* c, uint32_t* nbytes) {
+    if (!c || !c->loaded || !nbytes) return TSB_EINVAL;
+    *nbytes = c->g.reply_bytes; return TSB_OK;
+}
+
+int tsb_write_reply(tsb_ctx* c, void* out, uint32_t capacity) {
+    if (!c || !c->loaded || !out) return TSB_EINVAL;
+    if (capacity < c->g.reply_bytes) { c->err = "tsb_write_reply: buffer too small"; return TSB_EINVAL; }
+    std::vector<double> pose(3ull * c->g.P), lm(2ull * c->g.L);
+    TRY(tsb_read_state(c, pose.data(), lm.data()));
+    encode_reply(c->g, pose.data(), lm.data(), (uint8_t*)out);
+    return TSB_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,83 @@
+// device_graph.h -- device-resident graph, assembly structure and linear system (fp64 SoA in HBM).
+#pragma once
+#include <cuda_runtime.h>
+#include <cstdint>
+#include "host_graph.h"
+
+namespace tsb {
+
+constexpr int kThreads = 256;          // threads per block of the chunked kernels
+constexpr int kStageRows = 9;          // values staged per LM edge
+constexpr int kStageStride = kChunkEdges + 1;   // odd stride in doubles: rows land in different banks
+
+// scalars kept on the device (index into Dev::scal)
+enum Scal { S_CHI2 = 0, S_RZ0, S_RZ, S_PSP, S_ALPHA, S_BETA, S_DELTA2, S_DELTA2L, S_TOL2, S_PSP_EXTRA, S_COUNT };
+// integer flags (index into Dev::flags)
+enum Flag { F_DONE = 0, F_ITERS, F_MAXIT, F_COUNT };
+
+struct Dev {
+    uint32_t nP, nG, L, nE, nO, nOwned, nChunks, nBlocks, nSlots;
+    // state
+    double4* pose;              // nP + nG : x, y, cos(theta), sin(theta)
+    double2* lm;                // L
+    // LM edges, assembly order
+    const uint32_t* lm_packed;  // (pose - chunk.p0) << 16 | slot - chunk.s0
+    const double2* le_z;        // landmark in the sensor frame (r cos b, r sin b)
+    const double2* le_w;        // information diagonal
+    double* hpl;                // 6 per edge: A^T W B, 3x2 row-major
+    const uint32_t* pose_ptr;   // nP + 1
+    const ChunkDesc* chunks;
+    const uint32_t* blk_chunk_ptr;
+    const uint32_t* slot_lm;
+    const uint32_t* slot_ptr;
+    const uint16_t* slot_edge;
+    const uint32_t* lm_part_ptr;
+    const uint32_t* lm_part_idx;
+    // ODOM edges (owned first, then ghost)
+    const uint32_t* od_a; const uint32_t* od_b;
+    const double* od_zinv;      // 6 per edge
+    const double* od_w;         // 3 per edge
+    const uint32_t* od_out_ptr; const uint32_t* od_in_ptr; const uint32_t* od_in_edge;
+    double* hoo;                // 3 per edge: diagonal of the (i,j) block = -W
+    const uint32_t* fixed_pose_count; const uint32_t* fixed_lm_count;
+    // assembled system
+    double* hpp;                // 6 per pose (00 01 02 11 12 22), prior included
+    double* bp;                 // 3 per pose
+    double* lm_part;            // 5 per slot: partial (Hll 00 01 11, b_l 0 1)
+    double* lm_sum;             // 5 per landmark: sum over this rank's slots (all-reduced when world > 1)
+    double* hll;                // 3 per landmark
+    double* hinv;               // 3 per landmark: inverse of Hll (prior included)
+    double* bl;                 // 2 per landmark
+    // Schur / PCG
+    double* minv;               // 6 per pose: inverse of the diagonal block of S
+    double* rhs;                // 3 per pose
+    double* x; double* r; double* z; double* p; double* sp;   // 3 per pose (p: nP + nG)
+    double* w_part;             // 2 per slot
+    double* w_sum;              // 2 per landmark (+ tail used by the multi-GPU exchange)
+    double* dl;                 // 2 per landmark: delta of the landmarks
+    double* part;               // nBlocks partial sums (one reduction at a time)
+    double* part2;              // second set (chi2 of ODOM etc.)
+    double* scal;               // S_COUNT
+    int* flags;                 // F_COUNT
+};
+
+// kernel launchers (kernels.cu).  All take the launching stream.
+void launch_linearize(const Dev& d, cudaStream_t s);            // K1: residuals, Jacobians, Hpl, pose-side H/b, slot partials
+void launch_lm_sum(const Dev& d, cudaStream_t s);               // K2a: landmark-major sum of slot partials
+void launch_lm_finalize(const Dev& d, cudaStream_t s);          // K2b: Hll, b_l, prior, Hll^-1; chi2
+void launch_schur_prep(const Dev& d, cudaStream_t s);           // K3: diag(S)^-1 and reduced rhs
+void launch_pcg_init(const Dev& d, cudaStream_t s);
+void launch_pcg_pass_a(const Dev& d, int mode, cudaStream_t s); // mode 0: v = p (with p = z + beta p fused), 1: v = x
+void launch_pcg_w_sum(const Dev& d, int check_done, cudaStream_t s);
+void launch_pcg_pass_b(const Dev& d, cudaStream_t s);
+void launch_pcg_alpha(const Dev& d, cudaStream_t s);
+void launch_pcg_update(const Dev& d, cudaStream_t s);
+void launch_pcg_beta(const Dev& d, cudaStream_t s);
+void launch_backsub(const Dev& d, cudaStream_t s);              // delta_l = Hll^-1 (b_l - Hpl^T delta_p)
+void launch_update_state(const Dev& d, double step, cudaStream_t s);   // K5 + ||delta||^2
+void launch_init_pose(const double* xyt, uint32_t n, double4* out, cudaStream_t s);
+void launch_read_pose(const double4* pose, uint32_t n, double* xyt, cudaStream_t s);
+size_t linearize_smem_bytes();
+extern uint64_t g_launches;   // kernels launched by this library since load
+
+}  // namespace tsb

@@ -1,0 +1,72 @@
+// host_graph.h -- host-side graph in structure-of-arrays form + the assembly structure.
+// Replaces the per-object containers of remote/graph/GraphCpu.h and remote/cuda/graph/GraphGpu.h
+// (unique_ptr per vertex/edge) with flat arrays parsed straight from the wire payload.
+#pragma once
+#include <cstdint>
+#include <string>
+#include <vector>
+
+namespace tsb {
+
+struct HostGraph {
+    uint32_t P = 0, L = 0, Eo = 0, El = 0;
+    // canonical vertex order: poses by ascending id, then landmarks by ascending id
+    std::vector<uint32_t> pose_id, lm_id;
+    std::vector<double> pose_xyt;     // 3 per pose (x, y, theta) widened from fp32
+    std::vector<double> lm_xy;        // 2 per landmark
+    // edges in request order, split by type
+    std::vector<uint32_t> od_i, od_j; // canonical pose indices
+    std::vector<double> od_zinv;      // 6 per edge: top two rows of inverse(Z) (EdgeSe2.h:32), fp64
+    std::vector<double> od_w;         // 3 per edge: information diagonal
+    std::vector<uint32_t> le_i, le_l; // pose index, landmark index
+    std::vector<double> le_z;         // 2 per edge: (r cos b, r sin b)  (EdgeSe2Point2d.h:34-35)
+    std::vector<double> le_w;         // 2 per edge
+    std::vector<uint32_t> fixed;      // canonical vertex index (pose k -> k, landmark k -> P + k), repeats kept
+    // reply echo
+    std::vector<uint8_t> request;     // copy of the payload
+    std::vector<uint32_t> req_vertex; // per request vertex: canonical index | type << 31; 0xFFFFFFFF = dropped duplicate
+    uint32_t edges_offset = 0;        // byte offset of the edge count in `request`
+    uint32_t reply_bytes = 0;
+};
+
+// DeserializeGraph.h:9-174, bounds-checked.  Returns false and sets `err` on malformed input.
+bool parse_wire(const uint8_t* buf, uint32_t nbytes, HostGraph& g, std::string& err);
+// SerializeGraph.h:8-72 + SerializeGraphFuncCpu.h:10-65 (payload, no size prefix).
+// pose_xyt / lm_xy: current fp64 state in canonical order.
+void encode_reply(const HostGraph& g, const double* pose_xyt, const double* lm_xy, uint8_t* out);
+
+struct ChunkDesc { uint32_t e0, e1, p0, p1, s0, s1, block, flags; };
+
+// Assembly structure of one rank (all integer; compared bit-exactly in tests).
+struct Structure {
+    uint32_t pose_begin = 0, pose_end = 0;   // canonical pose range owned by this rank
+    uint32_t nP = 0, nG = 0;                 // local poses, ghost poses (ODOM neighbours owned elsewhere)
+    std::vector<uint32_t> ghost_pose;        // canonical index of each ghost pose
+    // LM edges of local poses, assembly order = sorted by (pose, landmark, request index)
+    std::vector<uint32_t> le_local;          // request-order indices (into HostGraph::le_*) of the local LM edges
+    std::vector<uint32_t> lm_perm;           // assembly k -> index into le_local
+    std::vector<uint32_t> lm_packed;         // (pose - chunk.p0) << 16 | slot - chunk.s0
+    std::vector<uint32_t> pose_ptr;          // nP + 1
+    std::vector<ChunkDesc> chunks;
+    std::vector<uint32_t> blk_chunk_ptr;     // n_blocks + 1
+    std::vector<uint32_t> slot_lm;           // landmark index per slot (one partial sum per slot)
+    std::vector<uint32_t> slot_ptr;          // n_slots + 1, offsets into slot_edge (== assembly positions)
+    std::vector<uint16_t> slot_edge;         // per assembly position: edge index within its chunk, grouped by slot
+    std::vector<uint32_t> lm_part_ptr, lm_part_idx;   // landmark-major CSR over slots
+    // ODOM edges touching a local pose.  Owned (id1 local) edges first, sorted by id1; then ghost
+    // edges (id2 local, id1 elsewhere).  Pose indices are local (0..nP) or ghost (nP..nP+nG).
+    std::vector<uint32_t> od_local;          // request-order index (into HostGraph::od_*)
+    uint32_t n_od_owned = 0;
+    std::vector<uint32_t> od_a, od_b;        // local/ghost pose index of id1, id2
+    std::vector<uint32_t> od_out_ptr;        // nP + 1 : owned edges by id1 (contiguous)
+    std::vector<uint32_t> od_in_ptr, od_in_edge;   // nP + 1 : edges (owned or ghost) by id2
+    std::vector<uint32_t> fixed_pose_count;  // nP : how many times the pose is listed as fixed
+    std::vector<uint32_t> fixed_lm_count;    // L
+};
+
+constexpr uint32_t kChunkEdges = 512;   // LM edges staged per chunk
+constexpr uint32_t kBlockPoses = 256;   // poses per thread block (upper bound)
+
+void build_structure(const HostGraph& g, uint32_t rank, uint32_t world, Structure& s);
+
+}  // namespace tsb

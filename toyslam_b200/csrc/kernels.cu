@@ -1,0 +1,636 @@
+// kernels.cu -- hand-written sm_100a kernels of the Gauss-Newton inner loop.
+//
+// Math restated from the reference's CPU pipeline (the parity target), not from remote/cuda:
+//   K1  linearize+assemble  EdgeSe2.h:24-38, EdgeSe2Point2d.h:28-70, OptimizerCpu.h:36-46,88-138
+//   K2  landmark blocks     OptimizerCpu.h:109-118 (the H_jj / b_j part for Point2 vertices)
+//   K3/K4 Schur + PCG       replaces SolverEigen.h:20 (dense pivoted QR of a dim x dim H)
+//   K5  update              VertexSe2.h:16-27, Vertex2d.h:16-19, OptimizerCpu.h:159-165,173
+// All reductions run in a fixed order (segmented sums over a precomputed pattern): no floating
+// point atomics anywhere, so results are bit-reproducible run to run.
+//
+// Memory-bound design (HBM roofline): every per-edge array is read or written once per pass with
+// unit-stride accesses in assembly order; vertex blocks (poses of the block, landmarks of the
+// chunk's slots) are staged in shared memory; per-edge products are staged in shared memory and
+// reduced along precomputed row segments (pose side) and slot lists (landmark side).
+#include "device_graph.h"
+
+namespace tsb {
+namespace {
+
+// Shared-memory carve-up (bytes).  `acc` aliases `stage`: it is only written after the last chunk.
+constexpr size_t kOffStage = 0;                                                   // 9 x 513 doubles
+constexpr size_t kStageBytes = (sizeof(double) * kStageRows * kStageStride + 31) & ~size_t(31);
+constexpr size_t kOffSlot2 = kOffStage + kStageBytes;                             // per-slot double2
+constexpr size_t kOffSlot3 = kOffSlot2 + sizeof(double2) * kChunkEdges;           // per-slot 3 doubles (K3 only)
+constexpr size_t kOffPose = kOffSlot3 + sizeof(double) * 3 * kChunkEdges;         // double4 per pose of the block
+constexpr size_t kOffSedge = kOffPose + sizeof(double4) * kBlockPoses;            // u16 per edge
+constexpr size_t kOffRed = kOffSedge + sizeof(uint16_t) * kChunkEdges;
+constexpr size_t kSmemBytes = kOffRed + sizeof(double) * (kThreads / 32);
+static_assert(kOffSlot2 % 16 == 0 && kOffPose % 32 == 0, "alignment");
+static_assert(sizeof(double) * kBlockPoses * kStageRows <= kStageBytes, "acc must fit in stage");
+
+struct Smem {
+    double* stage; double* acc; double2* slot2; double* slot3; double4* pose; uint16_t* sedge; double* red;
+    __device__ explicit Smem(unsigned char* b)
+        : stage(reinterpret_cast<double*>(b + kOffStage)), acc(reinterpret_cast<double*>(b + kOffStage)),
+          slot2(reinterpret_cast<double2*>(b + kOffSlot2)), slot3(reinterpret_cast<double*>(b + kOffSlot3)),
+          pose(reinterpret_cast<double4*>(b + kOffPose)), sedge(reinterpret_cast<uint16_t*>(b + kOffSedge)),
+          red(reinterpret_cast<double*>(b + kOffRed)) {}
+};
+
+__device__ __forceinline__ double warp_sum(double v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_down_sync(0xffffffffu, v, o);
+    return v;
+}
+
+// deterministic block sum; result valid in thread 0
+__device__ __forceinline__ double block_sum(double v, double* red) {
+    v = warp_sum(v);
+    if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = v;
+    __syncthreads();
+    double t = 0;
+    if (threadIdx.x == 0) { for (int i = 0; i < kThreads / 32; ++i) t += red[i]; }
+    __syncthreads();
+    return t;
+}
+
+// Huber on chi2 with delta = 1.5 (OptimizerCpu.h:36-46)
+__device__ __forceinline__ void robustify(double chi2, double& rho, double& w) {
+    if (chi2 <= 2.25) { rho = chi2; w = 1.0; }
+    else { const double sq = sqrt(chi2); rho = 3.0 * sq - 2.25; w = 1.5 / sq; }
+}
+
+// ODOM edge (EdgeSe2.h:24-38): e = (D02, D12, atan2(D10, D00)), D = Zinv * (Xa^-1 * Xb); A = -I, B = +I.
+// Returns the weighted information W = huber_w * diag(w) and W*e.
+__device__ __forceinline__ void odom_edge(const double4 a, const double4 b, const double* __restrict__ zi,
+                                          const double* __restrict__ w, double W[3], double We[3], double& rho) {
+    // Xa^-1 = [[c, s, -(c x + s y)], [-s, c, s x - c y]]
+    const double i02 = -(a.z * a.x + a.w * a.y), i12 = a.w * a.x - a.z * a.y;
+    const double p00 = a.z * b.z + a.w * b.w, p10 = -a.w * b.z + a.z * b.w;       // (Xa^-1 Xb) first column
+    const double p02 = a.z * b.x + a.w * b.y + i02, p12 = -a.w * b.x + a.z * b.y + i12;
+    const double d00 = zi[0] * p00 + zi[1] * p10, d10 = zi[3] * p00 + zi[4] * p10;
+    const double e0 = zi[0] * p02 + zi[1] * p12 + zi[2];
+    const double e1 = zi[3] * p02 + zi[4] * p12 + zi[5];
+    const double e2 = atan2(d10, d00);
+    const double chi2 = e0 * (w[0] * e0) + e1 * (w[1] * e1) + e2 * (w[2] * e2);
+    double hw; robustify(chi2, rho, hw);
+    W[0] = w[0] * hw; W[1] = w[1] * hw; W[2] = w[2] * hw;
+    We[0] = W[0] * e0; We[1] = W[1] * e1; We[2] = W[2] * e2;
+}
+
+// sums stage[row][k] over the edges of `pose` that fall in the chunk, for items (pose, row)
+template <int ROWS>
+__device__ __forceinline__ void pose_reduce(const Dev& d, const ChunkDesc& ch, const double* stage, uint32_t np,
+                                            double (&acc)[kStageRows]) {
+#pragma unroll
+    for (int it = 0; it < kStageRows; ++it) {
+        const uint32_t item = threadIdx.x + it * kThreads;
+        if (item < np * ROWS) {
+            const uint32_t pl = item / ROWS, row = item % ROWS;
+            const uint32_t b = max(d.pose_ptr[ch.p0 + pl], ch.e0) - ch.e0;
+            const uint32_t e = min(d.pose_ptr[ch.p0 + pl + 1], ch.e1) - ch.e0;
+            const double* s = stage + row * kStageStride;
+            double t = 0;
+            for (uint32_t k = b; k < e; ++k) t += s[k];
+            acc[it] += t;
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// K1: linearize + assemble.  One block = a run of whole poses (or one heavy pose), one or more chunks.
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(kThreads) k_linearize(const Dev d) {
+    extern __shared__ __align__(32) unsigned char smem_raw[];
+    Smem sm(smem_raw);
+    const uint32_t c0 = d.blk_chunk_ptr[blockIdx.x], c1 = d.blk_chunk_ptr[blockIdx.x + 1];
+    const uint32_t p0 = d.chunks[c0].p0, np = d.chunks[c0].p1 - p0;
+    for (uint32_t i = threadIdx.x; i < np; i += kThreads) sm.pose[i] = d.pose[p0 + i];
+    double acc[kStageRows];
+#pragma unroll
+    for (int i = 0; i < kStageRows; ++i) acc[i] = 0;
+    double rho_sum = 0;
+    for (uint32_t c = c0; c < c1; ++c) {
+        const ChunkDesc ch = d.chunks[c];
+        const uint32_t n = ch.e1 - ch.e0, ns = ch.s1 - ch.s0;
+        for (uint32_t s = threadIdx.x; s < ns; s += kThreads) sm.slot2[s] = d.lm[d.slot_lm[ch.s0 + s]];
+        for (uint32_t k = threadIdx.x; k < n; k += kThreads) sm.sedge[k] = d.slot_edge[ch.e0 + k];
+        __syncthreads();
+        for (uint32_t k = threadIdx.x; k < n; k += kThreads) {
+            const uint32_t pk = d.lm_packed[ch.e0 + k];
+            const double2 z = d.le_z[ch.e0 + k], w = d.le_w[ch.e0 + k];
+            const double4 ps = sm.pose[pk >> 16];
+            const double2 l = sm.slot2[pk & 0xffffu];
+            const double c_ = ps.z, s_ = ps.w;
+            // e = X^-1 * l - z_loc   (EdgeSe2Point2d.h:34-38)
+            const double e0 = c_ * l.x + s_ * l.y - (c_ * ps.x + s_ * ps.y) - z.x;
+            const double e1 = -s_ * l.x + c_ * l.y + (s_ * ps.x - c_ * ps.y) - z.y;
+            // A = [[-c,-s,q0],[s,-c,q1]], B = [[c,s],[-s,c]]   (:55-67)
+            const double q0 = c_ * l.y - s_ * l.x - c_ * ps.y + s_ * ps.x;
+            const double q1 = -s_ * l.y - c_ * l.x + s_ * ps.y + c_ * ps.x;
+            double rho, hw; robustify(e0 * (w.x * e0) + e1 * (w.y * e1), rho, hw);
+            rho_sum += rho;
+            const double i0 = w.x * hw, i1 = w.y * hw, f0 = i0 * e0, f1 = i1 * e1;
+            const double m00 = c_ * i0 * c_ + s_ * i1 * s_;          // B^T W B
+            const double m01 = c_ * i0 * s_ - s_ * i1 * c_;
+            const double m11 = s_ * i0 * s_ + c_ * i1 * c_;
+            const double t0 = c_ * i0 * q0 - s_ * i1 * q1;           // B^T W q  ( = -(A^T W A)[0:2,2] )
+            const double t1 = s_ * i0 * q0 + c_ * i1 * q1;
+            const double qq = q0 * i0 * q0 + q1 * i1 * q1;
+            const double g0 = c_ * f0 - s_ * f1, g1 = s_ * f0 + c_ * f1;   // B^T W e
+            const double qe = q0 * f0 + q1 * f1;
+            // Hpl = A^T W B = [[-m00,-m01],[-m01,-m11],[t0,t1]]
+            double2* h = reinterpret_cast<double2*>(d.hpl + 6ull * (ch.e0 + k));
+            h[0] = make_double2(-m00, -m01); h[1] = make_double2(-m01, -m11); h[2] = make_double2(t0, t1);
+            double* st = sm.stage + k;
+            st[0 * kStageStride] = m00; st[1 * kStageStride] = m01; st[2 * kStageStride] = m11;
+            st[3 * kStageStride] = -t0; st[4 * kStageStride] = -t1; st[5 * kStageStride] = qq;
+            st[6 * kStageStride] = g0;  st[7 * kStageStride] = g1;  st[8 * kStageStride] = qe;
+        }
+        __syncthreads();
+        pose_reduce<kStageRows>(d, ch, sm.stage, np, acc);
+        // landmark side: one partial (M00 M01 M11 g0 g1) per slot, edges of the slot in list order
+        for (uint32_t item = threadIdx.x; item < ns * 5; item += kThreads) {
+            const uint32_t sl = item / 5, comp = item % 5;
+            const double* s = sm.stage + (comp < 3 ? comp : comp + 3) * kStageStride;
+            const uint32_t b = d.slot_ptr[ch.s0 + sl] - ch.e0, e = d.slot_ptr[ch.s0 + sl + 1] - ch.e0;
+            double t = 0;
+            for (uint32_t q = b; q < e; ++q) t += s[sm.sedge[q]];
+            d.lm_part[5ull * (ch.s0 + sl) + comp] = t;
+        }
+        __syncthreads();
+    }
+#pragma unroll
+    for (int it = 0; it < kStageRows; ++it) {
+        const uint32_t item = threadIdx.x + it * kThreads;
+        if (item < np * kStageRows) sm.acc[item] = acc[it];
+    }
+    __syncthreads();
+    // pose finalize: LM sums + ODOM edges (out: id1 == pose, in: id2 == pose) + prior
+    for (uint32_t i = threadIdx.x; i < np; i += kThreads) {
+        const double* a = sm.acc + i * kStageRows;
+        double h00 = a[0], h01 = a[1], h11 = a[2], h02 = a[3], h12 = a[4], h22 = a[5];
+        double b0 = a[6], b1 = a[7], b2 = -a[8];              // b -= A^T W e
+        const uint32_t p = p0 + i;
+        for (uint32_t k = d.od_out_ptr[p]; k < d.od_out_ptr[p + 1]; ++k) {
+            double W[3], We[3], rho;
+            odom_edge(sm.pose[i], d.pose[d.od_b[k]], d.od_zinv + 6ull * k, d.od_w + 3ull * k, W, We, rho);
+            rho_sum += rho;
+            h00 += W[0]; h11 += W[1]; h22 += W[2];            // A^T W A, A = -I
+            b0 += We[0]; b1 += We[1]; b2 += We[2];            // b -= A^T W e
+            d.hoo[3ull * k] = -W[0]; d.hoo[3ull * k + 1] = -W[1]; d.hoo[3ull * k + 2] = -W[2];
+        }
+        for (uint32_t q = d.od_in_ptr[p]; q < d.od_in_ptr[p + 1]; ++q) {
+            const uint32_t k = d.od_in_edge[q];
+            double W[3], We[3], rho;
+            odom_edge(d.pose[d.od_a[k]], sm.pose[i], d.od_zinv + 6ull * k, d.od_w + 3ull * k, W, We, rho);
+            h00 += W[0]; h11 += W[1]; h22 += W[2];            // B^T W B, B = +I
+            b0 -= We[0]; b1 -= We[1]; b2 -= We[2];
+            if (k >= d.nOwned) { d.hoo[3ull * k] = -W[0]; d.hoo[3ull * k + 1] = -W[1]; d.hoo[3ull * k + 2] = -W[2]; }
+        }
+        const double prior = 1e6 * (double)d.fixed_pose_count[p];     // OptimizerCpu.h:132-138
+        h00 += prior; h11 += prior; h22 += prior;
+        double* H = d.hpp + 6ull * p;
+        H[0] = h00; H[1] = h01; H[2] = h02; H[3] = h11; H[4] = h12; H[5] = h22;
+        double* B = d.bp + 3ull * p;
+        B[0] = b0; B[1] = b1; B[2] = b2;
+    }
+    const double t = block_sum(rho_sum, sm.red);
+    if (threadIdx.x == 0) d.part[blockIdx.x] = t;
+}
+
+// ------------------------------------------------------------------------------------------------
+// K2a: landmark-major sum of the slot partials (5 values per landmark), fixed order.
+// K2b: prior, Hll, b_l, Hll^-1 (closed-form 2x2) and the chi2 total.
+// ------------------------------------------------------------------------------------------------
+__global__ void k_lm_sum(const Dev d) {
+    const uint32_t l = blockIdx.x * blockDim.x + threadIdx.x;
+    if (l >= d.L) return;
+    double a0 = 0, a1 = 0, a2 = 0, a3 = 0, a4 = 0;
+    for (uint32_t q = d.lm_part_ptr[l]; q < d.lm_part_ptr[l + 1]; ++q) {
+        const double* r = d.lm_part + 5ull * d.lm_part_idx[q];
+        a0 += r[0]; a1 += r[1]; a2 += r[2]; a3 += r[3]; a4 += r[4];
+    }
+    double* o = d.lm_sum + 5ull * l;
+    o[0] = a0; o[1] = a1; o[2] = a2; o[3] = a3; o[4] = a4;
+}
+
+__global__ void k_lm_finalize(const Dev d) {
+    const uint32_t l = blockIdx.x * blockDim.x + threadIdx.x;
+    if (l >= d.L) return;
+    const double* a = d.lm_sum + 5ull * l;
+    const double prior = 1e6 * (double)d.fixed_lm_count[l];
+    const double h00 = a[0] + prior, h01 = a[1], h11 = a[2] + prior;
+    d.hll[3ull * l] = h00; d.hll[3ull * l + 1] = h01; d.hll[3ull * l + 2] = h11;
+    d.bl[2ull * l] = -a[3]; d.bl[2ull * l + 1] = -a[4];           // b_l -= B^T W e
+    const double id = 1.0 / (h00 * h11 - h01 * h01);
+    d.hinv[3ull * l] = h11 * id; d.hinv[3ull * l + 1] = -h01 * id; d.hinv[3ull * l + 2] = h00 * id;
+}
+
+// sums `n` partials in a fixed order with one block; out[0] = total
+__device__ __forceinline__ double reduce_parts(const double* part, uint32_t n, double* red) {
+    double t = 0;
+    for (uint32_t i = threadIdx.x; i < n; i += blockDim.x) t += part[i];
+    t = warp_sum(t);
+    if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = t;
+    __syncthreads();
+    double r = 0;
+    if (threadIdx.x == 0) for (uint32_t i = 0; i < blockDim.x / 32; ++i) r += red[i];
+    return r;
+}
+
+__global__ void k_reduce_to(const double* part, uint32_t n, double* out) {
+    __shared__ double red[32];
+    const double r = reduce_parts(part, n, red);
+    if (threadIdx.x == 0) *out = r;
+}
+
+// ------------------------------------------------------------------------------------------------
+// K3: Schur preparation.  diag(S)_i = Hpp_ii - sum_e Hpl_e Hll^-1 Hpl_e^T,  rhs_i = b_i - sum_e Hpl_e Hll^-1 b_l
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(kThreads) k_schur_prep(const Dev d) {
+    extern __shared__ __align__(32) unsigned char smem_raw[];
+    Smem sm(smem_raw);
+    const uint32_t c0 = d.blk_chunk_ptr[blockIdx.x], c1 = d.blk_chunk_ptr[blockIdx.x + 1];
+    const uint32_t p0 = d.chunks[c0].p0, np = d.chunks[c0].p1 - p0;
+    double acc[kStageRows];
+#pragma unroll
+    for (int i = 0; i < kStageRows; ++i) acc[i] = 0;
+    for (uint32_t c = c0; c < c1; ++c) {
+        const ChunkDesc ch = d.chunks[c];
+        const uint32_t n = ch.e1 - ch.e0, ns = ch.s1 - ch.s0;
+        for (uint32_t s = threadIdx.x; s < ns; s += kThreads) {
+            const uint32_t l = d.slot_lm[ch.s0 + s];
+            sm.slot2[s] = make_double2(d.bl[2ull * l], d.bl[2ull * l + 1]);
+            sm.slot3[3 * s] = d.hinv[3ull * l]; sm.slot3[3 * s + 1] = d.hinv[3ull * l + 1]; sm.slot3[3 * s + 2] = d.hinv[3ull * l + 2];
+        }
+        __syncthreads();
+        for (uint32_t k = threadIdx.x; k < n; k += kThreads) {
+            const uint32_t sl = d.lm_packed[ch.e0 + k] & 0xffffu;
+            const double2* hp = reinterpret_cast<const double2*>(d.hpl + 6ull * (ch.e0 + k));
+            const double2 r0 = hp[0], r1 = hp[1], r2 = hp[2];
+            const double i00 = sm.slot3[3 * sl], i01 = sm.slot3[3 * sl + 1], i11 = sm.slot3[3 * sl + 2];
+            const double2 bl = sm.slot2[sl];
+            // T = Hpl * Hll^-1  (3x2)
+            const double t00 = r0.x * i00 + r0.y * i01, t01 = r0.x * i01 + r0.y * i11;
+            const double t10 = r1.x * i00 + r1.y * i01, t11 = r1.x * i01 + r1.y * i11;
+            const double t20 = r2.x * i00 + r2.y * i01, t21 = r2.x * i01 + r2.y * i11;
+            double* st = sm.stage + k;
+            st[0 * kStageStride] = t00 * r0.x + t01 * r0.y;      // (T Hpl^T) 00 01 02 11 12 22
+            st[1 * kStageStride] = t00 * r1.x + t01 * r1.y;
+            st[2 * kStageStride] = t00 * r2.x + t01 * r2.y;
+            st[3 * kStageStride] = t10 * r1.x + t11 * r1.y;
+            st[4 * kStageStride] = t10 * r2.x + t11 * r2.y;
+            st[5 * kStageStride] = t20 * r2.x + t21 * r2.y;
+            st[6 * kStageStride] = t00 * bl.x + t01 * bl.y;      // T b_l
+            st[7 * kStageStride] = t10 * bl.x + t11 * bl.y;
+            st[8 * kStageStride] = t20 * bl.x + t21 * bl.y;
+        }
+        __syncthreads();
+        pose_reduce<kStageRows>(d, ch, sm.stage, np, acc);
+        __syncthreads();
+    }
+#pragma unroll
+    for (int it = 0; it < kStageRows; ++it) {
+        const uint32_t item = threadIdx.x + it * kThreads;
+        if (item < np * kStageRows) sm.acc[item] = acc[it];
+    }
+    __syncthreads();
+    for (uint32_t i = threadIdx.x; i < np; i += kThreads) {
+        const double* a = sm.acc + i * kStageRows;
+        const uint32_t p = p0 + i;
+        const double* H = d.hpp + 6ull * p;
+        const double s00 = H[0] - a[0], s01 = H[1] - a[1], s02 = H[2] - a[2], s11 = H[3] - a[3], s12 = H[4] - a[4], s22 = H[5] - a[5];
+        // symmetric 3x3 inverse by cofactors
+        const double c00 = s11 * s22 - s12 * s12, c01 = s02 * s12 - s01 * s22, c02 = s01 * s12 - s02 * s11;
+        const double id = 1.0 / (s00 * c00 + s01 * c01 + s02 * c02);
+        double* M = d.minv + 6ull * p;
+        M[0] = c00 * id; M[1] = c01 * id; M[2] = c02 * id;
+        M[3] = (s00 * s22 - s02 * s02) * id; M[4] = (s01 * s02 - s00 * s12) * id; M[5] = (s00 * s11 - s01 * s01) * id;
+        d.rhs[3ull * p] = d.bp[3ull * p] - a[6]; d.rhs[3ull * p + 1] = d.bp[3ull * p + 1] - a[7]; d.rhs[3ull * p + 2] = d.bp[3ull * p + 2] - a[8];
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// K4: block-Jacobi PCG on the reduced pose system, matrix-free:
+//     S v = Hpp v - Hpl (Hll^-1 (Hpl^T v))
+//   pass A : t_e = Hpl_e^T v_pose(e)  -> per-slot partial sums            (one stream over Hpl)
+//   w_sum  : landmark-major sum of the slot partials
+//   pass B : u_l = Hll^-1 w_l;  (S v)_i = Hpp_ii v_i + sum_odom Hoo v_j - sum_e Hpl_e u_l(e); v'Sv partials
+// Scalars (alpha, beta, r'z, stop flag) stay on the device; kernels return at once when the flag is set.
+// ------------------------------------------------------------------------------------------------
+__device__ __forceinline__ void sym3_mul(const double* M, double a, double b, double c, double& o0, double& o1, double& o2) {
+    o0 = M[0] * a + M[1] * b + M[2] * c; o1 = M[1] * a + M[3] * b + M[4] * c; o2 = M[2] * a + M[4] * b + M[5] * c;
+}
+
+__global__ void k_pcg_init(const Dev d) {
+    __shared__ double red[kThreads / 32];
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    double dot = 0;
+    if (i < d.nP) {
+        const double r0 = d.rhs[3ull * i], r1 = d.rhs[3ull * i + 1], r2 = d.rhs[3ull * i + 2];
+        double z0, z1, z2; sym3_mul(d.minv + 6ull * i, r0, r1, r2, z0, z1, z2);
+        d.x[3ull * i] = 0; d.x[3ull * i + 1] = 0; d.x[3ull * i + 2] = 0;
+        d.r[3ull * i] = r0; d.r[3ull * i + 1] = r1; d.r[3ull * i + 2] = r2;
+        d.z[3ull * i] = z0; d.z[3ull * i + 1] = z1; d.z[3ull * i + 2] = z2;
+        d.p[3ull * i] = z0; d.p[3ull * i + 1] = z1; d.p[3ull * i + 2] = z2;
+        dot = r0 * z0 + r1 * z1 + r2 * z2;
+    }
+    const double t = block_sum(dot, red);
+    if (threadIdx.x == 0) d.part[blockIdx.x] = t;
+}
+
+__global__ void k_pcg_init_scal(const Dev d, uint32_t nparts) {
+    __shared__ double red[32];
+    const double rz = reduce_parts(d.part, nparts, red);
+    if (threadIdx.x == 0) {
+        d.scal[S_RZ0] = rz; d.scal[S_RZ] = rz; d.scal[S_BETA] = 0; d.scal[S_ALPHA] = 0;
+        d.flags[F_ITERS] = 0; d.flags[F_DONE] = (rz > 0) ? 0 : 1;
+    }
+}
+
+template <int MODE>   // 0: v = p, with the update p = z + beta p fused in;  1: v = x
+__global__ void __launch_bounds__(kThreads) k_pcg_pass_a(const Dev d) {
+    if (MODE == 0 && d.flags[F_DONE]) return;
+    extern __shared__ __align__(32) unsigned char smem_raw[];
+    Smem sm(smem_raw);
+    double* v = reinterpret_cast<double*>(sm.pose);
+    const uint32_t c0 = d.blk_chunk_ptr[blockIdx.x], c1 = d.blk_chunk_ptr[blockIdx.x + 1];
+    const uint32_t p0 = d.chunks[c0].p0, np = d.chunks[c0].p1 - p0;
+    if (MODE == 0) {
+        const double beta = d.scal[S_BETA];
+        for (uint32_t i = threadIdx.x; i < 3 * np; i += kThreads) {
+            const double t = d.z[3ull * p0 + i] + beta * d.p[3ull * p0 + i];
+            d.p[3ull * p0 + i] = t; v[i] = t;
+        }
+    } else {
+        for (uint32_t i = threadIdx.x; i < 3 * np; i += kThreads) v[i] = d.x[3ull * p0 + i];
+    }
+    for (uint32_t c = c0; c < c1; ++c) {
+        const ChunkDesc ch = d.chunks[c];
+        const uint32_t n = ch.e1 - ch.e0, ns = ch.s1 - ch.s0;
+        for (uint32_t k = threadIdx.x; k < n; k += kThreads) sm.sedge[k] = d.slot_edge[ch.e0 + k];
+        __syncthreads();
+        for (uint32_t k = threadIdx.x; k < n; k += kThreads) {
+            const uint32_t pl = d.lm_packed[ch.e0 + k] >> 16;
+            const double2* hp = reinterpret_cast<const double2*>(d.hpl + 6ull * (ch.e0 + k));
+            const double2 r0 = hp[0], r1 = hp[1], r2 = hp[2];
+            const double v0 = v[3 * pl], v1 = v[3 * pl + 1], v2 = v[3 * pl + 2];
+            sm.stage[k] = r0.x * v0 + r1.x * v1 + r2.x * v2;
+            sm.stage[kStageStride + k] = r0.y * v0 + r1.y * v1 + r2.y * v2;
+        }
+        __syncthreads();
+        for (uint32_t item = threadIdx.x; item < ns * 2; item += kThreads) {
+            const uint32_t sl = item >> 1, comp = item & 1;
+            const double* s = sm.stage + comp * kStageStride;
+            const uint32_t b = d.slot_ptr[ch.s0 + sl] - ch.e0, e = d.slot_ptr[ch.s0 + sl + 1] - ch.e0;
+            double t = 0;
+            for (uint32_t q = b; q < e; ++q) t += s[sm.sedge[q]];
+            d.w_part[2ull * (ch.s0 + sl) + comp] = t;
+        }
+        __syncthreads();
+    }
+}
+
+__global__ void k_pcg_w_sum(const Dev d, int check_done) {
+    if (check_done && d.flags[F_DONE]) return;
+    const uint32_t l = blockIdx.x * blockDim.x + threadIdx.x;
+    if (l >= d.L) return;
+    double a0 = 0, a1 = 0;
+    for (uint32_t q = d.lm_part_ptr[l]; q < d.lm_part_ptr[l + 1]; ++q) {
+        const double2 r = reinterpret_cast<const double2*>(d.w_part)[d.lm_part_idx[q]];
+        a0 += r.x; a1 += r.y;
+    }
+    reinterpret_cast<double2*>(d.w_sum)[l] = make_double2(a0, a1);
+}
+
+__global__ void __launch_bounds__(kThreads) k_pcg_pass_b(const Dev d) {
+    if (d.flags[F_DONE]) return;
+    extern __shared__ __align__(32) unsigned char smem_raw[];
+    Smem sm(smem_raw);
+    const uint32_t c0 = d.blk_chunk_ptr[blockIdx.x], c1 = d.blk_chunk_ptr[blockIdx.x + 1];
+    const uint32_t p0 = d.chunks[c0].p0, np = d.chunks[c0].p1 - p0;
+    double acc[kStageRows];
+#pragma unroll
+    for (int i = 0; i < kStageRows; ++i) acc[i] = 0;
+    for (uint32_t c = c0; c < c1; ++c) {
+        const ChunkDesc ch = d.chunks[c];
+        const uint32_t n = ch.e1 - ch.e0, ns = ch.s1 - ch.s0;
+        for (uint32_t s = threadIdx.x; s < ns; s += kThreads) {
+            const uint32_t l = d.slot_lm[ch.s0 + s];
+            const double2 w = reinterpret_cast<const double2*>(d.w_sum)[l];
+            const double* hi = d.hinv + 3ull * l;
+            sm.slot2[s] = make_double2(hi[0] * w.x + hi[1] * w.y, hi[1] * w.x + hi[2] * w.y);
+        }
+        __syncthreads();
+        for (uint32_t k = threadIdx.x; k < n; k += kThreads) {
+            const double2 u = sm.slot2[d.lm_packed[ch.e0 + k] & 0xffffu];
+            const double2* hp = reinterpret_cast<const double2*>(d.hpl + 6ull * (ch.e0 + k));
+            const double2 r0 = hp[0], r1 = hp[1], r2 = hp[2];
+            sm.stage[k] = r0.x * u.x + r0.y * u.y;
+            sm.stage[kStageStride + k] = r1.x * u.x + r1.y * u.y;
+            sm.stage[2 * kStageStride + k] = r2.x * u.x + r2.y * u.y;
+        }
+        __syncthreads();
+        pose_reduce<3>(d, ch, sm.stage, np, acc);
+        __syncthreads();
+    }
+#pragma unroll
+    for (int it = 0; it < 3; ++it) {
+        const uint32_t item = threadIdx.x + it * kThreads;
+        if (item < np * 3) sm.acc[item] = acc[it];
+    }
+    __syncthreads();
+    double dot = 0;
+    for (uint32_t i = threadIdx.x; i < np; i += kThreads) {
+        const uint32_t p = p0 + i;
+        const double v0 = d.p[3ull * p], v1 = d.p[3ull * p + 1], v2 = d.p[3ull * p + 2];
+        double y0, y1, y2; sym3_mul(d.hpp + 6ull * p, v0, v1, v2, y0, y1, y2);
+        for (uint32_t k = d.od_out_ptr[p]; k < d.od_out_ptr[p + 1]; ++k) {
+            const double* h = d.hoo + 3ull * k; const double* q = d.p + 3ull * d.od_b[k];
+            y0 += h[0] * q[0]; y1 += h[1] * q[1]; y2 += h[2] * q[2];
+        }
+        for (uint32_t j = d.od_in_ptr[p]; j < d.od_in_ptr[p + 1]; ++j) {
+            const uint32_t k = d.od_in_edge[j];
+            const double* h = d.hoo + 3ull * k; const double* q = d.p + 3ull * d.od_a[k];
+            y0 += h[0] * q[0]; y1 += h[1] * q[1]; y2 += h[2] * q[2];
+        }
+        y0 -= sm.acc[3 * i]; y1 -= sm.acc[3 * i + 1]; y2 -= sm.acc[3 * i + 2];
+        d.sp[3ull * p] = y0; d.sp[3ull * p + 1] = y1; d.sp[3ull * p + 2] = y2;
+        dot += v0 * y0 + v1 * y1 + v2 * y2;
+    }
+    const double t = block_sum(dot, sm.red);
+    if (threadIdx.x == 0) d.part[blockIdx.x] = t;
+}
+
+__global__ void k_pcg_alpha(const Dev d) {
+    if (d.flags[F_DONE]) return;
+    __shared__ double red[32];
+    const double psp = reduce_parts(d.part, d.nBlocks, red);
+    if (threadIdx.x == 0) { d.scal[S_PSP] = psp; d.scal[S_ALPHA] = d.scal[S_RZ] / (psp + d.scal[S_PSP_EXTRA]); }
+}
+
+__global__ void k_pcg_update(const Dev d) {
+    if (d.flags[F_DONE]) return;
+    __shared__ double red[kThreads / 32];
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    double dot = 0;
+    if (i < d.nP) {
+        const double alpha = d.scal[S_ALPHA];
+        double r[3], z[3];
+#pragma unroll
+        for (int q = 0; q < 3; ++q) {
+            d.x[3ull * i + q] += alpha * d.p[3ull * i + q];
+            r[q] = d.r[3ull * i + q] - alpha * d.sp[3ull * i + q];
+            d.r[3ull * i + q] = r[q];
+        }
+        sym3_mul(d.minv + 6ull * i, r[0], r[1], r[2], z[0], z[1], z[2]);
+        d.z[3ull * i] = z[0]; d.z[3ull * i + 1] = z[1]; d.z[3ull * i + 2] = z[2];
+        dot = r[0] * z[0] + r[1] * z[1] + r[2] * z[2];
+    }
+    const double t = block_sum(dot, red);
+    if (threadIdx.x == 0) d.part[blockIdx.x] = t;
+}
+
+__global__ void k_pcg_beta(const Dev d, uint32_t nparts) {
+    if (d.flags[F_DONE]) return;
+    __shared__ double red[32];
+    const double rz_new = reduce_parts(d.part, nparts, red);
+    if (threadIdx.x == 0) {
+        d.scal[S_BETA] = rz_new / d.scal[S_RZ]; d.scal[S_RZ] = rz_new;
+        const int it = d.flags[F_ITERS] + 1; d.flags[F_ITERS] = it;
+        if (!(rz_new > d.scal[S_TOL2] * d.scal[S_RZ0]) || it >= d.flags[F_MAXIT]) d.flags[F_DONE] = 1;
+    }
+}
+
+// delta_l = Hll^-1 (b_l - Hpl^T delta_p); w_sum holds Hpl^T delta_p
+__global__ void k_backsub(const Dev d) {
+    const uint32_t l = blockIdx.x * blockDim.x + threadIdx.x;
+    if (l >= d.L) return;
+    const double t0 = d.bl[2ull * l] - d.w_sum[2ull * l], t1 = d.bl[2ull * l + 1] - d.w_sum[2ull * l + 1];
+    const double* hi = d.hinv + 3ull * l;
+    d.dl[2ull * l] = hi[0] * t0 + hi[1] * t1; d.dl[2ull * l + 1] = hi[1] * t0 + hi[2] * t1;
+}
+
+// ------------------------------------------------------------------------------------------------
+// K5: x <- x [+] step * delta  (VertexSe2.h:16-27, Vertex2d.h:16-19) and ||delta||^2 partials
+// ------------------------------------------------------------------------------------------------
+__global__ void k_update_state(const Dev d, double step) {
+    __shared__ double red[kThreads / 32];
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    double np2 = 0, nl2 = 0;
+    if (i < d.nP) {
+        const double d0 = d.x[3ull * i], d1 = d.x[3ull * i + 1], d2 = d.x[3ull * i + 2];
+        double4 ps = d.pose[i];
+        const double th = atan2(ps.w, ps.z) + d2 * step;
+        double s, c; sincos(th, &s, &c);
+        ps.x += d0 * step; ps.y += d1 * step; ps.z = c; ps.w = s;
+        d.pose[i] = ps;
+        np2 = d0 * d0 + d1 * d1 + d2 * d2;
+    }
+    if (i < d.L) {
+        const double d0 = d.dl[2ull * i], d1 = d.dl[2ull * i + 1];
+        double2 l = d.lm[i]; l.x += d0 * step; l.y += d1 * step; d.lm[i] = l;
+        nl2 = d0 * d0 + d1 * d1;
+    }
+    const double t = block_sum(np2, red);
+    const double u = block_sum(nl2, red);
+    if (threadIdx.x == 0) { d.part[blockIdx.x] = t; d.part2[blockIdx.x] = u; }
+}
+
+__global__ void k_init_pose(const double* xyt, uint32_t n, double4* out) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    // CreateTransform2d (Helper.h:6-18): rotation through the unit quaternion (cos t/2, 0, 0, sin t/2)
+    const double th = xyt[3ull * i + 2];
+    double sh, ch; sincos(0.5 * th, &sh, &ch);
+    const double tz = 2.0 * sh;
+    out[i] = make_double4(xyt[3ull * i], xyt[3ull * i + 1], 1.0 - tz * sh, tz * ch);
+}
+
+__global__ void k_read_pose(const double4* pose, uint32_t n, double* xyt) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const double4 p = pose[i];
+    xyt[3ull * i] = p.x; xyt[3ull * i + 1] = p.y; xyt[3ull * i + 2] = atan2(p.w, p.z);   // SerializeGraphFuncCpu.h:28
+}
+
+}  // namespace
+
+// ------------------------------------------------------------------------------------------------
+// launchers
+// ------------------------------------------------------------------------------------------------
+uint64_t g_launches = 0;
+static inline uint32_t cdiv(uint32_t a, uint32_t b) { return (a + b - 1) / b; }
+size_t linearize_smem_bytes() { return kSmemBytes; }
+
+static bool g_attr_set = false;
+static void set_attrs() {
+    if (g_attr_set) return;
+    cudaFuncSetAttribute(k_linearize, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemBytes);
+    cudaFuncSetAttribute(k_schur_prep, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemBytes);
+    cudaFuncSetAttribute(k_pcg_pass_a<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemBytes);
+    cudaFuncSetAttribute(k_pcg_pass_a<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemBytes);
+    cudaFuncSetAttribute(k_pcg_pass_b, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemBytes);
+    g_attr_set = true;
+}
+
+void launch_linearize(const Dev& d, cudaStream_t s) {
+    set_attrs();
+    if (d.nBlocks) { k_linearize<<<d.nBlocks, kThreads, kSmemBytes, s>>>(d); ++g_launches; }
+    k_reduce_to<<<1, 1024, 0, s>>>(d.part, d.nBlocks, d.scal + S_CHI2); ++g_launches;
+}
+void launch_lm_sum(const Dev& d, cudaStream_t s) {
+    if (d.L) { k_lm_sum<<<cdiv(d.L, kThreads), kThreads, 0, s>>>(d); ++g_launches; }
+}
+void launch_lm_finalize(const Dev& d, cudaStream_t s) {
+    if (d.L) { k_lm_finalize<<<cdiv(d.L, kThreads), kThreads, 0, s>>>(d); ++g_launches; }
+}
+void launch_schur_prep(const Dev& d, cudaStream_t s) {
+    set_attrs();
+    if (d.nBlocks) { k_schur_prep<<<d.nBlocks, kThreads, kSmemBytes, s>>>(d); ++g_launches; }
+}
+void launch_pcg_init(const Dev& d, cudaStream_t s) {
+    const uint32_t nb = cdiv(d.nP, kThreads);
+    if (nb) { k_pcg_init<<<nb, kThreads, 0, s>>>(d); ++g_launches; }
+    k_pcg_init_scal<<<1, 1024, 0, s>>>(d, nb); ++g_launches;
+}
+void launch_pcg_pass_a(const Dev& d, int mode, cudaStream_t s) {
+    set_attrs();
+    if (!d.nBlocks) return;
+    if (mode == 0) k_pcg_pass_a<0><<<d.nBlocks, kThreads, kSmemBytes, s>>>(d);
+    else k_pcg_pass_a<1><<<d.nBlocks, kThreads, kSmemBytes, s>>>(d);
+    ++g_launches;
+}
+void launch_pcg_w_sum(const Dev& d, int check_done, cudaStream_t s) {
+    if (d.L) { k_pcg_w_sum<<<cdiv(d.L, kThreads), kThreads, 0, s>>>(d, check_done); ++g_launches; }
+}
+void launch_pcg_pass_b(const Dev& d, cudaStream_t s) {
+    set_attrs();
+    if (d.nBlocks) { k_pcg_pass_b<<<d.nBlocks, kThreads, kSmemBytes, s>>>(d); ++g_launches; }
+}
+void launch_pcg_alpha(const Dev& d, cudaStream_t s) { k_pcg_alpha<<<1, 1024, 0, s>>>(d); ++g_launches; }
+void launch_pcg_update(const Dev& d, cudaStream_t s) {
+    const uint32_t nb = cdiv(d.nP, kThreads);
+    if (nb) { k_pcg_update<<<nb, kThreads, 0, s>>>(d); ++g_launches; }
+}
+void launch_pcg_beta(const Dev& d, cudaStream_t s) { k_pcg_beta<<<1, 1024, 0, s>>>(d, cdiv(d.nP, kThreads)); ++g_launches; }
+void launch_backsub(const Dev& d, cudaStream_t s) {
+    if (d.L) { k_backsub<<<cdiv(d.L, kThreads), kThreads, 0, s>>>(d); ++g_launches; }
+}
+void launch_update_state(const Dev& d, double step, cudaStream_t s) {
+    const uint32_t nb = cdiv(d.nP > d.L ? d.nP : d.L, kThreads);
+    if (!nb) return;
+    k_update_state<<<nb, kThreads, 0, s>>>(d, step); ++g_launches;
+    k_reduce_to<<<1, 1024, 0, s>>>(d.part, nb, d.scal + S_DELTA2); ++g_launches;
+    k_reduce_to<<<1, 1024, 0, s>>>(d.part2, nb, d.scal + S_DELTA2L); ++g_launches;
+}
+void launch_init_pose(const double* xyt, uint32_t n, double4* out, cudaStream_t s) {
+    if (n) { k_init_pose<<<cdiv(n, kThreads), kThreads, 0, s>>>(xyt, n, out); ++g_launches; }
+}
+void launch_read_pose(const double4* pose, uint32_t n, double* xyt, cudaStream_t s) {
+    if (n) { k_read_pose<<<cdiv(n, kThreads), kThreads, 0, s>>>(pose, n, xyt); ++g_launches; }
+}
+
+}  // namespace tsb

@@ -1,0 +1,148 @@
+// structure.cpp -- integer assembly structure ("edge -> block index map").
+// Replaces the reference's per-edge hash lookups into a dense H (OptimizerCpu.h:48-68,96-99;
+// GraphGpu.h:95-111 `indexesInH`) by a precomputed block pattern:
+//   * LM edges sorted by (pose, landmark): pose-side sums are contiguous row segments;
+//   * chunks of <= kChunkEdges edges covering whole poses; inside a chunk every distinct landmark
+//     gets a slot, the chunk emits one partial (Hll, b_l) sum per slot, and a landmark-major CSR
+//     over slots finishes the sum.  Fixed summation order everywhere -> deterministic, no atomics.
+#include "host_graph.h"
+
+#include <algorithm>
+#include <numeric>
+
+namespace tsb {
+
+void build_structure(const HostGraph& g, uint32_t rank, uint32_t world, Structure& s) {
+    s = Structure();
+    const uint32_t P = g.P, L = g.L;
+    // ---- pose partition: contiguous ranges balanced by edge work --------------------------------
+    std::vector<uint32_t> deg(P + 1, 0);
+    for (uint32_t e = 0; e < g.El; ++e) deg[g.le_i[e]]++;
+    if (world <= 1) { s.pose_begin = 0; s.pose_end = P; }
+    else {
+        std::vector<uint64_t> wsum(P + 1, 0);
+        std::vector<uint32_t> odeg(P, 0);
+        for (uint32_t e = 0; e < g.Eo; ++e) odeg[g.od_i[e]]++;
+        for (uint32_t p = 0; p < P; ++p) wsum[p + 1] = wsum[p] + deg[p] + 2ull * odeg[p] + 1;
+        auto cut = [&](uint32_t r) -> uint32_t {
+            if (r == 0) return 0;
+            if (r >= world) return P;
+            const uint64_t target = wsum[P] * r / world;
+            return (uint32_t)(std::lower_bound(wsum.begin(), wsum.end(), target) - wsum.begin());
+        };
+        s.pose_begin = cut(rank); s.pose_end = cut(rank + 1);
+    }
+    const uint32_t pb = s.pose_begin, pe = s.pose_end, nP = pe - pb;
+    s.nP = nP;
+    // ---- local LM edges in assembly order --------------------------------------------------------
+    s.pose_ptr.assign(nP + 1, 0);
+    for (uint32_t p = 0; p < nP; ++p) s.pose_ptr[p + 1] = s.pose_ptr[p] + deg[pb + p];
+    const uint32_t nE = s.pose_ptr[nP];
+    s.le_local.reserve(nE);
+    std::vector<uint32_t> cur(s.pose_ptr.begin(), s.pose_ptr.end() - 1);
+    s.lm_perm.resize(nE);
+    for (uint32_t e = 0; e < g.El; ++e) {
+        const uint32_t p = g.le_i[e];
+        if (p < pb || p >= pe) continue;
+        s.lm_perm[cur[p - pb]++] = (uint32_t)s.le_local.size();     // stable: request order inside a pose
+        s.le_local.push_back(e);
+    }
+    for (uint32_t p = 0; p < nP; ++p) {                              // then by landmark inside a pose
+        auto b = s.lm_perm.begin() + s.pose_ptr[p], e = s.lm_perm.begin() + s.pose_ptr[p + 1];
+        std::sort(b, e, [&](uint32_t x, uint32_t y) {
+            const uint32_t lx = g.le_l[s.le_local[x]], ly = g.le_l[s.le_local[y]];
+            return lx != ly ? lx < ly : x < y; });
+    }
+    // ---- blocks and chunks ------------------------------------------------------------------------
+    s.blk_chunk_ptr.push_back(0);
+    for (uint32_t p = 0; p < nP;) {
+        const uint32_t d = s.pose_ptr[p + 1] - s.pose_ptr[p];
+        const uint32_t blk = (uint32_t)s.blk_chunk_ptr.size() - 1;
+        if (d > kChunkEdges) {                                       // a single heavy pose: several chunks
+            for (uint32_t e0 = s.pose_ptr[p]; e0 < s.pose_ptr[p + 1]; e0 += kChunkEdges)
+                s.chunks.push_back({e0, std::min(e0 + kChunkEdges, s.pose_ptr[p + 1]), p, p + 1, 0, 0, blk, 0});
+            ++p;
+        } else {
+            uint32_t q = p, cnt = 0;
+            while (q < nP && q - p < kBlockPoses) {
+                const uint32_t dq = s.pose_ptr[q + 1] - s.pose_ptr[q];
+                if (cnt + dq > kChunkEdges) break;
+                cnt += dq; ++q;
+            }
+            s.chunks.push_back({s.pose_ptr[p], s.pose_ptr[q], p, q, 0, 0, blk, 0});
+            p = q;
+        }
+        s.blk_chunk_ptr.push_back((uint32_t)s.chunks.size());
+    }
+    // ---- slots: distinct landmarks per chunk ---------------------------------------------------------
+    s.lm_packed.resize(nE); s.slot_edge.resize(nE);
+    s.slot_ptr.push_back(0);
+    std::vector<uint32_t> lms, cnt;
+    for (ChunkDesc& c : s.chunks) {
+        const uint32_t n = c.e1 - c.e0;
+        lms.resize(n);
+        for (uint32_t k = 0; k < n; ++k) lms[k] = g.le_l[s.le_local[s.lm_perm[c.e0 + k]]];
+        std::vector<uint32_t> uniq(lms);
+        std::sort(uniq.begin(), uniq.end()); uniq.erase(std::unique(uniq.begin(), uniq.end()), uniq.end());
+        c.s0 = (uint32_t)s.slot_lm.size(); c.s1 = c.s0 + (uint32_t)uniq.size();
+        s.slot_lm.insert(s.slot_lm.end(), uniq.begin(), uniq.end());
+        cnt.assign(uniq.size() + 1, 0);
+        uint32_t pose = c.p0;
+        for (uint32_t k = 0; k < n; ++k) {
+            const uint32_t slot = (uint32_t)(std::lower_bound(uniq.begin(), uniq.end(), lms[k]) - uniq.begin());
+            while (c.e0 + k >= s.pose_ptr[pose + 1]) ++pose;
+            s.lm_packed[c.e0 + k] = ((pose - c.p0) << 16) | slot;
+            lms[k] = slot; cnt[slot + 1]++;
+        }
+        for (size_t q = 0; q < uniq.size(); ++q) cnt[q + 1] += cnt[q];
+        for (size_t q = 0; q < uniq.size(); ++q) s.slot_ptr.push_back(c.e0 + cnt[q + 1]);
+        for (uint32_t k = 0; k < n; ++k) s.slot_edge[c.e0 + cnt[lms[k]]++] = (uint16_t)k;
+    }
+    // ---- landmark-major CSR over slots ---------------------------------------------------------------
+    const uint32_t nS = (uint32_t)s.slot_lm.size();
+    s.lm_part_ptr.assign(L + 1, 0);
+    for (uint32_t q = 0; q < nS; ++q) s.lm_part_ptr[s.slot_lm[q] + 1]++;
+    for (uint32_t l = 0; l < L; ++l) s.lm_part_ptr[l + 1] += s.lm_part_ptr[l];
+    s.lm_part_idx.resize(nS);
+    { std::vector<uint32_t> c2(s.lm_part_ptr.begin(), s.lm_part_ptr.end() - 1);
+      for (uint32_t q = 0; q < nS; ++q) s.lm_part_idx[c2[s.slot_lm[q]]++] = q; }
+    // ---- ODOM edges touching a local pose -----------------------------------------------------------
+    auto local = [&](uint32_t p) { return p >= pb && p < pe; };
+    std::vector<uint32_t> ghosts;
+    for (uint32_t e = 0; e < g.Eo; ++e) {
+        const bool a = local(g.od_i[e]), b = local(g.od_j[e]);
+        if (a && !b) ghosts.push_back(g.od_j[e]);
+        if (b && !a) ghosts.push_back(g.od_i[e]);
+    }
+    std::sort(ghosts.begin(), ghosts.end()); ghosts.erase(std::unique(ghosts.begin(), ghosts.end()), ghosts.end());
+    s.ghost_pose = ghosts; s.nG = (uint32_t)ghosts.size();
+    auto lidx = [&](uint32_t p) -> uint32_t {
+        if (local(p)) return p - pb;
+        return nP + (uint32_t)(std::lower_bound(ghosts.begin(), ghosts.end(), p) - ghosts.begin());
+    };
+    s.od_out_ptr.assign(nP + 1, 0);
+    for (uint32_t e = 0; e < g.Eo; ++e) if (local(g.od_i[e])) s.od_out_ptr[g.od_i[e] - pb + 1]++;
+    for (uint32_t p = 0; p < nP; ++p) s.od_out_ptr[p + 1] += s.od_out_ptr[p];
+    s.n_od_owned = s.od_out_ptr[nP];
+    s.od_local.assign(s.n_od_owned, 0);
+    { std::vector<uint32_t> c2(s.od_out_ptr.begin(), s.od_out_ptr.end() - 1);
+      for (uint32_t e = 0; e < g.Eo; ++e) if (local(g.od_i[e])) s.od_local[c2[g.od_i[e] - pb]++] = e; }
+    for (uint32_t e = 0; e < g.Eo; ++e) if (!local(g.od_i[e]) && local(g.od_j[e])) s.od_local.push_back(e);
+    const uint32_t nO = (uint32_t)s.od_local.size();
+    s.od_a.resize(nO); s.od_b.resize(nO);
+    for (uint32_t k = 0; k < nO; ++k) { s.od_a[k] = lidx(g.od_i[s.od_local[k]]); s.od_b[k] = lidx(g.od_j[s.od_local[k]]); }
+    s.od_in_ptr.assign(nP + 1, 0);
+    for (uint32_t k = 0; k < nO; ++k) if (s.od_b[k] < nP) s.od_in_ptr[s.od_b[k] + 1]++;
+    for (uint32_t p = 0; p < nP; ++p) s.od_in_ptr[p + 1] += s.od_in_ptr[p];
+    s.od_in_edge.resize(s.od_in_ptr[nP]);
+    { std::vector<uint32_t> c2(s.od_in_ptr.begin(), s.od_in_ptr.end() - 1);
+      for (uint32_t k = 0; k < nO; ++k) if (s.od_b[k] < nP) s.od_in_edge[c2[s.od_b[k]]++] = k; }
+    // ---- fixed vertices ---------------------------------------------------------------------------
+    s.fixed_pose_count.assign(nP, 0); s.fixed_lm_count.assign(L, 0);
+    for (uint32_t v : g.fixed) {
+        if (v < P) { if (local(v)) s.fixed_pose_count[v - pb]++; }
+        else s.fixed_lm_count[v - P]++;
+    }
+}
+
+}  // namespace tsb
