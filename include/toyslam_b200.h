@@ -127,6 +127,9 @@ int tsb_read_system(tsb_ctx* ctx, double* hpp_diag, double* b_pose, double* hpl,
 int tsb_read_structure(tsb_ctx* ctx, uint32_t* lm_perm, uint32_t* lm_packed, uint32_t* chunk_desc,
                        uint32_t* slot_lm, uint32_t* pose_ptr, uint32_t* lm_part_ptr, uint32_t* lm_part_idx);
 
+/* host<->device bytes copied since the last tsb_load_* (for the end-to-end bench accounting) */
+int tsb_get_transfer_bytes(const tsb_ctx* ctx, uint64_t* h2d, uint64_t* d2h);
+
 int tsb_reply_size(tsb_ctx* ctx, uint32_t* nbytes);
 int tsb_write_reply(tsb_ctx* ctx, void* out, uint32_t capacity);
 

@@ -189,3 +189,19 @@ def test_full_size_c2_properties(gpu):
     o = OracleGraph(payload)
     traj, _, _ = o.optimize_sparse(6, False, tol=1e-12, max_pcg=20000, threads=0)
     assert np.max(np.abs(chi - traj) / traj) < CHI2_TOL
+
+
+def test_phased_pcg_path_matches_persistent(gpu, monkeypatch):
+    """world == 1 normally runs the persistent cooperative PCG kernel; the one-launch-per-phase path
+    (used when collectives sit between the phases) must give the same answer."""
+    from toyslam_b200 import synth
+    payload = synth.to_payload(synth.make_config("c2", scale=0.1, seed=2))
+    res = []
+    for phased in ("0", "1"):
+        monkeypatch.setenv("TSB_PCG_PHASED", phased)
+        g = gpu(iterations=5, pcg_tol=1e-14, pcg_max_iters=20000, enable_exits=False); g.load_wire(payload)
+        rep, per = g.optimize()
+        res.append((np.array([p.chi2 for p in per]), g.state(), rep.kernel_launches))
+    assert res[0][2] < res[1][2]
+    assert np.max(np.abs(res[0][0] - res[1][0]) / res[0][0]) < CHI2_TOL
+    assert state_diff(*res[0][1], *res[1][1]) < STATE_TOL

@@ -19,7 +19,7 @@ LIB_PATH = os.path.join(_HERE, "libtoyslam_b200.so")
 
 SYMBOLS = ["tsb_create", "tsb_destroy", "tsb_last_error", "tsb_load_wire", "tsb_load_soa", "tsb_get_counts",
            "tsb_reset_state", "tsb_set_state", "tsb_linearize", "tsb_solve", "tsb_optimize", "tsb_read_ids",
-           "tsb_read_state", "tsb_read_delta", "tsb_read_system", "tsb_read_structure", "tsb_reply_size",
+           "tsb_read_state", "tsb_read_delta", "tsb_get_transfer_bytes", "tsb_read_system", "tsb_read_structure", "tsb_reply_size",
            "tsb_write_reply"]
 
 
@@ -176,6 +176,16 @@ class GraphOptimizerGpu:
         self._ck(self.L.tsb_read_structure(self.h, *(_p(out[k]) for k in ("lm_perm", "lm_packed", "chunk_desc", "slot_lm",
                                                                             "pose_ptr", "lm_part_ptr", "lm_part_idx"))))
         return out
+
+    def transfer_bytes(self):
+        a, b = C.c_uint64(), C.c_uint64()
+        self._ck(self.L.tsb_get_transfer_bytes(self.h, C.byref(a), C.byref(b))); return a.value, b.value
+
+    def write_reply_into(self, ptr, cap):
+        self._ck(self.L.tsb_write_reply(self.h, C.c_void_p(ptr), C.c_uint32(cap)))
+
+    def reply_size(self):
+        n = C.c_uint32(); self._ck(self.L.tsb_reply_size(self.h, C.byref(n))); return n.value
 
     def reply(self) -> bytes:
         n = C.c_uint32(); self._ck(self.L.tsb_reply_size(self.h, C.byref(n)))

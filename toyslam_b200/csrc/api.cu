@@ -6,6 +6,7 @@
 
 #include <cmath>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <string>
 #include <vector>
@@ -28,6 +29,8 @@ struct tsb_ctx {
     double* h_scal = nullptr; int* h_flags = nullptr;     // pinned
     bool loaded = false, linearized = false, solved = false;
     uint32_t part_cap = 0;
+    bool force_phased = false;                            // TSB_PCG_PHASED=1: one launch per PCG phase (the multi-GPU path)
+    uint64_t h2d = 0, d2h = 0;                            // bytes copied since the last tsb_load_*
 };
 
 namespace {
@@ -53,6 +56,7 @@ template <typename T, typename U> int upload(tsb_ctx* c, const U*& out, const st
     T* p = nullptr;
     if (int rc = dalloc(c, p, v.size())) return rc;
     if (!v.empty()) CU(cudaMemcpyAsync(p, v.data(), v.size() * sizeof(T), cudaMemcpyHostToDevice, c->stream));
+    c->h2d += v.size() * sizeof(T);
     out = reinterpret_cast<const U*>(p); return TSB_OK;
 }
 #define TRY(x) do { if (int rc_ = (x)) return rc_; } while (0)
@@ -94,6 +98,7 @@ int upload_graph(tsb_ctx* c) {
     if (nPG) CU(cudaMemcpyAsync(c->tmp_xyt, xyt.data(), 24ull * nPG, cudaMemcpyHostToDevice, c->stream));
     launch_init_pose(c->tmp_xyt, nPG, c->pose0, c->stream);
     if (g.L) CU(cudaMemcpyAsync(c->lm0, g.lm_xy.data(), 16ull * g.L, cudaMemcpyHostToDevice, c->stream));
+    c->h2d += 24ull * nPG + 16ull * g.L;
     // system and solver vectors
     TRY(dalloc(c, d.hpl, 6ull * d.nE)); TRY(dalloc(c, d.hoo, 3ull * d.nO));
     TRY(dalloc(c, d.hpp, 6ull * d.nP)); TRY(dalloc(c, d.bp, 3ull * d.nP));
@@ -126,6 +131,7 @@ int fetch_scalars(tsb_ctx* c) {
     CU(cudaMemcpyAsync(c->h_scal, c->d.scal, sizeof(double) * S_COUNT, cudaMemcpyDeviceToHost, c->stream));
     CU(cudaMemcpyAsync(c->h_flags, c->d.flags, sizeof(int) * F_COUNT, cudaMemcpyDeviceToHost, c->stream));
     CU(cudaStreamSynchronize(c->stream));
+    c->d2h += sizeof(double) * S_COUNT + sizeof(int) * F_COUNT;
     return TSB_OK;
 }
 
@@ -139,6 +145,8 @@ void enqueue_linearize(tsb_ctx* c) {
 int run_solve(tsb_ctx* c) {
     const Dev& d = c->d;
     launch_schur_prep(d, c->stream);
+    // single GPU: the whole PCG and the back-substitution run in one persistent cooperative kernel
+    if (c->cfg.world <= 1 && !c->force_phased && launch_pcg_persistent(d, c->stream)) return TSB_OK;
     launch_pcg_init(d, c->stream);
     const int maxit = c->cfg.pcg_max_iters > 0 ? c->cfg.pcg_max_iters : 4000;
     const int batch = 16;
@@ -153,6 +161,7 @@ int run_solve(tsb_ctx* c) {
         }
         CU(cudaMemcpyAsync(c->h_flags, d.flags, sizeof(int) * F_COUNT, cudaMemcpyDeviceToHost, c->stream));
         CU(cudaStreamSynchronize(c->stream));
+        c->d2h += sizeof(int) * F_COUNT;
         if (c->h_flags[F_DONE]) break;
     }
     launch_pcg_pass_a(d, 1, c->stream);
@@ -178,6 +187,7 @@ int tsb_create(const tsb_config* cfg, tsb_ctx** out) {
     if (cfg->world > 1) { g_create_error = "tsb_create: world > 1 not available in this build"; return TSB_EINVAL; }
     tsb_ctx* c = new tsb_ctx();
     c->cfg = *cfg; if (c->cfg.world < 1) { c->cfg.world = 1; c->cfg.rank = 0; }
+    { const char* e = std::getenv("TSB_PCG_PHASED"); c->force_phased = e && e[0] == '1'; }
     auto fail = [&](const char* what, cudaError_t e) { g_create_error = std::string(what) + ": " + cudaGetErrorString(e); delete c; return TSB_ECUDA; };
     cudaError_t e;
     if ((e = cudaSetDevice(cfg->device)) != cudaSuccess) return fail("cudaSetDevice", e);
@@ -203,7 +213,7 @@ void tsb_destroy(tsb_ctx* c) {
 int tsb_load_wire(tsb_ctx* c, const void* payload, uint32_t nbytes) {
     if (!c || (!payload && nbytes)) return TSB_EINVAL;
     CU(cudaSetDevice(c->cfg.device));
-    free_graph(c);
+    free_graph(c); c->h2d = c->d2h = 0;
     if (!parse_wire((const uint8_t*)payload, nbytes, c->g, c->err)) return TSB_EPARSE;
     build_structure(c->g, (uint32_t)c->cfg.rank, (uint32_t)c->cfg.world, c->st);
     return upload_graph(c);
@@ -375,6 +385,7 @@ int tsb_read_state(tsb_ctx* c, double* pose_xyt, double* lm_xy) {
     }
     if (lm_xy && c->g.L) CU(cudaMemcpyAsync(lm_xy, c->d.lm, 16ull * c->g.L, cudaMemcpyDeviceToHost, c->stream));
     CU(cudaStreamSynchronize(c->stream));
+    c->d2h += (pose_xyt ? 24ull * c->d.nP : 0) + (lm_xy ? 16ull * c->g.L : 0);
     return TSB_OK;
 }
 
@@ -415,6 +426,13 @@ int tsb_read_structure(tsb_ctx* c, uint32_t* lm_perm, uint32_t* lm_packed, uint3
     TRY(get(lm_packed, d.lm_packed, d.nE)); TRY(get(chunk_desc, d.chunks, 8ull * d.nChunks)); TRY(get(slot_lm, d.slot_lm, d.nSlots));
     TRY(get(pose_ptr, d.pose_ptr, d.nP + 1ull)); TRY(get(lm_part_ptr, d.lm_part_ptr, d.L + 1ull)); TRY(get(lm_part_idx, d.lm_part_idx, d.nSlots));
     CU(cudaStreamSynchronize(c->stream));
+    return TSB_OK;
+}
+
+int tsb_get_transfer_bytes(const tsb_ctx* c, uint64_t* h2d, uint64_t* d2h) {
+    if (!c) return TSB_EINVAL;
+    if (h2d) *h2d = c->h2d;
+    if (d2h) *d2h = c->d2h;
     return TSB_OK;
 }
 

@@ -66,6 +66,7 @@ void launch_linearize(const Dev& d, cudaStream_t s);            // K1: residuals
 void launch_lm_sum(const Dev& d, cudaStream_t s);               // K2a: landmark-major sum of slot partials
 void launch_lm_finalize(const Dev& d, cudaStream_t s);          // K2b: Hll, b_l, prior, Hll^-1; chi2
 void launch_schur_prep(const Dev& d, cudaStream_t s);           // K3: diag(S)^-1 and reduced rhs
+bool launch_pcg_persistent(const Dev& d, cudaStream_t s);     // whole PCG + back-substitution, one cooperative launch
 void launch_pcg_init(const Dev& d, cudaStream_t s);
 void launch_pcg_pass_a(const Dev& d, int mode, cudaStream_t s); // mode 0: v = p (with p = z + beta p fused), 1: v = x
 void launch_pcg_w_sum(const Dev& d, int check_done, cudaStream_t s);

@@ -9,33 +9,52 @@
 // point atomics anywhere, so results are bit-reproducible run to run.
 //
 // Memory-bound design (HBM roofline): every per-edge array is read or written once per pass with
-// unit-stride accesses in assembly order; vertex blocks (poses of the block, landmarks of the
+// unit-stride accesses in assembly order; vertex blocks (poses of the unit, landmarks of the
 // chunk's slots) are staged in shared memory; per-edge products are staged in shared memory and
 // reduced along precomputed row segments (pose side) and slot lists (landmark side).
+//
+// A "unit" is one entry of blk_chunk_ptr: a run of whole poses with <= kChunkEdges LM edges (or one
+// heavy pose split into several chunks).  Every chunked kernel is written as a device function over
+// one unit so that the same code serves the one-launch-per-phase kernels and the persistent
+// cooperative PCG kernel.
 #include "device_graph.h"
+
+#include <cooperative_groups.h>
+namespace cg = cooperative_groups;
 
 namespace tsb {
 namespace {
 
-// Shared-memory carve-up (bytes).  `acc` aliases `stage`: it is only written after the last chunk.
-constexpr size_t kOffStage = 0;                                                   // 9 x 513 doubles
-constexpr size_t kStageBytes = (sizeof(double) * kStageRows * kStageStride + 31) & ~size_t(31);
-constexpr size_t kOffSlot2 = kOffStage + kStageBytes;                             // per-slot double2
-constexpr size_t kOffSlot3 = kOffSlot2 + sizeof(double2) * kChunkEdges;           // per-slot 3 doubles (K3 only)
-constexpr size_t kOffPose = kOffSlot3 + sizeof(double) * 3 * kChunkEdges;         // double4 per pose of the block
-constexpr size_t kOffSedge = kOffPose + sizeof(double4) * kBlockPoses;            // u16 per edge
-constexpr size_t kOffRed = kOffSedge + sizeof(uint16_t) * kChunkEdges;
-constexpr size_t kSmemBytes = kOffRed + sizeof(double) * (kThreads / 32);
-static_assert(kOffSlot2 % 16 == 0 && kOffPose % 32 == 0, "alignment");
-static_assert(sizeof(double) * kBlockPoses * kStageRows <= kStageBytes, "acc must fit in stage");
+constexpr size_t align32(size_t x) { return (x + 31) & ~size_t(31); }
 
-struct Smem {
-    double* stage; double* acc; double2* slot2; double* slot3; double4* pose; uint16_t* sedge; double* red;
-    __device__ explicit Smem(unsigned char* b)
-        : stage(reinterpret_cast<double*>(b + kOffStage)), acc(reinterpret_cast<double*>(b + kOffStage)),
-          slot2(reinterpret_cast<double2*>(b + kOffSlot2)), slot3(reinterpret_cast<double*>(b + kOffSlot3)),
-          pose(reinterpret_cast<double4*>(b + kOffPose)), sedge(reinterpret_cast<uint16_t*>(b + kOffSedge)),
-          red(reinterpret_cast<double*>(b + kOffRed)) {}
+// Shared-memory layout of a chunked kernel, sized per kernel (occupancy is smem-limited).
+template <int ROWS, bool SLOT2, bool SLOT3, bool POSE, bool VEC, bool SEDGE>
+struct Layout {
+    static constexpr size_t oStage = 0;
+    static constexpr size_t oSlot2 = oStage + align32(sizeof(double) * ROWS * kStageStride);
+    static constexpr size_t oSlot3 = oSlot2 + (SLOT2 ? sizeof(double2) * kChunkEdges : 0);
+    static constexpr size_t oPose = oSlot3 + (SLOT3 ? sizeof(double) * 3 * kChunkEdges : 0);
+    static constexpr size_t oVec = oPose + (POSE ? sizeof(double4) * kBlockPoses : 0);
+    static constexpr size_t oSedge = oVec + (VEC ? sizeof(double) * 3 * kBlockPoses : 0);
+    static constexpr size_t oRed = oSedge + (SEDGE ? align32(sizeof(uint16_t) * kChunkEdges) : 0);
+    static constexpr size_t bytes = oRed + sizeof(double) * 32;
+};
+using LayLin = Layout<9, true, false, true, false, true>;
+using LaySchur = Layout<9, true, true, false, false, false>;
+using LayA = Layout<2, false, false, false, true, true>;
+using LayB = Layout<3, true, false, false, false, false>;
+using LayPcg = Layout<3, true, false, false, true, true>;     // persistent kernel: pass A and pass B
+
+struct Sm {
+    double* stage; double* acc; double2* slot2; double* slot3; double4* pose; double* vec; uint16_t* sedge; double* red;
+    template <class L> __device__ static Sm make(unsigned char* b) {
+        Sm s;
+        s.stage = reinterpret_cast<double*>(b + L::oStage); s.acc = s.stage;      // acc aliases stage (used after the last chunk)
+        s.slot2 = reinterpret_cast<double2*>(b + L::oSlot2); s.slot3 = reinterpret_cast<double*>(b + L::oSlot3);
+        s.pose = reinterpret_cast<double4*>(b + L::oPose); s.vec = reinterpret_cast<double*>(b + L::oVec);
+        s.sedge = reinterpret_cast<uint16_t*>(b + L::oSedge); s.red = reinterpret_cast<double*>(b + L::oRed);
+        return s;
+    }
 };
 
 __device__ __forceinline__ double warp_sum(double v) {
@@ -44,15 +63,28 @@ __device__ __forceinline__ double warp_sum(double v) {
     return v;
 }
 
-// deterministic block sum; result valid in thread 0
+// deterministic block sum; result valid in thread 0 (all threads must call)
 __device__ __forceinline__ double block_sum(double v, double* red) {
     v = warp_sum(v);
     if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = v;
     __syncthreads();
     double t = 0;
-    if (threadIdx.x == 0) { for (int i = 0; i < kThreads / 32; ++i) t += red[i]; }
+    if (threadIdx.x == 0) { for (uint32_t i = 0; i < blockDim.x / 32; ++i) t += red[i]; }
     __syncthreads();
     return t;
+}
+
+// sums `n` values in a fixed order with one block; every thread gets the total
+__device__ __forceinline__ double reduce_all(const double* part, uint32_t n, double* red) {
+    double t = 0;
+    for (uint32_t i = threadIdx.x; i < n; i += blockDim.x) t += part[i];
+    t = warp_sum(t);
+    if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = t;
+    __syncthreads();
+    double r = 0;
+    for (uint32_t i = 0; i < blockDim.x / 32; ++i) r += red[i];
+    __syncthreads();
+    return r;
 }
 
 // Huber on chi2 with delta = 1.5 (OptimizerCpu.h:36-46)
@@ -79,32 +111,76 @@ __device__ __forceinline__ void odom_edge(const double4 a, const double4 b, cons
     We[0] = W[0] * e0; We[1] = W[1] * e1; We[2] = W[2] * e2;
 }
 
-// sums stage[row][k] over the edges of `pose` that fall in the chunk, for items (pose, row)
+// fixed-order sum of s[b..e) with four independent partial sums (shortens the dependent chain)
+__device__ __forceinline__ double seg_sum(const double* s, uint32_t b, uint32_t e) {
+    double t0 = 0, t1 = 0, t2 = 0, t3 = 0;
+    uint32_t k = b;
+    for (; k + 3 < e; k += 4) { t0 += s[k]; t1 += s[k + 1]; t2 += s[k + 2]; t3 += s[k + 3]; }
+    for (; k < e; ++k) t0 += s[k];
+    return (t0 + t1) + (t2 + t3);
+}
+__device__ __forceinline__ double list_sum(const double* s, const uint16_t* idx, uint32_t b, uint32_t e) {
+    double t0 = 0, t1 = 0, t2 = 0, t3 = 0;
+    uint32_t k = b;
+    for (; k + 3 < e; k += 4) { t0 += s[idx[k]]; t1 += s[idx[k + 1]]; t2 += s[idx[k + 2]]; t3 += s[idx[k + 3]]; }
+    for (; k < e; ++k) t0 += s[idx[k]];
+    return (t0 + t1) + (t2 + t3);
+}
+
+// pose side: items (pose, row); sums stage[row][.] over the pose's edges that fall in the chunk
 template <int ROWS>
 __device__ __forceinline__ void pose_reduce(const Dev& d, const ChunkDesc& ch, const double* stage, uint32_t np,
-                                            double (&acc)[kStageRows]) {
+                                            double (&acc)[ROWS]) {
 #pragma unroll
-    for (int it = 0; it < kStageRows; ++it) {
+    for (int it = 0; it < ROWS; ++it) {
         const uint32_t item = threadIdx.x + it * kThreads;
         if (item < np * ROWS) {
             const uint32_t pl = item / ROWS, row = item % ROWS;
             const uint32_t b = max(d.pose_ptr[ch.p0 + pl], ch.e0) - ch.e0;
             const uint32_t e = min(d.pose_ptr[ch.p0 + pl + 1], ch.e1) - ch.e0;
-            const double* s = stage + row * kStageStride;
-            double t = 0;
-            for (uint32_t k = b; k < e; ++k) t += s[k];
-            acc[it] += t;
+            acc[it] += seg_sum(stage + row * kStageStride, b, e);
         }
     }
 }
 
+template <int ROWS>
+__device__ __forceinline__ void acc_to_smem(const double (&acc)[ROWS], double* sacc, uint32_t np) {
+#pragma unroll
+    for (int it = 0; it < ROWS; ++it) {
+        const uint32_t item = threadIdx.x + it * kThreads;
+        if (item < np * ROWS) sacc[item] = acc[it];
+    }
+}
+
+// one LM edge: residual, Jacobian products, Hpl block, staged per-edge products (EdgeSe2Point2d.h:28-70)
+__device__ __forceinline__ double lm_edge(const double4 ps, const double2 l, const double2 z, const double2 w,
+                                          double2* __restrict__ h, double* __restrict__ st) {
+    const double c_ = ps.z, s_ = ps.w;
+    const double e0 = c_ * l.x + s_ * l.y - (c_ * ps.x + s_ * ps.y) - z.x;       // e = X^-1 l - z_loc (:34-38)
+    const double e1 = -s_ * l.x + c_ * l.y + (s_ * ps.x - c_ * ps.y) - z.y;
+    const double q0 = c_ * l.y - s_ * l.x - c_ * ps.y + s_ * ps.x;              // A = [[-c,-s,q0],[s,-c,q1]] (:55-61)
+    const double q1 = -s_ * l.y - c_ * l.x + s_ * ps.y + c_ * ps.x;             // B = [[c,s],[-s,c]]        (:63-67)
+    double rho, hw; robustify(e0 * (w.x * e0) + e1 * (w.y * e1), rho, hw);
+    const double i0 = w.x * hw, i1 = w.y * hw, f0 = i0 * e0, f1 = i1 * e1;
+    const double m00 = c_ * i0 * c_ + s_ * i1 * s_;          // B^T W B
+    const double m01 = c_ * i0 * s_ - s_ * i1 * c_;
+    const double m11 = s_ * i0 * s_ + c_ * i1 * c_;
+    const double t0 = c_ * i0 * q0 - s_ * i1 * q1;           // B^T W q  ( = -(A^T W A)[0:2,2] )
+    const double t1 = s_ * i0 * q0 + c_ * i1 * q1;
+    // Hpl = A^T W B = [[-m00,-m01],[-m01,-m11],[t0,t1]]
+    h[0] = make_double2(-m00, -m01); h[1] = make_double2(-m01, -m11); h[2] = make_double2(t0, t1);
+    st[0 * kStageStride] = m00; st[1 * kStageStride] = m01; st[2 * kStageStride] = m11;
+    st[3 * kStageStride] = -t0; st[4 * kStageStride] = -t1; st[5 * kStageStride] = q0 * i0 * q0 + q1 * i1 * q1;
+    st[6 * kStageStride] = c_ * f0 - s_ * f1; st[7 * kStageStride] = s_ * f0 + c_ * f1;   // B^T W e
+    st[8 * kStageStride] = q0 * f0 + q1 * f1;
+    return rho;
+}
+
 // ------------------------------------------------------------------------------------------------
-// K1: linearize + assemble.  One block = a run of whole poses (or one heavy pose), one or more chunks.
+// K1 unit: linearize + assemble
 // ------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(kThreads) k_linearize(const Dev d) {
-    extern __shared__ __align__(32) unsigned char smem_raw[];
-    Smem sm(smem_raw);
-    const uint32_t c0 = d.blk_chunk_ptr[blockIdx.x], c1 = d.blk_chunk_ptr[blockIdx.x + 1];
+__device__ __forceinline__ void unit_linearize(const Dev& d, const uint32_t unit, const Sm& sm) {
+    const uint32_t c0 = d.blk_chunk_ptr[unit], c1 = d.blk_chunk_ptr[unit + 1];
     const uint32_t p0 = d.chunks[c0].p0, np = d.chunks[c0].p1 - p0;
     for (uint32_t i = threadIdx.x; i < np; i += kThreads) sm.pose[i] = d.pose[p0 + i];
     double acc[kStageRows];
@@ -114,58 +190,30 @@ __global__ void __launch_bounds__(kThreads) k_linearize(const Dev d) {
     for (uint32_t c = c0; c < c1; ++c) {
         const ChunkDesc ch = d.chunks[c];
         const uint32_t n = ch.e1 - ch.e0, ns = ch.s1 - ch.s0;
+        // issue the per-edge loads first: they do not depend on the staged vertex blocks
+        const uint32_t k0 = threadIdx.x, k1 = threadIdx.x + kThreads;
+        uint32_t pk0 = 0, pk1 = 0; double2 z0 = {}, w0 = {}, z1 = {}, w1 = {};
+        if (k0 < n) { pk0 = d.lm_packed[ch.e0 + k0]; z0 = d.le_z[ch.e0 + k0]; w0 = d.le_w[ch.e0 + k0]; }
+        if (k1 < n) { pk1 = d.lm_packed[ch.e0 + k1]; z1 = d.le_z[ch.e0 + k1]; w1 = d.le_w[ch.e0 + k1]; }
         for (uint32_t s = threadIdx.x; s < ns; s += kThreads) sm.slot2[s] = d.lm[d.slot_lm[ch.s0 + s]];
         for (uint32_t k = threadIdx.x; k < n; k += kThreads) sm.sedge[k] = d.slot_edge[ch.e0 + k];
         __syncthreads();
-        for (uint32_t k = threadIdx.x; k < n; k += kThreads) {
-            const uint32_t pk = d.lm_packed[ch.e0 + k];
-            const double2 z = d.le_z[ch.e0 + k], w = d.le_w[ch.e0 + k];
-            const double4 ps = sm.pose[pk >> 16];
-            const double2 l = sm.slot2[pk & 0xffffu];
-            const double c_ = ps.z, s_ = ps.w;
-            // e = X^-1 * l - z_loc   (EdgeSe2Point2d.h:34-38)
-            const double e0 = c_ * l.x + s_ * l.y - (c_ * ps.x + s_ * ps.y) - z.x;
-            const double e1 = -s_ * l.x + c_ * l.y + (s_ * ps.x - c_ * ps.y) - z.y;
-            // A = [[-c,-s,q0],[s,-c,q1]], B = [[c,s],[-s,c]]   (:55-67)
-            const double q0 = c_ * l.y - s_ * l.x - c_ * ps.y + s_ * ps.x;
-            const double q1 = -s_ * l.y - c_ * l.x + s_ * ps.y + c_ * ps.x;
-            double rho, hw; robustify(e0 * (w.x * e0) + e1 * (w.y * e1), rho, hw);
-            rho_sum += rho;
-            const double i0 = w.x * hw, i1 = w.y * hw, f0 = i0 * e0, f1 = i1 * e1;
-            const double m00 = c_ * i0 * c_ + s_ * i1 * s_;          // B^T W B
-            const double m01 = c_ * i0 * s_ - s_ * i1 * c_;
-            const double m11 = s_ * i0 * s_ + c_ * i1 * c_;
-            const double t0 = c_ * i0 * q0 - s_ * i1 * q1;           // B^T W q  ( = -(A^T W A)[0:2,2] )
-            const double t1 = s_ * i0 * q0 + c_ * i1 * q1;
-            const double qq = q0 * i0 * q0 + q1 * i1 * q1;
-            const double g0 = c_ * f0 - s_ * f1, g1 = s_ * f0 + c_ * f1;   // B^T W e
-            const double qe = q0 * f0 + q1 * f1;
-            // Hpl = A^T W B = [[-m00,-m01],[-m01,-m11],[t0,t1]]
-            double2* h = reinterpret_cast<double2*>(d.hpl + 6ull * (ch.e0 + k));
-            h[0] = make_double2(-m00, -m01); h[1] = make_double2(-m01, -m11); h[2] = make_double2(t0, t1);
-            double* st = sm.stage + k;
-            st[0 * kStageStride] = m00; st[1 * kStageStride] = m01; st[2 * kStageStride] = m11;
-            st[3 * kStageStride] = -t0; st[4 * kStageStride] = -t1; st[5 * kStageStride] = qq;
-            st[6 * kStageStride] = g0;  st[7 * kStageStride] = g1;  st[8 * kStageStride] = qe;
-        }
+        if (k0 < n) rho_sum += lm_edge(sm.pose[pk0 >> 16], sm.slot2[pk0 & 0xffffu], z0, w0,
+                                       reinterpret_cast<double2*>(d.hpl + 6ull * (ch.e0 + k0)), sm.stage + k0);
+        if (k1 < n) rho_sum += lm_edge(sm.pose[pk1 >> 16], sm.slot2[pk1 & 0xffffu], z1, w1,
+                                       reinterpret_cast<double2*>(d.hpl + 6ull * (ch.e0 + k1)), sm.stage + k1);
         __syncthreads();
         pose_reduce<kStageRows>(d, ch, sm.stage, np, acc);
         // landmark side: one partial (M00 M01 M11 g0 g1) per slot, edges of the slot in list order
         for (uint32_t item = threadIdx.x; item < ns * 5; item += kThreads) {
             const uint32_t sl = item / 5, comp = item % 5;
             const double* s = sm.stage + (comp < 3 ? comp : comp + 3) * kStageStride;
-            const uint32_t b = d.slot_ptr[ch.s0 + sl] - ch.e0, e = d.slot_ptr[ch.s0 + sl + 1] - ch.e0;
-            double t = 0;
-            for (uint32_t q = b; q < e; ++q) t += s[sm.sedge[q]];
-            d.lm_part[5ull * (ch.s0 + sl) + comp] = t;
+            d.lm_part[5ull * (ch.s0 + sl) + comp] =
+                list_sum(s, sm.sedge, d.slot_ptr[ch.s0 + sl] - ch.e0, d.slot_ptr[ch.s0 + sl + 1] - ch.e0);
         }
         __syncthreads();
     }
-#pragma unroll
-    for (int it = 0; it < kStageRows; ++it) {
-        const uint32_t item = threadIdx.x + it * kThreads;
-        if (item < np * kStageRows) sm.acc[item] = acc[it];
-    }
+    acc_to_smem<kStageRows>(acc, sm.acc, np);
     __syncthreads();
     // pose finalize: LM sums + ODOM edges (out: id1 == pose, in: id2 == pose) + prior
     for (uint32_t i = threadIdx.x; i < np; i += kThreads) {
@@ -197,12 +245,18 @@ __global__ void __launch_bounds__(kThreads) k_linearize(const Dev d) {
         B[0] = b0; B[1] = b1; B[2] = b2;
     }
     const double t = block_sum(rho_sum, sm.red);
-    if (threadIdx.x == 0) d.part[blockIdx.x] = t;
+    if (threadIdx.x == 0) d.part[unit] = t;
+}
+
+__global__ void __launch_bounds__(kThreads, 4) k_linearize(const Dev d) {
+    extern __shared__ __align__(32) unsigned char smem_raw[];
+    const Sm sm = Sm::make<LayLin>(smem_raw);
+    unit_linearize(d, blockIdx.x, sm);
 }
 
 // ------------------------------------------------------------------------------------------------
 // K2a: landmark-major sum of the slot partials (5 values per landmark), fixed order.
-// K2b: prior, Hll, b_l, Hll^-1 (closed-form 2x2) and the chi2 total.
+// K2b: prior, Hll, b_l, Hll^-1 (closed-form 2x2).
 // ------------------------------------------------------------------------------------------------
 __global__ void k_lm_sum(const Dev d) {
     const uint32_t l = blockIdx.x * blockDim.x + threadIdx.x;
@@ -228,31 +282,38 @@ __global__ void k_lm_finalize(const Dev d) {
     d.hinv[3ull * l] = h11 * id; d.hinv[3ull * l + 1] = -h01 * id; d.hinv[3ull * l + 2] = h00 * id;
 }
 
-// sums `n` partials in a fixed order with one block; out[0] = total
-__device__ __forceinline__ double reduce_parts(const double* part, uint32_t n, double* red) {
-    double t = 0;
-    for (uint32_t i = threadIdx.x; i < n; i += blockDim.x) t += part[i];
-    t = warp_sum(t);
-    if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = t;
-    __syncthreads();
-    double r = 0;
-    if (threadIdx.x == 0) for (uint32_t i = 0; i < blockDim.x / 32; ++i) r += red[i];
-    return r;
-}
-
 __global__ void k_reduce_to(const double* part, uint32_t n, double* out) {
     __shared__ double red[32];
-    const double r = reduce_parts(part, n, red);
+    const double r = reduce_all(part, n, red);
     if (threadIdx.x == 0) *out = r;
 }
 
 // ------------------------------------------------------------------------------------------------
 // K3: Schur preparation.  diag(S)_i = Hpp_ii - sum_e Hpl_e Hll^-1 Hpl_e^T,  rhs_i = b_i - sum_e Hpl_e Hll^-1 b_l
 // ------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(kThreads) k_schur_prep(const Dev d) {
+__device__ __forceinline__ void schur_edge(const double2* __restrict__ hp, const double* __restrict__ hi, const double2 bl,
+                                           double* __restrict__ st) {
+    const double2 r0 = hp[0], r1 = hp[1], r2 = hp[2];
+    const double i00 = hi[0], i01 = hi[1], i11 = hi[2];
+    const double t00 = r0.x * i00 + r0.y * i01, t01 = r0.x * i01 + r0.y * i11;     // T = Hpl * Hll^-1 (3x2)
+    const double t10 = r1.x * i00 + r1.y * i01, t11 = r1.x * i01 + r1.y * i11;
+    const double t20 = r2.x * i00 + r2.y * i01, t21 = r2.x * i01 + r2.y * i11;
+    st[0 * kStageStride] = t00 * r0.x + t01 * r0.y;      // (T Hpl^T) 00 01 02 11 12 22
+    st[1 * kStageStride] = t00 * r1.x + t01 * r1.y;
+    st[2 * kStageStride] = t00 * r2.x + t01 * r2.y;
+    st[3 * kStageStride] = t10 * r1.x + t11 * r1.y;
+    st[4 * kStageStride] = t10 * r2.x + t11 * r2.y;
+    st[5 * kStageStride] = t20 * r2.x + t21 * r2.y;
+    st[6 * kStageStride] = t00 * bl.x + t01 * bl.y;      // T b_l
+    st[7 * kStageStride] = t10 * bl.x + t11 * bl.y;
+    st[8 * kStageStride] = t20 * bl.x + t21 * bl.y;
+}
+
+__global__ void __launch_bounds__(kThreads, 3) k_schur_prep(const Dev d) {
     extern __shared__ __align__(32) unsigned char smem_raw[];
-    Smem sm(smem_raw);
-    const uint32_t c0 = d.blk_chunk_ptr[blockIdx.x], c1 = d.blk_chunk_ptr[blockIdx.x + 1];
+    const Sm sm = Sm::make<LaySchur>(smem_raw);
+    const uint32_t unit = blockIdx.x;
+    const uint32_t c0 = d.blk_chunk_ptr[unit], c1 = d.blk_chunk_ptr[unit + 1];
     const uint32_t p0 = d.chunks[c0].p0, np = d.chunks[c0].p1 - p0;
     double acc[kStageRows];
 #pragma unroll
@@ -268,34 +329,13 @@ __global__ void __launch_bounds__(kThreads) k_schur_prep(const Dev d) {
         __syncthreads();
         for (uint32_t k = threadIdx.x; k < n; k += kThreads) {
             const uint32_t sl = d.lm_packed[ch.e0 + k] & 0xffffu;
-            const double2* hp = reinterpret_cast<const double2*>(d.hpl + 6ull * (ch.e0 + k));
-            const double2 r0 = hp[0], r1 = hp[1], r2 = hp[2];
-            const double i00 = sm.slot3[3 * sl], i01 = sm.slot3[3 * sl + 1], i11 = sm.slot3[3 * sl + 2];
-            const double2 bl = sm.slot2[sl];
-            // T = Hpl * Hll^-1  (3x2)
-            const double t00 = r0.x * i00 + r0.y * i01, t01 = r0.x * i01 + r0.y * i11;
-            const double t10 = r1.x * i00 + r1.y * i01, t11 = r1.x * i01 + r1.y * i11;
-            const double t20 = r2.x * i00 + r2.y * i01, t21 = r2.x * i01 + r2.y * i11;
-            double* st = sm.stage + k;
-            st[0 * kStageStride] = t00 * r0.x + t01 * r0.y;      // (T Hpl^T) 00 01 02 11 12 22
-            st[1 * kStageStride] = t00 * r1.x + t01 * r1.y;
-            st[2 * kStageStride] = t00 * r2.x + t01 * r2.y;
-            st[3 * kStageStride] = t10 * r1.x + t11 * r1.y;
-            st[4 * kStageStride] = t10 * r2.x + t11 * r2.y;
-            st[5 * kStageStride] = t20 * r2.x + t21 * r2.y;
-            st[6 * kStageStride] = t00 * bl.x + t01 * bl.y;      // T b_l
-            st[7 * kStageStride] = t10 * bl.x + t11 * bl.y;
-            st[8 * kStageStride] = t20 * bl.x + t21 * bl.y;
+            schur_edge(reinterpret_cast<const double2*>(d.hpl + 6ull * (ch.e0 + k)), sm.slot3 + 3 * sl, sm.slot2[sl], sm.stage + k);
         }
         __syncthreads();
         pose_reduce<kStageRows>(d, ch, sm.stage, np, acc);
         __syncthreads();
     }
-#pragma unroll
-    for (int it = 0; it < kStageRows; ++it) {
-        const uint32_t item = threadIdx.x + it * kThreads;
-        if (item < np * kStageRows) sm.acc[item] = acc[it];
-    }
+    acc_to_smem<kStageRows>(acc, sm.acc, np);
     __syncthreads();
     for (uint32_t i = threadIdx.x; i < np; i += kThreads) {
         const double* a = sm.acc + i * kStageRows;
@@ -318,48 +358,18 @@ __global__ void __launch_bounds__(kThreads) k_schur_prep(const Dev d) {
 //   pass A : t_e = Hpl_e^T v_pose(e)  -> per-slot partial sums            (one stream over Hpl)
 //   w_sum  : landmark-major sum of the slot partials
 //   pass B : u_l = Hll^-1 w_l;  (S v)_i = Hpp_ii v_i + sum_odom Hoo v_j - sum_e Hpl_e u_l(e); v'Sv partials
-// Scalars (alpha, beta, r'z, stop flag) stay on the device; kernels return at once when the flag is set.
 // ------------------------------------------------------------------------------------------------
 __device__ __forceinline__ void sym3_mul(const double* M, double a, double b, double c, double& o0, double& o1, double& o2) {
     o0 = M[0] * a + M[1] * b + M[2] * c; o1 = M[1] * a + M[3] * b + M[4] * c; o2 = M[2] * a + M[4] * b + M[5] * c;
 }
 
-__global__ void k_pcg_init(const Dev d) {
-    __shared__ double red[kThreads / 32];
-    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-    double dot = 0;
-    if (i < d.nP) {
-        const double r0 = d.rhs[3ull * i], r1 = d.rhs[3ull * i + 1], r2 = d.rhs[3ull * i + 2];
-        double z0, z1, z2; sym3_mul(d.minv + 6ull * i, r0, r1, r2, z0, z1, z2);
-        d.x[3ull * i] = 0; d.x[3ull * i + 1] = 0; d.x[3ull * i + 2] = 0;
-        d.r[3ull * i] = r0; d.r[3ull * i + 1] = r1; d.r[3ull * i + 2] = r2;
-        d.z[3ull * i] = z0; d.z[3ull * i + 1] = z1; d.z[3ull * i + 2] = z2;
-        d.p[3ull * i] = z0; d.p[3ull * i + 1] = z1; d.p[3ull * i + 2] = z2;
-        dot = r0 * z0 + r1 * z1 + r2 * z2;
-    }
-    const double t = block_sum(dot, red);
-    if (threadIdx.x == 0) d.part[blockIdx.x] = t;
-}
-
-__global__ void k_pcg_init_scal(const Dev d, uint32_t nparts) {
-    __shared__ double red[32];
-    const double rz = reduce_parts(d.part, nparts, red);
-    if (threadIdx.x == 0) {
-        d.scal[S_RZ0] = rz; d.scal[S_RZ] = rz; d.scal[S_BETA] = 0; d.scal[S_ALPHA] = 0;
-        d.flags[F_ITERS] = 0; d.flags[F_DONE] = (rz > 0) ? 0 : 1;
-    }
-}
-
-template <int MODE>   // 0: v = p, with the update p = z + beta p fused in;  1: v = x
-__global__ void __launch_bounds__(kThreads) k_pcg_pass_a(const Dev d) {
-    if (MODE == 0 && d.flags[F_DONE]) return;
-    extern __shared__ __align__(32) unsigned char smem_raw[];
-    Smem sm(smem_raw);
-    double* v = reinterpret_cast<double*>(sm.pose);
-    const uint32_t c0 = d.blk_chunk_ptr[blockIdx.x], c1 = d.blk_chunk_ptr[blockIdx.x + 1];
+// MODE 0: v = p after the fused update p = z + beta p;  MODE 1: v = x
+template <int MODE>
+__device__ __forceinline__ void unit_pass_a(const Dev& d, const uint32_t unit, const Sm& sm, const double beta) {
+    double* v = sm.vec;
+    const uint32_t c0 = d.blk_chunk_ptr[unit], c1 = d.blk_chunk_ptr[unit + 1];
     const uint32_t p0 = d.chunks[c0].p0, np = d.chunks[c0].p1 - p0;
     if (MODE == 0) {
-        const double beta = d.scal[S_BETA];
         for (uint32_t i = threadIdx.x; i < 3 * np; i += kThreads) {
             const double t = d.z[3ull * p0 + i] + beta * d.p[3ull * p0 + i];
             d.p[3ull * p0 + i] = t; v[i] = t;
@@ -370,53 +380,42 @@ __global__ void __launch_bounds__(kThreads) k_pcg_pass_a(const Dev d) {
     for (uint32_t c = c0; c < c1; ++c) {
         const ChunkDesc ch = d.chunks[c];
         const uint32_t n = ch.e1 - ch.e0, ns = ch.s1 - ch.s0;
+        const uint32_t k0 = threadIdx.x, k1 = threadIdx.x + kThreads;
+        uint32_t pl0 = 0, pl1 = 0; double2 a0 = {}, a1 = {}, a2 = {}, b0 = {}, b1 = {}, b2 = {};
+        if (k0 < n) { const double2* hp = reinterpret_cast<const double2*>(d.hpl + 6ull * (ch.e0 + k0));
+            pl0 = d.lm_packed[ch.e0 + k0] >> 16; a0 = hp[0]; a1 = hp[1]; a2 = hp[2]; }
+        if (k1 < n) { const double2* hp = reinterpret_cast<const double2*>(d.hpl + 6ull * (ch.e0 + k1));
+            pl1 = d.lm_packed[ch.e0 + k1] >> 16; b0 = hp[0]; b1 = hp[1]; b2 = hp[2]; }
         for (uint32_t k = threadIdx.x; k < n; k += kThreads) sm.sedge[k] = d.slot_edge[ch.e0 + k];
         __syncthreads();
-        for (uint32_t k = threadIdx.x; k < n; k += kThreads) {
-            const uint32_t pl = d.lm_packed[ch.e0 + k] >> 16;
-            const double2* hp = reinterpret_cast<const double2*>(d.hpl + 6ull * (ch.e0 + k));
-            const double2 r0 = hp[0], r1 = hp[1], r2 = hp[2];
-            const double v0 = v[3 * pl], v1 = v[3 * pl + 1], v2 = v[3 * pl + 2];
-            sm.stage[k] = r0.x * v0 + r1.x * v1 + r2.x * v2;
-            sm.stage[kStageStride + k] = r0.y * v0 + r1.y * v1 + r2.y * v2;
-        }
+        if (k0 < n) { const double v0 = v[3 * pl0], v1 = v[3 * pl0 + 1], v2 = v[3 * pl0 + 2];
+            sm.stage[k0] = a0.x * v0 + a1.x * v1 + a2.x * v2; sm.stage[kStageStride + k0] = a0.y * v0 + a1.y * v1 + a2.y * v2; }
+        if (k1 < n) { const double v0 = v[3 * pl1], v1 = v[3 * pl1 + 1], v2 = v[3 * pl1 + 2];
+            sm.stage[k1] = b0.x * v0 + b1.x * v1 + b2.x * v2; sm.stage[kStageStride + k1] = b0.y * v0 + b1.y * v1 + b2.y * v2; }
         __syncthreads();
         for (uint32_t item = threadIdx.x; item < ns * 2; item += kThreads) {
             const uint32_t sl = item >> 1, comp = item & 1;
-            const double* s = sm.stage + comp * kStageStride;
-            const uint32_t b = d.slot_ptr[ch.s0 + sl] - ch.e0, e = d.slot_ptr[ch.s0 + sl + 1] - ch.e0;
-            double t = 0;
-            for (uint32_t q = b; q < e; ++q) t += s[sm.sedge[q]];
-            d.w_part[2ull * (ch.s0 + sl) + comp] = t;
+            d.w_part[2ull * (ch.s0 + sl) + comp] = list_sum(sm.stage + comp * kStageStride, sm.sedge,
+                d.slot_ptr[ch.s0 + sl] - ch.e0, d.slot_ptr[ch.s0 + sl + 1] - ch.e0);
         }
         __syncthreads();
     }
 }
 
-__global__ void k_pcg_w_sum(const Dev d, int check_done) {
-    if (check_done && d.flags[F_DONE]) return;
-    const uint32_t l = blockIdx.x * blockDim.x + threadIdx.x;
-    if (l >= d.L) return;
-    double a0 = 0, a1 = 0;
-    for (uint32_t q = d.lm_part_ptr[l]; q < d.lm_part_ptr[l + 1]; ++q) {
-        const double2 r = reinterpret_cast<const double2*>(d.w_part)[d.lm_part_idx[q]];
-        a0 += r.x; a1 += r.y;
-    }
-    reinterpret_cast<double2*>(d.w_sum)[l] = make_double2(a0, a1);
-}
-
-__global__ void __launch_bounds__(kThreads) k_pcg_pass_b(const Dev d) {
-    if (d.flags[F_DONE]) return;
-    extern __shared__ __align__(32) unsigned char smem_raw[];
-    Smem sm(smem_raw);
-    const uint32_t c0 = d.blk_chunk_ptr[blockIdx.x], c1 = d.blk_chunk_ptr[blockIdx.x + 1];
+// returns this unit's contribution to p'Sp in thread 0
+__device__ __forceinline__ double unit_pass_b(const Dev& d, const uint32_t unit, const Sm& sm) {
+    const uint32_t c0 = d.blk_chunk_ptr[unit], c1 = d.blk_chunk_ptr[unit + 1];
     const uint32_t p0 = d.chunks[c0].p0, np = d.chunks[c0].p1 - p0;
-    double acc[kStageRows];
-#pragma unroll
-    for (int i = 0; i < kStageRows; ++i) acc[i] = 0;
+    double acc[3] = {0, 0, 0};
     for (uint32_t c = c0; c < c1; ++c) {
         const ChunkDesc ch = d.chunks[c];
         const uint32_t n = ch.e1 - ch.e0, ns = ch.s1 - ch.s0;
+        const uint32_t k0 = threadIdx.x, k1 = threadIdx.x + kThreads;
+        uint32_t sl0 = 0, sl1 = 0; double2 a0 = {}, a1 = {}, a2 = {}, b0 = {}, b1 = {}, b2 = {};
+        if (k0 < n) { const double2* hp = reinterpret_cast<const double2*>(d.hpl + 6ull * (ch.e0 + k0));
+            sl0 = d.lm_packed[ch.e0 + k0] & 0xffffu; a0 = hp[0]; a1 = hp[1]; a2 = hp[2]; }
+        if (k1 < n) { const double2* hp = reinterpret_cast<const double2*>(d.hpl + 6ull * (ch.e0 + k1));
+            sl1 = d.lm_packed[ch.e0 + k1] & 0xffffu; b0 = hp[0]; b1 = hp[1]; b2 = hp[2]; }
         for (uint32_t s = threadIdx.x; s < ns; s += kThreads) {
             const uint32_t l = d.slot_lm[ch.s0 + s];
             const double2 w = reinterpret_cast<const double2*>(d.w_sum)[l];
@@ -424,23 +423,17 @@ __global__ void __launch_bounds__(kThreads) k_pcg_pass_b(const Dev d) {
             sm.slot2[s] = make_double2(hi[0] * w.x + hi[1] * w.y, hi[1] * w.x + hi[2] * w.y);
         }
         __syncthreads();
-        for (uint32_t k = threadIdx.x; k < n; k += kThreads) {
-            const double2 u = sm.slot2[d.lm_packed[ch.e0 + k] & 0xffffu];
-            const double2* hp = reinterpret_cast<const double2*>(d.hpl + 6ull * (ch.e0 + k));
-            const double2 r0 = hp[0], r1 = hp[1], r2 = hp[2];
-            sm.stage[k] = r0.x * u.x + r0.y * u.y;
-            sm.stage[kStageStride + k] = r1.x * u.x + r1.y * u.y;
-            sm.stage[2 * kStageStride + k] = r2.x * u.x + r2.y * u.y;
-        }
+        if (k0 < n) { const double2 u = sm.slot2[sl0];
+            sm.stage[k0] = a0.x * u.x + a0.y * u.y; sm.stage[kStageStride + k0] = a1.x * u.x + a1.y * u.y;
+            sm.stage[2 * kStageStride + k0] = a2.x * u.x + a2.y * u.y; }
+        if (k1 < n) { const double2 u = sm.slot2[sl1];
+            sm.stage[k1] = b0.x * u.x + b0.y * u.y; sm.stage[kStageStride + k1] = b1.x * u.x + b1.y * u.y;
+            sm.stage[2 * kStageStride + k1] = b2.x * u.x + b2.y * u.y; }
         __syncthreads();
         pose_reduce<3>(d, ch, sm.stage, np, acc);
         __syncthreads();
     }
-#pragma unroll
-    for (int it = 0; it < 3; ++it) {
-        const uint32_t item = threadIdx.x + it * kThreads;
-        if (item < np * 3) sm.acc[item] = acc[it];
-    }
+    acc_to_smem<3>(acc, sm.acc, np);
     __syncthreads();
     double dot = 0;
     for (uint32_t i = threadIdx.x; i < np; i += kThreads) {
@@ -460,47 +453,150 @@ __global__ void __launch_bounds__(kThreads) k_pcg_pass_b(const Dev d) {
         d.sp[3ull * p] = y0; d.sp[3ull * p + 1] = y1; d.sp[3ull * p + 2] = y2;
         dot += v0 * y0 + v1 * y1 + v2 * y2;
     }
-    const double t = block_sum(dot, sm.red);
-    if (threadIdx.x == 0) d.part[blockIdx.x] = t;
+    return block_sum(dot, sm.red);
 }
 
+__device__ __forceinline__ void lm_w_sum(const Dev& d, uint32_t l) {
+    double a0 = 0, a1 = 0;
+    for (uint32_t q = d.lm_part_ptr[l]; q < d.lm_part_ptr[l + 1]; ++q) {
+        const double2 r = reinterpret_cast<const double2*>(d.w_part)[d.lm_part_idx[q]];
+        a0 += r.x; a1 += r.y;
+    }
+    reinterpret_cast<double2*>(d.w_sum)[l] = make_double2(a0, a1);
+}
+
+// x += alpha p; r -= alpha Sp; z = M^-1 r; returns r'z of pose i
+__device__ __forceinline__ double pose_update(const Dev& d, uint32_t i, double alpha) {
+    double r[3], z[3];
+#pragma unroll
+    for (int q = 0; q < 3; ++q) {
+        d.x[3ull * i + q] += alpha * d.p[3ull * i + q];
+        r[q] = d.r[3ull * i + q] - alpha * d.sp[3ull * i + q];
+        d.r[3ull * i + q] = r[q];
+    }
+    sym3_mul(d.minv + 6ull * i, r[0], r[1], r[2], z[0], z[1], z[2]);
+    d.z[3ull * i] = z[0]; d.z[3ull * i + 1] = z[1]; d.z[3ull * i + 2] = z[2];
+    return r[0] * z[0] + r[1] * z[1] + r[2] * z[2];
+}
+
+__device__ __forceinline__ double pose_init(const Dev& d, uint32_t i) {
+    const double r0 = d.rhs[3ull * i], r1 = d.rhs[3ull * i + 1], r2 = d.rhs[3ull * i + 2];
+    double z0, z1, z2; sym3_mul(d.minv + 6ull * i, r0, r1, r2, z0, z1, z2);
+    d.x[3ull * i] = 0; d.x[3ull * i + 1] = 0; d.x[3ull * i + 2] = 0;
+    d.r[3ull * i] = r0; d.r[3ull * i + 1] = r1; d.r[3ull * i + 2] = r2;
+    d.z[3ull * i] = z0; d.z[3ull * i + 1] = z1; d.z[3ull * i + 2] = z2;
+    d.p[3ull * i] = z0; d.p[3ull * i + 1] = z1; d.p[3ull * i + 2] = z2;
+    return r0 * z0 + r1 * z1 + r2 * z2;
+}
+
+// ---- one launch per phase (used when collectives sit between the phases, world > 1) -------------------
+__global__ void k_pcg_init(const Dev d) {
+    __shared__ double red[32];
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    const double t = block_sum(i < d.nP ? pose_init(d, i) : 0.0, red);
+    if (threadIdx.x == 0) d.part[blockIdx.x] = t;
+}
+__global__ void k_pcg_init_scal(const Dev d, uint32_t nparts) {
+    __shared__ double red[32];
+    const double rz = reduce_all(d.part, nparts, red);
+    if (threadIdx.x == 0) {
+        d.scal[S_RZ0] = rz; d.scal[S_RZ] = rz; d.scal[S_BETA] = 0; d.scal[S_ALPHA] = 0;
+        d.flags[F_ITERS] = 0; d.flags[F_DONE] = (rz > 0) ? 0 : 1;
+    }
+}
+template <int MODE>
+__global__ void __launch_bounds__(kThreads) k_pcg_pass_a(const Dev d) {
+    if (MODE == 0 && d.flags[F_DONE]) return;
+    extern __shared__ __align__(32) unsigned char smem_raw[];
+    const Sm sm = Sm::make<LayA>(smem_raw);
+    unit_pass_a<MODE>(d, blockIdx.x, sm, MODE == 0 ? d.scal[S_BETA] : 0.0);
+}
+__global__ void k_pcg_w_sum(const Dev d, int check_done) {
+    if (check_done && d.flags[F_DONE]) return;
+    const uint32_t l = blockIdx.x * blockDim.x + threadIdx.x;
+    if (l < d.L) lm_w_sum(d, l);
+}
+__global__ void __launch_bounds__(kThreads) k_pcg_pass_b(const Dev d) {
+    if (d.flags[F_DONE]) return;
+    extern __shared__ __align__(32) unsigned char smem_raw[];
+    const Sm sm = Sm::make<LayB>(smem_raw);
+    const double t = unit_pass_b(d, blockIdx.x, sm);
+    if (threadIdx.x == 0) d.part[blockIdx.x] = t;
+}
 __global__ void k_pcg_alpha(const Dev d) {
     if (d.flags[F_DONE]) return;
     __shared__ double red[32];
-    const double psp = reduce_parts(d.part, d.nBlocks, red);
-    if (threadIdx.x == 0) { d.scal[S_PSP] = psp; d.scal[S_ALPHA] = d.scal[S_RZ] / (psp + d.scal[S_PSP_EXTRA]); }
+    const double psp = reduce_all(d.part, d.nBlocks, red);
+    if (threadIdx.x == 0) { d.scal[S_PSP] = psp; d.scal[S_ALPHA] = d.scal[S_RZ] / psp; }
 }
-
 __global__ void k_pcg_update(const Dev d) {
     if (d.flags[F_DONE]) return;
-    __shared__ double red[kThreads / 32];
+    __shared__ double red[32];
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-    double dot = 0;
-    if (i < d.nP) {
-        const double alpha = d.scal[S_ALPHA];
-        double r[3], z[3];
-#pragma unroll
-        for (int q = 0; q < 3; ++q) {
-            d.x[3ull * i + q] += alpha * d.p[3ull * i + q];
-            r[q] = d.r[3ull * i + q] - alpha * d.sp[3ull * i + q];
-            d.r[3ull * i + q] = r[q];
-        }
-        sym3_mul(d.minv + 6ull * i, r[0], r[1], r[2], z[0], z[1], z[2]);
-        d.z[3ull * i] = z[0]; d.z[3ull * i + 1] = z[1]; d.z[3ull * i + 2] = z[2];
-        dot = r[0] * z[0] + r[1] * z[1] + r[2] * z[2];
-    }
-    const double t = block_sum(dot, red);
+    const double t = block_sum(i < d.nP ? pose_update(d, i, d.scal[S_ALPHA]) : 0.0, red);
     if (threadIdx.x == 0) d.part[blockIdx.x] = t;
 }
-
 __global__ void k_pcg_beta(const Dev d, uint32_t nparts) {
     if (d.flags[F_DONE]) return;
     __shared__ double red[32];
-    const double rz_new = reduce_parts(d.part, nparts, red);
+    const double rz_new = reduce_all(d.part, nparts, red);
     if (threadIdx.x == 0) {
         d.scal[S_BETA] = rz_new / d.scal[S_RZ]; d.scal[S_RZ] = rz_new;
         const int it = d.flags[F_ITERS] + 1; d.flags[F_ITERS] = it;
         if (!(rz_new > d.scal[S_TOL2] * d.scal[S_RZ0]) || it >= d.flags[F_MAXIT]) d.flags[F_DONE] = 1;
+    }
+}
+
+// ---- persistent cooperative PCG: the whole solve in one launch (world == 1) ------------------------------
+// Four grid-wide barriers per iteration; alpha, beta and the stop test are computed redundantly by every
+// block from the same partial sums in the same order, so all blocks take the same branch.
+__global__ void __launch_bounds__(kThreads, 4) k_pcg_persistent(const Dev d) {
+    extern __shared__ __align__(32) unsigned char smem_raw[];
+    const Sm sm = Sm::make<LayPcg>(smem_raw);
+    cg::grid_group grid = cg::this_grid();
+    const uint32_t nb = gridDim.x, gtid = blockIdx.x * kThreads + threadIdx.x, gsz = nb * kThreads;
+    double dot = 0;
+    for (uint32_t i = gtid; i < d.nP; i += gsz) dot += pose_init(d, i);
+    double t = block_sum(dot, sm.red);
+    if (threadIdx.x == 0) d.part[blockIdx.x] = t;
+    grid.sync();
+    const double rz0 = reduce_all(d.part, nb, sm.red);
+    double rz = rz0, beta = 0;
+    const double tol2 = d.scal[S_TOL2]; const int maxit = d.flags[F_MAXIT];
+    int it = 0;
+    if (rz0 > 0) {
+        for (;;) {
+            for (uint32_t u = blockIdx.x; u < d.nBlocks; u += nb) unit_pass_a<0>(d, u, sm, beta);
+            grid.sync();
+            for (uint32_t l = gtid; l < d.L; l += gsz) lm_w_sum(d, l);
+            grid.sync();
+            double bsum = 0;
+            for (uint32_t u = blockIdx.x; u < d.nBlocks; u += nb) bsum += unit_pass_b(d, u, sm);
+            if (threadIdx.x == 0) d.part2[blockIdx.x] = bsum;
+            grid.sync();
+            const double alpha = rz / reduce_all(d.part2, nb, sm.red);
+            dot = 0;
+            for (uint32_t i = gtid; i < d.nP; i += gsz) dot += pose_update(d, i, alpha);
+            t = block_sum(dot, sm.red);
+            if (threadIdx.x == 0) d.part[blockIdx.x] = t;
+            grid.sync();
+            const double rz_new = reduce_all(d.part, nb, sm.red);
+            beta = rz_new / rz; rz = rz_new; ++it;
+            if (!(rz_new > tol2 * rz0) || it >= maxit) break;
+        }
+    }
+    if (blockIdx.x == 0 && threadIdx.x == 0) {
+        d.scal[S_RZ0] = rz0; d.scal[S_RZ] = rz; d.scal[S_BETA] = beta; d.flags[F_ITERS] = it; d.flags[F_DONE] = 1;
+    }
+    // landmark back-substitution: delta_l = Hll^-1 (b_l - Hpl^T delta_p)
+    grid.sync();
+    for (uint32_t u = blockIdx.x; u < d.nBlocks; u += nb) unit_pass_a<1>(d, u, sm, 0.0);
+    grid.sync();
+    for (uint32_t l = gtid; l < d.L; l += gsz) {
+        lm_w_sum(d, l);
+        const double t0 = d.bl[2ull * l] - d.w_sum[2ull * l], t1 = d.bl[2ull * l + 1] - d.w_sum[2ull * l + 1];
+        const double* hi = d.hinv + 3ull * l;
+        d.dl[2ull * l] = hi[0] * t0 + hi[1] * t1; d.dl[2ull * l + 1] = hi[1] * t0 + hi[2] * t1;
     }
 }
 
@@ -517,7 +613,7 @@ __global__ void k_backsub(const Dev d) {
 // K5: x <- x [+] step * delta  (VertexSe2.h:16-27, Vertex2d.h:16-19) and ||delta||^2 partials
 // ------------------------------------------------------------------------------------------------
 __global__ void k_update_state(const Dev d, double step) {
-    __shared__ double red[kThreads / 32];
+    __shared__ double red[32];
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     double np2 = 0, nl2 = 0;
     if (i < d.nP) {
@@ -563,22 +659,29 @@ __global__ void k_read_pose(const double4* pose, uint32_t n, double* xyt) {
 // ------------------------------------------------------------------------------------------------
 uint64_t g_launches = 0;
 static inline uint32_t cdiv(uint32_t a, uint32_t b) { return (a + b - 1) / b; }
-size_t linearize_smem_bytes() { return kSmemBytes; }
+size_t linearize_smem_bytes() { return LayLin::bytes; }
 
 static bool g_attr_set = false;
+static int g_coop_blocks = 0;      // co-resident blocks of the persistent PCG kernel on this device
 static void set_attrs() {
     if (g_attr_set) return;
-    cudaFuncSetAttribute(k_linearize, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemBytes);
-    cudaFuncSetAttribute(k_schur_prep, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemBytes);
-    cudaFuncSetAttribute(k_pcg_pass_a<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemBytes);
-    cudaFuncSetAttribute(k_pcg_pass_a<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemBytes);
-    cudaFuncSetAttribute(k_pcg_pass_b, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemBytes);
+    cudaFuncSetAttribute(k_linearize, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)LayLin::bytes);
+    cudaFuncSetAttribute(k_schur_prep, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)LaySchur::bytes);
+    cudaFuncSetAttribute(k_pcg_pass_a<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)LayA::bytes);
+    cudaFuncSetAttribute(k_pcg_pass_a<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)LayA::bytes);
+    cudaFuncSetAttribute(k_pcg_pass_b, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)LayB::bytes);
+    cudaFuncSetAttribute(k_pcg_persistent, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)LayPcg::bytes);
+    int dev = 0, sms = 0, per_sm = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_pcg_persistent, kThreads, LayPcg::bytes);
+    g_coop_blocks = sms * per_sm;
     g_attr_set = true;
 }
 
 void launch_linearize(const Dev& d, cudaStream_t s) {
     set_attrs();
-    if (d.nBlocks) { k_linearize<<<d.nBlocks, kThreads, kSmemBytes, s>>>(d); ++g_launches; }
+    if (d.nBlocks) { k_linearize<<<d.nBlocks, kThreads, LayLin::bytes, s>>>(d); ++g_launches; }
     k_reduce_to<<<1, 1024, 0, s>>>(d.part, d.nBlocks, d.scal + S_CHI2); ++g_launches;
 }
 void launch_lm_sum(const Dev& d, cudaStream_t s) {
@@ -589,7 +692,21 @@ void launch_lm_finalize(const Dev& d, cudaStream_t s) {
 }
 void launch_schur_prep(const Dev& d, cudaStream_t s) {
     set_attrs();
-    if (d.nBlocks) { k_schur_prep<<<d.nBlocks, kThreads, kSmemBytes, s>>>(d); ++g_launches; }
+    if (d.nBlocks) { k_schur_prep<<<d.nBlocks, kThreads, LaySchur::bytes, s>>>(d); ++g_launches; }
+}
+// whole PCG + back-substitution in one cooperative launch; returns false if the device cannot co-schedule it
+bool launch_pcg_persistent(const Dev& d, cudaStream_t s) {
+    set_attrs();
+    if (g_coop_blocks <= 0) return false;
+    uint32_t want = d.nBlocks > cdiv(d.nP, kThreads) ? d.nBlocks : cdiv(d.nP, kThreads);
+    if (cdiv(d.L, kThreads) > want) want = cdiv(d.L, kThreads);
+    uint32_t grid = want < (uint32_t)g_coop_blocks ? want : (uint32_t)g_coop_blocks;
+    if (grid == 0) grid = 1;
+    Dev dd = d; void* args[] = {&dd};
+    const cudaError_t e = cudaLaunchCooperativeKernel((void*)k_pcg_persistent, dim3(grid), dim3(kThreads), args, LayPcg::bytes, s);
+    if (e != cudaSuccess) { cudaGetLastError(); return false; }
+    ++g_launches;
+    return true;
 }
 void launch_pcg_init(const Dev& d, cudaStream_t s) {
     const uint32_t nb = cdiv(d.nP, kThreads);
@@ -599,8 +716,8 @@ void launch_pcg_init(const Dev& d, cudaStream_t s) {
 void launch_pcg_pass_a(const Dev& d, int mode, cudaStream_t s) {
     set_attrs();
     if (!d.nBlocks) return;
-    if (mode == 0) k_pcg_pass_a<0><<<d.nBlocks, kThreads, kSmemBytes, s>>>(d);
-    else k_pcg_pass_a<1><<<d.nBlocks, kThreads, kSmemBytes, s>>>(d);
+    if (mode == 0) k_pcg_pass_a<0><<<d.nBlocks, kThreads, LayA::bytes, s>>>(d);
+    else k_pcg_pass_a<1><<<d.nBlocks, kThreads, LayA::bytes, s>>>(d);
     ++g_launches;
 }
 void launch_pcg_w_sum(const Dev& d, int check_done, cudaStream_t s) {
@@ -608,7 +725,7 @@ void launch_pcg_w_sum(const Dev& d, int check_done, cudaStream_t s) {
 }
 void launch_pcg_pass_b(const Dev& d, cudaStream_t s) {
     set_attrs();
-    if (d.nBlocks) { k_pcg_pass_b<<<d.nBlocks, kThreads, kSmemBytes, s>>>(d); ++g_launches; }
+    if (d.nBlocks) { k_pcg_pass_b<<<d.nBlocks, kThreads, LayB::bytes, s>>>(d); ++g_launches; }
 }
 void launch_pcg_alpha(const Dev& d, cudaStream_t s) { k_pcg_alpha<<<1, 1024, 0, s>>>(d); ++g_launches; }
 void launch_pcg_update(const Dev& d, cudaStream_t s) {
