@@ -101,7 +101,7 @@ int upload_graph(tsb_ctx* c) {
     c->h2d += 24ull * nPG + 16ull * g.L;
     // system and solver vectors
     TRY(dalloc(c, d.hpl, 6ull * d.nE)); TRY(dalloc(c, d.hoo, 3ull * d.nO));
-    TRY(dalloc(c, d.hpp, 6ull * d.nP)); TRY(dalloc(c, d.bp, 3ull * d.nP));
+    TRY(dalloc(c, d.hpp, 6ull * d.nP)); TRY(dalloc(c, d.bp, 3ull * d.nP)); TRY(dalloc(c, d.pose_od, 6ull * d.nP));
     TRY(dalloc(c, d.lm_part, 5ull * d.nSlots)); TRY(dalloc(c, d.lm_sum, 5ull * g.L));
     TRY(dalloc(c, d.hll, 3ull * g.L)); TRY(dalloc(c, d.hinv, 3ull * g.L)); TRY(dalloc(c, d.bl, 2ull * g.L));
     TRY(dalloc(c, d.minv, 6ull * d.nP)); TRY(dalloc(c, d.rhs, 3ull * d.nP));
@@ -111,6 +111,7 @@ int upload_graph(tsb_ctx* c) {
     c->part_cap = std::max<uint32_t>(d.nBlocks, (std::max(d.nP, g.L) + kThreads - 1) / kThreads) + 1;
     TRY(dalloc(c, d.part, c->part_cap)); TRY(dalloc(c, d.part2, c->part_cap));
     TRY(dalloc(c, d.scal, (size_t)S_COUNT)); TRY(dalloc(c, d.flags, (size_t)F_COUNT));
+    { const char* e = std::getenv("TSB_PCG_TIMING"); if (e && e[0] == '1') { TRY(dalloc(c, d.dbg, (size_t)8)); CU(cudaMemsetAsync(d.dbg, 0, 64, c->stream)); } }
     CU(cudaMemsetAsync(d.scal, 0, sizeof(double) * S_COUNT, c->stream));
     CU(cudaMemsetAsync(d.flags, 0, sizeof(int) * F_COUNT, c->stream));
     CU(cudaMemsetAsync(d.p, 0, 24ull * nPG, c->stream));
@@ -146,14 +147,26 @@ int run_solve(tsb_ctx* c) {
     const Dev& d = c->d;
     launch_schur_prep(d, c->stream);
     // single GPU: the whole PCG and the back-substitution run in one persistent cooperative kernel
-    if (c->cfg.world <= 1 && !c->force_phased && launch_pcg_persistent(d, c->stream)) return TSB_OK;
+    if (c->cfg.world <= 1 && !c->force_phased && launch_pcg_persistent(d, c->stream)) {
+        if (d.dbg) {
+            long long t[8]; int its = 0;
+            CU(cudaMemcpyAsync(t, d.dbg, sizeof(t), cudaMemcpyDeviceToHost, c->stream));
+            CU(cudaMemcpyAsync(&its, d.flags + F_ITERS, 4, cudaMemcpyDeviceToHost, c->stream));
+            CU(cudaStreamSynchronize(c->stream));
+            const char* nm[8] = {"pass_a", "sync", "mid", "sync", "pass_b", "sync", "update", "sync"};
+            std::fprintf(stderr, "[tsb] persistent PCG, %d iterations, SM cycles per iteration (block 0):", its);
+            for (int q = 0; q < 8; ++q) std::fprintf(stderr, " %s=%lld", nm[q], its ? t[q] / its : 0);
+            std::fprintf(stderr, "\n");
+        }
+        return TSB_OK;
+    }
     launch_pcg_init(d, c->stream);
     const int maxit = c->cfg.pcg_max_iters > 0 ? c->cfg.pcg_max_iters : 4000;
     const int batch = 16;
     for (int it = 0; it < maxit + batch; it += batch) {
         for (int b = 0; b < batch; ++b) {
             launch_pcg_pass_a(d, 0, c->stream);
-            launch_pcg_w_sum(d, 1, c->stream);
+            launch_pcg_mid(d, 0, c->stream);
             launch_pcg_pass_b(d, c->stream);
             launch_pcg_alpha(d, c->stream);
             launch_pcg_update(d, c->stream);
@@ -165,7 +178,7 @@ int run_solve(tsb_ctx* c) {
         if (c->h_flags[F_DONE]) break;
     }
     launch_pcg_pass_a(d, 1, c->stream);
-    launch_pcg_w_sum(d, 0, c->stream);
+    launch_pcg_mid(d, 1, c->stream);
     launch_backsub(d, c->stream);
     return TSB_OK;
 }

@@ -41,6 +41,7 @@ struct Dev {
     double* hoo;                // 3 per edge: diagonal of the (i,j) block = -W
     const uint32_t* fixed_pose_count; const uint32_t* fixed_lm_count;
     // assembled system
+    double* pose_od;            // 6 per pose: ODOM + prior part of the diagonal block (3) and of b (3), from k_odom
     double* hpp;                // 6 per pose (00 01 02 11 12 22), prior included
     double* bp;                 // 3 per pose
     double* lm_part;            // 5 per slot: partial (Hll 00 01 11, b_l 0 1)
@@ -59,6 +60,7 @@ struct Dev {
     double* part2;              // second set (chi2 of ODOM etc.)
     double* scal;               // S_COUNT
     int* flags;                 // F_COUNT
+    long long* dbg;             // optional: 8 phase-cycle counters of the persistent PCG kernel (TSB_PCG_TIMING=1)
 };
 
 // kernel launchers (kernels.cu).  All take the launching stream.
@@ -69,7 +71,7 @@ void launch_schur_prep(const Dev& d, cudaStream_t s);           // K3: diag(S)^-
 bool launch_pcg_persistent(const Dev& d, cudaStream_t s);     // whole PCG + back-substitution, one cooperative launch
 void launch_pcg_init(const Dev& d, cudaStream_t s);
 void launch_pcg_pass_a(const Dev& d, int mode, cudaStream_t s); // mode 0: v = p (with p = z + beta p fused), 1: v = x
-void launch_pcg_w_sum(const Dev& d, int check_done, cudaStream_t s);
+void launch_pcg_mid(const Dev& d, int mode, cudaStream_t s);   // w = sum of slot partials; mode 0 also sp = Hpp p + ODOM part
 void launch_pcg_pass_b(const Dev& d, cudaStream_t s);
 void launch_pcg_alpha(const Dev& d, cudaStream_t s);
 void launch_pcg_update(const Dev& d, cudaStream_t s);

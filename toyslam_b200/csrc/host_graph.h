@@ -65,7 +65,7 @@ struct Structure {
 };
 
 constexpr uint32_t kChunkEdges = 512;   // LM edges staged per chunk
-constexpr uint32_t kBlockPoses = 256;   // poses per thread block (upper bound)
+constexpr uint32_t kBlockPoses = 128;   // poses per thread block (upper bound)
 
 void build_structure(const HostGraph& g, uint32_t rank, uint32_t world, Structure& s);
 

@@ -29,14 +29,16 @@ constexpr size_t align32(size_t x) { return (x + 31) & ~size_t(31); }
 
 // Shared-memory layout of a chunked kernel, sized per kernel (occupancy is smem-limited).
 template <int ROWS, bool SLOT2, bool SLOT3, bool POSE, bool VEC, bool SEDGE>
-struct Layout {
+struct Layout {   // every layout also holds the unit's row pointers and the chunk's slot pointers
     static constexpr size_t oStage = 0;
     static constexpr size_t oSlot2 = oStage + align32(sizeof(double) * ROWS * kStageStride);
     static constexpr size_t oSlot3 = oSlot2 + (SLOT2 ? sizeof(double2) * kChunkEdges : 0);
     static constexpr size_t oPose = oSlot3 + (SLOT3 ? sizeof(double) * 3 * kChunkEdges : 0);
     static constexpr size_t oVec = oPose + (POSE ? sizeof(double4) * kBlockPoses : 0);
     static constexpr size_t oSedge = oVec + (VEC ? sizeof(double) * 3 * kBlockPoses : 0);
-    static constexpr size_t oRed = oSedge + (SEDGE ? align32(sizeof(uint16_t) * kChunkEdges) : 0);
+    static constexpr size_t oPptr = oSedge + (SEDGE ? align32(sizeof(uint16_t) * kChunkEdges) : 0);
+    static constexpr size_t oSptr = oPptr + align32(sizeof(uint32_t) * (kBlockPoses + 1));
+    static constexpr size_t oRed = oSptr + align32(sizeof(uint32_t) * (kChunkEdges + 1));
     static constexpr size_t bytes = oRed + sizeof(double) * 32;
 };
 using LayLin = Layout<9, true, false, true, false, true>;
@@ -47,12 +49,14 @@ using LayPcg = Layout<3, true, false, false, true, true>;     // persistent kern
 
 struct Sm {
     double* stage; double* acc; double2* slot2; double* slot3; double4* pose; double* vec; uint16_t* sedge; double* red;
+    uint32_t* pptr; uint32_t* sptr;    // pose_ptr[p0..p0+np] and slot_ptr[s0..s1] of the current unit / chunk
     template <class L> __device__ static Sm make(unsigned char* b) {
         Sm s;
         s.stage = reinterpret_cast<double*>(b + L::oStage); s.acc = s.stage;      // acc aliases stage (used after the last chunk)
         s.slot2 = reinterpret_cast<double2*>(b + L::oSlot2); s.slot3 = reinterpret_cast<double*>(b + L::oSlot3);
         s.pose = reinterpret_cast<double4*>(b + L::oPose); s.vec = reinterpret_cast<double*>(b + L::oVec);
         s.sedge = reinterpret_cast<uint16_t*>(b + L::oSedge); s.red = reinterpret_cast<double*>(b + L::oRed);
+        s.pptr = reinterpret_cast<uint32_t*>(b + L::oPptr); s.sptr = reinterpret_cast<uint32_t*>(b + L::oSptr);
         return s;
     }
 };
@@ -129,15 +133,15 @@ __device__ __forceinline__ double list_sum(const double* s, const uint16_t* idx,
 
 // pose side: items (pose, row); sums stage[row][.] over the pose's edges that fall in the chunk
 template <int ROWS>
-__device__ __forceinline__ void pose_reduce(const Dev& d, const ChunkDesc& ch, const double* stage, uint32_t np,
+__device__ __forceinline__ void pose_reduce(const uint32_t* pptr, const ChunkDesc& ch, const double* stage, uint32_t np,
                                             double (&acc)[ROWS]) {
 #pragma unroll
     for (int it = 0; it < ROWS; ++it) {
         const uint32_t item = threadIdx.x + it * kThreads;
         if (item < np * ROWS) {
             const uint32_t pl = item / ROWS, row = item % ROWS;
-            const uint32_t b = max(d.pose_ptr[ch.p0 + pl], ch.e0) - ch.e0;
-            const uint32_t e = min(d.pose_ptr[ch.p0 + pl + 1], ch.e1) - ch.e0;
+            const uint32_t b = max(pptr[pl], ch.e0) - ch.e0;
+            const uint32_t e = min(pptr[pl + 1], ch.e1) - ch.e0;
             acc[it] += seg_sum(stage + row * kStageStride, b, e);
         }
     }
@@ -177,12 +181,60 @@ __device__ __forceinline__ double lm_edge(const double4 ps, const double2 l, con
 }
 
 // ------------------------------------------------------------------------------------------------
-// K1 unit: linearize + assemble
+// K1a: ODOM edges, pose-parallel.  Each pose sums its out-edges (id1 == pose) and in-edges
+// (id2 == pose); an edge is therefore evaluated twice, which costs less than a per-edge record
+// round trip through HBM, and the dependent index loads are hidden by P-way parallelism instead
+// of stalling a unit's 256 threads.  Writes pose_od (H diag 3, b 3), hoo and chi2 partials.
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(kThreads) k_odom(const Dev d) {
+    __shared__ double red[32];
+    const uint32_t p = blockIdx.x * blockDim.x + threadIdx.x;
+    double rho_sum = 0;
+    if (p < d.nP) {
+        const double4 me = d.pose[p];
+        double h0 = 0, h1 = 0, h2 = 0, b0 = 0, b1 = 0, b2 = 0;
+        for (uint32_t k = d.od_out_ptr[p]; k < d.od_out_ptr[p + 1]; ++k) {
+            double W[3], We[3], rho;
+            odom_edge(me, d.pose[d.od_b[k]], d.od_zinv + 6ull * k, d.od_w + 3ull * k, W, We, rho);
+            rho_sum += rho;
+            h0 += W[0]; h1 += W[1]; h2 += W[2];               // A^T W A, A = -I
+            b0 += We[0]; b1 += We[1]; b2 += We[2];            // b -= A^T W e
+            d.hoo[3ull * k] = -W[0]; d.hoo[3ull * k + 1] = -W[1]; d.hoo[3ull * k + 2] = -W[2];
+        }
+        for (uint32_t q = d.od_in_ptr[p]; q < d.od_in_ptr[p + 1]; ++q) {
+            const uint32_t k = d.od_in_edge[q];
+            double W[3], We[3], rho;
+            odom_edge(d.pose[d.od_a[k]], me, d.od_zinv + 6ull * k, d.od_w + 3ull * k, W, We, rho);
+            h0 += W[0]; h1 += W[1]; h2 += W[2];               // B^T W B, B = +I
+            b0 -= We[0]; b1 -= We[1]; b2 -= We[2];
+            if (k >= d.nOwned) { d.hoo[3ull * k] = -W[0]; d.hoo[3ull * k + 1] = -W[1]; d.hoo[3ull * k + 2] = -W[2]; }
+        }
+        const double prior = 1e6 * (double)d.fixed_pose_count[p];     // OptimizerCpu.h:132-138
+        double* o = d.pose_od + 6ull * p;
+        o[0] = h0 + prior; o[1] = h1 + prior; o[2] = h2 + prior; o[3] = b0; o[4] = b1; o[5] = b2;
+    }
+    const double t = block_sum(rho_sum, red);
+    if (threadIdx.x == 0) d.part2[blockIdx.x] = t;
+}
+
+// stages the unit's row pointers (pose_ptr[p0 .. p0+np]) in shared memory
+__device__ __forceinline__ void stage_pptr(const Dev& d, const Sm& sm, uint32_t p0, uint32_t np) {
+    for (uint32_t i = threadIdx.x; i <= np; i += kThreads) sm.pptr[i] = d.pose_ptr[p0 + i];
+}
+// stages the chunk's slot pointers, rebased to the chunk
+__device__ __forceinline__ void stage_sptr(const Dev& d, const Sm& sm, const ChunkDesc& ch) {
+    for (uint32_t i = threadIdx.x; i <= ch.s1 - ch.s0; i += kThreads) sm.sptr[i] = d.slot_ptr[ch.s0 + i] - ch.e0;
+}
+
+// ------------------------------------------------------------------------------------------------
+// K1b unit: LM edges -- linearize + assemble.  All global loads of a chunk are issued up front
+// (edge data, row/slot pointers, slot landmarks); the reductions then run out of shared memory.
 // ------------------------------------------------------------------------------------------------
 __device__ __forceinline__ void unit_linearize(const Dev& d, const uint32_t unit, const Sm& sm) {
     const uint32_t c0 = d.blk_chunk_ptr[unit], c1 = d.blk_chunk_ptr[unit + 1];
     const uint32_t p0 = d.chunks[c0].p0, np = d.chunks[c0].p1 - p0;
     for (uint32_t i = threadIdx.x; i < np; i += kThreads) sm.pose[i] = d.pose[p0 + i];
+    stage_pptr(d, sm, p0, np);
     double acc[kStageRows];
 #pragma unroll
     for (int i = 0; i < kStageRows; ++i) acc[i] = 0;
@@ -190,59 +242,39 @@ __device__ __forceinline__ void unit_linearize(const Dev& d, const uint32_t unit
     for (uint32_t c = c0; c < c1; ++c) {
         const ChunkDesc ch = d.chunks[c];
         const uint32_t n = ch.e1 - ch.e0, ns = ch.s1 - ch.s0;
-        // issue the per-edge loads first: they do not depend on the staged vertex blocks
         const uint32_t k0 = threadIdx.x, k1 = threadIdx.x + kThreads;
         uint32_t pk0 = 0, pk1 = 0; double2 z0 = {}, w0 = {}, z1 = {}, w1 = {};
         if (k0 < n) { pk0 = d.lm_packed[ch.e0 + k0]; z0 = d.le_z[ch.e0 + k0]; w0 = d.le_w[ch.e0 + k0]; }
         if (k1 < n) { pk1 = d.lm_packed[ch.e0 + k1]; z1 = d.le_z[ch.e0 + k1]; w1 = d.le_w[ch.e0 + k1]; }
         for (uint32_t s = threadIdx.x; s < ns; s += kThreads) sm.slot2[s] = d.lm[d.slot_lm[ch.s0 + s]];
         for (uint32_t k = threadIdx.x; k < n; k += kThreads) sm.sedge[k] = d.slot_edge[ch.e0 + k];
+        stage_sptr(d, sm, ch);
         __syncthreads();
         if (k0 < n) rho_sum += lm_edge(sm.pose[pk0 >> 16], sm.slot2[pk0 & 0xffffu], z0, w0,
                                        reinterpret_cast<double2*>(d.hpl + 6ull * (ch.e0 + k0)), sm.stage + k0);
         if (k1 < n) rho_sum += lm_edge(sm.pose[pk1 >> 16], sm.slot2[pk1 & 0xffffu], z1, w1,
                                        reinterpret_cast<double2*>(d.hpl + 6ull * (ch.e0 + k1)), sm.stage + k1);
         __syncthreads();
-        pose_reduce<kStageRows>(d, ch, sm.stage, np, acc);
+        pose_reduce<kStageRows>(sm.pptr, ch, sm.stage, np, acc);
         // landmark side: one partial (M00 M01 M11 g0 g1) per slot, edges of the slot in list order
         for (uint32_t item = threadIdx.x; item < ns * 5; item += kThreads) {
             const uint32_t sl = item / 5, comp = item % 5;
             const double* s = sm.stage + (comp < 3 ? comp : comp + 3) * kStageStride;
-            d.lm_part[5ull * (ch.s0 + sl) + comp] =
-                list_sum(s, sm.sedge, d.slot_ptr[ch.s0 + sl] - ch.e0, d.slot_ptr[ch.s0 + sl + 1] - ch.e0);
+            d.lm_part[5ull * (ch.s0 + sl) + comp] = list_sum(s, sm.sedge, sm.sptr[sl], sm.sptr[sl + 1]);
         }
         __syncthreads();
     }
     acc_to_smem<kStageRows>(acc, sm.acc, np);
     __syncthreads();
-    // pose finalize: LM sums + ODOM edges (out: id1 == pose, in: id2 == pose) + prior
+    // pose finalize: LM sums + the ODOM / prior part prepared by k_odom
     for (uint32_t i = threadIdx.x; i < np; i += kThreads) {
         const double* a = sm.acc + i * kStageRows;
-        double h00 = a[0], h01 = a[1], h11 = a[2], h02 = a[3], h12 = a[4], h22 = a[5];
-        double b0 = a[6], b1 = a[7], b2 = -a[8];              // b -= A^T W e
         const uint32_t p = p0 + i;
-        for (uint32_t k = d.od_out_ptr[p]; k < d.od_out_ptr[p + 1]; ++k) {
-            double W[3], We[3], rho;
-            odom_edge(sm.pose[i], d.pose[d.od_b[k]], d.od_zinv + 6ull * k, d.od_w + 3ull * k, W, We, rho);
-            rho_sum += rho;
-            h00 += W[0]; h11 += W[1]; h22 += W[2];            // A^T W A, A = -I
-            b0 += We[0]; b1 += We[1]; b2 += We[2];            // b -= A^T W e
-            d.hoo[3ull * k] = -W[0]; d.hoo[3ull * k + 1] = -W[1]; d.hoo[3ull * k + 2] = -W[2];
-        }
-        for (uint32_t q = d.od_in_ptr[p]; q < d.od_in_ptr[p + 1]; ++q) {
-            const uint32_t k = d.od_in_edge[q];
-            double W[3], We[3], rho;
-            odom_edge(d.pose[d.od_a[k]], sm.pose[i], d.od_zinv + 6ull * k, d.od_w + 3ull * k, W, We, rho);
-            h00 += W[0]; h11 += W[1]; h22 += W[2];            // B^T W B, B = +I
-            b0 -= We[0]; b1 -= We[1]; b2 -= We[2];
-            if (k >= d.nOwned) { d.hoo[3ull * k] = -W[0]; d.hoo[3ull * k + 1] = -W[1]; d.hoo[3ull * k + 2] = -W[2]; }
-        }
-        const double prior = 1e6 * (double)d.fixed_pose_count[p];     // OptimizerCpu.h:132-138
-        h00 += prior; h11 += prior; h22 += prior;
+        const double* o = d.pose_od + 6ull * p;
         double* H = d.hpp + 6ull * p;
-        H[0] = h00; H[1] = h01; H[2] = h02; H[3] = h11; H[4] = h12; H[5] = h22;
+        H[0] = a[0] + o[0]; H[1] = a[1]; H[2] = a[3]; H[3] = a[2] + o[1]; H[4] = a[4]; H[5] = a[5] + o[2];
         double* B = d.bp + 3ull * p;
-        B[0] = b0; B[1] = b1; B[2] = b2;
+        B[0] = a[6] + o[3]; B[1] = a[7] + o[4]; B[2] = o[5] - a[8];       // b -= A^T W e
     }
     const double t = block_sum(rho_sum, sm.red);
     if (threadIdx.x == 0) d.part[unit] = t;
@@ -259,15 +291,20 @@ __global__ void __launch_bounds__(kThreads, 4) k_linearize(const Dev d) {
 // K2b: prior, Hll, b_l, Hll^-1 (closed-form 2x2).
 // ------------------------------------------------------------------------------------------------
 __global__ void k_lm_sum(const Dev d) {
-    const uint32_t l = blockIdx.x * blockDim.x + threadIdx.x;
+    const uint32_t l = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
     if (l >= d.L) return;
-    double a0 = 0, a1 = 0, a2 = 0, a3 = 0, a4 = 0;
-    for (uint32_t q = d.lm_part_ptr[l]; q < d.lm_part_ptr[l + 1]; ++q) {
+    double a[5] = {0, 0, 0, 0, 0};
+    for (uint32_t q = d.lm_part_ptr[l] + lane; q < d.lm_part_ptr[l + 1]; q += 32) {
         const double* r = d.lm_part + 5ull * d.lm_part_idx[q];
-        a0 += r[0]; a1 += r[1]; a2 += r[2]; a3 += r[3]; a4 += r[4];
+#pragma unroll
+        for (int k = 0; k < 5; ++k) a[k] += r[k];
     }
-    double* o = d.lm_sum + 5ull * l;
-    o[0] = a0; o[1] = a1; o[2] = a2; o[3] = a3; o[4] = a4;
+#pragma unroll
+    for (int k = 0; k < 5; ++k) {
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) a[k] += __shfl_xor_sync(0xffffffffu, a[k], o);
+    }
+    if (lane < 5) d.lm_sum[5ull * l + lane] = lane == 0 ? a[0] : lane == 1 ? a[1] : lane == 2 ? a[2] : lane == 3 ? a[3] : a[4];
 }
 
 __global__ void k_lm_finalize(const Dev d) {
@@ -282,6 +319,11 @@ __global__ void k_lm_finalize(const Dev d) {
     d.hinv[3ull * l] = h11 * id; d.hinv[3ull * l + 1] = -h01 * id; d.hinv[3ull * l + 2] = h00 * id;
 }
 
+__global__ void k_reduce2_to(const double* a, uint32_t na, const double* b, uint32_t nb, double* out) {
+    __shared__ double red[32];
+    const double r = reduce_all(a, na, red) + reduce_all(b, nb, red);
+    if (threadIdx.x == 0) *out = r;
+}
 __global__ void k_reduce_to(const double* part, uint32_t n, double* out) {
     __shared__ double red[32];
     const double r = reduce_all(part, n, red);
@@ -315,6 +357,7 @@ __global__ void __launch_bounds__(kThreads, 3) k_schur_prep(const Dev d) {
     const uint32_t unit = blockIdx.x;
     const uint32_t c0 = d.blk_chunk_ptr[unit], c1 = d.blk_chunk_ptr[unit + 1];
     const uint32_t p0 = d.chunks[c0].p0, np = d.chunks[c0].p1 - p0;
+    stage_pptr(d, sm, p0, np);
     double acc[kStageRows];
 #pragma unroll
     for (int i = 0; i < kStageRows; ++i) acc[i] = 0;
@@ -332,7 +375,7 @@ __global__ void __launch_bounds__(kThreads, 3) k_schur_prep(const Dev d) {
             schur_edge(reinterpret_cast<const double2*>(d.hpl + 6ull * (ch.e0 + k)), sm.slot3 + 3 * sl, sm.slot2[sl], sm.stage + k);
         }
         __syncthreads();
-        pose_reduce<kStageRows>(d, ch, sm.stage, np, acc);
+        pose_reduce<kStageRows>(sm.pptr, ch, sm.stage, np, acc);
         __syncthreads();
     }
     acc_to_smem<kStageRows>(acc, sm.acc, np);
@@ -387,6 +430,7 @@ __device__ __forceinline__ void unit_pass_a(const Dev& d, const uint32_t unit, c
         if (k1 < n) { const double2* hp = reinterpret_cast<const double2*>(d.hpl + 6ull * (ch.e0 + k1));
             pl1 = d.lm_packed[ch.e0 + k1] >> 16; b0 = hp[0]; b1 = hp[1]; b2 = hp[2]; }
         for (uint32_t k = threadIdx.x; k < n; k += kThreads) sm.sedge[k] = d.slot_edge[ch.e0 + k];
+        stage_sptr(d, sm, ch);
         __syncthreads();
         if (k0 < n) { const double v0 = v[3 * pl0], v1 = v[3 * pl0 + 1], v2 = v[3 * pl0 + 2];
             sm.stage[k0] = a0.x * v0 + a1.x * v1 + a2.x * v2; sm.stage[kStageStride + k0] = a0.y * v0 + a1.y * v1 + a2.y * v2; }
@@ -395,17 +439,36 @@ __device__ __forceinline__ void unit_pass_a(const Dev& d, const uint32_t unit, c
         __syncthreads();
         for (uint32_t item = threadIdx.x; item < ns * 2; item += kThreads) {
             const uint32_t sl = item >> 1, comp = item & 1;
-            d.w_part[2ull * (ch.s0 + sl) + comp] = list_sum(sm.stage + comp * kStageStride, sm.sedge,
-                d.slot_ptr[ch.s0 + sl] - ch.e0, d.slot_ptr[ch.s0 + sl + 1] - ch.e0);
+            d.w_part[2ull * (ch.s0 + sl) + comp] = list_sum(sm.stage + comp * kStageStride, sm.sedge, sm.sptr[sl], sm.sptr[sl + 1]);
         }
         __syncthreads();
     }
 }
 
-// returns this unit's contribution to p'Sp in thread 0
+// sp_i = Hpp_ii p_i + sum over ODOM edges of Hoo p_j   (the part of S p that needs no landmark data)
+__device__ __forceinline__ void hpp_apply(const Dev& d, uint32_t p, double* out) {
+    const double v0 = d.p[3ull * p], v1 = d.p[3ull * p + 1], v2 = d.p[3ull * p + 2];
+    double y0, y1, y2; sym3_mul(d.hpp + 6ull * p, v0, v1, v2, y0, y1, y2);
+    for (uint32_t k = d.od_out_ptr[p]; k < d.od_out_ptr[p + 1]; ++k) {
+        const double* h = d.hoo + 3ull * k; const double* q = d.p + 3ull * d.od_b[k];
+        y0 += h[0] * q[0]; y1 += h[1] * q[1]; y2 += h[2] * q[2];
+    }
+    for (uint32_t j = d.od_in_ptr[p]; j < d.od_in_ptr[p + 1]; ++j) {
+        const uint32_t k = d.od_in_edge[j];
+        const double* h = d.hoo + 3ull * k; const double* q = d.p + 3ull * d.od_a[k];
+        y0 += h[0] * q[0]; y1 += h[1] * q[1]; y2 += h[2] * q[2];
+    }
+    out[0] = y0; out[1] = y1; out[2] = y2;
+}
+
+// Pass B over one unit; returns the unit's contribution to p'Sp in thread 0.  w_sum holds Hpl^T p reduced
+// over slots (and over ranks when world > 1); sp holds the Hpp part of S p from the middle phase.
+// (Summing the slot partials inside this pass instead -- one grid barrier less -- was measured slower:
+// landmarks shared by many units make the redundant gathers the critical path.)
 __device__ __forceinline__ double unit_pass_b(const Dev& d, const uint32_t unit, const Sm& sm) {
     const uint32_t c0 = d.blk_chunk_ptr[unit], c1 = d.blk_chunk_ptr[unit + 1];
     const uint32_t p0 = d.chunks[c0].p0, np = d.chunks[c0].p1 - p0;
+    stage_pptr(d, sm, p0, np);
     double acc[3] = {0, 0, 0};
     for (uint32_t c = c0; c < c1; ++c) {
         const ChunkDesc ch = d.chunks[c];
@@ -430,39 +493,32 @@ __device__ __forceinline__ double unit_pass_b(const Dev& d, const uint32_t unit,
             sm.stage[k1] = b0.x * u.x + b0.y * u.y; sm.stage[kStageStride + k1] = b1.x * u.x + b1.y * u.y;
             sm.stage[2 * kStageStride + k1] = b2.x * u.x + b2.y * u.y; }
         __syncthreads();
-        pose_reduce<3>(d, ch, sm.stage, np, acc);
+        pose_reduce<3>(sm.pptr, ch, sm.stage, np, acc);
         __syncthreads();
     }
     acc_to_smem<3>(acc, sm.acc, np);
     __syncthreads();
     double dot = 0;
-    for (uint32_t i = threadIdx.x; i < np; i += kThreads) {
-        const uint32_t p = p0 + i;
-        const double v0 = d.p[3ull * p], v1 = d.p[3ull * p + 1], v2 = d.p[3ull * p + 2];
-        double y0, y1, y2; sym3_mul(d.hpp + 6ull * p, v0, v1, v2, y0, y1, y2);
-        for (uint32_t k = d.od_out_ptr[p]; k < d.od_out_ptr[p + 1]; ++k) {
-            const double* h = d.hoo + 3ull * k; const double* q = d.p + 3ull * d.od_b[k];
-            y0 += h[0] * q[0]; y1 += h[1] * q[1]; y2 += h[2] * q[2];
-        }
-        for (uint32_t j = d.od_in_ptr[p]; j < d.od_in_ptr[p + 1]; ++j) {
-            const uint32_t k = d.od_in_edge[j];
-            const double* h = d.hoo + 3ull * k; const double* q = d.p + 3ull * d.od_a[k];
-            y0 += h[0] * q[0]; y1 += h[1] * q[1]; y2 += h[2] * q[2];
-        }
-        y0 -= sm.acc[3 * i]; y1 -= sm.acc[3 * i + 1]; y2 -= sm.acc[3 * i + 2];
-        d.sp[3ull * p] = y0; d.sp[3ull * p + 1] = y1; d.sp[3ull * p + 2] = y2;
-        dot += v0 * y0 + v1 * y1 + v2 * y2;
+    for (uint32_t i = threadIdx.x; i < 3 * np; i += kThreads) {
+        const double y = d.sp[3ull * p0 + i] - sm.acc[i];
+        d.sp[3ull * p0 + i] = y;
+        dot += d.p[3ull * p0 + i] * y;
     }
     return block_sum(dot, sm.red);
 }
 
-__device__ __forceinline__ void lm_w_sum(const Dev& d, uint32_t l) {
+// landmark-major sum of the slot partials of w = Hpl^T v, one warp per landmark: lane j takes the
+// partials j, j+32, ... in order, then a fixed shuffle tree combines the lanes (deterministic).
+__device__ __forceinline__ double2 lm_w_sum_warp(const Dev& d, uint32_t l) {
+    const uint32_t lane = threadIdx.x & 31;
     double a0 = 0, a1 = 0;
-    for (uint32_t q = d.lm_part_ptr[l]; q < d.lm_part_ptr[l + 1]; ++q) {
+    for (uint32_t q = d.lm_part_ptr[l] + lane; q < d.lm_part_ptr[l + 1]; q += 32) {
         const double2 r = reinterpret_cast<const double2*>(d.w_part)[d.lm_part_idx[q]];
         a0 += r.x; a1 += r.y;
     }
-    reinterpret_cast<double2*>(d.w_sum)[l] = make_double2(a0, a1);
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) { a0 += __shfl_xor_sync(0xffffffffu, a0, o); a1 += __shfl_xor_sync(0xffffffffu, a1, o); }
+    return make_double2(a0, a1);
 }
 
 // x += alpha p; r -= alpha Sp; z = M^-1 r; returns r'z of pose i
@@ -511,10 +567,16 @@ __global__ void __launch_bounds__(kThreads) k_pcg_pass_a(const Dev d) {
     const Sm sm = Sm::make<LayA>(smem_raw);
     unit_pass_a<MODE>(d, blockIdx.x, sm, MODE == 0 ? d.scal[S_BETA] : 0.0);
 }
-__global__ void k_pcg_w_sum(const Dev d, int check_done) {
-    if (check_done && d.flags[F_DONE]) return;
-    const uint32_t l = blockIdx.x * blockDim.x + threadIdx.x;
-    if (l < d.L) lm_w_sum(d, l);
+// landmark-major sum of the slot partials (warp per landmark); used where w must exist as an array:
+// before the all-reduce over ranks (world > 1) and before the back-substitution
+__global__ void k_pcg_mid(const Dev d, int mode) {
+    if (mode == 0 && d.flags[F_DONE]) return;
+    const uint32_t gtid = blockIdx.x * blockDim.x + threadIdx.x, gw = gtid >> 5, nw = (gridDim.x * blockDim.x) >> 5;
+    for (uint32_t l = gw; l < d.L; l += nw) {
+        const double2 w = lm_w_sum_warp(d, l);
+        if ((threadIdx.x & 31) == 0) reinterpret_cast<double2*>(d.w_sum)[l] = w;
+    }
+    if (mode == 0) for (uint32_t p = gtid; p < d.nP; p += gridDim.x * blockDim.x) hpp_apply(d, p, d.sp + 3ull * p);
 }
 __global__ void __launch_bounds__(kThreads) k_pcg_pass_b(const Dev d) {
     if (d.flags[F_DONE]) return;
@@ -550,7 +612,7 @@ __global__ void k_pcg_beta(const Dev d, uint32_t nparts) {
 // ---- persistent cooperative PCG: the whole solve in one launch (world == 1) ------------------------------
 // Four grid-wide barriers per iteration; alpha, beta and the stop test are computed redundantly by every
 // block from the same partial sums in the same order, so all blocks take the same branch.
-__global__ void __launch_bounds__(kThreads, 4) k_pcg_persistent(const Dev d) {
+__global__ void __launch_bounds__(kThreads, 3) k_pcg_persistent(const Dev d) {
     extern __shared__ __align__(32) unsigned char smem_raw[];
     const Sm sm = Sm::make<LayPcg>(smem_raw);
     cg::grid_group grid = cg::this_grid();
@@ -564,22 +626,39 @@ __global__ void __launch_bounds__(kThreads, 4) k_pcg_persistent(const Dev d) {
     double rz = rz0, beta = 0;
     const double tol2 = d.scal[S_TOL2]; const int maxit = d.flags[F_MAXIT];
     int it = 0;
+    // optional phase timing (TSB_PCG_TIMING=1): SM cycles of block 0 per phase, barrier waits separate
+    const bool timing = d.dbg != nullptr && blockIdx.x == 0 && threadIdx.x == 0;
+    long long tk = 0; long long tacc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+#define TICK(slot) do { if (timing) { const long long now_ = clock64(); tacc[slot] += now_ - tk; tk = now_; } } while (0)
     if (rz0 > 0) {
         for (;;) {
+            if (timing) tk = clock64();
             for (uint32_t u = blockIdx.x; u < d.nBlocks; u += nb) unit_pass_a<0>(d, u, sm, beta);
+            TICK(0);
             grid.sync();
-            for (uint32_t l = gtid; l < d.L; l += gsz) lm_w_sum(d, l);
+            TICK(1);
+            for (uint32_t l = gtid >> 5; l < d.L; l += gsz >> 5) {
+                const double2 w = lm_w_sum_warp(d, l);
+                if ((threadIdx.x & 31) == 0) reinterpret_cast<double2*>(d.w_sum)[l] = w;
+            }
+            for (uint32_t p = gtid; p < d.nP; p += gsz) hpp_apply(d, p, d.sp + 3ull * p);
+            TICK(2);
             grid.sync();
+            TICK(3);
             double bsum = 0;
             for (uint32_t u = blockIdx.x; u < d.nBlocks; u += nb) bsum += unit_pass_b(d, u, sm);
             if (threadIdx.x == 0) d.part2[blockIdx.x] = bsum;
+            TICK(4);
             grid.sync();
+            TICK(5);
             const double alpha = rz / reduce_all(d.part2, nb, sm.red);
             dot = 0;
             for (uint32_t i = gtid; i < d.nP; i += gsz) dot += pose_update(d, i, alpha);
             t = block_sum(dot, sm.red);
             if (threadIdx.x == 0) d.part[blockIdx.x] = t;
+            TICK(6);
             grid.sync();
+            TICK(7);
             const double rz_new = reduce_all(d.part, nb, sm.red);
             beta = rz_new / rz; rz = rz_new; ++it;
             if (!(rz_new > tol2 * rz0) || it >= maxit) break;
@@ -587,16 +666,20 @@ __global__ void __launch_bounds__(kThreads, 4) k_pcg_persistent(const Dev d) {
     }
     if (blockIdx.x == 0 && threadIdx.x == 0) {
         d.scal[S_RZ0] = rz0; d.scal[S_RZ] = rz; d.scal[S_BETA] = beta; d.flags[F_ITERS] = it; d.flags[F_DONE] = 1;
+        if (timing) for (int q = 0; q < 8; ++q) d.dbg[q] = tacc[q];
     }
+#undef TICK
     // landmark back-substitution: delta_l = Hll^-1 (b_l - Hpl^T delta_p)
     grid.sync();
     for (uint32_t u = blockIdx.x; u < d.nBlocks; u += nb) unit_pass_a<1>(d, u, sm, 0.0);
     grid.sync();
-    for (uint32_t l = gtid; l < d.L; l += gsz) {
-        lm_w_sum(d, l);
-        const double t0 = d.bl[2ull * l] - d.w_sum[2ull * l], t1 = d.bl[2ull * l + 1] - d.w_sum[2ull * l + 1];
-        const double* hi = d.hinv + 3ull * l;
-        d.dl[2ull * l] = hi[0] * t0 + hi[1] * t1; d.dl[2ull * l + 1] = hi[1] * t0 + hi[2] * t1;
+    for (uint32_t l = gtid >> 5; l < d.L; l += gsz >> 5) {
+        const double2 w = lm_w_sum_warp(d, l);
+        if ((threadIdx.x & 31) == 0) {
+            const double t0 = d.bl[2ull * l] - w.x, t1 = d.bl[2ull * l + 1] - w.y;
+            const double* hi = d.hinv + 3ull * l;
+            d.dl[2ull * l] = hi[0] * t0 + hi[1] * t1; d.dl[2ull * l + 1] = hi[1] * t0 + hi[2] * t1;
+        }
     }
 }
 
@@ -681,11 +764,13 @@ static void set_attrs() {
 
 void launch_linearize(const Dev& d, cudaStream_t s) {
     set_attrs();
+    const uint32_t nob = cdiv(d.nP, kThreads);
+    if (nob) { k_odom<<<nob, kThreads, 0, s>>>(d); ++g_launches; }
     if (d.nBlocks) { k_linearize<<<d.nBlocks, kThreads, LayLin::bytes, s>>>(d); ++g_launches; }
-    k_reduce_to<<<1, 1024, 0, s>>>(d.part, d.nBlocks, d.scal + S_CHI2); ++g_launches;
+    k_reduce2_to<<<1, 1024, 0, s>>>(d.part2, nob, d.part, d.nBlocks, d.scal + S_CHI2); ++g_launches;
 }
 void launch_lm_sum(const Dev& d, cudaStream_t s) {
-    if (d.L) { k_lm_sum<<<cdiv(d.L, kThreads), kThreads, 0, s>>>(d); ++g_launches; }
+    if (d.L) { k_lm_sum<<<cdiv(d.L, kThreads / 32), kThreads, 0, s>>>(d); ++g_launches; }
 }
 void launch_lm_finalize(const Dev& d, cudaStream_t s) {
     if (d.L) { k_lm_finalize<<<cdiv(d.L, kThreads), kThreads, 0, s>>>(d); ++g_launches; }
@@ -720,8 +805,11 @@ void launch_pcg_pass_a(const Dev& d, int mode, cudaStream_t s) {
     else k_pcg_pass_a<1><<<d.nBlocks, kThreads, LayA::bytes, s>>>(d);
     ++g_launches;
 }
-void launch_pcg_w_sum(const Dev& d, int check_done, cudaStream_t s) {
-    if (d.L) { k_pcg_w_sum<<<cdiv(d.L, kThreads), kThreads, 0, s>>>(d, check_done); ++g_launches; }
+void launch_pcg_mid(const Dev& d, int mode, cudaStream_t s) {
+    uint32_t nb = cdiv(d.L, kThreads / 32);
+    if (mode == 0 && cdiv(d.nP, kThreads) > nb) nb = cdiv(d.nP, kThreads);
+    if (nb > 148 * 8) nb = 148 * 8;
+    if (nb) { k_pcg_mid<<<nb, kThreads, 0, s>>>(d, mode); ++g_launches; }
 }
 void launch_pcg_pass_b(const Dev& d, cudaStream_t s) {
     set_attrs();
