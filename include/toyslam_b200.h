@@ -87,6 +87,8 @@ typedef struct tsb_report {
     float ms_linearize_total, ms_solve_total;
 } tsb_report;
 
+/* world > 1: rank 0 calls this once and ships the 128 bytes to every rank (e.g. over torch.distributed or MPI) */
+int tsb_nccl_unique_id(void* out128);
 int tsb_create(const tsb_config* cfg, tsb_ctx** out);
 void tsb_destroy(tsb_ctx* ctx);
 const char* tsb_last_error(const tsb_ctx* ctx);     /* ctx may be NULL: error of the last failed tsb_create */
@@ -94,6 +96,10 @@ const char* tsb_last_error(const tsb_ctx* ctx);     /* ctx may be NULL: error of
 int tsb_load_wire(tsb_ctx* ctx, const void* payload, uint32_t nbytes);
 int tsb_load_soa(tsb_ctx* ctx, const tsb_graph_soa* g);
 int tsb_get_counts(const tsb_ctx* ctx, tsb_counts* out);
+/* host-only planning (no GPU): rank `rank` of `world`'s share of a payload; structure_hash covers the
+ * rank-independent parts (pose cuts, boundary-pose list) and must be equal on every rank */
+int tsb_host_plan(const void* payload, uint32_t nbytes, int32_t rank, int32_t world, tsb_counts* out,
+                  uint32_t* n_ghost, uint32_t* n_boundary, uint64_t* structure_hash);
 int tsb_reset_state(tsb_ctx* ctx);                  /* state <- the values loaded (device-to-device)  */
 int tsb_set_state(tsb_ctx* ctx, const double* pose_xytheta, const double* lm_xy);
 

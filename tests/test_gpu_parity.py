@@ -205,3 +205,15 @@ def test_phased_pcg_path_matches_persistent(gpu, monkeypatch):
     assert res[0][2] < res[1][2]
     assert np.max(np.abs(res[0][0] - res[1][0]) / res[0][0]) < CHI2_TOL
     assert state_diff(*res[0][1], *res[1][1]) < STATE_TOL
+
+
+def test_two_ranks_match_one_rank(gpu):
+    """Edge-sharded run over 2 GPUs (NCCL) against the single-GPU run and the oracle; skipped on a 1-GPU box."""
+    import os, subprocess, sys, torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    from conftest import ROOT
+    r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2", "--master-addr",
+                        "127.0.0.1", "--master-port", "29741", os.path.join(ROOT, "tools", "mgpu_check.py")],
+                       capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0 and "MGPU OK" in r.stdout, r.stdout[-3000:] + r.stderr[-3000:]

@@ -1,0 +1,60 @@
+"""CPU tests of the multi-GPU host logic: pose partition / edge ownership / ghosts (tsb_host_plan), and a
+world_size-2 gloo run of the rendezvous helper that ships the NCCL unique id."""
+import os
+import subprocess
+import sys
+import numpy as np
+import pytest
+from conftest import ROOT
+from toyslam_b200 import synth, capi
+
+
+@pytest.mark.parametrize("world", [1, 2, 4, 8])
+def test_partition_tiles_the_graph(world):
+    g = synth.make_config("c2", scale=0.2, seed=4)
+    payload = synth.to_payload(g)
+    c0 = synth.counts(g)
+    plans = [capi.host_plan(payload, r, world) for r in range(world)]
+    assert plans[0][0].pose_begin == 0 and plans[-1][0].pose_end == c0["P"]
+    for a, b in zip(plans[:-1], plans[1:]):
+        assert a[0].pose_end == b[0].pose_begin
+    assert sum(p[0].n_lmedge_local for p in plans) == c0["El"]      # every LM edge linearised exactly once
+    assert sum(p[0].n_odom_local for p in plans) == c0["Eo"]        # every ODOM edge owned exactly once
+    assert len({p[3] for p in plans}) == 1                           # cuts + boundary list agree on all ranks
+    assert len({p[2] for p in plans}) == 1
+    if world == 1:
+        assert plans[0][1] == 0 and plans[0][2] == 0
+    else:
+        # a chain cut at world-1 places: 2 boundary poses per cut, each interior rank has 2 ghosts
+        assert plans[0][2] == 2 * (world - 1)
+        assert [p[1] for p in plans] == [1] + [2] * (world - 2) + [1]
+        work = np.array([p[0].n_lmedge_local for p in plans], float)
+        assert work.max() / work.mean() < 1.15                       # balanced by edge count
+
+
+def test_gloo_world2_unique_id_and_plan(tmp_path):
+    script = tmp_path / "w2.py"
+    script.write_text(f'''
+import os, sys
+sys.path.insert(0, {ROOT!r})
+import torch.distributed as dist
+from toyslam_b200 import synth, capi, dist as tdist
+dist.init_process_group("gloo")
+rank, world = dist.get_rank(), dist.get_world_size()
+uid = tdist.broadcast_unique_id(rank)
+payload = synth.to_payload(synth.make_config("c2", scale=0.05, seed=1))
+c, ng, nb, h = capi.host_plan(payload, rank, world)
+out = [None] * world
+dist.all_gather_object(out, (uid.hex(), c.pose_begin, c.pose_end, c.n_lmedge_local, ng, nb, h))
+if rank == 0:
+    assert out[0][0] == out[1][0] and len(uid) == 128 and any(uid)
+    assert out[0][2] == out[1][1] and out[0][1] == 0 and out[1][2] == c.n_pose
+    assert out[0][3] + out[1][3] == c.n_lmedge and out[0][5] == out[1][5] == 2 and out[0][6] == out[1][6]
+    print("W2 OK")
+dist.destroy_process_group()
+''')
+    env = dict(os.environ, MASTER_ADDR="127.0.0.1")
+    r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2",
+                        "--master-addr", "127.0.0.1", "--master-port", "29731", str(script)],
+                       capture_output=True, text=True, timeout=240, env=env)
+    assert r.returncode == 0 and "W2 OK" in r.stdout, r.stdout[-2000:] + r.stderr[-2000:]

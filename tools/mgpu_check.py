@@ -1,0 +1,47 @@
+#!/usr/bin/env python
+"""Run under torchrun (one rank per GPU): N-rank result against the 1-rank result and the CPU oracle.
+  torchrun --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 tools/mgpu_check.py [--workload c2 --scale 0.2]"""
+import argparse, os, sys
+import numpy as np
+sys.path.insert(0, os.path.join(os.path.dirname(os.path.abspath(__file__)), ".."))
+import torch
+import torch.distributed as dist
+from toyslam_b200 import synth, dist as tdist
+from toyslam_b200.capi import GraphOptimizerGpu
+
+ap = argparse.ArgumentParser()
+ap.add_argument("--workload", default="c2"); ap.add_argument("--scale", type=float, default=0.2)
+ap.add_argument("--iters", type=int, default=6); ap.add_argument("--oracle", type=int, default=1)
+a = ap.parse_args()
+rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
+torch.cuda.set_device(local)
+dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+uid = tdist.broadcast_unique_id(rank)
+payload = synth.to_payload(synth.make_config(a.workload, scale=a.scale, seed=11))
+g = GraphOptimizerGpu(iterations=a.iters, device=local, rank=rank, world=world, nccl_id=uid, pcg_tol=1e-13,
+                      pcg_max_iters=20000, enable_exits=False)
+c = g.load_wire(payload)
+rep, per = g.optimize()
+chi = np.array([p.chi2 for p in per]); ps, ls = g.state()
+ok = True
+if rank == 0:
+    g1 = GraphOptimizerGpu(iterations=a.iters, device=local, pcg_tol=1e-13, pcg_max_iters=20000, enable_exits=False)
+    g1.load_wire(payload); rep1, per1 = g1.optimize()
+    chi1 = np.array([p.chi2 for p in per1]); ps1, ls1 = g1.state()
+    d = ps - ps1; d[:, 2] = np.arctan2(np.sin(d[:, 2]), np.cos(d[:, 2]))
+    e_chi = float(np.max(np.abs(chi - chi1) / chi1)); e_st = float(max(np.abs(d).max(), np.abs(ls - ls1).max()))
+    print(f"world={world} poses {c.n_pose} edges {c.n_odom + c.n_lmedge}: rank0 owns [{c.pose_begin},{c.pose_end}) "
+          f"pcg {rep.pcg_iters_total} vs {rep1.pcg_iters_total}; N-vs-1 chi2 rel {e_chi:.2e} state abs {e_st:.2e}; "
+          f"ms {rep.ms_total:.1f} vs {rep1.ms_total:.1f}")
+    ok = e_chi < 1e-8 and e_st < 1e-8
+    if a.oracle:
+        from oracle.oracle import OracleGraph
+        o = OracleGraph(payload); traj, _, _ = o.optimize_sparse(a.iters, False, 1e-13, 20000, 0)
+        ops, ols = o.state(); d = ps - ops; d[:, 2] = np.arctan2(np.sin(d[:, 2]), np.cos(d[:, 2]))
+        e2 = float(np.max(np.abs(chi - traj) / traj)); e3 = float(max(np.abs(d).max(), np.abs(ls - ols).max()))
+        print(f"N-vs-oracle chi2 rel {e2:.2e} state abs {e3:.2e}")
+        ok = ok and e2 < 1e-8 and e3 < 1e-8
+    print("MGPU OK" if ok else "MGPU FAIL")
+flag = torch.tensor([1 if ok else 0], device="cuda"); dist.broadcast(flag, 0)
+g.close(); dist.destroy_process_group()
+sys.exit(0 if flag.item() else 1)

@@ -17,7 +17,7 @@ import numpy as np
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libtoyslam_b200.so")
 
-SYMBOLS = ["tsb_create", "tsb_destroy", "tsb_last_error", "tsb_load_wire", "tsb_load_soa", "tsb_get_counts",
+SYMBOLS = ["tsb_nccl_unique_id", "tsb_create", "tsb_destroy", "tsb_last_error", "tsb_load_wire", "tsb_load_soa", "tsb_get_counts", "tsb_host_plan",
            "tsb_reset_state", "tsb_set_state", "tsb_linearize", "tsb_solve", "tsb_optimize", "tsb_read_ids",
            "tsb_read_state", "tsb_read_delta", "tsb_get_transfer_bytes", "tsb_read_system", "tsb_read_structure", "tsb_reply_size",
            "tsb_write_reply"]
@@ -58,6 +58,10 @@ _lib = None
 def lib():
     global _lib
     if _lib is None:
+        try:                      # load torch first when present so that one libnccl.so.2 serves both
+            import torch  # noqa: F401
+        except Exception:
+            pass
         if not os.path.exists(LIB_PATH):
             raise RuntimeError(f"{LIB_PATH} is missing: build it with `make -C toyslam_b200/csrc` "
                                "(or __graft_entry__.build()); there is no fallback path")
@@ -67,6 +71,24 @@ def lib():
         L.tsb_destroy.restype = None
         _lib = L
     return _lib
+
+
+def nccl_unique_id() -> bytes:
+    buf = C.create_string_buffer(128)
+    rc = lib().tsb_nccl_unique_id(buf)
+    if rc:
+        raise TsbError(rc, lib().tsb_last_error(None).decode())
+    return buf.raw
+
+
+def host_plan(payload: bytes, rank: int, world: int):
+    """CPU-only: counts of rank `rank`'s share, ghost / boundary pose counts and the rank-independent hash."""
+    c, g, b, h = Counts(), C.c_uint32(), C.c_uint32(), C.c_uint64()
+    rc = lib().tsb_host_plan(payload, C.c_uint32(len(payload)), C.c_int32(rank), C.c_int32(world), C.byref(c),
+                             C.byref(g), C.byref(b), C.byref(h))
+    if rc:
+        raise TsbError(rc, lib().tsb_last_error(None).decode())
+    return c, g.value, b.value, h.value
 
 
 def _p(a):
@@ -87,7 +109,8 @@ class GraphOptimizerGpu:
         self.L = lib()
         self.iterations = iterations
         self._id = nccl_id
-        cfg = Config(device, rank, world, C.cast(C.c_char_p(nccl_id), C.c_void_p) if nccl_id else None,
+        self._idbuf = C.create_string_buffer(nccl_id, 128) if nccl_id else None
+        cfg = Config(device, rank, world, C.cast(self._idbuf, C.c_void_p) if nccl_id else None,
                      pcg_tol, pcg_max_iters, int(enable_exits), int(verbose))
         h = C.c_void_p()
         rc = self.L.tsb_create(C.byref(cfg), C.byref(h))

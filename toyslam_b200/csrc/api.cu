@@ -4,6 +4,8 @@
 #include "../../include/toyslam_b200.h"
 #include "device_graph.h"
 
+#include <nccl.h>
+
 #include <cmath>
 #include <cstdio>
 #include <cstdlib>
@@ -31,6 +33,7 @@ struct tsb_ctx {
     uint32_t part_cap = 0;
     bool force_phased = false;                            // TSB_PCG_PHASED=1: one launch per PCG phase (the multi-GPU path)
     uint64_t h2d = 0, d2h = 0;                            // bytes copied since the last tsb_load_*
+    ncclComm_t comm = nullptr;                            // world > 1: one communicator, collectives on `stream`
 };
 
 namespace {
@@ -107,7 +110,12 @@ int upload_graph(tsb_ctx* c) {
     TRY(dalloc(c, d.minv, 6ull * d.nP)); TRY(dalloc(c, d.rhs, 3ull * d.nP));
     TRY(dalloc(c, d.x, 3ull * d.nP)); TRY(dalloc(c, d.r, 3ull * d.nP)); TRY(dalloc(c, d.z, 3ull * d.nP));
     TRY(dalloc(c, d.p, 3ull * nPG)); TRY(dalloc(c, d.sp, 3ull * d.nP));
-    TRY(dalloc(c, d.w_part, 2ull * d.nSlots)); TRY(dalloc(c, d.w_sum, 2ull * g.L + 64)); TRY(dalloc(c, d.dl, 2ull * g.L));
+    TRY(dalloc(c, d.w_part, 2ull * d.nSlots)); d.nBnd = (uint32_t)s.boundary.size();
+    TRY(dalloc(c, d.w_sum, 2ull * g.L + 3ull * d.nBnd + 8)); d.bnd = d.w_sum + 2ull * g.L;
+    { std::vector<uint32_t> bl(d.nBnd, 0xFFFFFFFFu);
+      for (size_t k = 0; k < s.own_bnd_slot.size(); ++k) bl[s.own_bnd_slot[k]] = s.own_bnd_pose[k];
+      TRY(upload(c, d.bnd_local, bl)); TRY(upload(c, d.ghost_bnd_slot, s.ghost_bnd_slot)); }
+    TRY(dalloc(c, d.dl, 2ull * g.L));
     c->part_cap = std::max<uint32_t>(d.nBlocks, (std::max(d.nP, g.L) + kThreads - 1) / kThreads) + 1;
     TRY(dalloc(c, d.part, c->part_cap)); TRY(dalloc(c, d.part2, c->part_cap));
     TRY(dalloc(c, d.scal, (size_t)S_COUNT)); TRY(dalloc(c, d.flags, (size_t)F_COUNT));
@@ -128,6 +136,14 @@ int upload_graph(tsb_ctx* c) {
     return TSB_OK;
 }
 
+// in-place sum over ranks on the compute stream; no-op for world == 1
+int allreduce(tsb_ctx* c, double* buf, size_t n) {
+    if (c->cfg.world <= 1 || n == 0) return TSB_OK;
+    const ncclResult_t r = ncclAllReduce(buf, buf, n, ncclDouble, ncclSum, c->comm, c->stream);
+    if (r != ncclSuccess) { c->err = std::string("ncclAllReduce: ") + ncclGetErrorString(r); return TSB_ENCCL; }
+    return TSB_OK;
+}
+
 int fetch_scalars(tsb_ctx* c) {
     CU(cudaMemcpyAsync(c->h_scal, c->d.scal, sizeof(double) * S_COUNT, cudaMemcpyDeviceToHost, c->stream));
     CU(cudaMemcpyAsync(c->h_flags, c->d.flags, sizeof(int) * F_COUNT, cudaMemcpyDeviceToHost, c->stream));
@@ -136,10 +152,15 @@ int fetch_scalars(tsb_ctx* c) {
     return TSB_OK;
 }
 
-void enqueue_linearize(tsb_ctx* c) {
+// K1 + K2.  world > 1: every rank linearises the LM edges of its poses; the per-landmark partial
+// (Hll, b_l) sums and chi2 are summed over ranks before the landmark blocks are inverted.
+int enqueue_linearize(tsb_ctx* c) {
     launch_linearize(c->d, c->stream);
     launch_lm_sum(c->d, c->stream);
+    TRY(allreduce(c, c->d.lm_sum, 5ull * c->g.L));
+    TRY(allreduce(c, c->d.scal + S_CHI2, 1));
     launch_lm_finalize(c->d, c->stream);
+    return TSB_OK;
 }
 
 // Schur preparation + PCG + landmark back-substitution; leaves delta in d.x / d.dl
@@ -160,16 +181,28 @@ int run_solve(tsb_ctx* c) {
         }
         return TSB_OK;
     }
+    // one launch per phase, collectives between the phases (the multi-GPU path; also TSB_PCG_PHASED=1)
     launch_pcg_init(d, c->stream);
+    TRY(allreduce(c, d.scal + S_RZ, 1));
+    launch_pcg_init_fix(d, c->stream);
     const int maxit = c->cfg.pcg_max_iters > 0 ? c->cfg.pcg_max_iters : 4000;
     const int batch = 16;
+    const size_t nx = 2ull * c->g.L + 3ull * d.nBnd;          // [w | boundary p] travels as one all-reduce
     for (int it = 0; it < maxit + batch; it += batch) {
         for (int b = 0; b < batch; ++b) {
-            launch_pcg_pass_a(d, 0, c->stream);
-            launch_pcg_mid(d, 0, c->stream);
+            launch_pcg_pass_a(d, 0, c->stream);                // p = z + beta p; slot partials of Hpl^T p
+            launch_pcg_mid(d, 1, c->stream);                   // w = sum of this rank's slot partials
+            launch_pack_boundary(d, d.p, c->stream);
+            TRY(allreduce(c, d.w_sum, nx));
+            launch_unpack_ghost(d, d.p, c->stream);
+            launch_pcg_hpp(d, c->stream);                      // sp = Hpp p + ODOM part (needs the ghost p)
             launch_pcg_pass_b(d, c->stream);
+            launch_pcg_psp(d, c->stream);
+            TRY(allreduce(c, d.scal + S_PSP, 1));
             launch_pcg_alpha(d, c->stream);
             launch_pcg_update(d, c->stream);
+            launch_pcg_rznew(d, c->stream);
+            TRY(allreduce(c, d.scal + S_RZNEW, 1));
             launch_pcg_beta(d, c->stream);
         }
         CU(cudaMemcpyAsync(c->h_flags, d.flags, sizeof(int) * F_COUNT, cudaMemcpyDeviceToHost, c->stream));
@@ -179,7 +212,18 @@ int run_solve(tsb_ctx* c) {
     }
     launch_pcg_pass_a(d, 1, c->stream);
     launch_pcg_mid(d, 1, c->stream);
+    TRY(allreduce(c, d.w_sum, 2ull * c->g.L));
     launch_backsub(d, c->stream);
+    return TSB_OK;
+}
+
+// K5: damped update of poses and landmarks; ghost poses follow their owners
+int enqueue_update(tsb_ctx* c) {
+    const Dev& d = c->d;
+    launch_pack_boundary(d, d.x, c->stream);
+    TRY(allreduce(c, d.bnd, 3ull * d.nBnd));
+    launch_update_state(d, 0.2, c->stream);                    // OptimizerCpu.h:159-165
+    TRY(allreduce(c, d.scal + S_DELTA2, 1));
     return TSB_OK;
 }
 
@@ -197,7 +241,7 @@ int tsb_create(const tsb_config* cfg, tsb_ctx** out) {
         cudaGetLastError();
         g_create_error = "no CUDA device: the PIPELINE=gpu path has no CPU fallback"; return TSB_ECUDA; }
     if (cfg->device < 0 || cfg->device >= ndev) { g_create_error = "tsb_create: bad device ordinal"; return TSB_EINVAL; }
-    if (cfg->world > 1) { g_create_error = "tsb_create: world > 1 not available in this build"; return TSB_EINVAL; }
+    if (cfg->world > 1 && (!cfg->nccl_id || cfg->rank < 0 || cfg->rank >= cfg->world)) { g_create_error = "tsb_create: world > 1 needs nccl_id and 0 <= rank < world"; return TSB_EINVAL; }
     tsb_ctx* c = new tsb_ctx();
     c->cfg = *cfg; if (c->cfg.world < 1) { c->cfg.world = 1; c->cfg.rank = 0; }
     { const char* e = std::getenv("TSB_PCG_PHASED"); c->force_phased = e && e[0] == '1'; }
@@ -208,7 +252,21 @@ int tsb_create(const tsb_config* cfg, tsb_ctx** out) {
     for (auto& ev : c->ev) if ((e = cudaEventCreate(&ev)) != cudaSuccess) return fail("cudaEventCreate", e);
     if ((e = cudaMallocHost((void**)&c->h_scal, sizeof(double) * S_COUNT)) != cudaSuccess) return fail("cudaMallocHost", e);
     if ((e = cudaMallocHost((void**)&c->h_flags, sizeof(int) * F_COUNT)) != cudaSuccess) return fail("cudaMallocHost", e);
+    if (c->cfg.world > 1) {
+        ncclUniqueId id; std::memcpy(&id, cfg->nccl_id, sizeof(id));
+        const ncclResult_t r = ncclCommInitRank(&c->comm, c->cfg.world, id, c->cfg.rank);
+        if (r != ncclSuccess) { g_create_error = std::string("ncclCommInitRank: ") + ncclGetErrorString(r); delete c; return TSB_ENCCL; }
+    }
     *out = c;
+    return TSB_OK;
+}
+
+int tsb_nccl_unique_id(void* out128) {
+    static_assert(sizeof(ncclUniqueId) == 128, "ncclUniqueId size");
+    if (!out128) return TSB_EINVAL;
+    ncclUniqueId id;
+    if (ncclGetUniqueId(&id) != ncclSuccess) { g_create_error = "ncclGetUniqueId failed"; return TSB_ENCCL; }
+    std::memcpy(out128, &id, sizeof(id));
     return TSB_OK;
 }
 
@@ -216,6 +274,7 @@ void tsb_destroy(tsb_ctx* c) {
     if (!c) return;
     cudaSetDevice(c->cfg.device);
     free_graph(c);
+    if (c->comm) ncclCommDestroy(c->comm);
     if (c->h_scal) cudaFreeHost(c->h_scal);
     if (c->h_flags) cudaFreeHost(c->h_flags);
     for (auto& ev : c->ev) if (ev) cudaEventDestroy(ev);
@@ -258,6 +317,30 @@ int tsb_load_soa(tsb_ctx* c, const tsb_graph_soa* s) {
     return tsb_load_wire(c, buf.data(), (uint32_t)buf.size());
 }
 
+// Host-only: parse a payload and build rank `rank`'s assembly structure without touching a GPU.
+// Lets the partition logic (pose cuts, edge ownership, ghosts, boundary list) be tested on CPU.
+int tsb_host_plan(const void* payload, uint32_t nbytes, int32_t rank, int32_t world, tsb_counts* o,
+                  uint32_t* n_ghost, uint32_t* n_boundary, uint64_t* structure_hash) {
+    if (!payload || !o || world < 1 || rank < 0 || rank >= world) return TSB_EINVAL;
+    HostGraph g; Structure st; std::string err;
+    if (!parse_wire((const uint8_t*)payload, nbytes, g, err)) { g_create_error = err; return TSB_EPARSE; }
+    build_structure(g, (uint32_t)rank, (uint32_t)world, st);
+    std::memset(o, 0, sizeof(*o));
+    o->n_pose = g.P; o->n_lm = g.L; o->n_odom = g.Eo; o->n_lmedge = g.El; o->n_fixed = (uint32_t)g.fixed.size();
+    o->dim = 3 * g.P + 2 * g.L; o->pose_begin = st.pose_begin; o->pose_end = st.pose_end;
+    o->n_lmedge_local = (uint32_t)st.lm_perm.size(); o->n_odom_local = st.n_od_owned;
+    o->n_chunks = (uint32_t)st.chunks.size(); o->n_blocks = (uint32_t)st.blk_chunk_ptr.size() - 1; o->n_slots = (uint32_t)st.slot_lm.size();
+    if (n_ghost) *n_ghost = st.nG;
+    if (n_boundary) *n_boundary = (uint32_t)st.boundary.size();
+    if (structure_hash) {            // FNV-1a over the rank-independent parts (cuts, boundary list): must agree on all ranks
+        uint64_t h = 1469598103934665603ull;
+        auto mix = [&](const std::vector<uint32_t>& v) { for (uint32_t x : v) { h ^= x; h *= 1099511628211ull; } };
+        mix(st.cuts); mix(st.boundary);
+        *structure_hash = h;
+    }
+    return TSB_OK;
+}
+
 int tsb_get_counts(const tsb_ctx* c, tsb_counts* o) {
     if (!c || !o || !c->loaded) return TSB_EINVAL;
     o->n_pose = c->g.P; o->n_lm = c->g.L; o->n_odom = c->g.Eo; o->n_lmedge = c->g.El; o->n_fixed = (uint32_t)c->g.fixed.size();
@@ -295,7 +378,7 @@ int tsb_linearize(tsb_ctx* c, tsb_iter_stats* st) {
     if (!c || !c->loaded) return TSB_EINVAL;
     CU(cudaSetDevice(c->cfg.device));
     CU(cudaEventRecord(c->ev[0], c->stream));
-    enqueue_linearize(c);
+    TRY(enqueue_linearize(c));
     CU(cudaEventRecord(c->ev[1], c->stream));
     TRY(fetch_scalars(c));
     CU(cudaGetLastError());
@@ -329,7 +412,7 @@ int tsb_optimize(tsb_ctx* c, uint32_t iterations, tsb_report* rep, tsb_iter_stat
     CU(cudaEventRecord(c->ev[3], c->stream));
     for (uint32_t it = 0; it < iterations; ++it) {
         CU(cudaEventRecord(c->ev[0], c->stream));
-        enqueue_linearize(c);
+        TRY(enqueue_linearize(c));
         CU(cudaEventRecord(c->ev[1], c->stream));
         if (exits) {                                     // OptimizerCpu.h:140-153 needs err before the solve
             TRY(fetch_scalars(c)); err = c->h_scal[S_CHI2];
@@ -345,7 +428,7 @@ int tsb_optimize(tsb_ctx* c, uint32_t iterations, tsb_report* rep, tsb_iter_stat
         }
         TRY(run_solve(c));
         CU(cudaEventRecord(c->ev[2], c->stream));
-        launch_update_state(c->d, 0.2, c->stream);       // OptimizerCpu.h:159-165
+        TRY(enqueue_update(c));
         TRY(fetch_scalars(c));
         CU(cudaGetLastError());
         err = c->h_scal[S_CHI2];
@@ -392,7 +475,13 @@ int tsb_read_ids(const tsb_ctx* c, uint32_t* pose_id, uint32_t* lm_id) {
 int tsb_read_state(tsb_ctx* c, double* pose_xyt, double* lm_xy) {
     if (!c || !c->loaded) return TSB_EINVAL;
     CU(cudaSetDevice(c->cfg.device));
-    if (pose_xyt) {
+    if (pose_xyt && c->cfg.world > 1) {
+        // every rank returns the full state: local ranges summed into a zeroed 3P buffer (sum with zeros = gather)
+        CU(cudaMemsetAsync(c->tmp_xyt, 0, 24ull * c->g.P, c->stream));
+        launch_read_pose(c->d.pose, c->d.nP, c->tmp_xyt + 3ull * c->st.pose_begin, c->stream);
+        TRY(allreduce(c, c->tmp_xyt, 3ull * c->g.P));
+        if (c->g.P) CU(cudaMemcpyAsync(pose_xyt, c->tmp_xyt, 24ull * c->g.P, cudaMemcpyDeviceToHost, c->stream));
+    } else if (pose_xyt) {
         launch_read_pose(c->d.pose, c->d.nP, c->tmp_xyt, c->stream);
         if (c->d.nP) CU(cudaMemcpyAsync(pose_xyt + 3ull * c->st.pose_begin, c->tmp_xyt, 24ull * c->d.nP, cudaMemcpyDeviceToHost, c->stream));
     }

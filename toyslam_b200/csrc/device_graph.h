@@ -11,7 +11,7 @@ constexpr int kStageRows = 9;          // values staged per LM edge
 constexpr int kStageStride = kChunkEdges + 1;   // odd stride in doubles: rows land in different banks
 
 // scalars kept on the device (index into Dev::scal)
-enum Scal { S_CHI2 = 0, S_RZ0, S_RZ, S_PSP, S_ALPHA, S_BETA, S_DELTA2, S_DELTA2L, S_TOL2, S_PSP_EXTRA, S_COUNT };
+enum Scal { S_CHI2 = 0, S_RZ0, S_RZ, S_PSP, S_ALPHA, S_BETA, S_DELTA2, S_DELTA2L, S_TOL2, S_RZNEW, S_COUNT };
 // integer flags (index into Dev::flags)
 enum Flag { F_DONE = 0, F_ITERS, F_MAXIT, F_COUNT };
 
@@ -60,6 +60,11 @@ struct Dev {
     double* part2;              // second set (chi2 of ODOM etc.)
     double* scal;               // S_COUNT
     int* flags;                 // F_COUNT
+    // world > 1: boundary poses exchanged through the tail of the w_sum all-reduce buffer
+    uint32_t nBnd;
+    const uint32_t* bnd_local;  // per boundary slot: local pose index, or 0xFFFFFFFF if owned elsewhere
+    const uint32_t* ghost_bnd_slot;   // per ghost pose: boundary slot
+    double* bnd;                // 3 per boundary slot; == w_sum + 2 L (one contiguous all-reduce)
     long long* dbg;             // optional: 8 phase-cycle counters of the persistent PCG kernel (TSB_PCG_TIMING=1)
 };
 
@@ -73,11 +78,17 @@ void launch_pcg_init(const Dev& d, cudaStream_t s);
 void launch_pcg_pass_a(const Dev& d, int mode, cudaStream_t s); // mode 0: v = p (with p = z + beta p fused), 1: v = x
 void launch_pcg_mid(const Dev& d, int mode, cudaStream_t s);   // w = sum of slot partials; mode 0 also sp = Hpp p + ODOM part
 void launch_pcg_pass_b(const Dev& d, cudaStream_t s);
+void launch_pcg_hpp(const Dev& d, cudaStream_t s);              // sp = Hpp p + ODOM part (pose-parallel)
+void launch_pack_boundary(const Dev& d, const double* vec, cudaStream_t s);   // own boundary entries of vec -> d.bnd, zeros elsewhere
+void launch_unpack_ghost(const Dev& d, double* vec, cudaStream_t s);          // d.bnd -> ghost entries of vec
+void launch_pcg_psp(const Dev& d, cudaStream_t s);              // local p'Sp -> scal[S_PSP]
 void launch_pcg_alpha(const Dev& d, cudaStream_t s);
 void launch_pcg_update(const Dev& d, cudaStream_t s);
+void launch_pcg_rznew(const Dev& d, cudaStream_t s);            // local r'z -> scal[S_RZNEW]
 void launch_pcg_beta(const Dev& d, cudaStream_t s);
+void launch_pcg_init_fix(const Dev& d, cudaStream_t s);          // rz0 / done flag from the all-reduced scal[S_RZ]
 void launch_backsub(const Dev& d, cudaStream_t s);              // delta_l = Hll^-1 (b_l - Hpl^T delta_p)
-void launch_update_state(const Dev& d, double step, cudaStream_t s);   // K5 + ||delta||^2
+void launch_update_state(const Dev& d, double step, cudaStream_t s);   // K5 + ||delta||^2 (ghost poses take delta from d.bnd)
 void launch_init_pose(const double* xyt, uint32_t n, double4* out, cudaStream_t s);
 void launch_read_pose(const double4* pose, uint32_t n, double* xyt, cudaStream_t s);
 size_t linearize_smem_bytes();

@@ -42,6 +42,12 @@ struct Structure {
     uint32_t pose_begin = 0, pose_end = 0;   // canonical pose range owned by this rank
     uint32_t nP = 0, nG = 0;                 // local poses, ghost poses (ODOM neighbours owned elsewhere)
     std::vector<uint32_t> ghost_pose;        // canonical index of each ghost pose
+    // world > 1: poses that are a ghost on some rank ("boundary poses"), identical list on every rank.
+    // Their vector entries travel in the tail of the per-iteration all-reduce (sum with zeros = gather).
+    std::vector<uint32_t> cuts;              // world + 1 pose cut points
+    std::vector<uint32_t> boundary;          // canonical pose index, ascending
+    std::vector<uint32_t> own_bnd_slot, own_bnd_pose;   // slots of `boundary` owned here and their local pose index
+    std::vector<uint32_t> ghost_bnd_slot;    // per ghost pose: its slot in `boundary`
     // LM edges of local poses, assembly order = sorted by (pose, landmark, request index)
     std::vector<uint32_t> le_local;          // request-order indices (into HostGraph::le_*) of the local LM edges
     std::vector<uint32_t> lm_perm;           // assembly k -> index into le_local

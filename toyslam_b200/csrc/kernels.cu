@@ -585,11 +585,34 @@ __global__ void __launch_bounds__(kThreads) k_pcg_pass_b(const Dev d) {
     const double t = unit_pass_b(d, blockIdx.x, sm);
     if (threadIdx.x == 0) d.part[blockIdx.x] = t;
 }
-__global__ void k_pcg_alpha(const Dev d) {
+__global__ void k_pcg_psp(const Dev d) {          // local part of p'Sp (all-reduced over ranks before k_pcg_alpha)
     if (d.flags[F_DONE]) return;
     __shared__ double red[32];
     const double psp = reduce_all(d.part, d.nBlocks, red);
-    if (threadIdx.x == 0) { d.scal[S_PSP] = psp; d.scal[S_ALPHA] = d.scal[S_RZ] / psp; }
+    if (threadIdx.x == 0) d.scal[S_PSP] = psp;
+}
+__global__ void k_pcg_alpha(const Dev d) {
+    if (d.flags[F_DONE]) return;
+    d.scal[S_ALPHA] = d.scal[S_RZ] / d.scal[S_PSP];
+}
+__global__ void k_pcg_hpp(const Dev d) {
+    if (d.flags[F_DONE]) return;
+    const uint32_t p = blockIdx.x * blockDim.x + threadIdx.x;
+    if (p < d.nP) hpp_apply(d, p, d.sp + 3ull * p);
+}
+__global__ void k_pack_boundary(const Dev d, const double* vec) {
+    const uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= d.nBnd) return;
+    const uint32_t lp = d.bnd_local[k];
+#pragma unroll
+    for (int q = 0; q < 3; ++q) d.bnd[3ull * k + q] = lp != 0xFFFFFFFFu ? vec[3ull * lp + q] : 0.0;
+}
+__global__ void k_unpack_ghost(const Dev d, double* vec) {
+    const uint32_t g = blockIdx.x * blockDim.x + threadIdx.x;
+    if (g >= d.nG) return;
+    const uint32_t k = d.ghost_bnd_slot[g];
+#pragma unroll
+    for (int q = 0; q < 3; ++q) vec[3ull * (d.nP + g) + q] = d.bnd[3ull * k + q];
 }
 __global__ void k_pcg_update(const Dev d) {
     if (d.flags[F_DONE]) return;
@@ -598,15 +621,23 @@ __global__ void k_pcg_update(const Dev d) {
     const double t = block_sum(i < d.nP ? pose_update(d, i, d.scal[S_ALPHA]) : 0.0, red);
     if (threadIdx.x == 0) d.part[blockIdx.x] = t;
 }
-__global__ void k_pcg_beta(const Dev d, uint32_t nparts) {
+__global__ void k_pcg_rznew(const Dev d, uint32_t nparts) {   // local part of r'z (all-reduced over ranks before k_pcg_beta)
     if (d.flags[F_DONE]) return;
     __shared__ double red[32];
     const double rz_new = reduce_all(d.part, nparts, red);
-    if (threadIdx.x == 0) {
-        d.scal[S_BETA] = rz_new / d.scal[S_RZ]; d.scal[S_RZ] = rz_new;
-        const int it = d.flags[F_ITERS] + 1; d.flags[F_ITERS] = it;
-        if (!(rz_new > d.scal[S_TOL2] * d.scal[S_RZ0]) || it >= d.flags[F_MAXIT]) d.flags[F_DONE] = 1;
-    }
+    if (threadIdx.x == 0) d.scal[S_RZNEW] = rz_new;
+}
+__global__ void k_pcg_beta(const Dev d) {
+    if (d.flags[F_DONE]) return;
+    const double rz_new = d.scal[S_RZNEW];
+    d.scal[S_BETA] = rz_new / d.scal[S_RZ]; d.scal[S_RZ] = rz_new;
+    const int it = d.flags[F_ITERS] + 1; d.flags[F_ITERS] = it;
+    if (!(rz_new > d.scal[S_TOL2] * d.scal[S_RZ0]) || it >= d.flags[F_MAXIT]) d.flags[F_DONE] = 1;
+}
+// after the all-reduce of scal[S_RZ] at the start of a phased solve
+__global__ void k_pcg_init_fix(const Dev d) {
+    const double rz = d.scal[S_RZ];
+    d.scal[S_RZ0] = rz; d.flags[F_DONE] = (rz > 0) ? 0 : 1;
 }
 
 // ---- persistent cooperative PCG: the whole solve in one launch (world == 1) ------------------------------
@@ -713,6 +744,14 @@ __global__ void k_update_state(const Dev d, double step) {
         double2 l = d.lm[i]; l.x += d0 * step; l.y += d1 * step; d.lm[i] = l;
         nl2 = d0 * d0 + d1 * d1;
     }
+    if (i < d.nG) {        // ghost copy of a pose owned elsewhere: same delta, same arithmetic, same bits as its owner
+        const double* dd = d.bnd + 3ull * d.ghost_bnd_slot[i];
+        double4 ps = d.pose[d.nP + i];
+        const double th = atan2(ps.w, ps.z) + dd[2] * step;
+        double s, c; sincos(th, &s, &c);
+        ps.x += dd[0] * step; ps.y += dd[1] * step; ps.z = c; ps.w = s;
+        d.pose[d.nP + i] = ps;
+    }
     const double t = block_sum(np2, red);
     const double u = block_sum(nl2, red);
     if (threadIdx.x == 0) { d.part[blockIdx.x] = t; d.part2[blockIdx.x] = u; }
@@ -815,17 +854,30 @@ void launch_pcg_pass_b(const Dev& d, cudaStream_t s) {
     set_attrs();
     if (d.nBlocks) { k_pcg_pass_b<<<d.nBlocks, kThreads, LayB::bytes, s>>>(d); ++g_launches; }
 }
-void launch_pcg_alpha(const Dev& d, cudaStream_t s) { k_pcg_alpha<<<1, 1024, 0, s>>>(d); ++g_launches; }
+void launch_pcg_hpp(const Dev& d, cudaStream_t s) {
+    if (d.nP) { k_pcg_hpp<<<cdiv(d.nP, kThreads), kThreads, 0, s>>>(d); ++g_launches; }
+}
+void launch_pack_boundary(const Dev& d, const double* vec, cudaStream_t s) {
+    if (d.nBnd) { k_pack_boundary<<<cdiv(d.nBnd, kThreads), kThreads, 0, s>>>(d, vec); ++g_launches; }
+}
+void launch_unpack_ghost(const Dev& d, double* vec, cudaStream_t s) {
+    if (d.nG) { k_unpack_ghost<<<cdiv(d.nG, kThreads), kThreads, 0, s>>>(d, vec); ++g_launches; }
+}
+void launch_pcg_psp(const Dev& d, cudaStream_t s) { k_pcg_psp<<<1, 1024, 0, s>>>(d); ++g_launches; }
+void launch_pcg_alpha(const Dev& d, cudaStream_t s) { k_pcg_alpha<<<1, 1, 0, s>>>(d); ++g_launches; }
 void launch_pcg_update(const Dev& d, cudaStream_t s) {
     const uint32_t nb = cdiv(d.nP, kThreads);
     if (nb) { k_pcg_update<<<nb, kThreads, 0, s>>>(d); ++g_launches; }
 }
-void launch_pcg_beta(const Dev& d, cudaStream_t s) { k_pcg_beta<<<1, 1024, 0, s>>>(d, cdiv(d.nP, kThreads)); ++g_launches; }
+void launch_pcg_rznew(const Dev& d, cudaStream_t s) { k_pcg_rznew<<<1, 1024, 0, s>>>(d, cdiv(d.nP, kThreads)); ++g_launches; }
+void launch_pcg_beta(const Dev& d, cudaStream_t s) { k_pcg_beta<<<1, 1, 0, s>>>(d); ++g_launches; }
+void launch_pcg_init_fix(const Dev& d, cudaStream_t s) { k_pcg_init_fix<<<1, 1, 0, s>>>(d); ++g_launches; }
 void launch_backsub(const Dev& d, cudaStream_t s) {
     if (d.L) { k_backsub<<<cdiv(d.L, kThreads), kThreads, 0, s>>>(d); ++g_launches; }
 }
 void launch_update_state(const Dev& d, double step, cudaStream_t s) {
-    const uint32_t nb = cdiv(d.nP > d.L ? d.nP : d.L, kThreads);
+    uint32_t nmax = d.nP > d.L ? d.nP : d.L; if (d.nG > nmax) nmax = d.nG;
+    const uint32_t nb = cdiv(nmax, kThreads);
     if (!nb) return;
     k_update_state<<<nb, kThreads, 0, s>>>(d, step); ++g_launches;
     k_reduce_to<<<1, 1024, 0, s>>>(d.part, nb, d.scal + S_DELTA2); ++g_launches;

@@ -18,19 +18,19 @@ void build_structure(const HostGraph& g, uint32_t rank, uint32_t world, Structur
     // ---- pose partition: contiguous ranges balanced by edge work --------------------------------
     std::vector<uint32_t> deg(P + 1, 0);
     for (uint32_t e = 0; e < g.El; ++e) deg[g.le_i[e]]++;
-    if (world <= 1) { s.pose_begin = 0; s.pose_end = P; }
+    s.cuts.assign(world < 1 ? 2 : world + 1, 0);
+    if (world <= 1) { s.pose_begin = 0; s.pose_end = P; s.cuts = {0, P}; }
     else {
         std::vector<uint64_t> wsum(P + 1, 0);
         std::vector<uint32_t> odeg(P, 0);
         for (uint32_t e = 0; e < g.Eo; ++e) odeg[g.od_i[e]]++;
         for (uint32_t p = 0; p < P; ++p) wsum[p + 1] = wsum[p] + deg[p] + 2ull * odeg[p] + 1;
-        auto cut = [&](uint32_t r) -> uint32_t {
-            if (r == 0) return 0;
-            if (r >= world) return P;
-            const uint64_t target = wsum[P] * r / world;
-            return (uint32_t)(std::lower_bound(wsum.begin(), wsum.end(), target) - wsum.begin());
-        };
-        s.pose_begin = cut(rank); s.pose_end = cut(rank + 1);
+        for (uint32_t r = 0; r <= world; ++r) {
+            if (r == 0) s.cuts[r] = 0;
+            else if (r == world) s.cuts[r] = P;
+            else s.cuts[r] = (uint32_t)(std::lower_bound(wsum.begin(), wsum.end(), wsum[P] * r / world) - wsum.begin());
+        }
+        s.pose_begin = s.cuts[rank]; s.pose_end = s.cuts[rank + 1];
     }
     const uint32_t pb = s.pose_begin, pe = s.pose_end, nP = pe - pb;
     s.nP = nP;
@@ -137,6 +137,18 @@ void build_structure(const HostGraph& g, uint32_t rank, uint32_t world, Structur
     s.od_in_edge.resize(s.od_in_ptr[nP]);
     { std::vector<uint32_t> c2(s.od_in_ptr.begin(), s.od_in_ptr.end() - 1);
       for (uint32_t k = 0; k < nO; ++k) if (s.od_b[k] < nP) s.od_in_edge[c2[s.od_b[k]]++] = k; }
+    // ---- boundary poses (same list on every rank) ---------------------------------------------------
+    if (world > 1) {
+        auto owner = [&](uint32_t p) { return (uint32_t)(std::upper_bound(s.cuts.begin(), s.cuts.end(), p) - s.cuts.begin()) - 1; };
+        for (uint32_t e = 0; e < g.Eo; ++e)
+            if (owner(g.od_i[e]) != owner(g.od_j[e])) { s.boundary.push_back(g.od_i[e]); s.boundary.push_back(g.od_j[e]); }
+        std::sort(s.boundary.begin(), s.boundary.end());
+        s.boundary.erase(std::unique(s.boundary.begin(), s.boundary.end()), s.boundary.end());
+        for (uint32_t k = 0; k < s.boundary.size(); ++k)
+            if (local(s.boundary[k])) { s.own_bnd_slot.push_back(k); s.own_bnd_pose.push_back(s.boundary[k] - pb); }
+        for (uint32_t gp : s.ghost_pose)
+            s.ghost_bnd_slot.push_back((uint32_t)(std::lower_bound(s.boundary.begin(), s.boundary.end(), gp) - s.boundary.begin()));
+    }
     // ---- fixed vertices ---------------------------------------------------------------------------
     s.fixed_pose_count.assign(nP, 0); s.fixed_lm_count.assign(L, 0);
     for (uint32_t v : g.fixed) {
