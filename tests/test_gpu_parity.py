@@ -217,3 +217,44 @@ def test_two_ranks_match_one_rank(gpu):
                         "127.0.0.1", "--master-port", "29741", os.path.join(ROOT, "tools", "mgpu_check.py")],
                        capture_output=True, text=True, timeout=600)
     assert r.returncode == 0 and "MGPU OK" in r.stdout, r.stdout[-3000:] + r.stderr[-3000:]
+
+
+def test_graph_optimizer_server_end_to_end(gpu):
+    """`graph_optimizer 127.0.0.1 PORT 50 gpu cuda` serves the reference client's request for the default
+    simulation (C1) over the reference's framing; the reply matches the oracle's `cpu eigen` result."""
+    import os, socket, subprocess, time
+    from conftest import ROOT
+    from oracle.oracle import OracleGraph
+    from toyslam_b200 import wire
+    exe = os.path.join(ROOT, "toyslam_b200", "graph_optimizer")
+    assert os.path.exists(exe), "build it with make -C toyslam_b200/csrc all"
+    payload = load_golden("c1")["request"].tobytes()
+    port = 18000 + os.getpid() % 2000
+    srv = subprocess.Popen([exe, "127.0.0.1", str(port), "50", "gpu", "cuda"], stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
+    try:
+        s = None
+        for _ in range(150):
+            try:
+                s = socket.create_connection(("127.0.0.1", port), timeout=1); break
+            except OSError:
+                time.sleep(0.2)
+        assert s is not None, "server did not come up"
+        s.settimeout(120)
+        replies = []
+        for _ in range(2):                                   # the connection stays open for the next request
+            s.sendall(wire.frame(payload))
+            n = int(np.frombuffer(s.recv(4, socket.MSG_WAITALL), "<u4")[0])
+            buf = b""
+            while len(buf) < n:
+                buf += s.recv(n - len(buf))
+            replies.append(buf)
+        s.close()
+    finally:
+        srv.terminate(); out = srv.communicate(timeout=10)[0]
+    assert replies[0] == replies[1]
+    assert "Plateau: NO MORE OPT" in out and "Summary() error" in out      # the reference's stdout lines
+    o = OracleGraph(payload); o.optimize_dense(50, True)
+    a, b = wire.decode_reply(replies[0]), wire.decode_reply(o.reply())
+    assert set(a["vertices"]) == set(b["vertices"]) and len(a["edges"]) == len(b["edges"])
+    for vid, (t, v) in a["vertices"].items():
+        assert np.allclose(v, b["vertices"][vid][1], rtol=0, atol=2e-6)
