@@ -7,7 +7,7 @@
 // image, and the transport is outside the accelerated path.
 //
 // Only the PIPELINE=gpu branch is shipped: `cpu eigen` is the reference's own Eigen pipeline, which this
-// repository restates only as a test oracle, never as product code.
+// repository restates only as test infrastructure (the checker), never as product code.
 #include <arpa/inet.h>
 #include <netdb.h>
 #include <netinet/in.h>
