@@ -191,6 +191,28 @@ def test_full_size_c2_properties(gpu):
     assert np.max(np.abs(chi - traj) / traj) < CHI2_TOL
 
 
+@pytest.mark.parametrize("case", ["g_small", "c3_small", "c5_small"])
+def test_streaming_linearize_is_bit_identical(gpu, monkeypatch, case):
+    """HBM-sized graphs take the TMA-streamed persistent linearize kernel; forced on small graphs here it must
+    reproduce the one-unit-per-block kernel bit for bit (same device functions, same summation orders)."""
+    from toyslam_b200 import synth
+    if case == "g_small":
+        payload = load_golden("g_small")["request"].tobytes()
+    else:
+        payload = synth.to_payload(synth.make_config(case[:2], scale=0.04, seed=5))
+    out = []
+    for env in ({"TSB_NO_STREAM": "1"}, {"TSB_STREAM_MIN_UNITS": "1"}):
+        monkeypatch.delenv("TSB_NO_STREAM", raising=False); monkeypatch.delenv("TSB_STREAM_MIN_UNITS", raising=False)
+        for k, v in env.items():
+            monkeypatch.setenv(k, v)
+        g = gpu(iterations=1); g.load_wire(payload)
+        st = g.linearize()
+        out.append((st.chi2, g.system()))
+    assert abs(out[0][0] - out[1][0]) <= 1e-12 * abs(out[0][0])
+    for k in out[0][1]:
+        assert np.array_equal(out[0][1][k], out[1][1][k]), k
+
+
 def test_phased_pcg_path_matches_persistent(gpu, monkeypatch):
     """world == 1 normally runs the persistent cooperative PCG kernel; the one-launch-per-phase path
     (used when collectives sit between the phases) must give the same answer."""

@@ -23,4 +23,4 @@ for _ in range(a.lin):
 if a.pcg:
     st = g.solve(); print(f"solve {st.ms_solve:.3f} ms pcg_iters {st.pcg_iters} rel {st.pcg_rel_residual:.2e} -> {st.ms_solve / max(st.pcg_iters, 1) * 1e3:.1f} us/iter")
 if a.gn:
-    rep, per = g.optimize(a.gn); print(f"optimize {rep.ms_total:.2f} ms, pcg total {rep.pcg_iters_total}")
+    rep, per = g.optimize(a.gn); print(f"optimize {rep.ms_total:.2f} ms, pcg total {rep.pcg_iters_total}; per GN: " + " ".join(f"{q.pcg_iters}/{q.ms_solve:.2f}ms" for q in per))

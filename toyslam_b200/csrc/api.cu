@@ -5,6 +5,7 @@
 #include "device_graph.h"
 
 #include <nccl.h>
+#include <cusolverDn.h>
 
 #include <cmath>
 #include <cstdio>
@@ -34,6 +35,14 @@ struct tsb_ctx {
     bool force_phased = false;                            // TSB_PCG_PHASED=1: one launch per PCG phase (the multi-GPU path)
     uint64_t h2d = 0, d2h = 0;                            // bytes copied since the last tsb_load_*
     ncclComm_t comm = nullptr;                            // world > 1: one communicator, collectives on `stream`
+    // two-level preconditioner: dense coarse operator factored and inverted with cuSOLVER (potrf + potri)
+    bool use_coarse = true;                               // TSB_COARSE=0: block-Jacobi only
+    cusolverDnHandle_t solver = nullptr;
+    double* cwork = nullptr; int cwork_len = 0;
+    // the coarse inverse is reused across GN iterations while it keeps working (any SPD M is a valid
+    // preconditioner; a stale one only costs iterations): refreshed on the first solve of a request, when the
+    // PCG needs > 1.25x the iterations it took right after the last refresh, or after `coarse_max_age` solves
+    int coarse_age = -1, coarse_ref_iters = 0, coarse_max_age = 16;
 };
 
 namespace {
@@ -45,12 +54,13 @@ namespace {
 void free_graph(tsb_ctx* c) {
     for (void* p : c->allocs) cudaFree(p);
     c->allocs.clear(); c->d = Dev{}; c->loaded = c->linearized = c->solved = false;
-    c->pose0 = nullptr; c->lm0 = nullptr; c->tmp_xyt = nullptr;
+    c->pose0 = nullptr; c->lm0 = nullptr; c->tmp_xyt = nullptr; c->cwork = nullptr; c->cwork_len = 0; c->coarse_age = -1;
 }
 
 template <typename T> int dalloc(tsb_ctx* c, T*& out, size_t n) {
     void* p = nullptr;
-    if (cudaMalloc(&p, std::max<size_t>(n, 1) * sizeof(T)) != cudaSuccess) {
+    // 64 B of slack: the streaming kernels copy from addresses aligned down / sizes rounded up to 16 B
+    if (cudaMalloc(&p, std::max<size_t>(n, 1) * sizeof(T) + 64) != cudaSuccess) {
         cudaGetLastError(); c->err = "cudaMalloc failed (" + std::to_string(n * sizeof(T)) + " bytes)"; return TSB_ENOMEM; }
     c->allocs.push_back(p); out = (T*)p; return TSB_OK;
 }
@@ -116,7 +126,26 @@ int upload_graph(tsb_ctx* c) {
       for (size_t k = 0; k < s.own_bnd_slot.size(); ++k) bl[s.own_bnd_slot[k]] = s.own_bnd_pose[k];
       TRY(upload(c, d.bnd_local, bl)); TRY(upload(c, d.ghost_bnd_slot, s.ghost_bnd_slot)); }
     TRY(dalloc(c, d.dl, 2ull * g.L));
-    c->part_cap = std::max<uint32_t>(d.nBlocks, (std::max(d.nP, g.L) + kThreads - 1) / kThreads) + 1;
+    // coarse space
+    d.aggK = s.agg_K; d.nA = s.nA; d.nc = 3 * s.nA; d.nAS = (uint32_t)s.aslot_lm.size(); d.nPairs = (uint32_t)s.cpair_a.size();
+    d.nSeg = (d.nP + 31) / 32;
+    TRY(upload(c, d.edge_pose, s.edge_pose)); TRY(upload(c, d.aslot_lm, s.aslot_lm)); TRY(upload(c, d.aslot_agg, s.aslot_agg));
+    TRY(upload(c, d.aslot_ptr, s.aslot_ptr)); TRY(upload(c, d.aslot_edge, s.aslot_edge));
+    TRY(upload(c, d.cpair_a, s.cpair_a)); TRY(upload(c, d.cpair_b, s.cpair_b)); TRY(upload(c, d.cpair_ptr, s.cpair_ptr));
+    TRY(upload(c, d.ctrip, s.ctrip));
+    TRY(dalloc(c, d.zoff, d.nP)); TRY(dalloc(c, d.cC, 6ull * d.nAS)); TRY(dalloc(c, d.Ac, (size_t)d.nc * d.nc));
+    TRY(dalloc(c, d.rcp, 3ull * d.nSeg)); TRY(dalloc(c, d.yc, d.nc)); TRY(dalloc(c, d.cdot, d.nc)); TRY(dalloc(c, d.cinfo, (size_t)2));
+    CU(cudaMemsetAsync(d.cinfo, 0, 8, c->stream));
+    if (c->use_coarse && d.nc) {
+        int l1 = 0, l2 = 0;
+        if (cusolverDnDpotrf_bufferSize(c->solver, CUBLAS_FILL_MODE_LOWER, (int)d.nc, d.Ac, (int)d.nc, &l1) != CUSOLVER_STATUS_SUCCESS ||
+            cusolverDnDpotri_bufferSize(c->solver, CUBLAS_FILL_MODE_LOWER, (int)d.nc, d.Ac, (int)d.nc, &l2) != CUSOLVER_STATUS_SUCCESS) {
+            c->err = "cusolverDnDpotrf/potri_bufferSize failed"; return TSB_ECUDA; }
+        c->cwork_len = std::max(l1, l2);
+        TRY(dalloc(c, c->cwork, (size_t)c->cwork_len));
+    }
+    // partial-sum scratch: one entry per unit, per 256 vertices, or per block of a persistent kernel (<= 8 per SM)
+    c->part_cap = std::max<uint32_t>(std::max<uint32_t>(d.nBlocks, (std::max(d.nP, g.L) + kThreads - 1) / kThreads) + 1, 4096);
     TRY(dalloc(c, d.part, c->part_cap)); TRY(dalloc(c, d.part2, c->part_cap));
     TRY(dalloc(c, d.scal, (size_t)S_COUNT)); TRY(dalloc(c, d.flags, (size_t)F_COUNT));
     { const char* e = std::getenv("TSB_PCG_TIMING"); if (e && e[0] == '1') { TRY(dalloc(c, d.dbg, (size_t)8)); CU(cudaMemsetAsync(d.dbg, 0, 64, c->stream)); } }
@@ -164,9 +193,19 @@ int enqueue_linearize(tsb_ctx* c) {
 }
 
 // Schur preparation + PCG + landmark back-substitution; leaves delta in d.x / d.dl
-int run_solve(tsb_ctx* c) {
+int run_solve(tsb_ctx* c, bool refresh_coarse = true) {
     const Dev& d = c->d;
     launch_schur_prep(d, c->stream);
+    if (c->use_coarse && d.nc && (refresh_coarse || c->coarse_age < 0)) {
+        c->coarse_age = 0;
+        // coarse operator Ac = Z^T S Z of this rank's poses, inverted explicitly so that the PCG applies it as a
+        // dense mat-vec; a failed factorisation (cinfo != 0) turns the coarse level off for this solve on the device
+        launch_coarse_assemble(d, c->stream);
+        if (cusolverDnDpotrf(c->solver, CUBLAS_FILL_MODE_LOWER, (int)d.nc, d.Ac, (int)d.nc, c->cwork, c->cwork_len, d.cinfo) != CUSOLVER_STATUS_SUCCESS ||
+            cusolverDnDpotri(c->solver, CUBLAS_FILL_MODE_LOWER, (int)d.nc, d.Ac, (int)d.nc, c->cwork, c->cwork_len, d.cinfo + 1) != CUSOLVER_STATUS_SUCCESS) {
+            c->err = "cusolverDnDpotrf/potri failed"; return TSB_ECUDA; }
+        launch_coarse_finish(d, c->stream);
+    }
     // single GPU: the whole PCG and the back-substitution run in one persistent cooperative kernel
     if (c->cfg.world <= 1 && !c->force_phased && launch_pcg_persistent(d, c->stream)) {
         if (d.dbg) {
@@ -245,6 +284,8 @@ int tsb_create(const tsb_config* cfg, tsb_ctx** out) {
     tsb_ctx* c = new tsb_ctx();
     c->cfg = *cfg; if (c->cfg.world < 1) { c->cfg.world = 1; c->cfg.rank = 0; }
     { const char* e = std::getenv("TSB_PCG_PHASED"); c->force_phased = e && e[0] == '1'; }
+    { const char* e = std::getenv("TSB_COARSE"); c->use_coarse = !(e && e[0] == '0'); }
+    { const char* e = std::getenv("TSB_COARSE_MAX_AGE"); if (e && std::atoi(e) > 0) c->coarse_max_age = std::atoi(e); }
     auto fail = [&](const char* what, cudaError_t e) { g_create_error = std::string(what) + ": " + cudaGetErrorString(e); delete c; return TSB_ECUDA; };
     cudaError_t e;
     if ((e = cudaSetDevice(cfg->device)) != cudaSuccess) return fail("cudaSetDevice", e);
@@ -252,6 +293,8 @@ int tsb_create(const tsb_config* cfg, tsb_ctx** out) {
     for (auto& ev : c->ev) if ((e = cudaEventCreate(&ev)) != cudaSuccess) return fail("cudaEventCreate", e);
     if ((e = cudaMallocHost((void**)&c->h_scal, sizeof(double) * S_COUNT)) != cudaSuccess) return fail("cudaMallocHost", e);
     if ((e = cudaMallocHost((void**)&c->h_flags, sizeof(int) * F_COUNT)) != cudaSuccess) return fail("cudaMallocHost", e);
+    if (cusolverDnCreate(&c->solver) != CUSOLVER_STATUS_SUCCESS || cusolverDnSetStream(c->solver, c->stream) != CUSOLVER_STATUS_SUCCESS) {
+        g_create_error = "cusolverDnCreate failed"; delete c; return TSB_ECUDA; }
     if (c->cfg.world > 1) {
         ncclUniqueId id; std::memcpy(&id, cfg->nccl_id, sizeof(id));
         const ncclResult_t r = ncclCommInitRank(&c->comm, c->cfg.world, id, c->cfg.rank);
@@ -275,6 +318,7 @@ void tsb_destroy(tsb_ctx* c) {
     cudaSetDevice(c->cfg.device);
     free_graph(c);
     if (c->comm) ncclCommDestroy(c->comm);
+    if (c->solver) cusolverDnDestroy(c->solver);
     if (c->h_scal) cudaFreeHost(c->h_scal);
     if (c->h_flags) cudaFreeHost(c->h_flags);
     for (auto& ev : c->ev) if (ev) cudaEventDestroy(ev);
@@ -407,7 +451,8 @@ int tsb_optimize(tsb_ctx* c, uint32_t iterations, tsb_report* rep, tsb_iter_stat
     CU(cudaSetDevice(c->cfg.device));
     const uint64_t launches0 = g_launches;
     const bool exits = c->cfg.enable_exits != 0;
-    double prevErr = -1, err = 0; int penalty = 0, code = 0; uint32_t done = 0;
+    double prevErr = -1, prev2Err = -1, err = 0; int penalty = 0, code = 0; uint32_t done = 0;
+    c->coarse_age = -1;                                  // every request starts from a fresh coarse operator
     int64_t pcg_total = 0; float ms_lin = 0, ms_sol = 0;
     CU(cudaEventRecord(c->ev[3], c->stream));
     for (uint32_t it = 0; it < iterations; ++it) {
@@ -426,7 +471,12 @@ int tsb_optimize(tsb_ctx* c, uint32_t iterations, tsb_report* rep, tsb_iter_stat
                 }
             } else penalty = 0;
         }
-        TRY(run_solve(c));
+        // refresh while the system is still moving (chi2 changed by > 2 % over the last iteration: a stale
+        // operator then costs ~50 % more PCG iterations), when staleness has cost > 25 iterations, or by age
+        const bool moving = prevErr <= 0 || prev2Err <= 0 || std::fabs(prevErr - prev2Err) > 0.02 * std::fabs(prev2Err);
+        const bool refresh = c->coarse_age < 0 || c->coarse_age >= c->coarse_max_age || moving ||
+                             (c->coarse_age >= 1 && c->h_flags[F_ITERS] > c->coarse_ref_iters + 25);
+        TRY(run_solve(c, refresh));
         CU(cudaEventRecord(c->ev[2], c->stream));
         TRY(enqueue_update(c));
         TRY(fetch_scalars(c));
@@ -436,11 +486,13 @@ int tsb_optimize(tsb_ctx* c, uint32_t iterations, tsb_report* rep, tsb_iter_stat
         float a = 0, b = 0;
         CU(cudaEventElapsedTime(&a, c->ev[0], c->ev[1])); CU(cudaEventElapsedTime(&b, c->ev[1], c->ev[2]));
         ms_lin += a; ms_sol += b; pcg_total += c->h_flags[F_ITERS]; ++done;
+        if (c->coarse_age == 0) c->coarse_ref_iters = c->h_flags[F_ITERS];
+        ++c->coarse_age;
         if (per_iter) { tsb_iter_stats& s = per_iter[it]; s.chi2 = err; s.delta_norm = dnorm; s.pcg_iters = c->h_flags[F_ITERS];
             s.pcg_rel_residual = c->h_scal[S_RZ0] > 0 ? std::sqrt(c->h_scal[S_RZ] / c->h_scal[S_RZ0]) : 0; s.ms_linearize = a; s.ms_solve = b; }
         if (exits && std::fabs(err - prevErr) < 0.001) { code = 2; if (c->cfg.verbose) std::printf("Plateau: NO MORE OPT\n"); break; }
         if (exits && dnorm < 0.001) { code = 3; if (c->cfg.verbose) std::printf("CONVERGED\n"); break; }
-        prevErr = err;
+        prev2Err = prevErr; prevErr = err;
     }
     CU(cudaEventRecord(c->ev[2], c->stream));
     CU(cudaEventSynchronize(c->ev[2]));

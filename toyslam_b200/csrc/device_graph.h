@@ -13,7 +13,7 @@ constexpr int kStageStride = kChunkEdges + 1;   // odd stride in doubles: rows l
 // scalars kept on the device (index into Dev::scal)
 enum Scal { S_CHI2 = 0, S_RZ0, S_RZ, S_PSP, S_ALPHA, S_BETA, S_DELTA2, S_DELTA2L, S_TOL2, S_RZNEW, S_COUNT };
 // integer flags (index into Dev::flags)
-enum Flag { F_DONE = 0, F_ITERS, F_MAXIT, F_COUNT };
+enum Flag { F_DONE = 0, F_ITERS, F_MAXIT, F_COARSE, F_COUNT };   // F_COARSE: 1 = coarse inverse valid for this solve
 
 struct Dev {
     uint32_t nP, nG, L, nE, nO, nOwned, nChunks, nBlocks, nSlots;
@@ -65,6 +65,17 @@ struct Dev {
     const uint32_t* bnd_local;  // per boundary slot: local pose index, or 0xFFFFFFFF if owned elsewhere
     const uint32_t* ghost_bnd_slot;   // per ghost pose: boundary slot
     double* bnd;                // 3 per boundary slot; == w_sum + 2 L (one contiguous all-reduce)
+    // two-level preconditioner: M^-1 = blockdiag(S)^-1 + Z (Z^T S Z)^-1 Z^T, Z = rigid-body modes of pose aggregates
+    uint32_t aggK, nA, nc, nAS, nPairs, nSeg;     // nc = 3 nA; nSeg = ceil(nP / 32) restriction segments
+    const uint32_t* edge_pose; const uint32_t* aslot_lm; const uint32_t* aslot_agg; const uint32_t* aslot_ptr;
+    const uint32_t* aslot_edge; const uint32_t* cpair_a; const uint32_t* cpair_b; const uint32_t* cpair_ptr; const uint32_t* ctrip;
+    double2* zoff;              // per pose: (-(y - cy), x - cx) about its aggregate's centroid -> third column of Z_i
+    double* cC;                 // 6 per aslot: sum of Hpl_e^T Z_i (2x3 row-major)
+    double* Ac;                 // nc x nc: Z^T S Z, overwritten by its inverse
+    double* rcp;                // 3 per segment: Z^T r summed over the segment's 32 poses
+    double* yc;                 // nc: coarse correction Ac^-1 (Z^T r)
+    double* cdot;               // nc: (Z^T r)_j * yc_j  (the coarse part of r'z)
+    int* cinfo;                 // potrf / potri status words
     long long* dbg;             // optional: 8 phase-cycle counters of the persistent PCG kernel (TSB_PCG_TIMING=1)
 };
 
@@ -73,6 +84,9 @@ void launch_linearize(const Dev& d, cudaStream_t s);            // K1: residuals
 void launch_lm_sum(const Dev& d, cudaStream_t s);               // K2a: landmark-major sum of slot partials
 void launch_lm_finalize(const Dev& d, cudaStream_t s);          // K2b: Hll, b_l, prior, Hll^-1; chi2
 void launch_schur_prep(const Dev& d, cudaStream_t s);           // K3: diag(S)^-1 and reduced rhs
+void launch_coarse_assemble(const Dev& d, cudaStream_t s);      // zoff, C, Ac = Z^T S Z (dense, deterministic)
+void launch_coarse_finish(const Dev& d, cudaStream_t s);        // mirror the inverse's triangle, set F_COARSE from cinfo
+void launch_pcg_coarse(const Dev& d, int init, cudaStream_t s);           // yc = Ac^-1 Z^T r, cdot (phased path)
 bool launch_pcg_persistent(const Dev& d, cudaStream_t s);     // whole PCG + back-substitution, one cooperative launch
 void launch_pcg_init(const Dev& d, cudaStream_t s);
 void launch_pcg_pass_a(const Dev& d, int mode, cudaStream_t s); // mode 0: v = p (with p = z + beta p fused), 1: v = x

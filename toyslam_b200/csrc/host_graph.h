@@ -68,7 +68,17 @@ struct Structure {
     std::vector<uint32_t> od_in_ptr, od_in_edge;   // nP + 1 : edges (owned or ghost) by id2
     std::vector<uint32_t> fixed_pose_count;  // nP : how many times the pose is listed as fixed
     std::vector<uint32_t> fixed_lm_count;    // L
+    // ---- coarse space of the two-level PCG preconditioner (this rank's poses only) -------------------
+    // Aggregate a = local poses [a*agg_K, (a+1)*agg_K); agg_K is a multiple of 32 (one warp-wide restriction
+    // segment).  An "aslot" is a distinct (aggregate, landmark) pair; C_aslot = sum of Hpl_e^T Z_pose(e).
+    uint32_t agg_K = 32, nA = 0;
+    std::vector<uint32_t> edge_pose;         // nE : local pose of each LM edge in assembly order
+    std::vector<uint32_t> aslot_lm, aslot_agg;      // per aslot (sorted by aggregate, then landmark)
+    std::vector<uint32_t> aslot_ptr, aslot_edge;    // nAS + 1 offsets into aslot_edge (assembly edge index, ascending)
+    std::vector<uint32_t> cpair_a, cpair_b, cpair_ptr;   // coarse block pairs (a, b) sharing a landmark; offsets into ctrip
+    std::vector<uint32_t> ctrip;             // 2 per triple: (aslot of a, aslot of b) with the same landmark, landmark ascending
 };
+constexpr uint32_t kCoarseMaxAgg = 512;   // upper bound on aggregates per rank (coarse matrix is dense: (3*512)^2 doubles)
 
 constexpr uint32_t kChunkEdges = 512;   // LM edges staged per chunk
 constexpr uint32_t kBlockPoses = 128;   // poses per thread block (upper bound)

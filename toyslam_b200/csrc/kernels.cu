@@ -20,6 +20,7 @@
 #include "device_graph.h"
 
 #include <cooperative_groups.h>
+#include <cstdlib>
 namespace cg = cooperative_groups;
 
 namespace tsb {
@@ -286,6 +287,8 @@ __global__ void __launch_bounds__(kThreads, 4) k_linearize(const Dev d) {
     unit_linearize(d, blockIdx.x, sm);
 }
 
+#include "linearize_stream.cuh"
+
 // ------------------------------------------------------------------------------------------------
 // K2a: landmark-major sum of the slot partials (5 values per landmark), fixed order.
 // K2b: prior, Hll, b_l, Hll^-1 (closed-form 2x2).
@@ -407,14 +410,25 @@ __device__ __forceinline__ void sym3_mul(const double* M, double a, double b, do
 }
 
 // MODE 0: v = p after the fused update p = z + beta p;  MODE 1: v = x
+// z_i + Z_i yc[agg(i)] : the prolongated coarse correction added to the block-Jacobi part (component q of pose p)
+__device__ __forceinline__ double prolong(const Dev& d, uint32_t p, uint32_t q) {
+    const uint32_t a = p / d.aggK;
+    const double y2 = d.yc[3 * a + 2];
+    if (q == 2) return y2;
+    const double2 zo = d.zoff[p];
+    return q == 0 ? d.yc[3 * a] + zo.x * y2 : d.yc[3 * a + 1] + zo.y * y2;
+}
+
 template <int MODE>
-__device__ __forceinline__ void unit_pass_a(const Dev& d, const uint32_t unit, const Sm& sm, const double beta) {
+__device__ __forceinline__ void unit_pass_a(const Dev& d, const uint32_t unit, const Sm& sm, const double beta, const bool coarse) {
     double* v = sm.vec;
     const uint32_t c0 = d.blk_chunk_ptr[unit], c1 = d.blk_chunk_ptr[unit + 1];
     const uint32_t p0 = d.chunks[c0].p0, np = d.chunks[c0].p1 - p0;
     if (MODE == 0) {
         for (uint32_t i = threadIdx.x; i < 3 * np; i += kThreads) {
-            const double t = d.z[3ull * p0 + i] + beta * d.p[3ull * p0 + i];
+            double zz = d.z[3ull * p0 + i];
+            if (coarse) zz += prolong(d, p0 + i / 3, i % 3);
+            const double t = zz + beta * d.p[3ull * p0 + i];
             d.p[3ull * p0 + i] = t; v[i] = t;
         }
     } else {
@@ -521,40 +535,192 @@ __device__ __forceinline__ double2 lm_w_sum_warp(const Dev& d, uint32_t l) {
     return make_double2(a0, a1);
 }
 
-// x += alpha p; r -= alpha Sp; z = M^-1 r; returns r'z of pose i
-__device__ __forceinline__ double pose_update(const Dev& d, uint32_t i, double alpha) {
-    double r[3], z[3];
+// One PCG vector step for pose i (all 32 lanes of a warp call it; `valid` masks the tail):
+//   init : x = 0, r = rhs            else : x += alpha p, r -= alpha Sp
+//   z = blockdiag(S)^-1 r (the block-Jacobi part of the preconditioner); returns r'z of the pose.
+// With the coarse level on, the warp also restricts: rcp[segment] = sum over its 32 poses of Z_i^T r_i
+// (fixed xor tree -> deterministic).
+template <bool INIT>
+__device__ __forceinline__ double pose_step(const Dev& d, uint32_t i, bool valid, double alpha, bool coarse) {
+    double r[3] = {0, 0, 0}, dot = 0;
+    if (valid) {
+        double z[3];
 #pragma unroll
-    for (int q = 0; q < 3; ++q) {
-        d.x[3ull * i + q] += alpha * d.p[3ull * i + q];
-        r[q] = d.r[3ull * i + q] - alpha * d.sp[3ull * i + q];
-        d.r[3ull * i + q] = r[q];
+        for (int q = 0; q < 3; ++q) {
+            if (INIT) { r[q] = d.rhs[3ull * i + q]; d.x[3ull * i + q] = 0; d.p[3ull * i + q] = 0; }
+            else { d.x[3ull * i + q] += alpha * d.p[3ull * i + q]; r[q] = d.r[3ull * i + q] - alpha * d.sp[3ull * i + q]; }
+            d.r[3ull * i + q] = r[q];
+        }
+        sym3_mul(d.minv + 6ull * i, r[0], r[1], r[2], z[0], z[1], z[2]);
+        d.z[3ull * i] = z[0]; d.z[3ull * i + 1] = z[1]; d.z[3ull * i + 2] = z[2];
+        dot = r[0] * z[0] + r[1] * z[1] + r[2] * z[2];
     }
-    sym3_mul(d.minv + 6ull * i, r[0], r[1], r[2], z[0], z[1], z[2]);
-    d.z[3ull * i] = z[0]; d.z[3ull * i + 1] = z[1]; d.z[3ull * i + 2] = z[2];
-    return r[0] * z[0] + r[1] * z[1] + r[2] * z[2];
+    if (coarse) {
+        double2 zo = make_double2(0, 0);
+        if (valid) zo = d.zoff[i];
+        double c0 = r[0], c1 = r[1], c2 = zo.x * r[0] + zo.y * r[1] + r[2];
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            c0 += __shfl_xor_sync(0xffffffffu, c0, o); c1 += __shfl_xor_sync(0xffffffffu, c1, o); c2 += __shfl_xor_sync(0xffffffffu, c2, o);
+        }
+        if ((threadIdx.x & 31) == 0 && (i >> 5) < d.nSeg) { double* o = d.rcp + 3ull * (i >> 5); o[0] = c0; o[1] = c1; o[2] = c2; }
+    }
+    return dot;
 }
 
-__device__ __forceinline__ double pose_init(const Dev& d, uint32_t i) {
-    const double r0 = d.rhs[3ull * i], r1 = d.rhs[3ull * i + 1], r2 = d.rhs[3ull * i + 2];
-    double z0, z1, z2; sym3_mul(d.minv + 6ull * i, r0, r1, r2, z0, z1, z2);
-    d.x[3ull * i] = 0; d.x[3ull * i + 1] = 0; d.x[3ull * i + 2] = 0;
-    d.r[3ull * i] = r0; d.r[3ull * i + 1] = r1; d.r[3ull * i + 2] = r2;
-    d.z[3ull * i] = z0; d.z[3ull * i + 1] = z1; d.z[3ull * i + 2] = z2;
-    d.p[3ull * i] = z0; d.p[3ull * i + 1] = z1; d.p[3ull * i + 2] = z2;
-    return r0 * z0 + r1 * z1 + r2 * z2;
+// Coarse level: yc = Ac^-1 (Z^T r) with Z^T r summed from the segment partials, and cdot_j = (Z^T r)_j yc_j.
+// Rows are dealt to warps (`gwarp` of `nwarps`); rc_s is block shared memory for nc doubles.
+__device__ __forceinline__ void coarse_phase(const Dev& d, uint32_t gwarp, uint32_t nwarps, double* rc_s) {
+    const uint32_t spa = d.aggK >> 5, nc = d.nc;
+    for (uint32_t k = threadIdx.x; k < nc; k += blockDim.x) {
+        const uint32_t a = k / 3, q = k % 3, s0 = a * spa, s1 = min(d.nSeg, s0 + spa);
+        double t = 0;
+#pragma unroll 8
+        for (uint32_t sg = s0; sg < s1; ++sg) t += d.rcp[3ull * sg + q];
+        rc_s[k] = t;
+    }
+    __syncthreads();
+    const uint32_t lane = threadIdx.x & 31;
+    for (uint32_t j = gwarp; j < nc; j += nwarps) {
+        const double* row = d.Ac + (size_t)j * nc;
+        double t0 = 0, t1 = 0;
+        uint32_t k = lane;
+#pragma unroll 4
+        for (; k + 32 < nc; k += 64) { t0 += row[k] * rc_s[k]; t1 += row[k + 32] * rc_s[k + 32]; }
+        if (k < nc) t0 += row[k] * rc_s[k];
+        double t = t0 + t1;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) t += __shfl_xor_sync(0xffffffffu, t, o);
+        if (lane == 0) { d.yc[j] = t; d.cdot[j] = t * rc_s[j]; }
+    }
+    __syncthreads();
+}
+
+// ------------------------------------------------------------------------------------------------
+// Coarse operator of the two-level preconditioner: Ac = Z^T S Z (dense nc x nc, nc = 3 aggregates),
+//   Z_i = [[1,0,zo.x],[0,1,zo.y],[0,0,1]]: translation x, translation y and rigid rotation of aggregate
+//   agg(i) about its centroid -- the near-null vectors of S (a rigid motion of an aggregate together
+//   with its landmarks leaves every LM residual unchanged).  Every (a,b) block is accumulated by one
+//   thread in a fixed order: deterministic, no atomics.
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(kThreads) k_coarse_cen(const Dev d) {      // block per aggregate
+    __shared__ double red[32];
+    __shared__ double cxy[2];
+    const uint32_t a = blockIdx.x, p0 = a * d.aggK, p1 = min(d.nP, p0 + d.aggK);
+    double sx = 0, sy = 0;
+    for (uint32_t i = p0 + threadIdx.x; i < p1; i += kThreads) { const double4 ps = d.pose[i]; sx += ps.x; sy += ps.y; }
+    const double tx = block_sum(sx, red), ty = block_sum(sy, red);
+    if (threadIdx.x == 0) { cxy[0] = tx / (double)(p1 - p0); cxy[1] = ty / (double)(p1 - p0); }
+    __syncthreads();
+    for (uint32_t i = p0 + threadIdx.x; i < p1; i += kThreads) { const double4 ps = d.pose[i]; d.zoff[i] = make_double2(-(ps.y - cxy[1]), ps.x - cxy[0]); }
+}
+
+__global__ void k_coarse_C(const Dev d) {                                  // thread per aslot: C = sum Hpl_e^T Z_i
+    const uint32_t sidx = blockIdx.x * blockDim.x + threadIdx.x;
+    if (sidx >= d.nAS) return;
+    double c[6] = {0, 0, 0, 0, 0, 0};
+    for (uint32_t q = d.aslot_ptr[sidx]; q < d.aslot_ptr[sidx + 1]; ++q) {
+        const uint32_t e = d.aslot_edge[q];
+        const double2 zo = d.zoff[d.edge_pose[e]];
+        const double2* h = reinterpret_cast<const double2*>(d.hpl + 6ull * e);
+        const double2 h0 = h[0], h1 = h[1], h2 = h[2];
+        c[0] += h0.x; c[1] += h1.x; c[2] += zo.x * h0.x + zo.y * h1.x + h2.x;
+        c[3] += h0.y; c[4] += h1.y; c[5] += zo.x * h0.y + zo.y * h1.y + h2.y;
+    }
+#pragma unroll
+    for (int k = 0; k < 6; ++k) d.cC[6ull * sidx + k] = c[k];
+}
+
+// column c of Z_i as a 3-vector
+__device__ __forceinline__ void zcol(const double2 zo, int c, double& v0, double& v1, double& v2) {
+    v0 = c == 0 ? 1.0 : (c == 2 ? zo.x : 0.0); v1 = c == 1 ? 1.0 : (c == 2 ? zo.y : 0.0); v2 = c == 2 ? 1.0 : 0.0;
+}
+
+// pose-diagonal and ODOM part: warp per aggregate, lane (r,c) of 9 owns entry [r][c] of every block of block-row a
+__global__ void k_coarse_pose(const Dev d) {
+    const uint32_t a = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+    if (a >= d.nA || lane >= 9) return;
+    const int r = lane / 3, c = lane % 3;
+    const uint32_t p0 = a * d.aggK, p1 = min(d.nP, p0 + d.aggK), nc = d.nc;
+    double* rowp = d.Ac + (size_t)(3 * a + r) * nc;
+    double diag = 0;
+    for (uint32_t i = p0; i < p1; ++i) {
+        const double2 zi = d.zoff[i];
+        double a0, a1, a2, b0, b1, b2; zcol(zi, r, a0, a1, a2); zcol(zi, c, b0, b1, b2);
+        double y0, y1, y2; sym3_mul(d.hpp + 6ull * i, b0, b1, b2, y0, y1, y2);
+        diag += a0 * y0 + a1 * y1 + a2 * y2;
+        for (uint32_t k = d.od_out_ptr[i]; k < d.od_out_ptr[i + 1]; ++k) {
+            const uint32_t j = d.od_b[k];
+            if (j >= d.nP) continue;                                   // pose of another rank: not in this rank's coarse space
+            const double* h = d.hoo + 3ull * k; zcol(d.zoff[j], c, b0, b1, b2);
+            const double v = a0 * h[0] * b0 + a1 * h[1] * b1 + a2 * h[2] * b2;
+            const uint32_t b = j / d.aggK;
+            if (b == a) diag += v; else rowp[3 * b + c] += v;
+        }
+        for (uint32_t q = d.od_in_ptr[i]; q < d.od_in_ptr[i + 1]; ++q) {
+            const uint32_t k = d.od_in_edge[q], j = d.od_a[k];
+            if (j >= d.nP) continue;
+            const double* h = d.hoo + 3ull * k; zcol(d.zoff[j], c, b0, b1, b2);
+            const double v = a0 * h[0] * b0 + a1 * h[1] * b1 + a2 * h[2] * b2;
+            const uint32_t b = j / d.aggK;
+            if (b == a) diag += v; else rowp[3 * b + c] += v;
+        }
+    }
+    rowp[3 * a + c] += diag;
+}
+
+// landmark (Schur) part: thread per block pair (a,b): Ac[a,b] -= sum_l C_{l,a}^T Hll^-1 C_{l,b}
+__global__ void k_coarse_lm(const Dev d) {
+    const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= d.nPairs) return;
+    double acc[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0};
+    for (uint32_t q = d.cpair_ptr[t]; q < d.cpair_ptr[t + 1]; ++q) {
+        const uint32_t sa = d.ctrip[2ull * q], sb = d.ctrip[2ull * q + 1];
+        const double* hi = d.hinv + 3ull * d.aslot_lm[sa];
+        const double* ca = d.cC + 6ull * sa; const double* cb = d.cC + 6ull * sb;
+        const double i00 = hi[0], i01 = hi[1], i11 = hi[2];
+#pragma unroll
+        for (int r = 0; r < 3; ++r) {
+            const double t0 = i00 * ca[r] + i01 * ca[3 + r], t1 = i01 * ca[r] + i11 * ca[3 + r];
+#pragma unroll
+            for (int c = 0; c < 3; ++c) acc[3 * r + c] += t0 * cb[c] + t1 * cb[3 + c];
+        }
+    }
+    double* blk = d.Ac + (size_t)(3 * d.cpair_a[t]) * d.nc + 3 * d.cpair_b[t];
+#pragma unroll
+    for (int r = 0; r < 3; ++r)
+#pragma unroll
+        for (int c = 0; c < 3; ++c) blk[(size_t)r * d.nc + c] -= acc[3 * r + c];
+}
+
+// after potrf + potri (column-major lower = row-major upper holds the inverse): mirror it and publish the status
+__global__ void k_coarse_finish(const Dev d) {
+    const bool ok = d.cinfo[0] == 0 && d.cinfo[1] == 0;
+    const size_t n = d.nc, tot = n * n;
+    for (size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x; idx < tot; idx += (size_t)gridDim.x * blockDim.x) {
+        const size_t i = idx / n, j = idx % n;
+        if (i > j) d.Ac[idx] = d.Ac[j * n + i];
+    }
+    if (blockIdx.x == 0 && threadIdx.x == 0) d.flags[F_COARSE] = ok ? 1 : 0;
 }
 
 // ---- one launch per phase (used when collectives sit between the phases, world > 1) -------------------
 __global__ void k_pcg_init(const Dev d) {
     __shared__ double red[32];
-    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-    const double t = block_sum(i < d.nP ? pose_init(d, i) : 0.0, red);
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;        // grid covers nP rounded up to whole warps
+    const double t = block_sum(pose_step<true>(d, i, i < d.nP, 0.0, d.flags[F_COARSE] != 0), red);
     if (threadIdx.x == 0) d.part[blockIdx.x] = t;
+}
+// yc = Ac^-1 Z^T r and the coarse part of r'z (phased path; the persistent kernel calls coarse_phase itself)
+__global__ void __launch_bounds__(kThreads) k_pcg_coarse(const Dev d, int init) {
+    if (!d.flags[F_COARSE] || (!init && d.flags[F_DONE])) return;
+    __shared__ double rc_s[3 * kCoarseMaxAgg];
+    coarse_phase(d, (blockIdx.x * blockDim.x + threadIdx.x) >> 5, (gridDim.x * blockDim.x) >> 5, rc_s);
 }
 __global__ void k_pcg_init_scal(const Dev d, uint32_t nparts) {
     __shared__ double red[32];
-    const double rz = reduce_all(d.part, nparts, red);
+    double rz = reduce_all(d.part, nparts, red);
+    if (d.flags[F_COARSE]) rz += reduce_all(d.cdot, d.nc, red);
     if (threadIdx.x == 0) {
         d.scal[S_RZ0] = rz; d.scal[S_RZ] = rz; d.scal[S_BETA] = 0; d.scal[S_ALPHA] = 0;
         d.flags[F_ITERS] = 0; d.flags[F_DONE] = (rz > 0) ? 0 : 1;
@@ -565,7 +731,7 @@ __global__ void __launch_bounds__(kThreads) k_pcg_pass_a(const Dev d) {
     if (MODE == 0 && d.flags[F_DONE]) return;
     extern __shared__ __align__(32) unsigned char smem_raw[];
     const Sm sm = Sm::make<LayA>(smem_raw);
-    unit_pass_a<MODE>(d, blockIdx.x, sm, MODE == 0 ? d.scal[S_BETA] : 0.0);
+    unit_pass_a<MODE>(d, blockIdx.x, sm, MODE == 0 ? d.scal[S_BETA] : 0.0, MODE == 0 && d.flags[F_COARSE] != 0);
 }
 // landmark-major sum of the slot partials (warp per landmark); used where w must exist as an array:
 // before the all-reduce over ranks (world > 1) and before the back-substitution
@@ -618,13 +784,14 @@ __global__ void k_pcg_update(const Dev d) {
     if (d.flags[F_DONE]) return;
     __shared__ double red[32];
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-    const double t = block_sum(i < d.nP ? pose_update(d, i, d.scal[S_ALPHA]) : 0.0, red);
+    const double t = block_sum(pose_step<false>(d, i, i < d.nP, d.scal[S_ALPHA], d.flags[F_COARSE] != 0), red);
     if (threadIdx.x == 0) d.part[blockIdx.x] = t;
 }
 __global__ void k_pcg_rznew(const Dev d, uint32_t nparts) {   // local part of r'z (all-reduced over ranks before k_pcg_beta)
     if (d.flags[F_DONE]) return;
     __shared__ double red[32];
-    const double rz_new = reduce_all(d.part, nparts, red);
+    double rz_new = reduce_all(d.part, nparts, red);
+    if (d.flags[F_COARSE]) rz_new += reduce_all(d.cdot, d.nc, red);
     if (threadIdx.x == 0) d.scal[S_RZNEW] = rz_new;
 }
 __global__ void k_pcg_beta(const Dev d) {
@@ -648,12 +815,20 @@ __global__ void __launch_bounds__(kThreads, 3) k_pcg_persistent(const Dev d) {
     const Sm sm = Sm::make<LayPcg>(smem_raw);
     cg::grid_group grid = cg::this_grid();
     const uint32_t nb = gridDim.x, gtid = blockIdx.x * kThreads + threadIdx.x, gsz = nb * kThreads;
+    const bool coarse = d.flags[F_COARSE] != 0;
+    const uint32_t nP32 = (d.nP + 31u) & ~31u;                      // whole warps take part in the restriction
+    const bool crow = coarse && blockIdx.x * (kThreads / 32) < d.nc;   // this block owns coarse rows
     double dot = 0;
-    for (uint32_t i = gtid; i < d.nP; i += gsz) dot += pose_init(d, i);
+    for (uint32_t i = gtid; i < nP32; i += gsz) dot += pose_step<true>(d, i, i < d.nP, 0.0, coarse);
     double t = block_sum(dot, sm.red);
     if (threadIdx.x == 0) d.part[blockIdx.x] = t;
     grid.sync();
-    const double rz0 = reduce_all(d.part, nb, sm.red);
+    if (coarse) {
+        if (crow) coarse_phase(d, gtid >> 5, gsz >> 5, sm.stage);
+        grid.sync();
+    }
+    double rz0 = reduce_all(d.part, nb, sm.red);
+    if (coarse) rz0 += reduce_all(d.cdot, d.nc, sm.red);
     double rz = rz0, beta = 0;
     const double tol2 = d.scal[S_TOL2]; const int maxit = d.flags[F_MAXIT];
     int it = 0;
@@ -664,7 +839,7 @@ __global__ void __launch_bounds__(kThreads, 3) k_pcg_persistent(const Dev d) {
     if (rz0 > 0) {
         for (;;) {
             if (timing) tk = clock64();
-            for (uint32_t u = blockIdx.x; u < d.nBlocks; u += nb) unit_pass_a<0>(d, u, sm, beta);
+            for (uint32_t u = blockIdx.x; u < d.nBlocks; u += nb) unit_pass_a<0>(d, u, sm, beta, coarse);
             TICK(0);
             grid.sync();
             TICK(1);
@@ -684,13 +859,18 @@ __global__ void __launch_bounds__(kThreads, 3) k_pcg_persistent(const Dev d) {
             TICK(5);
             const double alpha = rz / reduce_all(d.part2, nb, sm.red);
             dot = 0;
-            for (uint32_t i = gtid; i < d.nP; i += gsz) dot += pose_update(d, i, alpha);
+            for (uint32_t i = gtid; i < nP32; i += gsz) dot += pose_step<false>(d, i, i < d.nP, alpha, coarse);
             t = block_sum(dot, sm.red);
             if (threadIdx.x == 0) d.part[blockIdx.x] = t;
             TICK(6);
             grid.sync();
+            if (coarse) {
+                if (crow) coarse_phase(d, gtid >> 5, gsz >> 5, sm.stage);
+                grid.sync();
+            }
             TICK(7);
-            const double rz_new = reduce_all(d.part, nb, sm.red);
+            double rz_new = reduce_all(d.part, nb, sm.red);
+            if (coarse) rz_new += reduce_all(d.cdot, d.nc, sm.red);
             beta = rz_new / rz; rz = rz_new; ++it;
             if (!(rz_new > tol2 * rz0) || it >= maxit) break;
         }
@@ -702,7 +882,7 @@ __global__ void __launch_bounds__(kThreads, 3) k_pcg_persistent(const Dev d) {
 #undef TICK
     // landmark back-substitution: delta_l = Hll^-1 (b_l - Hpl^T delta_p)
     grid.sync();
-    for (uint32_t u = blockIdx.x; u < d.nBlocks; u += nb) unit_pass_a<1>(d, u, sm, 0.0);
+    for (uint32_t u = blockIdx.x; u < d.nBlocks; u += nb) unit_pass_a<1>(d, u, sm, 0.0, false);
     grid.sync();
     for (uint32_t l = gtid >> 5; l < d.L; l += gsz >> 5) {
         const double2 w = lm_w_sum_warp(d, l);
@@ -785,6 +965,7 @@ size_t linearize_smem_bytes() { return LayLin::bytes; }
 
 static bool g_attr_set = false;
 static int g_coop_blocks = 0;      // co-resident blocks of the persistent PCG kernel on this device
+static int g_stream_blocks = 0;    // grid of the streaming kernels: resident blocks per SM x SMs
 static void set_attrs() {
     if (g_attr_set) return;
     cudaFuncSetAttribute(k_linearize, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)LayLin::bytes);
@@ -798,6 +979,10 @@ static void set_attrs() {
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
     cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_pcg_persistent, kThreads, LayPcg::bytes);
     g_coop_blocks = sms * per_sm;
+    cudaFuncSetAttribute(k_linearize_stream, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kLsSmemBytes);
+    int ls_per_sm = 0;
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&ls_per_sm, k_linearize_stream, kThreads, kLsSmemBytes);
+    g_stream_blocks = sms * ls_per_sm;
     g_attr_set = true;
 }
 
@@ -805,8 +990,17 @@ void launch_linearize(const Dev& d, cudaStream_t s) {
     set_attrs();
     const uint32_t nob = cdiv(d.nP, kThreads);
     if (nob) { k_odom<<<nob, kThreads, 0, s>>>(d); ++g_launches; }
-    if (d.nBlocks) { k_linearize<<<d.nBlocks, kThreads, LayLin::bytes, s>>>(d); ++g_launches; }
-    k_reduce2_to<<<1, 1024, 0, s>>>(d.part2, nob, d.part, d.nBlocks, d.scal + S_CHI2); ++g_launches;
+    // HBM-sized graphs stream their chunks through persistent blocks (2 per SM); small ones take one unit per block
+    uint32_t nparts = d.nBlocks;
+    uint32_t min_units = 4u * (uint32_t)g_stream_blocks;
+    bool no_stream = false;
+    { const char* e = getenv("TSB_STREAM_MIN_UNITS"); if (e) min_units = (uint32_t)atoi(e);      // tests force either path
+      e = getenv("TSB_NO_STREAM"); no_stream = e && e[0] == '1'; }
+    if (g_stream_blocks > 0 && !no_stream && d.nBlocks >= min_units && d.nBlocks) {
+        k_linearize_stream<<<g_stream_blocks, kThreads, kLsSmemBytes, s>>>(d); ++g_launches;
+        nparts = (uint32_t)g_stream_blocks;
+    } else if (d.nBlocks) { k_linearize<<<d.nBlocks, kThreads, LayLin::bytes, s>>>(d); ++g_launches; }
+    k_reduce2_to<<<1, 1024, 0, s>>>(d.part2, nob, d.part, nparts, d.scal + S_CHI2); ++g_launches;
 }
 void launch_lm_sum(const Dev& d, cudaStream_t s) {
     if (d.L) { k_lm_sum<<<cdiv(d.L, kThreads / 32), kThreads, 0, s>>>(d); ++g_launches; }
@@ -832,9 +1026,24 @@ bool launch_pcg_persistent(const Dev& d, cudaStream_t s) {
     ++g_launches;
     return true;
 }
+void launch_coarse_assemble(const Dev& d, cudaStream_t s) {
+    if (!d.nA) return;
+    cudaMemsetAsync(d.Ac, 0, sizeof(double) * (size_t)d.nc * d.nc, s);
+    k_coarse_cen<<<d.nA, kThreads, 0, s>>>(d); ++g_launches;
+    if (d.nAS) { k_coarse_C<<<cdiv(d.nAS, kThreads), kThreads, 0, s>>>(d); ++g_launches; }
+    k_coarse_pose<<<cdiv(d.nA * 32, kThreads), kThreads, 0, s>>>(d); ++g_launches;
+    if (d.nPairs) { k_coarse_lm<<<cdiv(d.nPairs, 128), 128, 0, s>>>(d); ++g_launches; }
+}
+void launch_coarse_finish(const Dev& d, cudaStream_t s) {
+    k_coarse_finish<<<148 * 4, kThreads, 0, s>>>(d); ++g_launches;
+}
+void launch_pcg_coarse(const Dev& d, int init, cudaStream_t s) {
+    if (d.nc) { k_pcg_coarse<<<cdiv(d.nc, kThreads / 32), kThreads, 0, s>>>(d, init); ++g_launches; }
+}
 void launch_pcg_init(const Dev& d, cudaStream_t s) {
     const uint32_t nb = cdiv(d.nP, kThreads);
     if (nb) { k_pcg_init<<<nb, kThreads, 0, s>>>(d); ++g_launches; }
+    launch_pcg_coarse(d, 1, s);
     k_pcg_init_scal<<<1, 1024, 0, s>>>(d, nb); ++g_launches;
 }
 void launch_pcg_pass_a(const Dev& d, int mode, cudaStream_t s) {
@@ -869,7 +1078,7 @@ void launch_pcg_update(const Dev& d, cudaStream_t s) {
     const uint32_t nb = cdiv(d.nP, kThreads);
     if (nb) { k_pcg_update<<<nb, kThreads, 0, s>>>(d); ++g_launches; }
 }
-void launch_pcg_rznew(const Dev& d, cudaStream_t s) { k_pcg_rznew<<<1, 1024, 0, s>>>(d, cdiv(d.nP, kThreads)); ++g_launches; }
+void launch_pcg_rznew(const Dev& d, cudaStream_t s) { launch_pcg_coarse(d, 0, s); k_pcg_rznew<<<1, 1024, 0, s>>>(d, cdiv(d.nP, kThreads)); ++g_launches; }
 void launch_pcg_beta(const Dev& d, cudaStream_t s) { k_pcg_beta<<<1, 1, 0, s>>>(d); ++g_launches; }
 void launch_pcg_init_fix(const Dev& d, cudaStream_t s) { k_pcg_init_fix<<<1, 1, 0, s>>>(d); ++g_launches; }
 void launch_backsub(const Dev& d, cudaStream_t s) {

@@ -149,6 +149,67 @@ void build_structure(const HostGraph& g, uint32_t rank, uint32_t world, Structur
         for (uint32_t gp : s.ghost_pose)
             s.ghost_bnd_slot.push_back((uint32_t)(std::lower_bound(s.boundary.begin(), s.boundary.end(), gp) - s.boundary.begin()));
     }
+    // ---- coarse space: aggregates of agg_K consecutive local poses ------------------------------------
+    {
+        uint32_t K = 32;
+        if (nP > 32ull * kCoarseMaxAgg) K = 32 * (uint32_t)((nP + 32ull * kCoarseMaxAgg - 1) / (32ull * kCoarseMaxAgg));
+        s.agg_K = K; s.nA = (nP + K - 1) / K;
+        s.edge_pose.resize(nE);
+        for (uint32_t p = 0; p < nP; ++p) for (uint32_t k = s.pose_ptr[p]; k < s.pose_ptr[p + 1]; ++k) s.edge_pose[k] = p;
+        s.aslot_ptr.push_back(0); s.aslot_edge.reserve(nE);
+        std::vector<uint64_t> key;
+        for (uint32_t a = 0; a < s.nA; ++a) {
+            const uint32_t e0 = s.pose_ptr[a * K], e1 = s.pose_ptr[std::min(nP, (a + 1) * K)];
+            key.resize(e1 - e0);
+            for (uint32_t k = e0; k < e1; ++k) key[k - e0] = ((uint64_t)g.le_l[s.le_local[s.lm_perm[k]]] << 32) | k;
+            std::sort(key.begin(), key.end());
+            for (size_t q = 0; q < key.size(); ++q) {
+                const uint32_t l = (uint32_t)(key[q] >> 32);
+                if (q == 0 || l != (uint32_t)(key[q - 1] >> 32)) {
+                    if (q) s.aslot_ptr.push_back((uint32_t)s.aslot_edge.size());
+                    s.aslot_lm.push_back(l); s.aslot_agg.push_back(a);
+                }
+                s.aslot_edge.push_back((uint32_t)key[q]);
+            }
+            if (!key.empty()) s.aslot_ptr.push_back((uint32_t)s.aslot_edge.size());
+        }
+        const uint32_t nAS = (uint32_t)s.aslot_lm.size();
+        // landmark-major lists of aslots (ascending aslot id = ascending aggregate)
+        std::vector<uint32_t> lptr(L + 1, 0), lidx(nAS);
+        for (uint32_t q = 0; q < nAS; ++q) lptr[s.aslot_lm[q] + 1]++;
+        for (uint32_t l = 0; l < L; ++l) lptr[l + 1] += lptr[l];
+        { std::vector<uint32_t> c2(lptr.begin(), lptr.end() - 1);
+          for (uint32_t q = 0; q < nAS; ++q) lidx[c2[s.aslot_lm[q]]++] = q; }
+        // pairs (a, b) and their triples, grouped by a, then b, landmark ascending inside
+        s.cpair_ptr.push_back(0);
+        std::vector<uint64_t> trip;                       // b << 32 | position in the a-major emission order
+        std::vector<std::pair<uint32_t, uint32_t>> ss;
+        uint32_t q0 = 0;
+        for (uint32_t a = 0; a < s.nA; ++a) {
+            trip.clear(); ss.clear();
+            uint32_t q1 = q0;
+            while (q1 < nAS && s.aslot_agg[q1] == a) ++q1;
+            for (uint32_t q = q0; q < q1; ++q) {
+                const uint32_t l = s.aslot_lm[q];
+                for (uint32_t j = lptr[l]; j < lptr[l + 1]; ++j) {
+                    trip.push_back(((uint64_t)s.aslot_agg[lidx[j]] << 32) | (uint32_t)ss.size());
+                    ss.emplace_back(q, lidx[j]);
+                }
+            }
+            std::sort(trip.begin(), trip.end());
+            for (size_t t = 0; t < trip.size(); ++t) {
+                const uint32_t b = (uint32_t)(trip[t] >> 32);
+                if (t == 0 || b != (uint32_t)(trip[t - 1] >> 32)) {
+                    if (t) s.cpair_ptr.push_back((uint32_t)(s.ctrip.size() / 2));
+                    s.cpair_a.push_back(a); s.cpair_b.push_back(b);
+                }
+                const auto& pr = ss[(uint32_t)trip[t]];
+                s.ctrip.push_back(pr.first); s.ctrip.push_back(pr.second);
+            }
+            if (!trip.empty()) s.cpair_ptr.push_back((uint32_t)(s.ctrip.size() / 2));
+            q0 = q1;
+        }
+    }
     // ---- fixed vertices ---------------------------------------------------------------------------
     s.fixed_pose_count.assign(nP, 0); s.fixed_lm_count.assign(L, 0);
     for (uint32_t v : g.fixed) {
