@@ -101,10 +101,12 @@ def test_structure_is_bit_exact(gpu):
         for (e0, e1, p0, p1, s0, s1, blk, _) in s["chunk_desc"]:
             assert e1 - e0 <= 512 or p1 - p0 == 1
             assert ptr[p0] <= e0 and e1 <= ptr[p1]
-            lms = lm_l[order[e0:e1]]; uniq = np.unique(lms)
-            assert s1 - s0 == len(uniq); slot_lm_expect.append(uniq)
+            lms = lm_l[order[e0:e1]]; uniq, cnt = np.unique(lms, return_counts=True)
+            by_len = np.lexsort((uniq, -cnt))                   # slots: descending edge count, then ascending landmark
+            rank = np.empty(len(uniq), np.uint32); rank[by_len] = np.arange(len(uniq), dtype=np.uint32)
+            assert s1 - s0 == len(uniq); slot_lm_expect.append(uniq[by_len])
             pose_local = lm_i[order[e0:e1]] - p0
-            packed = (pose_local.astype(np.uint32) << 16) | np.searchsorted(uniq, lms).astype(np.uint32)
+            packed = (pose_local.astype(np.uint32) << 16) | rank[np.searchsorted(uniq, lms)]
             assert np.array_equal(s["lm_packed"][e0:e1], packed)
         slot_lm = np.concatenate(slot_lm_expect) if slot_lm_expect else np.zeros(0, np.uint32)
         assert np.array_equal(s["slot_lm"], slot_lm)

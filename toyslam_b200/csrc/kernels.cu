@@ -981,7 +981,7 @@ static void set_attrs() {
     g_coop_blocks = sms * per_sm;
     cudaFuncSetAttribute(k_linearize_stream, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kLsSmemBytes);
     int ls_per_sm = 0;
-    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&ls_per_sm, k_linearize_stream, kThreads, kLsSmemBytes);
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&ls_per_sm, k_linearize_stream, kLsThreads, kLsSmemBytes);
     g_stream_blocks = sms * ls_per_sm;
     g_attr_set = true;
 }
@@ -997,7 +997,7 @@ void launch_linearize(const Dev& d, cudaStream_t s) {
     { const char* e = getenv("TSB_STREAM_MIN_UNITS"); if (e) min_units = (uint32_t)atoi(e);      // tests force either path
       e = getenv("TSB_NO_STREAM"); no_stream = e && e[0] == '1'; }
     if (g_stream_blocks > 0 && !no_stream && d.nBlocks >= min_units && d.nBlocks) {
-        k_linearize_stream<<<g_stream_blocks, kThreads, kLsSmemBytes, s>>>(d); ++g_launches;
+        k_linearize_stream<<<g_stream_blocks, kLsThreads, kLsSmemBytes, s>>>(d); ++g_launches;
         nparts = (uint32_t)g_stream_blocks;
     } else if (d.nBlocks) { k_linearize<<<d.nBlocks, kThreads, LayLin::bytes, s>>>(d); ++g_launches; }
     k_reduce2_to<<<1, 1024, 0, s>>>(d.part2, nob, d.part, nparts, d.scal + S_CHI2); ++g_launches;

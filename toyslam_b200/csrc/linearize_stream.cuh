@@ -72,7 +72,40 @@ __device__ __forceinline__ void ls_issue(const Dev& d, const ChunkDesc& ch, unsi
     if (np) bulk_g2s(s + kLsPose, d.pose + ch.p0, bPose, bar);
 }
 
-__global__ void __launch_bounds__(kThreads, 2) k_linearize_stream(const Dev d) {
+constexpr int kLsThreads = 512;         // one LM edge per thread; 2 blocks (32 warps) per SM at <= 64 registers
+
+// same association as seg_sum / list_sum (four strided partial sums, then (t0+t1)+(t2+t3)), kept as rolled
+// loops: the fully unrolled variants cost more in divergent control flow than they save (ncu: 82 % of the
+// issued instructions of the first streaming version were integer / branch overhead)
+__device__ __forceinline__ double seg_sum_lean(const double* s, uint32_t b, uint32_t e) {
+    double t0 = 0, t1 = 0, t2 = 0, t3 = 0;
+    uint32_t k = b;
+#pragma unroll 1
+    for (; k + 3 < e; k += 4) { t0 += s[k]; t1 += s[k + 1]; t2 += s[k + 2]; t3 += s[k + 3]; }
+#pragma unroll 1
+    for (; k < e; ++k) t0 += s[k];
+    return (t0 + t1) + (t2 + t3);
+}
+__device__ __forceinline__ double list_sum_lean(const double* s, const uint16_t* idx, uint32_t b, uint32_t e) {
+    double t0 = 0, t1 = 0, t2 = 0, t3 = 0;
+    uint32_t k = b;
+#pragma unroll 1
+    for (; k + 3 < e; k += 4) { t0 += s[idx[k]]; t1 += s[idx[k + 1]]; t2 += s[idx[k + 2]]; t3 += s[idx[k + 3]]; }
+#pragma unroll 1
+    for (; k < e; ++k) t0 += s[idx[k]];
+    return (t0 + t1) + (t2 + t3);
+}
+
+// reduction item (pose, row) -> where its value goes: Hpp (00 01 02 11 12 22) or b_p, and which entry of
+// pose_od (the ODOM / prior part prepared by k_odom) is added; b_2 = od - sum (b -= A^T W e)
+__device__ __forceinline__ int ls_od_index(uint32_t row) { return row == 0 ? 0 : row == 2 ? 1 : row == 5 ? 2 : row >= 6 ? (int)row - 3 : -1; }
+__device__ __forceinline__ void ls_store(const Dev& d, uint32_t p, uint32_t row, double sum, double od) {
+    if (row < 6) { const int hi = row == 2 ? 3 : row == 3 ? 2 : (int)row; d.hpp[6ull * p + hi] = sum + od; }
+    else if (row < 8) d.bp[3ull * p + (row - 6)] = sum + od;
+    else d.bp[3ull * p + 2] = od - sum;
+}
+
+__global__ void __launch_bounds__(kLsThreads, 2) k_linearize_stream(const Dev d) {
     extern __shared__ __align__(32) unsigned char smem_raw[];
     double* rows = reinterpret_cast<double*>(smem_raw + kLsRows);
     double2* slot2 = reinterpret_cast<double2*>(smem_raw + kLsSlot2);
@@ -93,7 +126,7 @@ __global__ void __launch_bounds__(kThreads, 2) k_linearize_stream(const Dev d) {
     __syncthreads();
     if (cb >= ce) { if (tid == 0) d.part[blockIdx.x] = 0; return; }
 
-    // chunk descriptors, read by every thread (uniform loads) one and two chunks ahead
+    // chunk descriptors, read by every thread (uniform loads) up to three chunks ahead
     const ChunkDesc zero = {0, 0, 0, 0, 0, 0, 0xFFFFFFFFu, 0};
     ChunkDesc cur = d.chunks[cb];
     ChunkDesc nx1 = cb + 1 < ce ? d.chunks[cb + 1] : zero;
@@ -104,14 +137,10 @@ __global__ void __launch_bounds__(kThreads, 2) k_linearize_stream(const Dev d) {
         if (cb + 2 < ce) ls_issue(d, nx2, ring + 2 * kLsStageBytes, bar0 + 16);
     }
     // per-edge values of the first chunk (afterwards prefetched one chunk ahead)
-    double2 z0 = {}, w0 = {}, z1 = {}, w1 = {};
-    { const uint32_t n = cur.e1 - cur.e0;
-      if (tid < n) { z0 = d.le_z[cur.e0 + tid]; w0 = d.le_w[cur.e0 + tid]; }
-      if (tid + kThreads < n) { z1 = d.le_z[cur.e0 + tid + kThreads]; w1 = d.le_w[cur.e0 + tid + kThreads]; } }
+    double2 z0 = {}, w0 = {};
+    if (tid < cur.e1 - cur.e0) { z0 = d.le_z[cur.e0 + tid]; w0 = d.le_w[cur.e0 + tid]; }
 
-    double acc[kStageRows];
-#pragma unroll
-    for (int i = 0; i < kStageRows; ++i) acc[i] = 0;
+    double heavy = 0;            // a pose with > kChunkEdges edges spans several chunks: its nine sums live in threads 0..8
     double rho_sum = 0;
 
     for (uint32_t c = cb; c < ce; ++c) {
@@ -129,70 +158,58 @@ __global__ void __launch_bounds__(kThreads, 2) k_linearize_stream(const Dev d) {
         const double4* pose = reinterpret_cast<const double4*>(st + kLsPose);
 
         if (k == 0) {        // first chunk of the block: its landmarks have not been prefetched
-            for (uint32_t s = tid; s < ns; s += kThreads) slot2[s] = d.lm[slm[s]];
+            if (tid < ns) slot2[tid] = d.lm[slm[tid]];
             __syncthreads();
         }
         // ---- prefetch for the next chunk: per-edge values and slot landmarks into registers -------------------
-        double2 nz0 = {}, nw0 = {}, nz1 = {}, nw1 = {}, lmv0 = {}, lmv1 = {};
-        const uint32_t n_next = nx1.e1 - nx1.e0, ns_next = nx1.s1 - nx1.s0;
-        if (tid < n_next) { nz0 = d.le_z[nx1.e0 + tid]; nw0 = d.le_w[nx1.e0 + tid]; }
-        if (tid + kThreads < n_next) { nz1 = d.le_z[nx1.e0 + tid + kThreads]; nw1 = d.le_w[nx1.e0 + tid + kThreads]; }
+        double2 nz0 = {}, nw0 = {}, lmv0 = {};
+        const uint32_t ns_next = nx1.s1 - nx1.s0;
+        if (tid < nx1.e1 - nx1.e0) { nz0 = d.le_z[nx1.e0 + tid]; nw0 = d.le_w[nx1.e0 + tid]; }
         if (c + 1 < ce) {
             const uint32_t s2 = (k + 1) % kLsStages;
             mbar_wait(bar0 + 8 * s2, ((k + 1) / kLsStages) & 1u);          // issued two iterations ago
             const uint32_t* slm2 = reinterpret_cast<const uint32_t*>(ring + s2 * kLsStageBytes + kLsSl) + (nx1.s0 & 3u);
             if (tid < ns_next) lmv0 = d.lm[slm2[tid]];
-            if (tid + kThreads < ns_next) lmv1 = d.lm[slm2[tid + kThreads]];
         }
-        // the ODOM / prior part of this unit's poses: one value per reduction item, used when the unit ends
-        double od[kStageRows];
-#pragma unroll
-        for (int it = 0; it < kStageRows; ++it) {
-            const uint32_t item = tid + it * kThreads;
-            od[it] = 0;
-            if (last && item < np * kStageRows) {
-                const uint32_t pl = item / kStageRows, row = item % kStageRows;
-                const int oi = row == 0 ? 0 : row == 2 ? 1 : row == 5 ? 2 : row >= 6 ? (int)row - 3 : -1;
-                if (oi >= 0) od[it] = d.pose_od[6ull * (cur.p0 + pl) + oi];
-            }
-        }
+        // the ODOM / prior part of this unit's poses for this thread's first reduction item
+        const uint32_t nitems = np * kStageRows;
+        double od0 = 0;
+        if (last && tid < nitems) { const int oi = ls_od_index(tid % kStageRows); if (oi >= 0) od0 = d.pose_od[6ull * (cur.p0 + tid / kStageRows) + oi]; }
 
-        // ---- per-edge linearisation (two edges per thread), products staged in `rows`, Hpl written once -------
+        // ---- per-edge linearisation, products staged in `rows`, Hpl written once ------------------------------
         if (tid < n) { const uint32_t q = pk[tid];
             rho_sum += lm_edge(pose[q >> 16], slot2[q & 0xffffu], z0, w0, reinterpret_cast<double2*>(d.hpl + 6ull * (cur.e0 + tid)), rows + tid); }
-        if (tid + kThreads < n) { const uint32_t q = pk[tid + kThreads];
-            rho_sum += lm_edge(pose[q >> 16], slot2[q & 0xffffu], z1, w1,
-                               reinterpret_cast<double2*>(d.hpl + 6ull * (cur.e0 + tid + kThreads)), rows + tid + kThreads); }
         __syncthreads();
 
-        // ---- pose side: row segments; landmark side: one partial per slot -------------------------------------
-        pose_reduce<kStageRows>(pptr, cur, rows, np, acc);
-        for (uint32_t item = tid; item < ns * 5; item += kThreads) {
+        // ---- pose side: one (pose, row) item per thread sums its row segment ----------------------------------
+        const bool multi = np == 1 && pptr[1] - pptr[0] > kChunkEdges;      // only a single heavy pose is ever split
+#pragma unroll 1
+        for (uint32_t item = tid; item < nitems; item += kLsThreads) {
+            const uint32_t pl = item / kStageRows, row = item % kStageRows;
+            const uint32_t b = max(pptr[pl], cur.e0) - cur.e0, e = min(pptr[pl + 1], cur.e1) - cur.e0;
+            double sum = seg_sum_lean(rows + row * kStageStride, b, e);
+            if (multi) { heavy += sum; sum = heavy; }             // np == 1: item == tid < 9; same order as acc += seg_sum
+            if (last) {
+                double od = od0;
+                if (item >= kLsThreads) { const int oi = ls_od_index(row); od = oi >= 0 ? d.pose_od[6ull * (cur.p0 + pl) + oi] : 0.0; }
+                ls_store(d, cur.p0 + pl, row, sum, od);
+            }
+        }
+        if (last) heavy = 0;
+        // ---- landmark side: one partial per slot and component, edges of the slot in list order ----------------
+#pragma unroll 1
+        for (uint32_t item = tid; item < ns * 5; item += kLsThreads) {
             const uint32_t sl = item / 5, comp = item % 5;
             const double* s = rows + (comp < 3 ? comp : comp + 3) * kStageStride;
-            d.lm_part[5ull * (cur.s0 + sl) + comp] = list_sum(s, sedge, sptr[sl] - cur.e0, sptr[sl + 1] - cur.e0);
+            d.lm_part[5ull * (cur.s0 + sl) + comp] = list_sum_lean(s, sedge, sptr[sl] - cur.e0, sptr[sl + 1] - cur.e0);
         }
         // slot2 is no longer read by this chunk: hand it to the next one
         if (tid < ns_next) slot2[tid] = lmv0;
-        if (tid + kThreads < ns_next) slot2[tid + kThreads] = lmv1;
-        if (last) {              // unit complete: every reduction item owns exactly one output value
-#pragma unroll
-            for (int it = 0; it < kStageRows; ++it) {
-                const uint32_t item = tid + it * kThreads;
-                if (item < np * kStageRows) {
-                    const uint32_t pl = item / kStageRows, row = item % kStageRows, p = cur.p0 + pl;
-                    if (row < 6) { const int hi = row == 2 ? 3 : row == 3 ? 2 : (int)row; d.hpp[6ull * p + hi] = acc[it] + od[it]; }
-                    else if (row < 8) d.bp[3ull * p + (row - 6)] = acc[it] + od[it];
-                    else d.bp[3ull * p + 2] = od[it] - acc[it];
-                }
-                acc[it] = 0;
-            }
-        }
         __syncthreads();
         // stage `sidx` is free: refill it with the chunk three ahead
         if (tid == 0 && c + 3 < ce) ls_issue(d, nx3, st, bar0 + 8 * sidx);
         cur = nx1; nx1 = nx2; nx2 = nx3;
-        z0 = nz0; w0 = nw0; z1 = nz1; w1 = nw1;
+        z0 = nz0; w0 = nw0;
     }
     const double t = block_sum(rho_sum, red);
     if (tid == 0) d.part[blockIdx.x] = t;

@@ -84,18 +84,29 @@ void build_structure(const HostGraph& g, uint32_t rank, uint32_t world, Structur
         for (uint32_t k = 0; k < n; ++k) lms[k] = g.le_l[s.le_local[s.lm_perm[c.e0 + k]]];
         std::vector<uint32_t> uniq(lms);
         std::sort(uniq.begin(), uniq.end()); uniq.erase(std::unique(uniq.begin(), uniq.end()), uniq.end());
-        c.s0 = (uint32_t)s.slot_lm.size(); c.s1 = c.s0 + (uint32_t)uniq.size();
-        s.slot_lm.insert(s.slot_lm.end(), uniq.begin(), uniq.end());
-        cnt.assign(uniq.size() + 1, 0);
+        const uint32_t nu = (uint32_t)uniq.size();
+        // slots are numbered by descending edge count (ties: ascending landmark): the 32 lanes of a warp that sum
+        // neighbouring slots then run the same number of iterations
+        std::vector<uint32_t> ucnt(nu, 0), rank(nu), order(nu);
+        for (uint32_t k = 0; k < n; ++k) {
+            lms[k] = (uint32_t)(std::lower_bound(uniq.begin(), uniq.end(), lms[k]) - uniq.begin());   // landmark-sorted index
+            ucnt[lms[k]]++;
+        }
+        std::iota(order.begin(), order.end(), 0u);
+        std::stable_sort(order.begin(), order.end(), [&](uint32_t x, uint32_t y) { return ucnt[x] > ucnt[y]; });
+        for (uint32_t q = 0; q < nu; ++q) rank[order[q]] = q;
+        c.s0 = (uint32_t)s.slot_lm.size(); c.s1 = c.s0 + nu;
+        for (uint32_t q = 0; q < nu; ++q) s.slot_lm.push_back(uniq[order[q]]);
+        cnt.assign(nu + 1, 0);
         uint32_t pose = c.p0;
         for (uint32_t k = 0; k < n; ++k) {
-            const uint32_t slot = (uint32_t)(std::lower_bound(uniq.begin(), uniq.end(), lms[k]) - uniq.begin());
+            const uint32_t slot = rank[lms[k]];
             while (c.e0 + k >= s.pose_ptr[pose + 1]) ++pose;
             s.lm_packed[c.e0 + k] = ((pose - c.p0) << 16) | slot;
             lms[k] = slot; cnt[slot + 1]++;
         }
-        for (size_t q = 0; q < uniq.size(); ++q) cnt[q + 1] += cnt[q];
-        for (size_t q = 0; q < uniq.size(); ++q) s.slot_ptr.push_back(c.e0 + cnt[q + 1]);
+        for (size_t q = 0; q < nu; ++q) cnt[q + 1] += cnt[q];
+        for (size_t q = 0; q < nu; ++q) s.slot_ptr.push_back(c.e0 + cnt[q + 1]);
         for (uint32_t k = 0; k < n; ++k) s.slot_edge[c.e0 + cnt[lms[k]]++] = (uint16_t)k;
     }
     // ---- landmark-major CSR over slots ---------------------------------------------------------------
