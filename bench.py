@@ -128,7 +128,7 @@ def main():
     ap.add_argument("--lin-reps", type=int, default=20)
     args = ap.parse_args()
     if args.workload is None:
-        args.workload = "c2" if args.gpus == 1 else "c3"
+        args.workload = "c2"          # BASELINE configs[1] at every N, so the per-N lines are comparable (strong scaling)
     if args.impl == "reference":
         return run_reference(args)
 
@@ -187,6 +187,8 @@ def main():
     pcg_total = sum(r.pcg_iters_total for r, _ in reps) / args.steps
     ms_lin = sum(r.ms_linearize_total for r, _ in reps) / args.steps / GN_ITERS
     ms_sol = sum(r.ms_solve_total for r, _ in reps) / args.steps
+    ms_pcg = sum(r.ms_pcg_total for r, _ in reps) / args.steps       # the PCG proper (one persistent kernel per solve at N=1)
+    refreshes = sum(r.coarse_refreshes for r, _ in reps) / args.steps
     t = torch.tensor([dev_ms], dtype=torch.float64, device="cuda")
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
@@ -201,7 +203,7 @@ def main():
         if i >= 3:
             lin.append(st.ms_linearize)
     lin_ms = float(np.median(lin))
-    pcg_ms = ms_sol / max(pcg_total, 1)                      # solve time per PCG iteration (includes prep/backsub)
+    pcg_ms = ms_pcg / max(pcg_total, 1)                      # device time per PCG iteration inside the PCG kernel(s)
 
     # ---- end-to-end leg -----------------------------------------------------------------------------
     def step_e2e():
@@ -235,16 +237,25 @@ def main():
                 "ms_per_step": 1e3 * e2e_s},
         "gpu_launches": int(launches),
         "clocks": clk.summary(),
-        "roofline": {"kernel": "linearize+assemble (k_linearize + k_lm_sum + k_lm_finalize)", "bound": "hbm",
-                     "achieved": B_lin / (lin_ms * 1e-3) / 1e9, "peak": peak, "peak_kind": peak_kind, "unit": "GB/s",
-                     "frac": B_lin / (lin_ms * 1e-3) / 1e9 / peak, "traffic": None, "algorithmic_bytes": B_lin,
-                     "ms": lin_ms, "note": "working set is L2-resident at this size" if B_lin < 100e6 else ""},
-        "roofline_pcg_iteration": {"bound": "hbm", "achieved": B_pcg / (pcg_ms * 1e-3) / 1e9, "peak": peak, "unit": "GB/s",
-                                   "frac": B_pcg / (pcg_ms * 1e-3) / 1e9 / peak, "algorithmic_bytes": B_pcg, "ms": pcg_ms},
+        # dominant kernel of the step (profiles/: > 90 % of the C2 step): the persistent PCG kernel, one launch per solve.
+        # algorithmic bytes per launch = B_pcg x the PCG iterations of that solve; duration by CUDA events around the launch.
+        "roofline": {"kernel": "k_pcg_persistent (whole PCG solve in one cooperative launch)" if world == 1 else "k_pcg_* phases + NCCL all-reduces",
+                     "bound": "hbm", "achieved": B_pcg / (pcg_ms * 1e-3) / 1e9, "peak": peak, "peak_kind": peak_kind, "unit": "GB/s",
+                     "frac": B_pcg / (pcg_ms * 1e-3) / 1e9 / peak, "traffic": None,
+                     "algorithmic_bytes_per_launch": B_pcg * pcg_total / GN_ITERS, "algorithmic_bytes_per_pcg_iteration": B_pcg,
+                     "launch_ms": ms_pcg / GN_ITERS, "pcg_iterations_per_launch": pcg_total / GN_ITERS,
+                     "share_of_step": ms_pcg / dev_ms,
+                     "note": "working set (%.0f MB) is L2-resident at this size: latency-bound, not HBM-bound" % (B_pcg / 1e6) if B_pcg < 100e6 else ""},
+        "roofline_linearize": {"kernel": "k_odom + k_linearize[_stream] + k_lm_sum", "bound": "hbm",
+                               "achieved": B_lin / (lin_ms * 1e-3) / 1e9, "peak": peak, "unit": "GB/s",
+                               "frac": B_lin / (lin_ms * 1e-3) / 1e9 / peak, "algorithmic_bytes": B_lin, "ms": lin_ms,
+                               "note": "working set is L2-resident at this size" if B_lin < 100e6 else ""},
+        "solve_breakdown_ms_per_gn": {"linearize": ms_lin, "solve_total": ms_sol / GN_ITERS, "pcg": ms_pcg / GN_ITERS,
+                                      "schur_prep_and_coarse_setup": (ms_sol - ms_pcg) / GN_ITERS, "coarse_refreshes_per_step": refreshes},
     }
 
     # ---- the north-star size (1M poses / 20M edges) for the linearize roofline, single GPU only ---------------
-    if world == 1 and not args.no_c4 and args.workload != "c4":
+    if not args.no_c4 and args.workload != "c4":
         try:
             p4, c4 = make_workload("c4")
             r4 = torch.frombuffer(bytearray(p4), dtype=torch.uint8)
@@ -256,9 +267,11 @@ def main():
                 if i >= 3:
                     l4.append(st.ms_linearize)
             ms4 = float(np.median(l4)); B4, _ = algorithmic_bytes(c4)
+            if world > 1:                                     # edge-sharded over the ranks: the slowest rank counts
+                t4 = torch.tensor([ms4], dtype=torch.float64, device="cuda"); dist.all_reduce(t4, op=dist.ReduceOp.MAX); ms4 = float(t4.item())
             line["roofline_linearize_c4"] = {"workload": f"c4: P={c4['P']} L={c4['L']} Eo={c4['Eo']} El={c4['El']}", "bound": "hbm",
-                                             "achieved": B4 / (ms4 * 1e-3) / 1e9, "peak": peak, "unit": "GB/s",
-                                             "frac": B4 / (ms4 * 1e-3) / 1e9 / peak, "algorithmic_bytes": B4, "ms": ms4,
+                                             "achieved": B4 / (ms4 * 1e-3) / 1e9, "peak": peak * world, "unit": "GB/s", "n_gpus": world,
+                                             "frac": B4 / (ms4 * 1e-3) / 1e9 / (peak * world), "algorithmic_bytes": B4, "ms": ms4,
                                              "edges_linearized_per_s": (c4["Eo"] + c4["El"]) / (ms4 * 1e-3)}
         except Exception as e:                                # never lose the main line to the extra measurement
             line["roofline_linearize_c4"] = {"error": str(e)}

@@ -85,6 +85,8 @@ typedef struct tsb_report {
     int64_t kernel_launches;   /* kernels this library launched during the call                       */
     float ms_total;            /* device time of the whole call (CUDA events)                         */
     float ms_linearize_total, ms_solve_total;
+    float ms_pcg_total;        /* part of ms_solve_total spent in the PCG itself (the persistent kernel when world == 1) */
+    int32_t coarse_refreshes;  /* how many solves rebuilt the coarse operator of the two-level preconditioner */
 } tsb_report;
 
 /* world > 1: rank 0 calls this once and ships the 128 bytes to every rank (e.g. over torch.distributed or MPI) */

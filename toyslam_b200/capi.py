@@ -49,7 +49,8 @@ class IterStats(C.Structure):
 class Report(C.Structure):
     _fields_ = [("iterations_run", C.c_int32), ("exit_code", C.c_int32), ("final_chi2", C.c_double),
                 ("pcg_iters_total", C.c_int64), ("kernel_launches", C.c_int64), ("ms_total", C.c_float),
-                ("ms_linearize_total", C.c_float), ("ms_solve_total", C.c_float)]
+                ("ms_linearize_total", C.c_float), ("ms_solve_total", C.c_float), ("ms_pcg_total", C.c_float),
+                ("coarse_refreshes", C.c_int32)]
 
 
 _lib = None

@@ -22,7 +22,7 @@ struct tsb_ctx {
     tsb_config cfg{};
     std::string err;
     cudaStream_t stream = nullptr;
-    cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
+    cudaEvent_t ev[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};   // [4],[5]: around the PCG proper
     HostGraph g;
     Structure st;
     Dev d{};
@@ -35,14 +35,14 @@ struct tsb_ctx {
     bool force_phased = false;                            // TSB_PCG_PHASED=1: one launch per PCG phase (the multi-GPU path)
     uint64_t h2d = 0, d2h = 0;                            // bytes copied since the last tsb_load_*
     ncclComm_t comm = nullptr;                            // world > 1: one communicator, collectives on `stream`
-    // two-level preconditioner: dense coarse operator factored and inverted with cuSOLVER (potrf + potri)
+    // two-level preconditioner: dense coarse operator factored and inverted with cuSOLVER (potrf + potrs against I)
     bool use_coarse = true;                               // TSB_COARSE=0: block-Jacobi only
     cusolverDnHandle_t solver = nullptr;
     double* cwork = nullptr; int cwork_len = 0;
     // the coarse inverse is reused across GN iterations while it keeps working (any SPD M is a valid
     // preconditioner; a stale one only costs iterations): refreshed on the first solve of a request, when the
     // PCG needs > 1.25x the iterations it took right after the last refresh, or after `coarse_max_age` solves
-    int coarse_age = -1, coarse_ref_iters = 0, coarse_max_age = 16;
+    int coarse_age = -1, coarse_ref_iters = 0, coarse_max_age = 16, coarse_refreshes = 0, coarse_hold = 0, coarse_backoff = 1;
 };
 
 namespace {
@@ -133,14 +133,13 @@ int upload_graph(tsb_ctx* c) {
     TRY(upload(c, d.aslot_ptr, s.aslot_ptr)); TRY(upload(c, d.aslot_edge, s.aslot_edge));
     TRY(upload(c, d.cpair_a, s.cpair_a)); TRY(upload(c, d.cpair_b, s.cpair_b)); TRY(upload(c, d.cpair_ptr, s.cpair_ptr));
     TRY(upload(c, d.ctrip, s.ctrip));
-    TRY(dalloc(c, d.zoff, d.nP)); TRY(dalloc(c, d.cC, 6ull * d.nAS)); TRY(dalloc(c, d.Ac, (size_t)d.nc * d.nc));
+    TRY(dalloc(c, d.zoff, d.nP)); TRY(dalloc(c, d.cC, 6ull * d.nAS)); TRY(dalloc(c, d.Ac, (size_t)d.nc * d.nc)); TRY(dalloc(c, d.Ai, (size_t)d.nc * d.nc));
     TRY(dalloc(c, d.rcp, 3ull * d.nSeg)); TRY(dalloc(c, d.yc, d.nc)); TRY(dalloc(c, d.cdot, d.nc)); TRY(dalloc(c, d.cinfo, (size_t)2));
     CU(cudaMemsetAsync(d.cinfo, 0, 8, c->stream));
     if (c->use_coarse && d.nc) {
         int l1 = 0, l2 = 0;
-        if (cusolverDnDpotrf_bufferSize(c->solver, CUBLAS_FILL_MODE_LOWER, (int)d.nc, d.Ac, (int)d.nc, &l1) != CUSOLVER_STATUS_SUCCESS ||
-            cusolverDnDpotri_bufferSize(c->solver, CUBLAS_FILL_MODE_LOWER, (int)d.nc, d.Ac, (int)d.nc, &l2) != CUSOLVER_STATUS_SUCCESS) {
-            c->err = "cusolverDnDpotrf/potri_bufferSize failed"; return TSB_ECUDA; }
+        if (cusolverDnDpotrf_bufferSize(c->solver, CUBLAS_FILL_MODE_LOWER, (int)d.nc, d.Ac, (int)d.nc, &l1) != CUSOLVER_STATUS_SUCCESS) {
+            c->err = "cusolverDnDpotrf_bufferSize failed"; return TSB_ECUDA; }
         c->cwork_len = std::max(l1, l2);
         TRY(dalloc(c, c->cwork, (size_t)c->cwork_len));
     }
@@ -185,7 +184,8 @@ int fetch_scalars(tsb_ctx* c) {
 // (Hll, b_l) sums and chi2 are summed over ranks before the landmark blocks are inverted.
 int enqueue_linearize(tsb_ctx* c) {
     launch_linearize(c->d, c->stream);
-    launch_lm_sum(c->d, c->stream);
+    if (c->cfg.world <= 1) { launch_lm_sum(c->d, true, c->stream); return TSB_OK; }     // sum + finalize in one kernel
+    launch_lm_sum(c->d, false, c->stream);
     TRY(allreduce(c, c->d.lm_sum, 5ull * c->g.L));
     TRY(allreduce(c, c->d.scal + S_CHI2, 1));
     launch_lm_finalize(c->d, c->stream);
@@ -197,15 +197,30 @@ int run_solve(tsb_ctx* c, bool refresh_coarse = true) {
     const Dev& d = c->d;
     launch_schur_prep(d, c->stream);
     if (c->use_coarse && d.nc && (refresh_coarse || c->coarse_age < 0)) {
-        c->coarse_age = 0;
+        c->coarse_age = 0; ++c->coarse_refreshes;
         // coarse operator Ac = Z^T S Z of this rank's poses, inverted explicitly so that the PCG applies it as a
         // dense mat-vec; a failed factorisation (cinfo != 0) turns the coarse level off for this solve on the device
+        cudaEvent_t te[4] = {nullptr, nullptr, nullptr, nullptr};
+        const bool timing = d.dbg != nullptr;
+        if (timing) { for (auto& e : te) cudaEventCreate(&e); cudaEventRecord(te[0], c->stream); }
         launch_coarse_assemble(d, c->stream);
-        if (cusolverDnDpotrf(c->solver, CUBLAS_FILL_MODE_LOWER, (int)d.nc, d.Ac, (int)d.nc, c->cwork, c->cwork_len, d.cinfo) != CUSOLVER_STATUS_SUCCESS ||
-            cusolverDnDpotri(c->solver, CUBLAS_FILL_MODE_LOWER, (int)d.nc, d.Ac, (int)d.nc, c->cwork, c->cwork_len, d.cinfo + 1) != CUSOLVER_STATUS_SUCCESS) {
-            c->err = "cusolverDnDpotrf/potri failed"; return TSB_ECUDA; }
+        if (timing) cudaEventRecord(te[1], c->stream);
+        if (cusolverDnDpotrf(c->solver, CUBLAS_FILL_MODE_LOWER, (int)d.nc, d.Ac, (int)d.nc, c->cwork, c->cwork_len, d.cinfo) != CUSOLVER_STATUS_SUCCESS) {
+            c->err = "cusolverDnDpotrf failed"; return TSB_ECUDA; }
+        if (timing) cudaEventRecord(te[2], c->stream);
+        // inverse = solve against the identity (two triangular solves with nc right-hand sides); potri was 3.5x slower
+        launch_coarse_identity(d, c->stream);
+        if (cusolverDnDpotrs(c->solver, CUBLAS_FILL_MODE_LOWER, (int)d.nc, (int)d.nc, d.Ac, (int)d.nc, d.Ai, (int)d.nc, d.cinfo + 1) != CUSOLVER_STATUS_SUCCESS) {
+            c->err = "cusolverDnDpotrs failed"; return TSB_ECUDA; }
         launch_coarse_finish(d, c->stream);
+        if (timing) {
+            cudaEventRecord(te[3], c->stream); cudaEventSynchronize(te[3]);
+            float a = 0, b = 0, e = 0; cudaEventElapsedTime(&a, te[0], te[1]); cudaEventElapsedTime(&b, te[1], te[2]); cudaEventElapsedTime(&e, te[2], te[3]);
+            std::fprintf(stderr, "[tsb] coarse setup nc=%u: assemble %.3f ms, potrf %.3f ms, potrs(I) %.3f ms\n", d.nc, a, b, e);
+            for (auto& ev : te) cudaEventDestroy(ev);
+        }
     }
+    cudaEventRecord(c->ev[4], c->stream);
     // single GPU: the whole PCG and the back-substitution run in one persistent cooperative kernel
     if (c->cfg.world <= 1 && !c->force_phased && launch_pcg_persistent(d, c->stream)) {
         if (d.dbg) {
@@ -218,6 +233,7 @@ int run_solve(tsb_ctx* c, bool refresh_coarse = true) {
             for (int q = 0; q < 8; ++q) std::fprintf(stderr, " %s=%lld", nm[q], its ? t[q] / its : 0);
             std::fprintf(stderr, "\n");
         }
+        cudaEventRecord(c->ev[5], c->stream);
         return TSB_OK;
     }
     // one launch per phase, collectives between the phases (the multi-GPU path; also TSB_PCG_PHASED=1)
@@ -253,6 +269,7 @@ int run_solve(tsb_ctx* c, bool refresh_coarse = true) {
     launch_pcg_mid(d, 1, c->stream);
     TRY(allreduce(c, d.w_sum, 2ull * c->g.L));
     launch_backsub(d, c->stream);
+    cudaEventRecord(c->ev[5], c->stream);
     return TSB_OK;
 }
 
@@ -451,9 +468,9 @@ int tsb_optimize(tsb_ctx* c, uint32_t iterations, tsb_report* rep, tsb_iter_stat
     CU(cudaSetDevice(c->cfg.device));
     const uint64_t launches0 = g_launches;
     const bool exits = c->cfg.enable_exits != 0;
-    double prevErr = -1, prev2Err = -1, err = 0; int penalty = 0, code = 0; uint32_t done = 0;
-    c->coarse_age = -1;                                  // every request starts from a fresh coarse operator
-    int64_t pcg_total = 0; float ms_lin = 0, ms_sol = 0;
+    double prevErr = -1, err = 0; int penalty = 0, code = 0; uint32_t done = 0;
+    c->coarse_age = -1; c->coarse_hold = 0; c->coarse_backoff = 1;   // every request starts from a fresh coarse operator
+    int64_t pcg_total = 0; float ms_lin = 0, ms_sol = 0, ms_pcg = 0; const int refreshes0 = c->coarse_refreshes;
     CU(cudaEventRecord(c->ev[3], c->stream));
     for (uint32_t it = 0; it < iterations; ++it) {
         CU(cudaEventRecord(c->ev[0], c->stream));
@@ -471,11 +488,17 @@ int tsb_optimize(tsb_ctx* c, uint32_t iterations, tsb_report* rep, tsb_iter_stat
                 }
             } else penalty = 0;
         }
-        // refresh while the system is still moving (chi2 changed by > 2 % over the last iteration: a stale
-        // operator then costs ~50 % more PCG iterations), when staleness has cost > 25 iterations, or by age
-        const bool moving = prevErr <= 0 || prev2Err <= 0 || std::fabs(prevErr - prev2Err) > 0.02 * std::fabs(prev2Err);
-        const bool refresh = c->coarse_age < 0 || c->coarse_age >= c->coarse_max_age || moving ||
-                             (c->coarse_age >= 1 && c->h_flags[F_ITERS] > c->coarse_ref_iters + 25);
+        // Refresh policy (iteration counts only: deterministic and identical on every rank).  A stale operator is
+        // probed after each refresh; if the very first stale solve already costs > 15 % more iterations the system
+        // is still moving and the next `backoff` solves refresh unconditionally (backoff doubles up to 16, halves
+        // when a stale operator lasted); otherwise it is kept until it degrades or reaches coarse_max_age.
+        bool refresh = c->coarse_age < 0 || c->coarse_age >= c->coarse_max_age;
+        if (!refresh && c->coarse_hold > 0) { refresh = true; --c->coarse_hold; }
+        if (!refresh && c->coarse_age >= 2 && 20 * c->h_flags[F_ITERS] > 23 * c->coarse_ref_iters + 100) {
+            refresh = true;
+            if (c->coarse_age == 2) { c->coarse_hold = c->coarse_backoff; c->coarse_backoff = std::min(2 * c->coarse_backoff, 16); }
+            else c->coarse_backoff = std::max(1, c->coarse_backoff / 2);
+        }
         TRY(run_solve(c, refresh));
         CU(cudaEventRecord(c->ev[2], c->stream));
         TRY(enqueue_update(c));
@@ -485,6 +508,7 @@ int tsb_optimize(tsb_ctx* c, uint32_t iterations, tsb_report* rep, tsb_iter_stat
         const double dnorm = std::sqrt(c->h_scal[S_DELTA2] + c->h_scal[S_DELTA2L]);
         float a = 0, b = 0;
         CU(cudaEventElapsedTime(&a, c->ev[0], c->ev[1])); CU(cudaEventElapsedTime(&b, c->ev[1], c->ev[2]));
+        { float p_ = 0; CU(cudaEventElapsedTime(&p_, c->ev[4], c->ev[5])); ms_pcg += p_; }
         ms_lin += a; ms_sol += b; pcg_total += c->h_flags[F_ITERS]; ++done;
         if (c->coarse_age == 0) c->coarse_ref_iters = c->h_flags[F_ITERS];
         ++c->coarse_age;
@@ -492,7 +516,7 @@ int tsb_optimize(tsb_ctx* c, uint32_t iterations, tsb_report* rep, tsb_iter_stat
             s.pcg_rel_residual = c->h_scal[S_RZ0] > 0 ? std::sqrt(c->h_scal[S_RZ] / c->h_scal[S_RZ0]) : 0; s.ms_linearize = a; s.ms_solve = b; }
         if (exits && std::fabs(err - prevErr) < 0.001) { code = 2; if (c->cfg.verbose) std::printf("Plateau: NO MORE OPT\n"); break; }
         if (exits && dnorm < 0.001) { code = 3; if (c->cfg.verbose) std::printf("CONVERGED\n"); break; }
-        prev2Err = prevErr; prevErr = err;
+        prevErr = err;
     }
     CU(cudaEventRecord(c->ev[2], c->stream));
     CU(cudaEventSynchronize(c->ev[2]));
@@ -500,6 +524,7 @@ int tsb_optimize(tsb_ctx* c, uint32_t iterations, tsb_report* rep, tsb_iter_stat
     c->linearized = c->solved = false;
     if (rep) { rep->iterations_run = (int32_t)done; rep->exit_code = code; rep->final_chi2 = err; rep->pcg_iters_total = pcg_total;
         rep->kernel_launches = (int64_t)(g_launches - launches0); rep->ms_linearize_total = ms_lin; rep->ms_solve_total = ms_sol;
+        rep->ms_pcg_total = ms_pcg; rep->coarse_refreshes = c->coarse_refreshes - refreshes0;
         CU(cudaEventElapsedTime(&rep->ms_total, c->ev[3], c->ev[2])); }
     return TSB_OK;
 }

@@ -71,21 +71,23 @@ struct Dev {
     const uint32_t* aslot_edge; const uint32_t* cpair_a; const uint32_t* cpair_b; const uint32_t* cpair_ptr; const uint32_t* ctrip;
     double2* zoff;              // per pose: (-(y - cy), x - cx) about its aggregate's centroid -> third column of Z_i
     double* cC;                 // 6 per aslot: sum of Hpl_e^T Z_i (2x3 row-major)
-    double* Ac;                 // nc x nc: Z^T S Z, overwritten by its inverse
+    double* Ac;                 // nc x nc: Z^T S Z, overwritten by its Cholesky factor
+    double* Ai;                 // nc x nc: (Z^T S Z)^-1, applied as a dense mat-vec by the PCG
     double* rcp;                // 3 per segment: Z^T r summed over the segment's 32 poses
     double* yc;                 // nc: coarse correction Ac^-1 (Z^T r)
     double* cdot;               // nc: (Z^T r)_j * yc_j  (the coarse part of r'z)
-    int* cinfo;                 // potrf / potri status words
+    int* cinfo;                 // potrf / potrs status words
     long long* dbg;             // optional: 8 phase-cycle counters of the persistent PCG kernel (TSB_PCG_TIMING=1)
 };
 
 // kernel launchers (kernels.cu).  All take the launching stream.
 void launch_linearize(const Dev& d, cudaStream_t s);            // K1: residuals, Jacobians, Hpl, pose-side H/b, slot partials
-void launch_lm_sum(const Dev& d, cudaStream_t s);               // K2a: landmark-major sum of slot partials
+void launch_lm_sum(const Dev& d, bool finalize, cudaStream_t s);   // K2a: landmark-major sum of slot partials (+ K2b when finalize)
 void launch_lm_finalize(const Dev& d, cudaStream_t s);          // K2b: Hll, b_l, prior, Hll^-1; chi2
 void launch_schur_prep(const Dev& d, cudaStream_t s);           // K3: diag(S)^-1 and reduced rhs
 void launch_coarse_assemble(const Dev& d, cudaStream_t s);      // zoff, C, Ac = Z^T S Z (dense, deterministic)
-void launch_coarse_finish(const Dev& d, cudaStream_t s);        // mirror the inverse's triangle, set F_COARSE from cinfo
+void launch_coarse_identity(const Dev& d, cudaStream_t s);      // Ai = I (right-hand side of the inverse solve)
+void launch_coarse_finish(const Dev& d, cudaStream_t s);        // set F_COARSE from cinfo
 void launch_pcg_coarse(const Dev& d, int init, cudaStream_t s);           // yc = Ac^-1 Z^T r, cdot (phased path)
 bool launch_pcg_persistent(const Dev& d, cudaStream_t s);     // whole PCG + back-substitution, one cooperative launch
 void launch_pcg_init(const Dev& d, cudaStream_t s);

@@ -293,33 +293,45 @@ __global__ void __launch_bounds__(kThreads, 4) k_linearize(const Dev d) {
 // K2a: landmark-major sum of the slot partials (5 values per landmark), fixed order.
 // K2b: prior, Hll, b_l, Hll^-1 (closed-form 2x2).
 // ------------------------------------------------------------------------------------------------
-__global__ void k_lm_sum(const Dev d) {
+// prior, Hll, b_l and the closed-form inverse of the 2x2 landmark block from the five landmark sums
+__device__ __forceinline__ void lm_finalize_one(const Dev& d, uint32_t l, double a0, double a1, double a2, double a3, double a4) {
+    const double prior = 1e6 * (double)d.fixed_lm_count[l];
+    const double h00 = a0 + prior, h01 = a1, h11 = a2 + prior;
+    d.hll[3ull * l] = h00; d.hll[3ull * l + 1] = h01; d.hll[3ull * l + 2] = h11;
+    d.bl[2ull * l] = -a3; d.bl[2ull * l + 1] = -a4;               // b_l -= B^T W e
+    const double id = 1.0 / (h00 * h11 - h01 * h01);
+    d.hinv[3ull * l] = h11 * id; d.hinv[3ull * l + 1] = -h01 * id; d.hinv[3ull * l + 2] = h00 * id;
+}
+
+// Warp per landmark.  Lane (j, comp) = (lane / 5, lane % 5), lanes 0..29: slot partials j, j+6, j+12, ... of the
+// landmark are summed in order (the five components of a slot are one contiguous 40-byte read), then the six
+// strided sums are combined as ((v0+v1)+(v2+v3))+(v4+v5): a fixed order.  FIN (world == 1): finalize in place.
+template <bool FIN>
+__global__ void __launch_bounds__(kThreads) k_lm_sum(const Dev d) {
     const uint32_t l = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
     if (l >= d.L) return;
-    double a[5] = {0, 0, 0, 0, 0};
-    for (uint32_t q = d.lm_part_ptr[l] + lane; q < d.lm_part_ptr[l + 1]; q += 32) {
-        const double* r = d.lm_part + 5ull * d.lm_part_idx[q];
-#pragma unroll
-        for (int k = 0; k < 5; ++k) a[k] += r[k];
+    const uint32_t j = lane / 5, comp = lane - 5 * j;
+    double a = 0;
+    if (lane < 30) {
+        const uint32_t qe = d.lm_part_ptr[l + 1];
+        for (uint32_t q = d.lm_part_ptr[l] + j; q < qe; q += 6) a += d.lm_part[5ull * d.lm_part_idx[q] + comp];
     }
-#pragma unroll
-    for (int k = 0; k < 5; ++k) {
-#pragma unroll
-        for (int o = 16; o > 0; o >>= 1) a[k] += __shfl_xor_sync(0xffffffffu, a[k], o);
-    }
-    if (lane < 5) d.lm_sum[5ull * l + lane] = lane == 0 ? a[0] : lane == 1 ? a[1] : lane == 2 ? a[2] : lane == 3 ? a[3] : a[4];
+    const uint32_t c = lane < 5 ? lane : 0;
+    const double v0 = __shfl_sync(0xffffffffu, a, c), v1 = __shfl_sync(0xffffffffu, a, c + 5), v2 = __shfl_sync(0xffffffffu, a, c + 10);
+    const double v3 = __shfl_sync(0xffffffffu, a, c + 15), v4 = __shfl_sync(0xffffffffu, a, c + 20), v5 = __shfl_sync(0xffffffffu, a, c + 25);
+    const double t = ((v0 + v1) + (v2 + v3)) + (v4 + v5);
+    if (FIN) {
+        const double s0 = __shfl_sync(0xffffffffu, t, 0), s1 = __shfl_sync(0xffffffffu, t, 1), s2 = __shfl_sync(0xffffffffu, t, 2);
+        const double s3 = __shfl_sync(0xffffffffu, t, 3), s4 = __shfl_sync(0xffffffffu, t, 4);
+        if (lane == 0) lm_finalize_one(d, l, s0, s1, s2, s3, s4);
+    } else if (lane < 5) d.lm_sum[5ull * l + lane] = t;
 }
 
 __global__ void k_lm_finalize(const Dev d) {
     const uint32_t l = blockIdx.x * blockDim.x + threadIdx.x;
     if (l >= d.L) return;
     const double* a = d.lm_sum + 5ull * l;
-    const double prior = 1e6 * (double)d.fixed_lm_count[l];
-    const double h00 = a[0] + prior, h01 = a[1], h11 = a[2] + prior;
-    d.hll[3ull * l] = h00; d.hll[3ull * l + 1] = h01; d.hll[3ull * l + 2] = h11;
-    d.bl[2ull * l] = -a[3]; d.bl[2ull * l + 1] = -a[4];           // b_l -= B^T W e
-    const double id = 1.0 / (h00 * h11 - h01 * h01);
-    d.hinv[3ull * l] = h11 * id; d.hinv[3ull * l + 1] = -h01 * id; d.hinv[3ull * l + 2] = h00 * id;
+    lm_finalize_one(d, l, a[0], a[1], a[2], a[3], a[4]);
 }
 
 __global__ void k_reduce2_to(const double* a, uint32_t na, const double* b, uint32_t nb, double* out) {
@@ -582,7 +594,7 @@ __device__ __forceinline__ void coarse_phase(const Dev& d, uint32_t gwarp, uint3
     __syncthreads();
     const uint32_t lane = threadIdx.x & 31;
     for (uint32_t j = gwarp; j < nc; j += nwarps) {
-        const double* row = d.Ac + (size_t)j * nc;
+        const double* row = d.Ai + (size_t)j * nc;
         double t0 = 0, t1 = 0;
         uint32_t k = lane;
 #pragma unroll 4
@@ -693,15 +705,14 @@ __global__ void k_coarse_lm(const Dev d) {
         for (int c = 0; c < 3; ++c) blk[(size_t)r * d.nc + c] -= acc[3 * r + c];
 }
 
-// after potrf + potri (column-major lower = row-major upper holds the inverse): mirror it and publish the status
-__global__ void k_coarse_finish(const Dev d) {
-    const bool ok = d.cinfo[0] == 0 && d.cinfo[1] == 0;
+__global__ void k_coarse_identity(const Dev d) {
     const size_t n = d.nc, tot = n * n;
-    for (size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x; idx < tot; idx += (size_t)gridDim.x * blockDim.x) {
-        const size_t i = idx / n, j = idx % n;
-        if (i > j) d.Ac[idx] = d.Ac[j * n + i];
-    }
-    if (blockIdx.x == 0 && threadIdx.x == 0) d.flags[F_COARSE] = ok ? 1 : 0;
+    for (size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x; idx < tot; idx += (size_t)gridDim.x * blockDim.x)
+        d.Ai[idx] = (idx / n == idx % n) ? 1.0 : 0.0;
+}
+// after potrf + potrs: publish whether the coarse inverse is usable for this solve
+__global__ void k_coarse_finish(const Dev d) {
+    if (threadIdx.x == 0) d.flags[F_COARSE] = (d.cinfo[0] == 0 && d.cinfo[1] == 0) ? 1 : 0;
 }
 
 // ---- one launch per phase (used when collectives sit between the phases, world > 1) -------------------
@@ -1002,8 +1013,11 @@ void launch_linearize(const Dev& d, cudaStream_t s) {
     } else if (d.nBlocks) { k_linearize<<<d.nBlocks, kThreads, LayLin::bytes, s>>>(d); ++g_launches; }
     k_reduce2_to<<<1, 1024, 0, s>>>(d.part2, nob, d.part, nparts, d.scal + S_CHI2); ++g_launches;
 }
-void launch_lm_sum(const Dev& d, cudaStream_t s) {
-    if (d.L) { k_lm_sum<<<cdiv(d.L, kThreads / 32), kThreads, 0, s>>>(d); ++g_launches; }
+void launch_lm_sum(const Dev& d, bool finalize, cudaStream_t s) {
+    if (!d.L) return;
+    if (finalize) k_lm_sum<true><<<cdiv(d.L, kThreads / 32), kThreads, 0, s>>>(d);
+    else k_lm_sum<false><<<cdiv(d.L, kThreads / 32), kThreads, 0, s>>>(d);
+    ++g_launches;
 }
 void launch_lm_finalize(const Dev& d, cudaStream_t s) {
     if (d.L) { k_lm_finalize<<<cdiv(d.L, kThreads), kThreads, 0, s>>>(d); ++g_launches; }
@@ -1034,9 +1048,8 @@ void launch_coarse_assemble(const Dev& d, cudaStream_t s) {
     k_coarse_pose<<<cdiv(d.nA * 32, kThreads), kThreads, 0, s>>>(d); ++g_launches;
     if (d.nPairs) { k_coarse_lm<<<cdiv(d.nPairs, 128), 128, 0, s>>>(d); ++g_launches; }
 }
-void launch_coarse_finish(const Dev& d, cudaStream_t s) {
-    k_coarse_finish<<<148 * 4, kThreads, 0, s>>>(d); ++g_launches;
-}
+void launch_coarse_identity(const Dev& d, cudaStream_t s) { k_coarse_identity<<<148 * 4, kThreads, 0, s>>>(d); ++g_launches; }
+void launch_coarse_finish(const Dev& d, cudaStream_t s) { k_coarse_finish<<<1, 32, 0, s>>>(d); ++g_launches; }
 void launch_pcg_coarse(const Dev& d, int init, cudaStream_t s) {
     if (d.nc) { k_pcg_coarse<<<cdiv(d.nc, kThreads / 32), kThreads, 0, s>>>(d, init); ++g_launches; }
 }

@@ -197,8 +197,9 @@ __global__ void __launch_bounds__(kLsThreads, 2) k_linearize_stream(const Dev d)
         }
         if (last) heavy = 0;
         // ---- landmark side: one partial per slot and component, edges of the slot in list order ----------------
+        // (items are dealt from the top thread down: the pose items above occupy the low threads, so both run at once)
 #pragma unroll 1
-        for (uint32_t item = tid; item < ns * 5; item += kLsThreads) {
+        for (uint32_t item = kLsThreads - 1 - tid; item < ns * 5; item += kLsThreads) {
             const uint32_t sl = item / 5, comp = item % 5;
             const double* s = rows + (comp < 3 ? comp : comp + 3) * kStageStride;
             d.lm_part[5ull * (cur.s0 + sl) + comp] = list_sum_lean(s, sedge, sptr[sl] - cur.e0, sptr[sl + 1] - cur.e0);
