@@ -215,6 +215,27 @@ def test_streaming_linearize_is_bit_identical(gpu, monkeypatch, case):
         assert np.array_equal(out[0][1][k], out[1][1][k]), k
 
 
+def test_resident_pcg_matches_streaming_pcg(gpu, monkeypatch):
+    """Small graphs run the shared-memory-resident PCG kernel (3 grid barriers per iteration); it must agree with
+    the general persistent kernel (TSB_NO_RESIDENT=1) and with block-Jacobi only (TSB_COARSE=0)."""
+    from toyslam_b200 import synth
+    payload = synth.to_payload(synth.make_config("c2", scale=0.3, seed=4))
+    res = []
+    for env in ({}, {"TSB_NO_RESIDENT": "1"}, {"TSB_COARSE": "0"}):
+        for k in ("TSB_NO_RESIDENT", "TSB_COARSE"):
+            monkeypatch.delenv(k, raising=False)
+        for k, v in env.items():
+            monkeypatch.setenv(k, v)
+        g = gpu(iterations=4, pcg_tol=1e-13, pcg_max_iters=20000, enable_exits=False); g.load_wire(payload)
+        rep, per = g.optimize()
+        assert all(p.pcg_rel_residual <= 1e-13 for p in per)
+        res.append((np.array([p.chi2 for p in per]), g.state(), rep.pcg_iters_total))
+    for other in res[1:]:
+        assert np.max(np.abs(res[0][0] - other[0]) / res[0][0]) < CHI2_TOL
+        assert state_diff(*res[0][1], *other[1]) < STATE_TOL
+    assert res[0][2] < res[2][2]            # the coarse level pays for itself
+
+
 def test_phased_pcg_path_matches_persistent(gpu, monkeypatch):
     """world == 1 normally runs the persistent cooperative PCG kernel; the one-launch-per-phase path
     (used when collectives sit between the phases) must give the same answer."""

@@ -25,6 +25,7 @@ struct tsb_ctx {
     cudaEvent_t ev[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};   // [4],[5]: around the PCG proper
     HostGraph g;
     Structure st;
+    ResidentPlan rp;                                      // rp.nb > 0: this graph runs the shared-memory-resident PCG kernel
     Dev d{};
     std::vector<void*> allocs;
     double4* pose0 = nullptr; double2* lm0 = nullptr;     // state as loaded (tsb_reset_state)
@@ -129,6 +130,12 @@ int upload_graph(tsb_ctx* c) {
     // coarse space
     d.aggK = s.agg_K; d.nA = s.nA; d.nc = 3 * s.nA; d.nAS = (uint32_t)s.aslot_lm.size(); d.nPairs = (uint32_t)s.cpair_a.size();
     d.nSeg = (d.nP + 31) / 32;
+    TRY(upload(c, d.agg_ptr, s.agg_ptr)); TRY(upload(c, d.pose_agg, s.pose_agg));
+    d.res_nb = c->rp.nb;
+    if (d.res_nb) {
+        TRY(upload(c, d.res_pose_cut, c->rp.pose_cut)); TRY(upload(c, d.res_lm_cut, c->rp.lm_cut)); TRY(upload(c, d.res_agg_cut, c->rp.agg_cut));
+        TRY(upload(c, d.lmo_ptr, c->rp.lmo_ptr)); TRY(upload(c, d.lmo_edge, c->rp.lmo_edge)); TRY(upload(c, d.edge_lm, c->rp.edge_lm));
+    }
     TRY(upload(c, d.edge_pose, s.edge_pose)); TRY(upload(c, d.aslot_lm, s.aslot_lm)); TRY(upload(c, d.aslot_agg, s.aslot_agg));
     TRY(upload(c, d.aslot_ptr, s.aslot_ptr)); TRY(upload(c, d.aslot_edge, s.aslot_edge));
     TRY(upload(c, d.cpair_a, s.cpair_a)); TRY(upload(c, d.cpair_b, s.cpair_b)); TRY(upload(c, d.cpair_ptr, s.cpair_ptr));
@@ -221,6 +228,11 @@ int run_solve(tsb_ctx* c, bool refresh_coarse = true) {
         }
     }
     cudaEventRecord(c->ev[4], c->stream);
+    if (d.res_nb) {            // small graph: Hpl stays in shared memory for the whole solve, three grid barriers per iteration
+        if (!launch_pcg_resident(d, c->stream)) { c->err = "resident PCG kernel could not be launched"; return TSB_ECUDA; }
+        cudaEventRecord(c->ev[5], c->stream);
+        return TSB_OK;
+    }
     // single GPU: the whole PCG and the back-substitution run in one persistent cooperative kernel
     if (c->cfg.world <= 1 && !c->force_phased && launch_pcg_persistent(d, c->stream)) {
         if (d.dbg) {
@@ -348,7 +360,10 @@ int tsb_load_wire(tsb_ctx* c, const void* payload, uint32_t nbytes) {
     CU(cudaSetDevice(c->cfg.device));
     free_graph(c); c->h2d = c->d2h = 0;
     if (!parse_wire((const uint8_t*)payload, nbytes, c->g, c->err)) return TSB_EPARSE;
-    build_structure(c->g, (uint32_t)c->cfg.rank, (uint32_t)c->cfg.world, c->st);
+    uint32_t res_nb = 0;
+    { const char* e = std::getenv("TSB_NO_RESIDENT");
+      if (c->cfg.world <= 1 && c->use_coarse && !c->force_phased && !(e && e[0] == '1')) res_nb = (uint32_t)resident_blocks_available(); }
+    build_structure(c->g, (uint32_t)c->cfg.rank, (uint32_t)c->cfg.world, c->st, res_nb, &c->rp);
     return upload_graph(c);
 }
 

@@ -69,6 +69,12 @@ struct Dev {
     uint32_t aggK, nA, nc, nAS, nPairs, nSeg;     // nc = 3 nA; nSeg = ceil(nP / 32) restriction segments
     const uint32_t* edge_pose; const uint32_t* aslot_lm; const uint32_t* aslot_agg; const uint32_t* aslot_ptr;
     const uint32_t* aslot_edge; const uint32_t* cpair_a; const uint32_t* cpair_b; const uint32_t* cpair_ptr; const uint32_t* ctrip;
+    const uint32_t* agg_ptr;    // nA + 1 pose offsets of the aggregates; pose_agg: aggregate of each pose
+    const uint32_t* pose_agg;
+    // resident plan (res_nb > 0): block b owns poses [res_pose_cut[b], +1), landmarks [res_lm_cut[b], +1), aggregates [res_agg_cut[b], +1)
+    uint32_t res_nb;
+    const uint32_t* res_pose_cut; const uint32_t* res_lm_cut; const uint32_t* res_agg_cut;
+    const uint32_t* lmo_ptr; const uint32_t* lmo_edge; const uint32_t* edge_lm;
     double2* zoff;              // per pose: (-(y - cy), x - cx) about its aggregate's centroid -> third column of Z_i
     double* cC;                 // 6 per aslot: sum of Hpl_e^T Z_i (2x3 row-major)
     double* Ac;                 // nc x nc: Z^T S Z, overwritten by its Cholesky factor
@@ -90,6 +96,8 @@ void launch_coarse_identity(const Dev& d, cudaStream_t s);      // Ai = I (right
 void launch_coarse_finish(const Dev& d, cudaStream_t s);        // set F_COARSE from cinfo
 void launch_pcg_coarse(const Dev& d, int init, cudaStream_t s);           // yc = Ac^-1 Z^T r, cdot (phased path)
 bool launch_pcg_persistent(const Dev& d, cudaStream_t s);     // whole PCG + back-substitution, one cooperative launch
+bool launch_pcg_resident(const Dev& d, cudaStream_t s);       // same, Hpl resident in shared memory (needs d.res_nb > 0)
+int resident_blocks_available();                              // SM count if the resident kernel can be co-scheduled, else 0
 void launch_pcg_init(const Dev& d, cudaStream_t s);
 void launch_pcg_pass_a(const Dev& d, int mode, cudaStream_t s); // mode 0: v = p (with p = z + beta p fused), 1: v = x
 void launch_pcg_mid(const Dev& d, int mode, cudaStream_t s);   // w = sum of slot partials; mode 0 also sp = Hpp p + ODOM part

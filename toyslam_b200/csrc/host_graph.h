@@ -71,18 +71,39 @@ struct Structure {
     // ---- coarse space of the two-level PCG preconditioner (this rank's poses only) -------------------
     // Aggregate a = local poses [a*agg_K, (a+1)*agg_K); agg_K is a multiple of 32 (one warp-wide restriction
     // segment).  An "aslot" is a distinct (aggregate, landmark) pair; C_aslot = sum of Hpl_e^T Z_pose(e).
-    uint32_t agg_K = 32, nA = 0;
+    uint32_t agg_K = 32, nA = 0;             // agg_K == 0: aggregates of varying size (resident plan), see agg_ptr
+    std::vector<uint32_t> agg_ptr;           // nA + 1 pose offsets; pose_agg: nP, aggregate of each pose
+    std::vector<uint32_t> pose_agg;
     std::vector<uint32_t> edge_pose;         // nE : local pose of each LM edge in assembly order
     std::vector<uint32_t> aslot_lm, aslot_agg;      // per aslot (sorted by aggregate, then landmark)
     std::vector<uint32_t> aslot_ptr, aslot_edge;    // nAS + 1 offsets into aslot_edge (assembly edge index, ascending)
     std::vector<uint32_t> cpair_a, cpair_b, cpair_ptr;   // coarse block pairs (a, b) sharing a landmark; offsets into ctrip
     std::vector<uint32_t> ctrip;             // 2 per triple: (aslot of a, aslot of b) with the same landmark, landmark ascending
 };
+// ---- resident plan (world == 1, graphs whose Hpl fits the shared memory of the whole GPU) -----------------
+// One block per SM owns a contiguous pose range with all its LM edges (assembly order) and a contiguous landmark
+// range with all its LM edges in landmark-major order; both copies of Hpl stay in shared memory for the whole PCG.
+struct ResidentPlan {
+    uint32_t nb = 0;                          // blocks; 0 = not resident
+    std::vector<uint32_t> pose_cut, lm_cut;   // nb + 1 each
+    std::vector<uint32_t> agg_cut;            // nb + 1: aggregates owned by each block (aggregates never straddle blocks)
+    std::vector<uint32_t> lmo_ptr;            // L + 1: landmark-major CSR over LM edges
+    std::vector<uint32_t> lmo_edge;           // nE: assembly index of each landmark-major position (ascending inside a landmark)
+    std::vector<uint32_t> edge_lm;            // nE: landmark of each LM edge in assembly order
+};
+constexpr uint32_t kResEdgeCap = 1280;    // LM edges per block, either order
+constexpr uint32_t kResPoseCap = 96;      // poses per block
+constexpr uint32_t kResLmCap = 64;        // landmarks per block
+constexpr uint32_t kResAggCap = 4;        // aggregates per block
+constexpr uint32_t kResOdomCap = 512;     // ODOM neighbour entries per block
 constexpr uint32_t kCoarseMaxAgg = 512;   // upper bound on aggregates per rank (coarse matrix is dense: (3*512)^2 doubles)
 
 constexpr uint32_t kChunkEdges = 512;   // LM edges staged per chunk
 constexpr uint32_t kBlockPoses = 128;   // poses per thread block (upper bound)
 
-void build_structure(const HostGraph& g, uint32_t rank, uint32_t world, Structure& s);
+// resident_blocks > 0 (world == 1): try to lay the graph out for the shared-memory-resident PCG kernel with that many
+// blocks; `rp.nb` stays 0 when it does not fit and the uniform aggregates (agg_K) are used instead
+void build_structure(const HostGraph& g, uint32_t rank, uint32_t world, Structure& s, uint32_t resident_blocks = 0,
+                     ResidentPlan* rp = nullptr);
 
 }  // namespace tsb

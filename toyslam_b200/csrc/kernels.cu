@@ -424,7 +424,7 @@ __device__ __forceinline__ void sym3_mul(const double* M, double a, double b, do
 // MODE 0: v = p after the fused update p = z + beta p;  MODE 1: v = x
 // z_i + Z_i yc[agg(i)] : the prolongated coarse correction added to the block-Jacobi part (component q of pose p)
 __device__ __forceinline__ double prolong(const Dev& d, uint32_t p, uint32_t q) {
-    const uint32_t a = p / d.aggK;
+    const uint32_t a = d.pose_agg[p];
     const double y2 = d.yc[3 * a + 2];
     if (q == 2) return y2;
     const double2 zo = d.zoff[p];
@@ -618,7 +618,7 @@ __device__ __forceinline__ void coarse_phase(const Dev& d, uint32_t gwarp, uint3
 __global__ void __launch_bounds__(kThreads) k_coarse_cen(const Dev d) {      // block per aggregate
     __shared__ double red[32];
     __shared__ double cxy[2];
-    const uint32_t a = blockIdx.x, p0 = a * d.aggK, p1 = min(d.nP, p0 + d.aggK);
+    const uint32_t a = blockIdx.x, p0 = d.agg_ptr[a], p1 = d.agg_ptr[a + 1];
     double sx = 0, sy = 0;
     for (uint32_t i = p0 + threadIdx.x; i < p1; i += kThreads) { const double4 ps = d.pose[i]; sx += ps.x; sy += ps.y; }
     const double tx = block_sum(sx, red), ty = block_sum(sy, red);
@@ -653,7 +653,7 @@ __global__ void k_coarse_pose(const Dev d) {
     const uint32_t a = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
     if (a >= d.nA || lane >= 9) return;
     const int r = lane / 3, c = lane % 3;
-    const uint32_t p0 = a * d.aggK, p1 = min(d.nP, p0 + d.aggK), nc = d.nc;
+    const uint32_t p0 = d.agg_ptr[a], p1 = d.agg_ptr[a + 1], nc = d.nc;
     double* rowp = d.Ac + (size_t)(3 * a + r) * nc;
     double diag = 0;
     for (uint32_t i = p0; i < p1; ++i) {
@@ -666,7 +666,7 @@ __global__ void k_coarse_pose(const Dev d) {
             if (j >= d.nP) continue;                                   // pose of another rank: not in this rank's coarse space
             const double* h = d.hoo + 3ull * k; zcol(d.zoff[j], c, b0, b1, b2);
             const double v = a0 * h[0] * b0 + a1 * h[1] * b1 + a2 * h[2] * b2;
-            const uint32_t b = j / d.aggK;
+            const uint32_t b = d.pose_agg[j];
             if (b == a) diag += v; else rowp[3 * b + c] += v;
         }
         for (uint32_t q = d.od_in_ptr[i]; q < d.od_in_ptr[i + 1]; ++q) {
@@ -674,7 +674,7 @@ __global__ void k_coarse_pose(const Dev d) {
             if (j >= d.nP) continue;
             const double* h = d.hoo + 3ull * k; zcol(d.zoff[j], c, b0, b1, b2);
             const double v = a0 * h[0] * b0 + a1 * h[1] * b1 + a2 * h[2] * b2;
-            const uint32_t b = j / d.aggK;
+            const uint32_t b = d.pose_agg[j];
             if (b == a) diag += v; else rowp[3 * b + c] += v;
         }
     }
@@ -905,6 +905,8 @@ __global__ void __launch_bounds__(kThreads, 3) k_pcg_persistent(const Dev d) {
     }
 }
 
+#include "pcg_resident.cuh"
+
 // delta_l = Hll^-1 (b_l - Hpl^T delta_p); w_sum holds Hpl^T delta_p
 __global__ void k_backsub(const Dev d) {
     const uint32_t l = blockIdx.x * blockDim.x + threadIdx.x;
@@ -1052,6 +1054,26 @@ void launch_coarse_identity(const Dev& d, cudaStream_t s) { k_coarse_identity<<<
 void launch_coarse_finish(const Dev& d, cudaStream_t s) { k_coarse_finish<<<1, 32, 0, s>>>(d); ++g_launches; }
 void launch_pcg_coarse(const Dev& d, int init, cudaStream_t s) {
     if (d.nc) { k_pcg_coarse<<<cdiv(d.nc, kThreads / 32), kThreads, 0, s>>>(d, init); ++g_launches; }
+}
+static int g_res_blocks = -1;      // SM count if k_pcg_resident can be co-scheduled with one block per SM, else 0
+int resident_blocks_available() {
+    if (g_res_blocks >= 0) return g_res_blocks;
+    int dev = 0, sms = 0, per_sm = 0, coop = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, dev);
+    if (cudaFuncSetAttribute(k_pcg_resident, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kResSmemBytes) != cudaSuccess) { cudaGetLastError(); per_sm = 0; }
+    else cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_pcg_resident, kResThreads, kResSmemBytes);
+    g_res_blocks = (coop && per_sm >= 1) ? sms : 0;
+    return g_res_blocks;
+}
+bool launch_pcg_resident(const Dev& d, cudaStream_t s) {
+    if (!d.res_nb || (int)d.res_nb != resident_blocks_available()) return false;
+    Dev dd = d; void* args[] = {&dd};
+    const cudaError_t e = cudaLaunchCooperativeKernel((void*)k_pcg_resident, dim3(d.res_nb), dim3(kResThreads), args, kResSmemBytes, s);
+    if (e != cudaSuccess) { cudaGetLastError(); return false; }
+    ++g_launches;
+    return true;
 }
 void launch_pcg_init(const Dev& d, cudaStream_t s) {
     const uint32_t nb = cdiv(d.nP, kThreads);

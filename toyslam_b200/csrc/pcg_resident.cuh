@@ -1,0 +1,255 @@
+// pcg_resident.cuh -- K4 for graphs whose Hpl fits the shared memory of the whole GPU (C2-class: <= ~1280 LM
+// edges per SM).  One block per SM, 1024 threads, one cooperative launch per solve.
+//
+// Why: at this size the PCG is latency-bound, not bandwidth-bound (profiles/r1_pcg_phase_cycles_c2.txt: five
+// phases of 3-5 us each, most of it dependent L2 round trips, plus five grid barriers per iteration).  Here
+//   * both orders of Hpl a block needs (its poses' edges in assembly order; its landmarks' edges in landmark-
+//     major order) are loaded into shared memory once per solve, with the block's pose vectors (x, r, p, S p,
+//     z), diagonal blocks, ODOM neighbour lists and landmark inverses: an iteration touches global memory only
+//     for what crosses blocks (p and z of other poses, u of other landmarks, 2 x nb partial dot products, nc
+//     coarse residuals);
+//   * the landmark sum is computed landmark-major (one warp per landmark gathers p = z + beta p_old of its
+//     edges' poses), so Hpl^T p needs no slot partials and no separate summation phase;
+//   * the coarse residual is carried by recurrence, rc -= alpha Z^T(S p), every block redundantly, so that the
+//     coarse solve of a block's own aggregates, the prolongation and r'z need no barrier of their own.
+// Three grid barriers per iteration instead of five.  Every sum runs in a fixed order (deterministic).
+//
+// Included inside the anonymous namespace of kernels.cu.
+
+constexpr int kResThreads = 1024;
+constexpr uint32_t kResEC = kResEdgeCap, kResPC = kResPoseCap, kResLC = kResLmCap, kResAC = kResAggCap, kResOC = kResOdomCap;
+
+struct ResSm {
+    double* hplP; double* hplL; double* rows; double* x; double* r; double* p; double* y; double* zf;
+    double* minv; double* hpp; double2* zoff; double* onb_h; double* hinvL; double* rc; double* yc; double* red;
+    uint32_t* elm; uint32_t* epos; uint32_t* eptr; uint32_t* lptr; uint32_t* pagg; uint32_t* onb_ptr; uint32_t* onb_idx;
+};
+constexpr size_t kResSmemBytes =
+    sizeof(double) * (6 * kResEC * 2 + 3 * kResEC + 5 * 3 * kResPC + 2 * 6 * kResPC + 2 * kResPC + 3 * kResOC + 3 * kResLC +
+                      3 * kCoarseMaxAgg + 3 * kResAC + 4 + 32) +
+    sizeof(uint32_t) * (2 * kResEC + (kResPC + 4) + (kResLC + 4) + kResPC + (kResPC + 4) + kResOC);
+
+__device__ __forceinline__ ResSm res_carve(unsigned char* b) {
+    ResSm s; double* f = reinterpret_cast<double*>(b);
+    s.hplP = f; f += 6 * kResEC; s.hplL = f; f += 6 * kResEC; s.rows = f; f += 3 * kResEC;
+    s.x = f; f += 3 * kResPC; s.r = f; f += 3 * kResPC; s.p = f; f += 3 * kResPC; s.y = f; f += 3 * kResPC; s.zf = f; f += 3 * kResPC;
+    s.minv = f; f += 6 * kResPC; s.hpp = f; f += 6 * kResPC; s.zoff = reinterpret_cast<double2*>(f); f += 2 * kResPC;
+    s.onb_h = f; f += 3 * kResOC; s.hinvL = f; f += 3 * kResLC; s.rc = f; f += 3 * kCoarseMaxAgg; s.yc = f; f += 3 * kResAC + 4;
+    s.red = f; f += 32;
+    uint32_t* u = reinterpret_cast<uint32_t*>(f);
+    s.elm = u; u += kResEC; s.epos = u; u += kResEC; s.eptr = u; u += kResPC + 4; s.lptr = u; u += kResLC + 4;
+    s.pagg = u; u += kResPC; s.onb_ptr = u; u += kResPC + 4; s.onb_idx = u;
+    return s;
+}
+
+// component q of Z_i^T v for pose-local vector v (3 doubles)
+__device__ __forceinline__ double res_zt(const double2 zo, const double* v, uint32_t q) {
+    return q == 0 ? v[0] : q == 1 ? v[1] : zo.x * v[0] + zo.y * v[1] + v[2];
+}
+
+// sum over the poses of aggregate `a` (local pose range [b, e)) of component q of Z_i^T v_i, in pose order
+__device__ __forceinline__ double res_restrict(const ResSm& s, const double* v, uint32_t b, uint32_t e, uint32_t q) {
+    double t = 0;
+    for (uint32_t i = b; i < e; ++i) t += res_zt(s.zoff[i], v + 3 * i, q);
+    return t;
+}
+
+// Coarse rows of this block's aggregates, prolongation, z = zj + Z yc (kept in zf, published to d.z) and the
+// block's part of r'z -> d.part2[block].  zf holds zj = blockdiag(S)^-1 r on entry.
+__device__ __forceinline__ void res_finish(const Dev& d, const ResSm& s, bool coarse, uint32_t p0, uint32_t np, uint32_t a0, uint32_t na) {
+    const uint32_t tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, nc = d.nc;
+    if (coarse) {
+        if (warp < 3 * na) {
+            const double* row = d.Ai + (size_t)(3 * a0 + warp) * nc;
+            double t0 = 0, t1 = 0;
+            uint32_t k = lane;
+#pragma unroll 4
+            for (; k + 32 < nc; k += 64) { t0 += row[k] * s.rc[k]; t1 += row[k + 32] * s.rc[k + 32]; }
+            if (k < nc) t0 += row[k] * s.rc[k];
+            double t = t0 + t1;
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) t += __shfl_xor_sync(0xffffffffu, t, o);
+            if (lane == 0) s.yc[warp] = t;
+        }
+        __syncthreads();
+    }
+    double dot = 0;
+    if (tid < 3 * np) {
+        const uint32_t pl = tid / 3, q = tid - 3 * pl;
+        double z = s.zf[tid];
+        if (coarse) {
+            const uint32_t a = s.pagg[pl];
+            const double y2 = s.yc[3 * a + 2];
+            z += q == 2 ? y2 : q == 0 ? s.yc[3 * a] + s.zoff[pl].x * y2 : s.yc[3 * a + 1] + s.zoff[pl].y * y2;
+        }
+        s.zf[tid] = z; d.z[3ull * p0 + tid] = z;
+        dot = s.r[tid] * z;
+    }
+    const double t = block_sum(dot, s.red);
+    if (tid == 0) d.part2[blockIdx.x] = t;
+}
+
+// landmark-major pass over this block's landmarks: w_l = sum_e Hpl_e^T v_pose(e), v = va + beta vb gathered from
+// global memory; MODE 0 stores u_l = Hll^-1 w_l to d.w_sum, MODE 1 stores delta_l = Hll^-1 (b_l - w_l) to d.dl
+template <int MODE>
+__device__ __forceinline__ void res_landmarks(const Dev& d, const ResSm& s, const double* va, const double* vb, double beta, uint32_t l0, uint32_t nl) {
+    const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    for (uint32_t l = warp; l < nl; l += kResThreads / 32) {
+        double w0 = 0, w1 = 0;
+        for (uint32_t k = s.lptr[l] + lane; k < s.lptr[l + 1]; k += 32) {
+            const uint32_t i = s.epos[k];
+            double v0 = va[3ull * i], v1 = va[3ull * i + 1], v2 = va[3ull * i + 2];
+            if (MODE == 0) { v0 += beta * vb[3ull * i]; v1 += beta * vb[3ull * i + 1]; v2 += beta * vb[3ull * i + 2]; }
+            const double* h = s.hplL + 6 * k;
+            w0 += h[0] * v0 + h[2] * v1 + h[4] * v2; w1 += h[1] * v0 + h[3] * v1 + h[5] * v2;
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) { w0 += __shfl_xor_sync(0xffffffffu, w0, o); w1 += __shfl_xor_sync(0xffffffffu, w1, o); }
+        if (lane == 0) {
+            const double* hi = s.hinvL + 3 * l;
+            if (MODE == 0) { d.w_sum[2ull * (l0 + l)] = hi[0] * w0 + hi[1] * w1; d.w_sum[2ull * (l0 + l) + 1] = hi[1] * w0 + hi[2] * w1; }
+            else { const double t0 = d.bl[2ull * (l0 + l)] - w0, t1 = d.bl[2ull * (l0 + l) + 1] - w1;
+                   d.dl[2ull * (l0 + l)] = hi[0] * t0 + hi[1] * t1; d.dl[2ull * (l0 + l) + 1] = hi[1] * t0 + hi[2] * t1; }
+        }
+    }
+}
+
+__global__ void __launch_bounds__(kResThreads, 1) k_pcg_resident(const Dev d) {
+    extern __shared__ __align__(32) unsigned char smem_raw[];
+    const ResSm s = res_carve(smem_raw);
+    cg::grid_group grid = cg::this_grid();
+    const uint32_t tid = threadIdx.x, b = blockIdx.x, nb = gridDim.x;
+    const uint32_t p0 = d.res_pose_cut[b], np = d.res_pose_cut[b + 1] - p0;
+    const uint32_t l0 = d.res_lm_cut[b], nl = d.res_lm_cut[b + 1] - l0;
+    const uint32_t a0 = d.res_agg_cut[b], na = d.res_agg_cut[b + 1] - a0;
+    const uint32_t e0 = d.pose_ptr[p0], ne = d.pose_ptr[p0 + np] - e0;
+    const uint32_t k0 = d.lmo_ptr[l0], nk = d.lmo_ptr[l0 + nl] - k0;
+    const bool coarse = d.flags[F_COARSE] != 0;
+    const uint32_t nc = d.nc;
+    const double tol2 = d.scal[S_TOL2]; const int maxit = d.flags[F_MAXIT];
+    double* pp[2] = {d.p, d.sp};                              // p of all poses, double-buffered across iterations
+
+    // ---- once per solve: everything this block owns goes to shared memory ------------------------------------
+    for (uint32_t i = tid; i < 6 * ne; i += kResThreads) s.hplP[i] = d.hpl[6ull * e0 + i];
+    for (uint32_t i = tid; i < ne; i += kResThreads) s.elm[i] = d.edge_lm[e0 + i];
+    for (uint32_t i = tid; i < 6 * nk; i += kResThreads) { const uint32_t k = i / 6; s.hplL[i] = d.hpl[6ull * d.lmo_edge[k0 + k] + (i - 6 * k)]; }
+    for (uint32_t k = tid; k < nk; k += kResThreads) s.epos[k] = d.edge_pose[d.lmo_edge[k0 + k]];
+    for (uint32_t i = tid; i <= np; i += kResThreads) s.eptr[i] = d.pose_ptr[p0 + i] - e0;
+    for (uint32_t i = tid; i <= nl; i += kResThreads) s.lptr[i] = d.lmo_ptr[l0 + i] - k0;
+    for (uint32_t i = tid; i < 3 * nl; i += kResThreads) s.hinvL[i] = d.hinv[3ull * l0 + i];
+    for (uint32_t i = tid; i < 6 * np; i += kResThreads) { s.minv[i] = d.minv[6ull * p0 + i]; s.hpp[i] = d.hpp[6ull * p0 + i]; }
+    for (uint32_t i = tid; i < np; i += kResThreads) { s.zoff[i] = d.zoff[p0 + i]; s.pagg[i] = d.pose_agg[p0 + i] - a0; }
+    for (uint32_t i = tid; i < 3 * np; i += kResThreads) {
+        s.r[i] = d.rhs[3ull * p0 + i]; s.x[i] = 0; s.p[i] = 0; pp[0][3ull * p0 + i] = 0;
+    }
+    if (tid == 0) {                                           // ODOM neighbour lists of the block's poses (CSR)
+        uint32_t n = 0;
+        for (uint32_t i = 0; i < np; ++i) {
+            s.onb_ptr[i] = n;
+            n += (d.od_out_ptr[p0 + i + 1] - d.od_out_ptr[p0 + i]) + (d.od_in_ptr[p0 + i + 1] - d.od_in_ptr[p0 + i]);
+        }
+        s.onb_ptr[np] = n;
+    }
+    __syncthreads();
+    if (tid < np) {
+        uint32_t n = s.onb_ptr[tid];
+        for (uint32_t k = d.od_out_ptr[p0 + tid]; k < d.od_out_ptr[p0 + tid + 1]; ++k, ++n) {
+            s.onb_idx[n] = d.od_b[k]; s.onb_h[3 * n] = d.hoo[3ull * k]; s.onb_h[3 * n + 1] = d.hoo[3ull * k + 1]; s.onb_h[3 * n + 2] = d.hoo[3ull * k + 2];
+        }
+        for (uint32_t q = d.od_in_ptr[p0 + tid]; q < d.od_in_ptr[p0 + tid + 1]; ++q, ++n) {
+            const uint32_t k = d.od_in_edge[q];
+            s.onb_idx[n] = d.od_a[k]; s.onb_h[3 * n] = d.hoo[3ull * k]; s.onb_h[3 * n + 1] = d.hoo[3ull * k + 1]; s.onb_h[3 * n + 2] = d.hoo[3ull * k + 2];
+        }
+        sym3_mul(s.minv + 6 * tid, s.r[3 * tid], s.r[3 * tid + 1], s.r[3 * tid + 2], s.zf[3 * tid], s.zf[3 * tid + 1], s.zf[3 * tid + 2]);
+    }
+    __syncthreads();
+    // coarse residual Z^T r: this block's aggregates -> global, then every block keeps the whole vector
+    if (coarse && tid < 3 * na) {
+        const uint32_t a = tid / 3, q = tid - 3 * a;
+        d.yc[3 * a0 + tid] = res_restrict(s, s.r, d.agg_ptr[a0 + a] - p0, d.agg_ptr[a0 + a + 1] - p0, q);
+    }
+    grid.sync();
+    if (coarse) { for (uint32_t k = tid; k < nc; k += kResThreads) s.rc[k] = d.yc[k]; __syncthreads(); }
+    res_finish(d, s, coarse, p0, np, a0, na);
+    grid.sync();
+
+    double rz = 0, rz0 = 0, rz_last = 0;
+    int it = 0, cur = 0;
+    for (;;) {
+        // ---- phase 1: beta, p = z + beta p (own poses), u_l = Hll^-1 Hpl^T p (own landmarks) -------------------
+        const double rz_new = reduce_all(d.part2, nb, s.red);
+        rz_last = rz_new;
+        double beta = 0;
+        if (it == 0) { rz0 = rz_new; if (!(rz0 > 0)) break; }
+        else { beta = rz_new / rz; if (!(rz_new > tol2 * rz0) || it >= maxit) break; }
+        rz = rz_new;
+        const double* pold = pp[cur]; double* pnew = pp[cur ^ 1];
+        if (tid < 3 * np) { const double v = fma(beta, s.p[tid], s.zf[tid]); s.p[tid] = v; pnew[3ull * p0 + tid] = v; }
+        {   // same arithmetic as the owner's line above, on gathered z and p_old
+            const uint32_t warp = tid >> 5, lane = tid & 31;
+            for (uint32_t l = warp; l < nl; l += kResThreads / 32) {
+                double w0 = 0, w1 = 0;
+                for (uint32_t k = s.lptr[l] + lane; k < s.lptr[l + 1]; k += 32) {
+                    const uint32_t i = s.epos[k];
+                    const double v0 = fma(beta, pold[3ull * i], d.z[3ull * i]), v1 = fma(beta, pold[3ull * i + 1], d.z[3ull * i + 1]);
+                    const double v2 = fma(beta, pold[3ull * i + 2], d.z[3ull * i + 2]);
+                    const double* h = s.hplL + 6 * k;
+                    w0 += h[0] * v0 + h[2] * v1 + h[4] * v2; w1 += h[1] * v0 + h[3] * v1 + h[5] * v2;
+                }
+#pragma unroll
+                for (int o = 16; o > 0; o >>= 1) { w0 += __shfl_xor_sync(0xffffffffu, w0, o); w1 += __shfl_xor_sync(0xffffffffu, w1, o); }
+                if (lane == 0) {
+                    const double* hi = s.hinvL + 3 * l;
+                    d.w_sum[2ull * (l0 + l)] = hi[0] * w0 + hi[1] * w1; d.w_sum[2ull * (l0 + l) + 1] = hi[1] * w0 + hi[2] * w1;
+                }
+            }
+        }
+        cur ^= 1;
+        grid.sync();
+        // ---- phase 2: y = S p for the own poses, p'y and Z^T y ---------------------------------------------------
+        double yo = 0;                                             // ODOM neighbours: blocks are diagonal, component-wise
+        const uint32_t pl = tid / 3, q = tid - 3 * pl;
+        if (tid < 3 * np) {
+            const double* pg = pp[cur];
+            for (uint32_t n = s.onb_ptr[pl]; n < s.onb_ptr[pl + 1]; ++n) yo += s.onb_h[3 * n + q] * pg[3ull * s.onb_idx[n] + q];
+        }
+        for (uint32_t e = tid; e < ne; e += kResThreads) {
+            const uint32_t l = s.elm[e];
+            const double u0 = d.w_sum[2ull * l], u1 = d.w_sum[2ull * l + 1];
+            const double* h = s.hplP + 6 * e;
+            s.rows[e] = h[0] * u0 + h[1] * u1; s.rows[kResEC + e] = h[2] * u0 + h[3] * u1; s.rows[2 * kResEC + e] = h[4] * u0 + h[5] * u1;
+        }
+        __syncthreads();
+        double dot = 0;
+        if (tid < 3 * np) {
+            const double acc = seg_sum_lean(s.rows + q * kResEC, s.eptr[pl], s.eptr[pl + 1]);
+            const double* H = s.hpp + 6 * pl; const double* v = s.p + 3 * pl;
+            const double hp = q == 0 ? H[0] * v[0] + H[1] * v[1] + H[2] * v[2] : q == 1 ? H[1] * v[0] + H[3] * v[1] + H[4] * v[2]
+                                                                                        : H[2] * v[0] + H[4] * v[1] + H[5] * v[2];
+            const double y = hp + yo - acc;
+            s.y[tid] = y; dot = s.p[tid] * y;
+        }
+        const double t = block_sum(dot, s.red);                    // (its barriers also publish s.y to the block)
+        if (tid == 0) d.part[b] = t;
+        if (coarse && tid < 3 * na) {
+            const uint32_t a = tid / 3, qa = tid - 3 * a;
+            d.cdot[3 * a0 + tid] = res_restrict(s, s.y, d.agg_ptr[a0 + a] - p0, d.agg_ptr[a0 + a + 1] - p0, qa);
+        }
+        grid.sync();
+        // ---- phase 3: alpha, x, r, coarse residual by recurrence, z and r'z ----------------------------------------
+        const double alpha = rz / reduce_all(d.part, nb, s.red);
+        if (coarse) for (uint32_t k = tid; k < nc; k += kResThreads) s.rc[k] -= alpha * d.cdot[k];
+        if (tid < 3 * np) { s.x[tid] += alpha * s.p[tid]; s.r[tid] -= alpha * s.y[tid]; }
+        __syncthreads();
+        if (tid < np) sym3_mul(s.minv + 6 * tid, s.r[3 * tid], s.r[3 * tid + 1], s.r[3 * tid + 2], s.zf[3 * tid], s.zf[3 * tid + 1], s.zf[3 * tid + 2]);
+        __syncthreads();
+        res_finish(d, s, coarse, p0, np, a0, na);
+        ++it;
+        grid.sync();
+    }
+    // ---- results: delta_p, the PCG scalars, landmark back-substitution delta_l = Hll^-1 (b_l - Hpl^T delta_p) ----
+    if (tid < 3 * np) d.x[3ull * p0 + tid] = s.x[tid];
+    if (b == 0 && tid == 0) { d.scal[S_RZ0] = rz0; d.scal[S_RZ] = rz_last; d.flags[F_ITERS] = it; d.flags[F_DONE] = 1; }
+    grid.sync();
+    res_landmarks<1>(d, s, d.x, nullptr, 0.0, l0, nl);
+}

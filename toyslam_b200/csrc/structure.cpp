@@ -12,7 +12,7 @@
 
 namespace tsb {
 
-void build_structure(const HostGraph& g, uint32_t rank, uint32_t world, Structure& s) {
+void build_structure(const HostGraph& g, uint32_t rank, uint32_t world, Structure& s, uint32_t resident_blocks, ResidentPlan* rp) {
     s = Structure();
     const uint32_t P = g.P, L = g.L;
     // ---- pose partition: contiguous ranges balanced by edge work --------------------------------
@@ -162,15 +162,70 @@ void build_structure(const HostGraph& g, uint32_t rank, uint32_t world, Structur
     }
     // ---- coarse space: aggregates of agg_K consecutive local poses ------------------------------------
     {
-        uint32_t K = 32;
-        if (nP > 32ull * kCoarseMaxAgg) K = 32 * (uint32_t)((nP + 32ull * kCoarseMaxAgg - 1) / (32ull * kCoarseMaxAgg));
-        s.agg_K = K; s.nA = (nP + K - 1) / K;
+        // ---- resident plan: pose / landmark ranges per block, balanced by LM edges ----------------------------
+        bool resident = false;
+        if (rp) *rp = ResidentPlan();
+        if (rp && resident_blocks > 0 && world <= 1 && nP > 0 && nE <= (uint64_t)resident_blocks * kResEdgeCap) {
+            const uint32_t nb = resident_blocks;
+            ResidentPlan& r = *rp;
+            r.pose_cut.assign(nb + 1, nP); r.pose_cut[0] = 0;
+            for (uint32_t b = 1; b < nb; ++b) {          // first pose whose edge offset reaches b/nb of the edges (ties: by pose count)
+                const uint64_t target = ((uint64_t)nE + nP) * b / nb;
+                uint32_t lo = r.pose_cut[b - 1], hi = nP;
+                while (lo < hi) { const uint32_t mid = (lo + hi) / 2; if ((uint64_t)s.pose_ptr[mid] + mid < target) lo = mid + 1; else hi = mid; }
+                r.pose_cut[b] = lo;
+            }
+            std::vector<uint32_t> ldeg(L + 1, 0);
+            for (uint32_t k = 0; k < nE; ++k) ldeg[g.le_l[s.le_local[s.lm_perm[k]]] + 1]++;
+            r.lmo_ptr.assign(L + 1, 0);
+            for (uint32_t l = 0; l < L; ++l) r.lmo_ptr[l + 1] = r.lmo_ptr[l] + ldeg[l + 1];
+            r.lm_cut.assign(nb + 1, L); r.lm_cut[0] = 0;
+            for (uint32_t b = 1; b < nb; ++b) {
+                const uint64_t target = ((uint64_t)nE + L) * b / nb;
+                uint32_t lo = r.lm_cut[b - 1], hi = L;
+                while (lo < hi) { const uint32_t mid = (lo + hi) / 2; if ((uint64_t)r.lmo_ptr[mid] + mid < target) lo = mid + 1; else hi = mid; }
+                r.lm_cut[b] = lo;
+            }
+            r.edge_lm.resize(nE); r.lmo_edge.resize(nE);
+            { std::vector<uint32_t> c2(r.lmo_ptr.begin(), r.lmo_ptr.end() - 1);
+              for (uint32_t k = 0; k < nE; ++k) { const uint32_t l = g.le_l[s.le_local[s.lm_perm[k]]]; r.edge_lm[k] = l; r.lmo_edge[c2[l]++] = k; } }
+            // ODOM neighbour entries per block (owned out-edges + in-edges of its poses)
+            resident = true;
+            r.agg_cut.assign(nb + 1, 0);
+            for (uint32_t b = 0; b < nb && resident; ++b) {
+                const uint32_t p0 = r.pose_cut[b], p1 = r.pose_cut[b + 1], l0 = r.lm_cut[b], l1 = r.lm_cut[b + 1];
+                uint32_t nod = 0;
+                for (uint32_t p = p0; p < p1; ++p) nod += (s.od_out_ptr[p + 1] - s.od_out_ptr[p]) + (s.od_in_ptr[p + 1] - s.od_in_ptr[p]);
+                if (p1 - p0 > kResPoseCap || l1 - l0 > kResLmCap || s.pose_ptr[p1] - s.pose_ptr[p0] > kResEdgeCap ||
+                    r.lmo_ptr[l1] - r.lmo_ptr[l0] > kResEdgeCap || nod > kResOdomCap) resident = false;
+                const uint32_t m = p1 > p0 ? std::min<uint32_t>(kResAggCap, std::max<uint32_t>(1, (p1 - p0 + 16) / 32)) : 0;
+                r.agg_cut[b + 1] = r.agg_cut[b] + m;
+            }
+            if (resident && r.agg_cut[nb] > kCoarseMaxAgg) resident = false;
+            if (resident) {
+                r.nb = nb; s.agg_K = 0; s.nA = r.agg_cut[nb];
+                s.agg_ptr.assign(s.nA + 1, nP);
+                for (uint32_t b = 0; b < nb; ++b) {
+                    const uint32_t p0 = r.pose_cut[b], np = r.pose_cut[b + 1] - p0, m = r.agg_cut[b + 1] - r.agg_cut[b];
+                    for (uint32_t q = 0; q < m; ++q) s.agg_ptr[r.agg_cut[b] + q] = p0 + (uint32_t)((uint64_t)np * q / m);
+                }
+            } else *rp = ResidentPlan();
+        }
+        if (!resident) {
+            uint32_t K = 32;
+            if (nP > 32ull * kCoarseMaxAgg) K = 32 * (uint32_t)((nP + 32ull * kCoarseMaxAgg - 1) / (32ull * kCoarseMaxAgg));
+            s.agg_K = K; s.nA = (nP + K - 1) / K;
+            s.agg_ptr.resize(s.nA + 1);
+            for (uint32_t a = 0; a <= s.nA; ++a) s.agg_ptr[a] = std::min<uint64_t>(nP, (uint64_t)a * K);
+        }
+        s.pose_agg.resize(nP);
+        for (uint32_t a = 0; a < s.nA; ++a) for (uint32_t p = s.agg_ptr[a]; p < s.agg_ptr[a + 1]; ++p) s.pose_agg[p] = a;
         s.edge_pose.resize(nE);
         for (uint32_t p = 0; p < nP; ++p) for (uint32_t k = s.pose_ptr[p]; k < s.pose_ptr[p + 1]; ++k) s.edge_pose[k] = p;
         s.aslot_ptr.push_back(0); s.aslot_edge.reserve(nE);
         std::vector<uint64_t> key;
         for (uint32_t a = 0; a < s.nA; ++a) {
-            const uint32_t e0 = s.pose_ptr[a * K], e1 = s.pose_ptr[std::min(nP, (a + 1) * K)];
+            const uint32_t e0 = s.pose_ptr[s.agg_ptr[a]], e1 = s.pose_ptr[s.agg_ptr[a + 1]];
             key.resize(e1 - e0);
             for (uint32_t k = e0; k < e1; ++k) key[k - e0] = ((uint64_t)g.le_l[s.le_local[s.lm_perm[k]]] << 32) | k;
             std::sort(key.begin(), key.end());
