@@ -254,6 +254,25 @@ def main():
                                       "schur_prep_and_coarse_setup": (ms_sol - ms_pcg) / GN_ITERS, "coarse_refreshes_per_step": refreshes},
     }
 
+    replicated = world > 1 and counts.pose_end - counts.pose_begin == counts.n_pose
+    line["config"]["parallelism"] = ("single GPU" if world == 1 else
+                                     f"replicated x{world}: the graph fits one GPU's shared-memory-resident PCG kernel, every rank solves it whole "
+                                     "without collectives (sharding a latency-bound 20 MB problem over NVLink only adds latency; see `sharded`)"
+                                     if replicated else f"edge-sharded over {world} ranks, NCCL all-reduces")
+    # ---- world > 1: the same workload forced through the edge-sharded NCCL path, for the record --------------------
+    if world > 1 and replicated:
+        os.environ["TSB_FORCE_SHARD"] = "1"
+        opt.load_wire_ptr(req.data_ptr(), req.numel())
+        step_resident()
+        barrier()
+        sh = [step_resident()[0] for _ in range(max(1, args.steps - 1))]
+        barrier()
+        ts = torch.tensor([sum(r.ms_total for r in sh) / len(sh)], dtype=torch.float64, device="cuda")
+        dist.all_reduce(ts, op=dist.ReduceOp.MAX)
+        line["sharded"] = {"value": GN_ITERS / (float(ts.item()) * 1e-3), "unit": "iter/s", "ms_per_step": float(ts.item()),
+                           "pcg_iters_per_gn": sum(r.pcg_iters_total for r in sh) / len(sh) / GN_ITERS,
+                           "note": "contiguous pose ranges per rank, per-rank coarse spaces, 3 NCCL all-reduces per PCG iteration"}
+
     # ---- the north-star size (1M poses / 20M edges) for the linearize roofline, single GPU only ---------------
     if not args.no_c4 and args.workload != "c4":
         try:

@@ -18,6 +18,7 @@ torch.cuda.set_device(local)
 dist.init_process_group("nccl", device_id=torch.device("cuda", local))
 uid = tdist.broadcast_unique_id(rank)
 payload = synth.to_payload(synth.make_config(a.workload, scale=a.scale, seed=11))
+os.environ["TSB_FORCE_SHARD"] = "1"      # small graphs would otherwise be solved replicated (no collectives): this checks the sharded path
 g = GraphOptimizerGpu(iterations=a.iters, device=local, rank=rank, world=world, nccl_id=uid, pcg_tol=1e-13,
                       pcg_max_iters=20000, enable_exits=False)
 c = g.load_wire(payload)
@@ -41,6 +42,14 @@ if rank == 0:
         e2 = float(np.max(np.abs(chi - traj) / traj)); e3 = float(max(np.abs(d).max(), np.abs(ls - ols).max()))
         print(f"N-vs-oracle chi2 rel {e2:.2e} state abs {e3:.2e}")
         ok = ok and e2 < 1e-8 and e3 < 1e-8
+# replicated mode (the default for graphs that fit one GPU's resident kernel): every rank solves the whole graph
+os.environ.pop("TSB_FORCE_SHARD", None)
+cr = g.load_wire(payload); repr_, perr = g.optimize()
+if rank == 0:
+    chir = np.array([p.chi2 for p in perr])
+    same = cr.pose_end - cr.pose_begin == cr.n_pose and np.array_equal(chir, chi1)
+    print(f"replicated: owns [{cr.pose_begin},{cr.pose_end}) of {cr.n_pose}, chi2 trajectory identical to 1 rank: {bool(np.array_equal(chir, chi1))}, ms {repr_.ms_total:.1f}")
+    ok = ok and (same or cr.pose_end - cr.pose_begin != cr.n_pose)
     print("MGPU OK" if ok else "MGPU FAIL")
 flag = torch.tensor([1 if ok else 0], device="cuda"); dist.broadcast(flag, 0)
 g.close(); dist.destroy_process_group()

@@ -25,6 +25,7 @@ struct tsb_ctx {
     cudaEvent_t ev[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};   // [4],[5]: around the PCG proper
     HostGraph g;
     Structure st;
+    int world = 1, rank = 0;                              // effective for the loaded graph: (1, 0) when replicated
     ResidentPlan rp;                                      // rp.nb > 0: this graph runs the shared-memory-resident PCG kernel
     Dev d{};
     std::vector<void*> allocs;
@@ -173,7 +174,7 @@ int upload_graph(tsb_ctx* c) {
 
 // in-place sum over ranks on the compute stream; no-op for world == 1
 int allreduce(tsb_ctx* c, double* buf, size_t n) {
-    if (c->cfg.world <= 1 || n == 0) return TSB_OK;
+    if (c->world <= 1 || n == 0) return TSB_OK;
     const ncclResult_t r = ncclAllReduce(buf, buf, n, ncclDouble, ncclSum, c->comm, c->stream);
     if (r != ncclSuccess) { c->err = std::string("ncclAllReduce: ") + ncclGetErrorString(r); return TSB_ENCCL; }
     return TSB_OK;
@@ -191,7 +192,7 @@ int fetch_scalars(tsb_ctx* c) {
 // (Hll, b_l) sums and chi2 are summed over ranks before the landmark blocks are inverted.
 int enqueue_linearize(tsb_ctx* c) {
     launch_linearize(c->d, c->stream);
-    if (c->cfg.world <= 1) { launch_lm_sum(c->d, true, c->stream); return TSB_OK; }     // sum + finalize in one kernel
+    if (c->world <= 1) { launch_lm_sum(c->d, true, c->stream); return TSB_OK; }     // sum + finalize in one kernel
     launch_lm_sum(c->d, false, c->stream);
     TRY(allreduce(c, c->d.lm_sum, 5ull * c->g.L));
     TRY(allreduce(c, c->d.scal + S_CHI2, 1));
@@ -234,7 +235,7 @@ int run_solve(tsb_ctx* c, bool refresh_coarse = true) {
         return TSB_OK;
     }
     // single GPU: the whole PCG and the back-substitution run in one persistent cooperative kernel
-    if (c->cfg.world <= 1 && !c->force_phased && launch_pcg_persistent(d, c->stream)) {
+    if (c->world <= 1 && !c->force_phased && launch_pcg_persistent(d, c->stream)) {
         if (d.dbg) {
             long long t[8]; int its = 0;
             CU(cudaMemcpyAsync(t, d.dbg, sizeof(t), cudaMemcpyDeviceToHost, c->stream));
@@ -360,10 +361,20 @@ int tsb_load_wire(tsb_ctx* c, const void* payload, uint32_t nbytes) {
     CU(cudaSetDevice(c->cfg.device));
     free_graph(c); c->h2d = c->d2h = 0;
     if (!parse_wire((const uint8_t*)payload, nbytes, c->g, c->err)) return TSB_EPARSE;
+    // Sharding decision.  A graph that fits the shared-memory-resident kernel of ONE GPU is latency-bound, not
+    // bandwidth-bound: splitting it over NVLink only adds collective latency to every PCG phase, so with world > 1
+    // every rank solves it whole (replicated, no collective; results are bit-identical on all ranks).  Larger
+    // graphs -- and TSB_FORCE_SHARD=1 -- are edge-sharded over the ranks.
     uint32_t res_nb = 0;
     { const char* e = std::getenv("TSB_NO_RESIDENT");
-      if (c->cfg.world <= 1 && c->use_coarse && !c->force_phased && !(e && e[0] == '1')) res_nb = (uint32_t)resident_blocks_available(); }
-    build_structure(c->g, (uint32_t)c->cfg.rank, (uint32_t)c->cfg.world, c->st, res_nb, &c->rp);
+      if (c->use_coarse && !c->force_phased && !(e && e[0] == '1')) res_nb = (uint32_t)resident_blocks_available(); }
+    const char* fs = std::getenv("TSB_FORCE_SHARD");
+    c->world = c->cfg.world; c->rank = c->cfg.rank;
+    if (c->cfg.world > 1 && res_nb > 0 && !(fs && fs[0] == '1')) {
+        build_structure(c->g, 0, 1, c->st, res_nb, &c->rp);
+        if (c->rp.nb > 0) { c->world = 1; c->rank = 0; return upload_graph(c); }
+    }
+    build_structure(c->g, (uint32_t)c->rank, (uint32_t)c->world, c->st, c->world <= 1 ? res_nb : 0, &c->rp);
     return upload_graph(c);
 }
 
@@ -567,7 +578,7 @@ int tsb_read_ids(const tsb_ctx* c, uint32_t* pose_id, uint32_t* lm_id) {
 int tsb_read_state(tsb_ctx* c, double* pose_xyt, double* lm_xy) {
     if (!c || !c->loaded) return TSB_EINVAL;
     CU(cudaSetDevice(c->cfg.device));
-    if (pose_xyt && c->cfg.world > 1) {
+    if (pose_xyt && c->world > 1) {
         // every rank returns the full state: local ranges summed into a zeroed 3P buffer (sum with zeros = gather)
         CU(cudaMemsetAsync(c->tmp_xyt, 0, 24ull * c->g.P, c->stream));
         launch_read_pose(c->d.pose, c->d.nP, c->tmp_xyt + 3ull * c->st.pose_begin, c->stream);

@@ -10,8 +10,9 @@
 //     coarse residuals);
 //   * the landmark sum is computed landmark-major (one warp per landmark gathers p = z + beta p_old of its
 //     edges' poses), so Hpl^T p needs no slot partials and no separate summation phase;
-//   * the coarse residual is carried by recurrence, rc -= alpha Z^T(S p), every block redundantly, so that the
-//     coarse solve of a block's own aggregates, the prolongation and r'z need no barrier of their own.
+//   * the coarse correction is carried by recurrence, yc -= alpha Ai Z^T(S p), each block for its own aggregates,
+//     so that the coarse solve, the prolongation and r'z need no barrier of their own and the dense rows of
+//     Ai are multiplied while alpha is still being reduced.
 // Three grid barriers per iteration instead of five.  Every sum runs in a fixed order (deterministic).
 //
 // Included inside the anonymous namespace of kernels.cu.
@@ -54,23 +55,45 @@ __device__ __forceinline__ double res_restrict(const ResSm& s, const double* v, 
     return t;
 }
 
-// Coarse rows of this block's aggregates, prolongation, z = zj + Z yc (kept in zf, published to d.z) and the
-// block's part of r'z -> d.part2[block].  zf holds zj = blockdiag(S)^-1 r on entry.
-__device__ __forceinline__ void res_finish(const Dev& d, const ResSm& s, bool coarse, uint32_t p0, uint32_t np, uint32_t a0, uint32_t na) {
-    const uint32_t tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, nc = d.nc;
-    if (coarse) {
-        if (warp < 3 * na) {
-            const double* row = d.Ai + (size_t)(3 * a0 + warp) * nc;
-            double t0 = 0, t1 = 0;
-            uint32_t k = lane;
-#pragma unroll 4
-            for (; k + 32 < nc; k += 64) { t0 += row[k] * s.rc[k]; t1 += row[k + 32] * s.rc[k + 32]; }
-            if (k < nc) t0 += row[k] * s.rc[k];
-            double t = t0 + t1;
+// sum of one preloaded value per thread over the block, fixed order; every thread gets the total.
+// (The loads are issued by the caller before other work so that their latency overlaps it.)
+__device__ __forceinline__ double res_block_total(double v, double* red) {
+    v = warp_sum(v);
+    if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = v;
+    __syncthreads();
+    double t = 0;
 #pragma unroll
-            for (int o = 16; o > 0; o >>= 1) t += __shfl_xor_sync(0xffffffffu, t, o);
-            if (lane == 0) s.yc[warp] = t;
-        }
+    for (int i = 0; i < kResThreads / 32; ++i) t += red[i];
+    __syncthreads();
+    return t;
+}
+
+// Coarse rows of this block's aggregates: t = Ai[row, :] . src (src = Z^T r at the start, Z^T (S p) afterwards,
+// read from global memory); independent of alpha, so it is issued before alpha is known.
+__device__ __forceinline__ double res_coarse_row(const Dev& d, const double* src, uint32_t a0, uint32_t na) {
+    const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nc = d.nc;
+    double t = 0;
+    if (warp < 3 * na) {
+        const double* row = d.Ai + (size_t)(3 * a0 + warp) * nc;
+        double t0 = 0, t1 = 0;
+        uint32_t k = lane;
+#pragma unroll 4
+        for (; k + 32 < nc; k += 64) { t0 += row[k] * src[k]; t1 += row[k + 32] * src[k + 32]; }
+        if (k < nc) t0 += row[k] * src[k];
+        t = t0 + t1;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) t += __shfl_xor_sync(0xffffffffu, t, o);
+    }
+    return t;
+}
+
+// yc -= alpha * t (the coarse correction carried by recurrence), prolongation z = zj + Z yc (kept in zf, published
+// to d.z) and the block's part of r'z -> d.part2[block].  zf holds zj = blockdiag(S)^-1 r on entry.
+__device__ __forceinline__ void res_finish(const Dev& d, const ResSm& s, bool coarse, double alpha, double trow,
+                                           uint32_t p0, uint32_t np, uint32_t a0, uint32_t na) {
+    const uint32_t tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    if (coarse) {
+        if (warp < 3 * na && lane == 0) s.yc[warp] -= alpha * trow;
         __syncthreads();
     }
     double dot = 0;
@@ -168,40 +191,63 @@ __global__ void __launch_bounds__(kResThreads, 1) k_pcg_resident(const Dev d) {
         const uint32_t a = tid / 3, q = tid - 3 * a;
         d.yc[3 * a0 + tid] = res_restrict(s, s.r, d.agg_ptr[a0 + a] - p0, d.agg_ptr[a0 + a + 1] - p0, q);
     }
+    if (tid < 3 * kResAC) s.yc[tid] = 0;
     grid.sync();
-    if (coarse) { for (uint32_t k = tid; k < nc; k += kResThreads) s.rc[k] = d.yc[k]; __syncthreads(); }
-    res_finish(d, s, coarse, p0, np, a0, na);
+    { const double trow = coarse ? res_coarse_row(d, d.yc, a0, na) : 0.0;      // yc = Ai (Z^T r)
+      res_finish(d, s, coarse, -1.0, trow, p0, np, a0, na); }
     grid.sync();
 
     double rz = 0, rz0 = 0, rz_last = 0;
     int it = 0, cur = 0;
     for (;;) {
         // ---- phase 1: beta, p = z + beta p (own poses), u_l = Hll^-1 Hpl^T p (own landmarks) -------------------
-        const double rz_new = reduce_all(d.part2, nb, s.red);
+        const double pv2 = tid < nb ? d.part2[tid] : 0.0;
+        // gathers of z and p_old for this warp's first landmark are issued before beta is known (they do not depend on it)
+        const uint32_t warp = tid >> 5, lane = tid & 31;
+        const double* pold = pp[cur]; double* pnew = pp[cur ^ 1];
+        double gz[2][3], gp[2][3];
+        const uint32_t kf = warp < nl ? s.lptr[warp] + lane : 0u, kfe = warp < nl ? s.lptr[warp + 1] : 0u;
+#pragma unroll
+        for (int j = 0; j < 2; ++j) {
+            const uint32_t k = kf + 32 * j;
+            if (k < kfe) { const uint32_t i = s.epos[k];
+#pragma unroll
+                for (int c = 0; c < 3; ++c) { gz[j][c] = d.z[3ull * i + c]; gp[j][c] = pold[3ull * i + c]; } }
+        }
+        const double rz_new = res_block_total(pv2, s.red);
         rz_last = rz_new;
         double beta = 0;
         if (it == 0) { rz0 = rz_new; if (!(rz0 > 0)) break; }
         else { beta = rz_new / rz; if (!(rz_new > tol2 * rz0) || it >= maxit) break; }
         rz = rz_new;
-        const double* pold = pp[cur]; double* pnew = pp[cur ^ 1];
         if (tid < 3 * np) { const double v = fma(beta, s.p[tid], s.zf[tid]); s.p[tid] = v; pnew[3ull * p0 + tid] = v; }
-        {   // same arithmetic as the owner's line above, on gathered z and p_old
-            const uint32_t warp = tid >> 5, lane = tid & 31;
-            for (uint32_t l = warp; l < nl; l += kResThreads / 32) {
-                double w0 = 0, w1 = 0;
-                for (uint32_t k = s.lptr[l] + lane; k < s.lptr[l + 1]; k += 32) {
-                    const uint32_t i = s.epos[k];
-                    const double v0 = fma(beta, pold[3ull * i], d.z[3ull * i]), v1 = fma(beta, pold[3ull * i + 1], d.z[3ull * i + 1]);
-                    const double v2 = fma(beta, pold[3ull * i + 2], d.z[3ull * i + 2]);
-                    const double* h = s.hplL + 6 * k;
-                    w0 += h[0] * v0 + h[2] * v1 + h[4] * v2; w1 += h[1] * v0 + h[3] * v1 + h[5] * v2;
-                }
+        // same arithmetic as the owner's line above, on gathered z and p_old
+        for (uint32_t l = warp; l < nl; l += kResThreads / 32) {
+            double w0 = 0, w1 = 0;
+            uint32_t k = s.lptr[l] + lane;
+            const uint32_t ke = s.lptr[l + 1];
+            if (l == warp) {
 #pragma unroll
-                for (int o = 16; o > 0; o >>= 1) { w0 += __shfl_xor_sync(0xffffffffu, w0, o); w1 += __shfl_xor_sync(0xffffffffu, w1, o); }
-                if (lane == 0) {
-                    const double* hi = s.hinvL + 3 * l;
-                    d.w_sum[2ull * (l0 + l)] = hi[0] * w0 + hi[1] * w1; d.w_sum[2ull * (l0 + l) + 1] = hi[1] * w0 + hi[2] * w1;
+                for (int j = 0; j < 2; ++j, k += 32) {
+                    if (k < ke) {
+                        const double v0 = fma(beta, gp[j][0], gz[j][0]), v1 = fma(beta, gp[j][1], gz[j][1]), v2 = fma(beta, gp[j][2], gz[j][2]);
+                        const double* h = s.hplL + 6 * k;
+                        w0 += h[0] * v0 + h[2] * v1 + h[4] * v2; w1 += h[1] * v0 + h[3] * v1 + h[5] * v2;
+                    }
                 }
+            }
+            for (; k < ke; k += 32) {
+                const uint32_t i = s.epos[k];
+                const double v0 = fma(beta, pold[3ull * i], d.z[3ull * i]), v1 = fma(beta, pold[3ull * i + 1], d.z[3ull * i + 1]);
+                const double v2 = fma(beta, pold[3ull * i + 2], d.z[3ull * i + 2]);
+                const double* h = s.hplL + 6 * k;
+                w0 += h[0] * v0 + h[2] * v1 + h[4] * v2; w1 += h[1] * v0 + h[3] * v1 + h[5] * v2;
+            }
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) { w0 += __shfl_xor_sync(0xffffffffu, w0, o); w1 += __shfl_xor_sync(0xffffffffu, w1, o); }
+            if (lane == 0) {
+                const double* hi = s.hinvL + 3 * l;
+                d.w_sum[2ull * (l0 + l)] = hi[0] * w0 + hi[1] * w1; d.w_sum[2ull * (l0 + l) + 1] = hi[1] * w0 + hi[2] * w1;
             }
         }
         cur ^= 1;
@@ -237,13 +283,14 @@ __global__ void __launch_bounds__(kResThreads, 1) k_pcg_resident(const Dev d) {
         }
         grid.sync();
         // ---- phase 3: alpha, x, r, coarse residual by recurrence, z and r'z ----------------------------------------
-        const double alpha = rz / reduce_all(d.part, nb, s.red);
-        if (coarse) for (uint32_t k = tid; k < nc; k += kResThreads) s.rc[k] -= alpha * d.cdot[k];
+        const double pv = tid < nb ? d.part[tid] : 0.0;          // issued first: overlaps the coarse rows below
+        const double trow = coarse ? res_coarse_row(d, d.cdot, a0, na) : 0.0;
+        const double alpha = rz / res_block_total(pv, s.red);
         if (tid < 3 * np) { s.x[tid] += alpha * s.p[tid]; s.r[tid] -= alpha * s.y[tid]; }
         __syncthreads();
         if (tid < np) sym3_mul(s.minv + 6 * tid, s.r[3 * tid], s.r[3 * tid + 1], s.r[3 * tid + 2], s.zf[3 * tid], s.zf[3 * tid + 1], s.zf[3 * tid + 2]);
         __syncthreads();
-        res_finish(d, s, coarse, p0, np, a0, na);
+        res_finish(d, s, coarse, alpha, trow, p0, np, a0, na);
         ++it;
         grid.sync();
     }

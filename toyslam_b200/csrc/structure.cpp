@@ -77,37 +77,38 @@ void build_structure(const HostGraph& g, uint32_t rank, uint32_t world, Structur
     // ---- slots: distinct landmarks per chunk ---------------------------------------------------------
     s.lm_packed.resize(nE); s.slot_edge.resize(nE);
     s.slot_ptr.push_back(0);
-    std::vector<uint32_t> lms, cnt;
-    for (ChunkDesc& c : s.chunks) {
+    std::vector<uint32_t> elm(nE);                       // landmark of each LM edge in assembly order
+    for (uint32_t k = 0; k < nE; ++k) elm[k] = g.le_l[s.le_local[s.lm_perm[k]]];
+    std::vector<uint32_t> stamp(L, 0xFFFFFFFFu), lslot(L, 0), uniq, ucnt, order, srank, cnt;
+    for (uint32_t ci = 0; ci < s.chunks.size(); ++ci) {
+        ChunkDesc& c = s.chunks[ci];
         const uint32_t n = c.e1 - c.e0;
-        lms.resize(n);
-        for (uint32_t k = 0; k < n; ++k) lms[k] = g.le_l[s.le_local[s.lm_perm[c.e0 + k]]];
-        std::vector<uint32_t> uniq(lms);
-        std::sort(uniq.begin(), uniq.end()); uniq.erase(std::unique(uniq.begin(), uniq.end()), uniq.end());
+        // distinct landmarks of the chunk (stamp table: O(n)), then sorted by landmark
+        uniq.clear();
+        for (uint32_t k = 0; k < n; ++k) { const uint32_t l = elm[c.e0 + k]; if (stamp[l] != ci) { stamp[l] = ci; uniq.push_back(l); } }
+        std::sort(uniq.begin(), uniq.end());
         const uint32_t nu = (uint32_t)uniq.size();
+        for (uint32_t q = 0; q < nu; ++q) lslot[uniq[q]] = q;          // landmark-sorted index
         // slots are numbered by descending edge count (ties: ascending landmark): the 32 lanes of a warp that sum
         // neighbouring slots then run the same number of iterations
-        std::vector<uint32_t> ucnt(nu, 0), rank(nu), order(nu);
-        for (uint32_t k = 0; k < n; ++k) {
-            lms[k] = (uint32_t)(std::lower_bound(uniq.begin(), uniq.end(), lms[k]) - uniq.begin());   // landmark-sorted index
-            ucnt[lms[k]]++;
-        }
+        ucnt.assign(nu, 0); srank.resize(nu); order.resize(nu);
+        for (uint32_t k = 0; k < n; ++k) ucnt[lslot[elm[c.e0 + k]]]++;
         std::iota(order.begin(), order.end(), 0u);
         std::stable_sort(order.begin(), order.end(), [&](uint32_t x, uint32_t y) { return ucnt[x] > ucnt[y]; });
-        for (uint32_t q = 0; q < nu; ++q) rank[order[q]] = q;
+        for (uint32_t q = 0; q < nu; ++q) srank[order[q]] = q;
         c.s0 = (uint32_t)s.slot_lm.size(); c.s1 = c.s0 + nu;
         for (uint32_t q = 0; q < nu; ++q) s.slot_lm.push_back(uniq[order[q]]);
         cnt.assign(nu + 1, 0);
         uint32_t pose = c.p0;
         for (uint32_t k = 0; k < n; ++k) {
-            const uint32_t slot = rank[lms[k]];
+            const uint32_t slot = srank[lslot[elm[c.e0 + k]]];
             while (c.e0 + k >= s.pose_ptr[pose + 1]) ++pose;
             s.lm_packed[c.e0 + k] = ((pose - c.p0) << 16) | slot;
-            lms[k] = slot; cnt[slot + 1]++;
+            cnt[slot + 1]++;
         }
         for (size_t q = 0; q < nu; ++q) cnt[q + 1] += cnt[q];
         for (size_t q = 0; q < nu; ++q) s.slot_ptr.push_back(c.e0 + cnt[q + 1]);
-        for (uint32_t k = 0; k < n; ++k) s.slot_edge[c.e0 + cnt[lms[k]]++] = (uint16_t)k;
+        for (uint32_t k = 0; k < n; ++k) s.slot_edge[c.e0 + cnt[s.lm_packed[c.e0 + k] & 0xffffu]++] = (uint16_t)k;
     }
     // ---- landmark-major CSR over slots ---------------------------------------------------------------
     const uint32_t nS = (uint32_t)s.slot_lm.size();
@@ -176,7 +177,7 @@ void build_structure(const HostGraph& g, uint32_t rank, uint32_t world, Structur
                 r.pose_cut[b] = lo;
             }
             std::vector<uint32_t> ldeg(L + 1, 0);
-            for (uint32_t k = 0; k < nE; ++k) ldeg[g.le_l[s.le_local[s.lm_perm[k]]] + 1]++;
+            for (uint32_t k = 0; k < nE; ++k) ldeg[elm[k] + 1]++;
             r.lmo_ptr.assign(L + 1, 0);
             for (uint32_t l = 0; l < L; ++l) r.lmo_ptr[l + 1] = r.lmo_ptr[l] + ldeg[l + 1];
             r.lm_cut.assign(nb + 1, L); r.lm_cut[0] = 0;
@@ -188,7 +189,7 @@ void build_structure(const HostGraph& g, uint32_t rank, uint32_t world, Structur
             }
             r.edge_lm.resize(nE); r.lmo_edge.resize(nE);
             { std::vector<uint32_t> c2(r.lmo_ptr.begin(), r.lmo_ptr.end() - 1);
-              for (uint32_t k = 0; k < nE; ++k) { const uint32_t l = g.le_l[s.le_local[s.lm_perm[k]]]; r.edge_lm[k] = l; r.lmo_edge[c2[l]++] = k; } }
+              for (uint32_t k = 0; k < nE; ++k) { const uint32_t l = elm[k]; r.edge_lm[k] = l; r.lmo_edge[c2[l]++] = k; } }
             // ODOM neighbour entries per block (owned out-edges + in-edges of its poses)
             resident = true;
             r.agg_cut.assign(nb + 1, 0);
@@ -222,22 +223,20 @@ void build_structure(const HostGraph& g, uint32_t rank, uint32_t world, Structur
         for (uint32_t a = 0; a < s.nA; ++a) for (uint32_t p = s.agg_ptr[a]; p < s.agg_ptr[a + 1]; ++p) s.pose_agg[p] = a;
         s.edge_pose.resize(nE);
         for (uint32_t p = 0; p < nP; ++p) for (uint32_t k = s.pose_ptr[p]; k < s.pose_ptr[p + 1]; ++k) s.edge_pose[k] = p;
-        s.aslot_ptr.push_back(0); s.aslot_edge.reserve(nE);
-        std::vector<uint64_t> key;
+        s.aslot_ptr.push_back(0); s.aslot_edge.resize(nE);
+        std::fill(stamp.begin(), stamp.end(), 0xFFFFFFFFu);
         for (uint32_t a = 0; a < s.nA; ++a) {
             const uint32_t e0 = s.pose_ptr[s.agg_ptr[a]], e1 = s.pose_ptr[s.agg_ptr[a + 1]];
-            key.resize(e1 - e0);
-            for (uint32_t k = e0; k < e1; ++k) key[k - e0] = ((uint64_t)g.le_l[s.le_local[s.lm_perm[k]]] << 32) | k;
-            std::sort(key.begin(), key.end());
-            for (size_t q = 0; q < key.size(); ++q) {
-                const uint32_t l = (uint32_t)(key[q] >> 32);
-                if (q == 0 || l != (uint32_t)(key[q - 1] >> 32)) {
-                    if (q) s.aslot_ptr.push_back((uint32_t)s.aslot_edge.size());
-                    s.aslot_lm.push_back(l); s.aslot_agg.push_back(a);
-                }
-                s.aslot_edge.push_back((uint32_t)key[q]);
-            }
-            if (!key.empty()) s.aslot_ptr.push_back((uint32_t)s.aslot_edge.size());
+            uniq.clear();
+            for (uint32_t k = e0; k < e1; ++k) { const uint32_t l = elm[k]; if (stamp[l] != a) { stamp[l] = a; uniq.push_back(l); } }
+            std::sort(uniq.begin(), uniq.end());
+            const uint32_t nu = (uint32_t)uniq.size(), base = (uint32_t)s.aslot_lm.size();
+            cnt.assign(nu + 1, 0);
+            for (uint32_t q = 0; q < nu; ++q) { lslot[uniq[q]] = q; s.aslot_lm.push_back(uniq[q]); s.aslot_agg.push_back(a); }
+            for (uint32_t k = e0; k < e1; ++k) cnt[lslot[elm[k]] + 1]++;
+            for (uint32_t q = 0; q < nu; ++q) { cnt[q + 1] += cnt[q]; s.aslot_ptr.push_back(e0 + cnt[q + 1]); }
+            for (uint32_t k = e0; k < e1; ++k) s.aslot_edge[e0 + cnt[lslot[elm[k]]]++] = k;      // ascending edge index inside an aslot
+            (void)base;
         }
         const uint32_t nAS = (uint32_t)s.aslot_lm.size();
         // landmark-major lists of aslots (ascending aslot id = ascending aggregate)
@@ -248,31 +247,31 @@ void build_structure(const HostGraph& g, uint32_t rank, uint32_t world, Structur
           for (uint32_t q = 0; q < nAS; ++q) lidx[c2[s.aslot_lm[q]]++] = q; }
         // pairs (a, b) and their triples, grouped by a, then b, landmark ascending inside
         s.cpair_ptr.push_back(0);
-        std::vector<uint64_t> trip;                       // b << 32 | position in the a-major emission order
+        std::vector<uint32_t> tb, cntb(s.nA + 1), posb;        // per emitted triple: aggregate b; counting sort by b (stable)
         std::vector<std::pair<uint32_t, uint32_t>> ss;
         uint32_t q0 = 0;
         for (uint32_t a = 0; a < s.nA; ++a) {
-            trip.clear(); ss.clear();
+            tb.clear(); ss.clear();
             uint32_t q1 = q0;
             while (q1 < nAS && s.aslot_agg[q1] == a) ++q1;
             for (uint32_t q = q0; q < q1; ++q) {
                 const uint32_t l = s.aslot_lm[q];
-                for (uint32_t j = lptr[l]; j < lptr[l + 1]; ++j) {
-                    trip.push_back(((uint64_t)s.aslot_agg[lidx[j]] << 32) | (uint32_t)ss.size());
-                    ss.emplace_back(q, lidx[j]);
-                }
+                for (uint32_t j = lptr[l]; j < lptr[l + 1]; ++j) { tb.push_back(s.aslot_agg[lidx[j]]); ss.emplace_back(q, lidx[j]); }
             }
-            std::sort(trip.begin(), trip.end());
-            for (size_t t = 0; t < trip.size(); ++t) {
-                const uint32_t b = (uint32_t)(trip[t] >> 32);
-                if (t == 0 || b != (uint32_t)(trip[t - 1] >> 32)) {
-                    if (t) s.cpair_ptr.push_back((uint32_t)(s.ctrip.size() / 2));
-                    s.cpair_a.push_back(a); s.cpair_b.push_back(b);
-                }
-                const auto& pr = ss[(uint32_t)trip[t]];
-                s.ctrip.push_back(pr.first); s.ctrip.push_back(pr.second);
+            // group by b, keeping the emission order (landmark ascending) inside each group
+            std::fill(cntb.begin(), cntb.end(), 0u);
+            for (uint32_t b : tb) cntb[b + 1]++;
+            const size_t base = s.ctrip.size() / 2;
+            for (uint32_t b = 0; b < s.nA; ++b) {
+                if (cntb[b + 1]) { s.cpair_a.push_back(a); s.cpair_b.push_back(b); s.cpair_ptr.push_back((uint32_t)(base + cntb[b] + cntb[b + 1])); }
+                cntb[b + 1] += cntb[b];
             }
-            if (!trip.empty()) s.cpair_ptr.push_back((uint32_t)(s.ctrip.size() / 2));
+            s.ctrip.resize(2 * (base + tb.size()));
+            posb.assign(cntb.begin(), cntb.end() - 1);
+            for (size_t t = 0; t < tb.size(); ++t) {
+                const size_t at = base + posb[tb[t]]++;
+                s.ctrip[2 * at] = ss[t].first; s.ctrip[2 * at + 1] = ss[t].second;
+            }
             q0 = q1;
         }
     }

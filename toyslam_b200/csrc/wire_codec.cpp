@@ -107,6 +107,12 @@ bool parse_wire(const uint8_t* buf, uint32_t nbytes, HostGraph& g, std::string& 
     if (!r.have(4)) return fail("truncated payload: edge count");
     const uint32_t E = r.u32();
     if ((uint64_t)E * 44 > nbytes) return fail("edge count exceeds payload size");
+    {   // no reallocation while the edges stream in (E bounds both kinds)
+        const size_t cap = E;
+        g.le_i.reserve(cap); g.le_l.reserve(cap); g.le_z.reserve(2 * cap); g.le_w.reserve(2 * cap);
+        const size_t ocap = std::min<size_t>(cap, (size_t)g.P * 4 + 1024);
+        g.od_i.reserve(ocap); g.od_j.reserve(ocap); g.od_zinv.reserve(6 * ocap); g.od_w.reserve(3 * ocap);
+    }
     uint32_t reply = g.edges_offset + 4;     // bytes of the reply so far (vertex section is the same size
                                              // unless duplicates were dropped; fixed below)
     for (uint32_t i = 0; i < E; ++i) {
@@ -143,7 +149,8 @@ bool parse_wire(const uint8_t* buf, uint32_t nbytes, HostGraph& g, std::string& 
         } else {
             if ((a & 0x80000000u) || !(b & 0x80000000u)) return fail("LM edge must be (Se2, Point2)");
             g.le_i.push_back(a); g.le_l.push_back(b & 0x7FFFFFFFu);
-            g.le_z.push_back(rb[0] * std::cos(rb[1])); g.le_z.push_back(rb[0] * std::sin(rb[1]));
+            double sb, cb; sincos(rb[1], &sb, &cb);          // same values as separate cos / sin calls (glibc)
+            g.le_z.push_back(rb[0] * cb); g.le_z.push_back(rb[0] * sb);
             g.le_w.push_back(w[0]); g.le_w.push_back(w[1]);
             reply += 12 + 8 + 8 + 8 + 8;
         }
