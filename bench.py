@@ -225,6 +225,9 @@ def main():
         dist.all_reduce(te, op=dist.ReduceOp.MAX)
     e2e_s = float(te.item())
 
+    # one launch per solve + ~6 per GN iteration for the rest: the resident / persistent kernels show up as few launches
+    resident_kernel = (counts.pose_end - counts.pose_begin == counts.n_pose) and launches / args.steps / GN_ITERS < 40 and \
+        counts.n_lmedge <= 148 * 1280
     line = {
         "metric": "gn_iterations_per_s", "value": value, "unit": "iter/s", "n_gpus": world, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": dev_ms, "higher_is_better": True, "scaling": "strong" if world > 1 else "weak",
@@ -239,7 +242,8 @@ def main():
         "clocks": clk.summary(),
         # dominant kernel of the step (profiles/: > 90 % of the C2 step): the persistent PCG kernel, one launch per solve.
         # algorithmic bytes per launch = B_pcg x the PCG iterations of that solve; duration by CUDA events around the launch.
-        "roofline": {"kernel": "k_pcg_persistent (whole PCG solve in one cooperative launch)" if world == 1 else "k_pcg_* phases + NCCL all-reduces",
+        "roofline": {"kernel": ("k_pcg_resident (whole PCG solve in one cooperative launch, Hpl resident in shared memory)" if resident_kernel else
+                                "k_pcg_persistent (whole PCG solve in one cooperative launch)" if world == 1 else "k_pcg_* phases + NCCL all-reduces"),
                      "bound": "hbm", "achieved": B_pcg / (pcg_ms * 1e-3) / 1e9, "peak": peak, "peak_kind": peak_kind, "unit": "GB/s",
                      "frac": B_pcg / (pcg_ms * 1e-3) / 1e9 / peak, "traffic": None,
                      "algorithmic_bytes_per_launch": B_pcg * pcg_total / GN_ITERS, "algorithmic_bytes_per_pcg_iteration": B_pcg,

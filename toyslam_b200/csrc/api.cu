@@ -155,7 +155,7 @@ int upload_graph(tsb_ctx* c) {
     c->part_cap = std::max<uint32_t>(std::max<uint32_t>(d.nBlocks, (std::max(d.nP, g.L) + kThreads - 1) / kThreads) + 1, 4096);
     TRY(dalloc(c, d.part, c->part_cap)); TRY(dalloc(c, d.part2, c->part_cap));
     TRY(dalloc(c, d.scal, (size_t)S_COUNT)); TRY(dalloc(c, d.flags, (size_t)F_COUNT));
-    { const char* e = std::getenv("TSB_PCG_TIMING"); if (e && e[0] == '1') { TRY(dalloc(c, d.dbg, (size_t)8)); CU(cudaMemsetAsync(d.dbg, 0, 64, c->stream)); } }
+    { const char* e = std::getenv("TSB_PCG_TIMING"); if (e && e[0] == '1') { TRY(dalloc(c, d.dbg, (size_t)16)); CU(cudaMemsetAsync(d.dbg, 0, 128, c->stream)); } }
     CU(cudaMemsetAsync(d.scal, 0, sizeof(double) * S_COUNT, c->stream));
     CU(cudaMemsetAsync(d.flags, 0, sizeof(int) * F_COUNT, c->stream));
     CU(cudaMemsetAsync(d.p, 0, 24ull * nPG, c->stream));
@@ -231,6 +231,16 @@ int run_solve(tsb_ctx* c, bool refresh_coarse = true) {
     cudaEventRecord(c->ev[4], c->stream);
     if (d.res_nb) {            // small graph: Hpl stays in shared memory for the whole solve, three grid barriers per iteration
         if (!launch_pcg_resident(d, c->stream)) { c->err = "resident PCG kernel could not be launched"; return TSB_ECUDA; }
+        if (d.dbg) {
+            long long t[16]; int its = 0;
+            CU(cudaMemcpyAsync(t, d.dbg, sizeof(t), cudaMemcpyDeviceToHost, c->stream));
+            CU(cudaMemcpyAsync(&its, d.flags + F_ITERS, 4, cudaMemcpyDeviceToHost, c->stream));
+            CU(cudaStreamSynchronize(c->stream));
+            const char* nm[14] = {"phase1", "sync", "phase2(rest)", "sync", "phase3(finish)", "sync", "", "", "p2:gather+products", "p2:bar", "p2:segsum", "p2:blocksum", "p3:alpha", "p3:update"};
+            std::fprintf(stderr, "[tsb] resident PCG, %d iterations, SM cycles per iteration (block 0):", its);
+            for (int q = 0; q < 14; ++q) if (nm[q][0]) std::fprintf(stderr, " %s=%lld", nm[q], its ? t[q] / its : 0);
+            std::fprintf(stderr, "\n");
+        }
         cudaEventRecord(c->ev[5], c->stream);
         return TSB_OK;
     }

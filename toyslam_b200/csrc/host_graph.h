@@ -95,7 +95,7 @@ constexpr uint32_t kResEdgeCap = 1280;    // LM edges per block, either order
 constexpr uint32_t kResPoseCap = 96;      // poses per block
 constexpr uint32_t kResLmCap = 64;        // landmarks per block
 constexpr uint32_t kResAggCap = 4;        // aggregates per block
-constexpr uint32_t kResOdomCap = 512;     // ODOM neighbour entries per block
+constexpr uint32_t kResOdomCap = 384;     // ODOM neighbour entries per block
 constexpr uint32_t kCoarseMaxAgg = 512;   // upper bound on aggregates per rank (coarse matrix is dense: (3*512)^2 doubles)
 
 constexpr uint32_t kChunkEdges = 512;   // LM edges staged per chunk

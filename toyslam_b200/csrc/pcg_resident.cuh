@@ -10,9 +10,8 @@
 //     coarse residuals);
 //   * the landmark sum is computed landmark-major (one warp per landmark gathers p = z + beta p_old of its
 //     edges' poses), so Hpl^T p needs no slot partials and no separate summation phase;
-//   * the coarse correction is carried by recurrence, yc -= alpha Ai Z^T(S p), each block for its own aggregates,
-//     so that the coarse solve, the prolongation and r'z need no barrier of their own and the dense rows of
-//     Ai are multiplied while alpha is still being reduced.
+//   * the coarse residual is carried by recurrence, rc -= alpha Z^T(S p), every block redundantly, so that the
+//     coarse solve of a block's own aggregates, the prolongation and r'z need no barrier of their own.
 // Three grid barriers per iteration instead of five.  Every sum runs in a fixed order (deterministic).
 //
 // Included inside the anonymous namespace of kernels.cu.
@@ -22,24 +21,24 @@ constexpr uint32_t kResEC = kResEdgeCap, kResPC = kResPoseCap, kResLC = kResLmCa
 
 struct ResSm {
     double* hplP; double* hplL; double* rows; double* x; double* r; double* p; double* y; double* zf;
-    double* minv; double* hpp; double2* zoff; double* onb_h; double* hinvL; double* rc; double* yc; double* red;
-    uint32_t* elm; uint32_t* epos; uint32_t* eptr; uint32_t* lptr; uint32_t* pagg; uint32_t* onb_ptr; uint32_t* onb_idx;
+    double* minv; double* hpp; double2* zoff; double* onb_h; double* onb_p; double* hinvL; double* rc; double* yc; double* red;
+    uint32_t* elm; uint32_t* epos; uint32_t* eptr; uint32_t* lptr; uint32_t* pagg; uint32_t* onb_ptr; uint32_t* onb_idx; uint32_t* aptr;
 };
 constexpr size_t kResSmemBytes =
-    sizeof(double) * (6 * kResEC * 2 + 3 * kResEC + 5 * 3 * kResPC + 2 * 6 * kResPC + 2 * kResPC + 3 * kResOC + 3 * kResLC +
-                      3 * kCoarseMaxAgg + 3 * kResAC + 4 + 32) +
-    sizeof(uint32_t) * (2 * kResEC + (kResPC + 4) + (kResLC + 4) + kResPC + (kResPC + 4) + kResOC);
+    sizeof(double) * (6 * kResEC * 2 + 3 * kResEC + 5 * 3 * kResPC + 2 * 6 * kResPC + 2 * kResPC + 6 * kResOC + 3 * kResLC +
+                      3 * kCoarseMaxAgg + 3 * kResAC + 4 + 32 + 32 * 4) +
+    sizeof(uint32_t) * (2 * kResEC + (kResPC + 4) + (kResLC + 4) + kResPC + (kResPC + 4) + kResOC + kResAC + 4);
 
 __device__ __forceinline__ ResSm res_carve(unsigned char* b) {
     ResSm s; double* f = reinterpret_cast<double*>(b);
     s.hplP = f; f += 6 * kResEC; s.hplL = f; f += 6 * kResEC; s.rows = f; f += 3 * kResEC;
     s.x = f; f += 3 * kResPC; s.r = f; f += 3 * kResPC; s.p = f; f += 3 * kResPC; s.y = f; f += 3 * kResPC; s.zf = f; f += 3 * kResPC;
     s.minv = f; f += 6 * kResPC; s.hpp = f; f += 6 * kResPC; s.zoff = reinterpret_cast<double2*>(f); f += 2 * kResPC;
-    s.onb_h = f; f += 3 * kResOC; s.hinvL = f; f += 3 * kResLC; s.rc = f; f += 3 * kCoarseMaxAgg; s.yc = f; f += 3 * kResAC + 4;
-    s.red = f; f += 32;
+    s.onb_h = f; f += 3 * kResOC; s.onb_p = f; f += 3 * kResOC; s.hinvL = f; f += 3 * kResLC; s.rc = f; f += 3 * kCoarseMaxAgg; s.yc = f; f += 3 * kResAC + 4;
+    s.red = f; f += 32 + 32 * 4;      // + partial row sums of the coarse mat-vec (one per warp)
     uint32_t* u = reinterpret_cast<uint32_t*>(f);
     s.elm = u; u += kResEC; s.epos = u; u += kResEC; s.eptr = u; u += kResPC + 4; s.lptr = u; u += kResLC + 4;
-    s.pagg = u; u += kResPC; s.onb_ptr = u; u += kResPC + 4; s.onb_idx = u;
+    s.pagg = u; u += kResPC; s.onb_ptr = u; u += kResPC + 4; s.onb_idx = u; u += kResOC; s.aptr = u;
     return s;
 }
 
@@ -48,52 +47,59 @@ __device__ __forceinline__ double res_zt(const double2 zo, const double* v, uint
     return q == 0 ? v[0] : q == 1 ? v[1] : zo.x * v[0] + zo.y * v[1] + v[2];
 }
 
-// sum over the poses of aggregate `a` (local pose range [b, e)) of component q of Z_i^T v_i, in pose order
-__device__ __forceinline__ double res_restrict(const ResSm& s, const double* v, uint32_t b, uint32_t e, uint32_t q) {
-    double t = 0;
-    for (uint32_t i = b; i < e; ++i) t += res_zt(s.zoff[i], v + 3 * i, q);
-    return t;
-}
-
-// sum of one preloaded value per thread over the block, fixed order; every thread gets the total.
-// (The loads are issued by the caller before other work so that their latency overlaps it.)
-__device__ __forceinline__ double res_block_total(double v, double* red) {
-    v = warp_sum(v);
-    if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = v;
-    __syncthreads();
-    double t = 0;
+// Z^T v summed over the poses of each of this block's aggregates -> out[3 (a0 + a) + q]: warp a, lanes stride
+// the aggregate's poses, fixed xor tree (deterministic).  aptr = local pose offsets of the aggregates.
+__device__ __forceinline__ void res_restrict(const ResSm& s, const double* v, const uint32_t* aptr, uint32_t na, double* out) {
+    const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    if (warp >= na) return;
+    double t0 = 0, t1 = 0, t2 = 0;
+    for (uint32_t i = aptr[warp] + lane; i < aptr[warp + 1]; i += 32) {
+        const double2 zo = s.zoff[i];
+        const double v0 = v[3 * i], v1 = v[3 * i + 1], v2 = v[3 * i + 2];
+        t0 += v0; t1 += v1; t2 += zo.x * v0 + zo.y * v1 + v2;
+    }
 #pragma unroll
-    for (int i = 0; i < kResThreads / 32; ++i) t += red[i];
-    __syncthreads();
-    return t;
+    for (int o = 16; o > 0; o >>= 1) {
+        t0 += __shfl_xor_sync(0xffffffffu, t0, o); t1 += __shfl_xor_sync(0xffffffffu, t1, o); t2 += __shfl_xor_sync(0xffffffffu, t2, o);
+    }
+    if (lane == 0) { out[3 * warp] = t0; out[3 * warp + 1] = t1; out[3 * warp + 2] = t2; }
 }
 
-// Coarse rows of this block's aggregates: t = Ai[row, :] . src (src = Z^T r at the start, Z^T (S p) afterwards,
-// read from global memory); independent of alpha, so it is issued before alpha is known.
-__device__ __forceinline__ double res_coarse_row(const Dev& d, const double* src, uint32_t a0, uint32_t na) {
-    const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nc = d.nc;
-    double t = 0;
-    if (warp < 3 * na) {
-        const double* row = d.Ai + (size_t)(3 * a0 + warp) * nc;
-        double t0 = 0, t1 = 0;
-        uint32_t k = lane;
-#pragma unroll 4
-        for (; k + 32 < nc; k += 64) { t0 += row[k] * src[k]; t1 += row[k + 32] * src[k + 32]; }
-        if (k < nc) t0 += row[k] * src[k];
-        t = t0 + t1;
+// total of the nb (<= 1024) per-block partial sums, every thread gets it: warp 0 loads them with all its loads in
+// flight at once (lane-strided), adds in a fixed order and publishes the total through shared memory
+__device__ __forceinline__ double res_total(const double* part, uint32_t nb, double* red) {
+    if (threadIdx.x < 32) {
+        double t = 0;
+#pragma unroll 8
+        for (uint32_t i = threadIdx.x; i < nb; i += 32) t += part[i];
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1) t += __shfl_xor_sync(0xffffffffu, t, o);
+        if (threadIdx.x == 0) red[0] = t;
     }
-    return t;
+    __syncthreads();
+    const double r = red[0];
+    __syncthreads();
+    return r;
 }
 
-// yc -= alpha * t (the coarse correction carried by recurrence), prolongation z = zj + Z yc (kept in zf, published
-// to d.z) and the block's part of r'z -> d.part2[block].  zf holds zj = blockdiag(S)^-1 r on entry.
-__device__ __forceinline__ void res_finish(const Dev& d, const ResSm& s, bool coarse, double alpha, double trow,
-                                           uint32_t p0, uint32_t np, uint32_t a0, uint32_t na) {
-    const uint32_t tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-    if (coarse) {
-        if (warp < 3 * na && lane == 0) s.yc[warp] -= alpha * trow;
+// Coarse rows of this block's aggregates, prolongation, z = zj + Z yc (kept in zf, published to d.z) and the
+// block's part of r'z -> d.part2[block].  zf holds zj = blockdiag(S)^-1 r on entry.
+__device__ __forceinline__ void res_finish(const Dev& d, const ResSm& s, bool coarse, uint32_t p0, uint32_t np, uint32_t a0, uint32_t na) {
+    const uint32_t tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, nc = d.nc;
+    if (coarse && na) {
+        // each of the 3 na rows of Ai is split over `wpr` warps so that every lane has all its loads in flight at once
+        const uint32_t rows = 3 * na, wpr = (kResThreads / 32) / rows;            // >= 2 (rows <= 12)
+        double* part = s.red + 32;
+        if (warp < rows * wpr) {
+            const uint32_t rw = warp / wpr, sub = warp - rw * wpr;
+            const double* row = d.Ai + (size_t)(3 * a0 + rw) * nc;
+            double t = 0;
+#pragma unroll 8
+            for (uint32_t k = sub * 32 + lane; k < nc; k += 32 * wpr) t += row[k] * s.rc[k];
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) t += __shfl_xor_sync(0xffffffffu, t, o);
+            if (lane == 0) part[warp] = t;
+        }
         __syncthreads();
     }
     double dot = 0;
@@ -101,9 +107,12 @@ __device__ __forceinline__ void res_finish(const Dev& d, const ResSm& s, bool co
         const uint32_t pl = tid / 3, q = tid - 3 * pl;
         double z = s.zf[tid];
         if (coarse) {
-            const uint32_t a = s.pagg[pl];
-            const double y2 = s.yc[3 * a + 2];
-            z += q == 2 ? y2 : q == 0 ? s.yc[3 * a] + s.zoff[pl].x * y2 : s.yc[3 * a + 1] + s.zoff[pl].y * y2;
+            // yc of the pose's aggregate: the partial row sums are added in warp order by every thread that needs them
+            const uint32_t a = s.pagg[pl], wpr = (kResThreads / 32) / (3 * na);
+            const double* part = s.red + 32 + 3 * a * wpr;
+            double y0 = 0, y1 = 0, y2 = 0;
+            for (uint32_t j = 0; j < wpr; ++j) { y0 += part[j]; y1 += part[wpr + j]; y2 += part[2 * wpr + j]; }
+            z += q == 2 ? y2 : q == 0 ? y0 + s.zoff[pl].x * y2 : y1 + s.zoff[pl].y * y2;
         }
         s.zf[tid] = z; d.z[3ull * p0 + tid] = z;
         dot = s.r[tid] * z;
@@ -159,6 +168,7 @@ __global__ void __launch_bounds__(kResThreads, 1) k_pcg_resident(const Dev d) {
     for (uint32_t k = tid; k < nk; k += kResThreads) s.epos[k] = d.edge_pose[d.lmo_edge[k0 + k]];
     for (uint32_t i = tid; i <= np; i += kResThreads) s.eptr[i] = d.pose_ptr[p0 + i] - e0;
     for (uint32_t i = tid; i <= nl; i += kResThreads) s.lptr[i] = d.lmo_ptr[l0 + i] - k0;
+    for (uint32_t i = tid; i <= na; i += kResThreads) s.aptr[i] = d.agg_ptr[a0 + i] - p0;
     for (uint32_t i = tid; i < 3 * nl; i += kResThreads) s.hinvL[i] = d.hinv[3ull * l0 + i];
     for (uint32_t i = tid; i < 6 * np; i += kResThreads) { s.minv[i] = d.minv[6ull * p0 + i]; s.hpp[i] = d.hpp[6ull * p0 + i]; }
     for (uint32_t i = tid; i < np; i += kResThreads) { s.zoff[i] = d.zoff[p0 + i]; s.pagg[i] = d.pose_agg[p0 + i] - a0; }
@@ -187,77 +197,57 @@ __global__ void __launch_bounds__(kResThreads, 1) k_pcg_resident(const Dev d) {
     }
     __syncthreads();
     // coarse residual Z^T r: this block's aggregates -> global, then every block keeps the whole vector
-    if (coarse && tid < 3 * na) {
-        const uint32_t a = tid / 3, q = tid - 3 * a;
-        d.yc[3 * a0 + tid] = res_restrict(s, s.r, d.agg_ptr[a0 + a] - p0, d.agg_ptr[a0 + a + 1] - p0, q);
-    }
-    if (tid < 3 * kResAC) s.yc[tid] = 0;
+    if (coarse) res_restrict(s, s.r, s.aptr, na, d.yc + 3 * a0);
     grid.sync();
-    { const double trow = coarse ? res_coarse_row(d, d.yc, a0, na) : 0.0;      // yc = Ai (Z^T r)
-      res_finish(d, s, coarse, -1.0, trow, p0, np, a0, na); }
+    if (coarse) { for (uint32_t k = tid; k < nc; k += kResThreads) s.rc[k] = d.yc[k]; __syncthreads(); }
+    res_finish(d, s, coarse, p0, np, a0, na);
     grid.sync();
 
     double rz = 0, rz0 = 0, rz_last = 0;
     int it = 0, cur = 0;
+    const bool timing = d.dbg != nullptr && b == 0 && tid == 0;      // TSB_PCG_TIMING=1: SM cycles of block 0 per phase
+    long long tk = 0, tacc[16] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0};
+#define RTICK(slot) do { if (timing) { const long long now_ = clock64(); tacc[slot] += now_ - tk; tk = now_; } } while (0)
     for (;;) {
+        if (timing) tk = clock64();
         // ---- phase 1: beta, p = z + beta p (own poses), u_l = Hll^-1 Hpl^T p (own landmarks) -------------------
-        const double pv2 = tid < nb ? d.part2[tid] : 0.0;
-        // gathers of z and p_old for this warp's first landmark are issued before beta is known (they do not depend on it)
-        const uint32_t warp = tid >> 5, lane = tid & 31;
-        const double* pold = pp[cur]; double* pnew = pp[cur ^ 1];
-        double gz[2][3], gp[2][3];
-        const uint32_t kf = warp < nl ? s.lptr[warp] + lane : 0u, kfe = warp < nl ? s.lptr[warp + 1] : 0u;
-#pragma unroll
-        for (int j = 0; j < 2; ++j) {
-            const uint32_t k = kf + 32 * j;
-            if (k < kfe) { const uint32_t i = s.epos[k];
-#pragma unroll
-                for (int c = 0; c < 3; ++c) { gz[j][c] = d.z[3ull * i + c]; gp[j][c] = pold[3ull * i + c]; } }
-        }
-        const double rz_new = res_block_total(pv2, s.red);
+        const double rz_new = res_total(d.part2, nb, s.red);
         rz_last = rz_new;
         double beta = 0;
         if (it == 0) { rz0 = rz_new; if (!(rz0 > 0)) break; }
         else { beta = rz_new / rz; if (!(rz_new > tol2 * rz0) || it >= maxit) break; }
         rz = rz_new;
+        const double* pold = pp[cur]; double* pnew = pp[cur ^ 1];
         if (tid < 3 * np) { const double v = fma(beta, s.p[tid], s.zf[tid]); s.p[tid] = v; pnew[3ull * p0 + tid] = v; }
-        // same arithmetic as the owner's line above, on gathered z and p_old
-        for (uint32_t l = warp; l < nl; l += kResThreads / 32) {
-            double w0 = 0, w1 = 0;
-            uint32_t k = s.lptr[l] + lane;
-            const uint32_t ke = s.lptr[l + 1];
-            if (l == warp) {
-#pragma unroll
-                for (int j = 0; j < 2; ++j, k += 32) {
-                    if (k < ke) {
-                        const double v0 = fma(beta, gp[j][0], gz[j][0]), v1 = fma(beta, gp[j][1], gz[j][1]), v2 = fma(beta, gp[j][2], gz[j][2]);
-                        const double* h = s.hplL + 6 * k;
-                        w0 += h[0] * v0 + h[2] * v1 + h[4] * v2; w1 += h[1] * v0 + h[3] * v1 + h[5] * v2;
-                    }
+        {   // same arithmetic as the owner's line above, on gathered z and p_old
+            const uint32_t warp = tid >> 5, lane = tid & 31;
+            for (uint32_t l = warp; l < nl; l += kResThreads / 32) {
+                double w0 = 0, w1 = 0;
+                for (uint32_t k = s.lptr[l] + lane; k < s.lptr[l + 1]; k += 32) {
+                    const uint32_t i = s.epos[k];
+                    const double v0 = fma(beta, pold[3ull * i], d.z[3ull * i]), v1 = fma(beta, pold[3ull * i + 1], d.z[3ull * i + 1]);
+                    const double v2 = fma(beta, pold[3ull * i + 2], d.z[3ull * i + 2]);
+                    const double* h = s.hplL + 6 * k;
+                    w0 += h[0] * v0 + h[2] * v1 + h[4] * v2; w1 += h[1] * v0 + h[3] * v1 + h[5] * v2;
                 }
-            }
-            for (; k < ke; k += 32) {
-                const uint32_t i = s.epos[k];
-                const double v0 = fma(beta, pold[3ull * i], d.z[3ull * i]), v1 = fma(beta, pold[3ull * i + 1], d.z[3ull * i + 1]);
-                const double v2 = fma(beta, pold[3ull * i + 2], d.z[3ull * i + 2]);
-                const double* h = s.hplL + 6 * k;
-                w0 += h[0] * v0 + h[2] * v1 + h[4] * v2; w1 += h[1] * v0 + h[3] * v1 + h[5] * v2;
-            }
 #pragma unroll
-            for (int o = 16; o > 0; o >>= 1) { w0 += __shfl_xor_sync(0xffffffffu, w0, o); w1 += __shfl_xor_sync(0xffffffffu, w1, o); }
-            if (lane == 0) {
-                const double* hi = s.hinvL + 3 * l;
-                d.w_sum[2ull * (l0 + l)] = hi[0] * w0 + hi[1] * w1; d.w_sum[2ull * (l0 + l) + 1] = hi[1] * w0 + hi[2] * w1;
+                for (int o = 16; o > 0; o >>= 1) { w0 += __shfl_xor_sync(0xffffffffu, w0, o); w1 += __shfl_xor_sync(0xffffffffu, w1, o); }
+                if (lane == 0) {
+                    const double* hi = s.hinvL + 3 * l;
+                    d.w_sum[2ull * (l0 + l)] = hi[0] * w0 + hi[1] * w1; d.w_sum[2ull * (l0 + l) + 1] = hi[1] * w0 + hi[2] * w1;
+                }
             }
         }
         cur ^= 1;
+        RTICK(0);
         grid.sync();
+        RTICK(1);
         // ---- phase 2: y = S p for the own poses, p'y and Z^T y ---------------------------------------------------
-        double yo = 0;                                             // ODOM neighbours: blocks are diagonal, component-wise
         const uint32_t pl = tid / 3, q = tid - 3 * pl;
-        if (tid < 3 * np) {
+        {   // ODOM neighbours' p: one thread per (entry, component), all loads in flight at once
             const double* pg = pp[cur];
-            for (uint32_t n = s.onb_ptr[pl]; n < s.onb_ptr[pl + 1]; ++n) yo += s.onb_h[3 * n + q] * pg[3ull * s.onb_idx[n] + q];
+            const uint32_t nent = 3 * s.onb_ptr[np];
+            for (uint32_t i = tid; i < nent; i += kResThreads) { const uint32_t n = i / 3; s.onb_p[i] = pg[3ull * s.onb_idx[n] + (i - 3 * n)]; }
         }
         for (uint32_t e = tid; e < ne; e += kResThreads) {
             const uint32_t l = s.elm[e];
@@ -265,35 +255,45 @@ __global__ void __launch_bounds__(kResThreads, 1) k_pcg_resident(const Dev d) {
             const double* h = s.hplP + 6 * e;
             s.rows[e] = h[0] * u0 + h[1] * u1; s.rows[kResEC + e] = h[2] * u0 + h[3] * u1; s.rows[2 * kResEC + e] = h[4] * u0 + h[5] * u1;
         }
+        RTICK(8);
         __syncthreads();
+        RTICK(9);
         double dot = 0;
         if (tid < 3 * np) {
             const double acc = seg_sum_lean(s.rows + q * kResEC, s.eptr[pl], s.eptr[pl + 1]);
             const double* H = s.hpp + 6 * pl; const double* v = s.p + 3 * pl;
             const double hp = q == 0 ? H[0] * v[0] + H[1] * v[1] + H[2] * v[2] : q == 1 ? H[1] * v[0] + H[3] * v[1] + H[4] * v[2]
                                                                                         : H[2] * v[0] + H[4] * v[1] + H[5] * v[2];
+            double yo = 0;                                         // ODOM blocks are diagonal: component-wise
+            for (uint32_t n = s.onb_ptr[pl]; n < s.onb_ptr[pl + 1]; ++n) yo += s.onb_h[3 * n + q] * s.onb_p[3 * n + q];
             const double y = hp + yo - acc;
             s.y[tid] = y; dot = s.p[tid] * y;
         }
+        RTICK(10);
         const double t = block_sum(dot, s.red);                    // (its barriers also publish s.y to the block)
+        RTICK(11);
         if (tid == 0) d.part[b] = t;
-        if (coarse && tid < 3 * na) {
-            const uint32_t a = tid / 3, qa = tid - 3 * a;
-            d.cdot[3 * a0 + tid] = res_restrict(s, s.y, d.agg_ptr[a0 + a] - p0, d.agg_ptr[a0 + a + 1] - p0, qa);
-        }
+        if (coarse) res_restrict(s, s.y, s.aptr, na, d.cdot + 3 * a0);
+        RTICK(2);
         grid.sync();
+        RTICK(3);
         // ---- phase 3: alpha, x, r, coarse residual by recurrence, z and r'z ----------------------------------------
-        const double pv = tid < nb ? d.part[tid] : 0.0;          // issued first: overlaps the coarse rows below
-        const double trow = coarse ? res_coarse_row(d, d.cdot, a0, na) : 0.0;
-        const double alpha = rz / res_block_total(pv, s.red);
+        const double alpha = rz / res_total(d.part, nb, s.red);
+        RTICK(12);
+        if (coarse) for (uint32_t k = tid; k < nc; k += kResThreads) s.rc[k] -= alpha * d.cdot[k];
         if (tid < 3 * np) { s.x[tid] += alpha * s.p[tid]; s.r[tid] -= alpha * s.y[tid]; }
         __syncthreads();
         if (tid < np) sym3_mul(s.minv + 6 * tid, s.r[3 * tid], s.r[3 * tid + 1], s.r[3 * tid + 2], s.zf[3 * tid], s.zf[3 * tid + 1], s.zf[3 * tid + 2]);
         __syncthreads();
-        res_finish(d, s, coarse, alpha, trow, p0, np, a0, na);
+        RTICK(13);
+        res_finish(d, s, coarse, p0, np, a0, na);
         ++it;
+        RTICK(4);
         grid.sync();
+        RTICK(5);
     }
+    if (timing) for (int q = 0; q < 16; ++q) d.dbg[q] = tacc[q];
+#undef RTICK
     // ---- results: delta_p, the PCG scalars, landmark back-substitution delta_l = Hll^-1 (b_l - Hpl^T delta_p) ----
     if (tid < 3 * np) d.x[3ull * p0 + tid] = s.x[tid];
     if (b == 0 && tid == 0) { d.scal[S_RZ0] = rz0; d.scal[S_RZ] = rz_last; d.flags[F_ITERS] = it; d.flags[F_DONE] = 1; }
