@@ -225,9 +225,7 @@ def main():
         dist.all_reduce(te, op=dist.ReduceOp.MAX)
     e2e_s = float(te.item())
 
-    # one launch per solve + ~6 per GN iteration for the rest: the resident / persistent kernels show up as few launches
-    resident_kernel = (counts.pose_end - counts.pose_begin == counts.n_pose) and launches / args.steps / GN_ITERS < 40 and \
-        counts.n_lmedge <= 148 * 1280
+    resident_kernel = counts.pcg_path == 1
     line = {
         "metric": "gn_iterations_per_s", "value": value, "unit": "iter/s", "n_gpus": world, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": dev_ms, "higher_is_better": True, "scaling": "strong" if world > 1 else "weak",
@@ -258,7 +256,7 @@ def main():
                                       "schur_prep_and_coarse_setup": (ms_sol - ms_pcg) / GN_ITERS, "coarse_refreshes_per_step": refreshes},
     }
 
-    replicated = world > 1 and counts.pose_end - counts.pose_begin == counts.n_pose
+    replicated = counts.replicated == 1
     line["config"]["parallelism"] = ("single GPU" if world == 1 else
                                      f"replicated x{world}: the graph fits one GPU's shared-memory-resident PCG kernel, every rank solves it whole "
                                      "without collectives (sharding a latency-bound 20 MB problem over NVLink only adds latency; see `sharded`)"

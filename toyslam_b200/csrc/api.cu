@@ -444,6 +444,8 @@ int tsb_get_counts(const tsb_ctx* c, tsb_counts* o) {
     o->dim = 3 * c->g.P + 2 * c->g.L; o->pose_begin = c->st.pose_begin; o->pose_end = c->st.pose_end;
     o->n_lmedge_local = c->d.nE; o->n_odom_local = c->d.nOwned;
     o->n_chunks = c->d.nChunks; o->n_blocks = c->d.nBlocks; o->n_slots = c->d.nSlots;
+    o->pcg_path = c->d.res_nb ? 1u : (c->world <= 1 && !c->force_phased ? 0u : 2u);
+    o->replicated = (c->cfg.world > 1 && c->world == 1) ? 1u : 0u; o->n_aggregates = c->d.nA;
     return TSB_OK;
 }
 
@@ -623,7 +625,8 @@ int tsb_read_system(tsb_ctx* c, double* hpp_diag, double* b_pose, double* hpl, d
     if (b_lm && d.L) CU(cudaMemcpyAsync(b_lm, d.bl, 16ull * d.L, cudaMemcpyDeviceToHost, c->stream));
     CU(cudaStreamSynchronize(c->stream));
     if (hpl) { std::vector<double> t; TRY(download(c, t, d.hpl, 6ull * d.nE));
-        for (uint32_t k = 0; k < d.nE; ++k) std::memcpy(hpl + 6ull * s.le_local[s.lm_perm[k]], &t[6ull * k], 48); }
+        for (uint32_t k = 0; k < d.nE; ++k) for (int r = 0; r < 3; ++r)      // device: three planes of double2; out: 3x2 per edge
+            std::memcpy(hpl + 6ull * s.le_local[s.lm_perm[k]] + 2 * r, &t[TSB_HPL_PLANES ? 2ull * ((uint64_t)r * d.nE + k) : 6ull * k + 2 * r], 16); }
     if (hpp_off) { std::vector<double> t; TRY(download(c, t, d.hoo, 3ull * d.nOwned));
         for (uint32_t k = 0; k < d.nOwned; ++k) std::memcpy(hpp_off + 3ull * s.od_local[k], &t[3ull * k], 24); }
     return TSB_OK;

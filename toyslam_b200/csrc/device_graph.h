@@ -7,6 +7,9 @@
 namespace tsb {
 
 constexpr int kThreads = 256;          // threads per block of the chunked kernels
+#ifndef TSB_HPL_PLANES
+#define TSB_HPL_PLANES 1              // Hpl as three planes of nE double2 (1) or 3x2 per edge (0)
+#endif
 constexpr int kStageRows = 9;          // values staged per LM edge
 constexpr int kStageStride = kChunkEdges + 1;   // odd stride in doubles: rows land in different banks
 
@@ -24,7 +27,7 @@ struct Dev {
     const uint32_t* lm_packed;  // (pose - chunk.p0) << 16 | slot - chunk.s0
     const double2* le_z;        // landmark in the sensor frame (r cos b, r sin b)
     const double2* le_w;        // information diagonal
-    double* hpl;                // 6 per edge: A^T W B, 3x2 row-major
+    double* hpl;                // A^T W B (3x2) per LM edge, as three planes of nE double2: row r of edge e at 2*(r*nE+e)
     const uint32_t* pose_ptr;   // nP + 1
     const ChunkDesc* chunks;
     const uint32_t* blk_chunk_ptr;

@@ -79,6 +79,11 @@ __device__ __forceinline__ double block_sum(double v, double* red) {
     return t;
 }
 
+// Hpl of LM edge e (3x2, A^T W B): row r is the double2 at hpl_row(d, e)[r * d.nE] -- three planes, so that the
+// threads of a warp, which hold consecutive edges, read and write consecutive 16-byte words
+__device__ __forceinline__ double2* hpl_row(const Dev& d, uint64_t e) { return reinterpret_cast<double2*>(d.hpl) + (TSB_HPL_PLANES ? e : 3 * e); }
+__device__ __forceinline__ size_t hpl_stride(const Dev& d) { return TSB_HPL_PLANES ? (size_t)d.nE : 1; }
+
 // sums `n` values in a fixed order with one block; every thread gets the total
 __device__ __forceinline__ double reduce_all(const double* part, uint32_t n, double* red) {
     double t = 0;
@@ -159,7 +164,7 @@ __device__ __forceinline__ void acc_to_smem(const double (&acc)[ROWS], double* s
 
 // one LM edge: residual, Jacobian products, Hpl block, staged per-edge products (EdgeSe2Point2d.h:28-70)
 __device__ __forceinline__ double lm_edge(const double4 ps, const double2 l, const double2 z, const double2 w,
-                                          double2* __restrict__ h, double* __restrict__ st) {
+                                          double2* __restrict__ h, size_t hs, double* __restrict__ st) {
     const double c_ = ps.z, s_ = ps.w;
     const double e0 = c_ * l.x + s_ * l.y - (c_ * ps.x + s_ * ps.y) - z.x;       // e = X^-1 l - z_loc (:34-38)
     const double e1 = -s_ * l.x + c_ * l.y + (s_ * ps.x - c_ * ps.y) - z.y;
@@ -173,7 +178,7 @@ __device__ __forceinline__ double lm_edge(const double4 ps, const double2 l, con
     const double t0 = c_ * i0 * q0 - s_ * i1 * q1;           // B^T W q  ( = -(A^T W A)[0:2,2] )
     const double t1 = s_ * i0 * q0 + c_ * i1 * q1;
     // Hpl = A^T W B = [[-m00,-m01],[-m01,-m11],[t0,t1]]
-    h[0] = make_double2(-m00, -m01); h[1] = make_double2(-m01, -m11); h[2] = make_double2(t0, t1);
+    h[0] = make_double2(-m00, -m01); h[hs] = make_double2(-m01, -m11); h[2 * hs] = make_double2(t0, t1);
     st[0 * kStageStride] = m00; st[1 * kStageStride] = m01; st[2 * kStageStride] = m11;
     st[3 * kStageStride] = -t0; st[4 * kStageStride] = -t1; st[5 * kStageStride] = q0 * i0 * q0 + q1 * i1 * q1;
     st[6 * kStageStride] = c_ * f0 - s_ * f1; st[7 * kStageStride] = s_ * f0 + c_ * f1;   // B^T W e
@@ -252,9 +257,9 @@ __device__ __forceinline__ void unit_linearize(const Dev& d, const uint32_t unit
         stage_sptr(d, sm, ch);
         __syncthreads();
         if (k0 < n) rho_sum += lm_edge(sm.pose[pk0 >> 16], sm.slot2[pk0 & 0xffffu], z0, w0,
-                                       reinterpret_cast<double2*>(d.hpl + 6ull * (ch.e0 + k0)), sm.stage + k0);
+                                       hpl_row(d, ch.e0 + k0), hpl_stride(d), sm.stage + k0);
         if (k1 < n) rho_sum += lm_edge(sm.pose[pk1 >> 16], sm.slot2[pk1 & 0xffffu], z1, w1,
-                                       reinterpret_cast<double2*>(d.hpl + 6ull * (ch.e0 + k1)), sm.stage + k1);
+                                       hpl_row(d, ch.e0 + k1), hpl_stride(d), sm.stage + k1);
         __syncthreads();
         pose_reduce<kStageRows>(sm.pptr, ch, sm.stage, np, acc);
         // landmark side: one partial (M00 M01 M11 g0 g1) per slot, edges of the slot in list order
@@ -348,9 +353,9 @@ __global__ void k_reduce_to(const double* part, uint32_t n, double* out) {
 // ------------------------------------------------------------------------------------------------
 // K3: Schur preparation.  diag(S)_i = Hpp_ii - sum_e Hpl_e Hll^-1 Hpl_e^T,  rhs_i = b_i - sum_e Hpl_e Hll^-1 b_l
 // ------------------------------------------------------------------------------------------------
-__device__ __forceinline__ void schur_edge(const double2* __restrict__ hp, const double* __restrict__ hi, const double2 bl,
+__device__ __forceinline__ void schur_edge(const double2* __restrict__ hp, size_t hs, const double* __restrict__ hi, const double2 bl,
                                            double* __restrict__ st) {
-    const double2 r0 = hp[0], r1 = hp[1], r2 = hp[2];
+    const double2 r0 = hp[0], r1 = hp[hs], r2 = hp[2 * hs];
     const double i00 = hi[0], i01 = hi[1], i11 = hi[2];
     const double t00 = r0.x * i00 + r0.y * i01, t01 = r0.x * i01 + r0.y * i11;     // T = Hpl * Hll^-1 (3x2)
     const double t10 = r1.x * i00 + r1.y * i01, t11 = r1.x * i01 + r1.y * i11;
@@ -387,7 +392,7 @@ __global__ void __launch_bounds__(kThreads, 3) k_schur_prep(const Dev d) {
         __syncthreads();
         for (uint32_t k = threadIdx.x; k < n; k += kThreads) {
             const uint32_t sl = d.lm_packed[ch.e0 + k] & 0xffffu;
-            schur_edge(reinterpret_cast<const double2*>(d.hpl + 6ull * (ch.e0 + k)), sm.slot3 + 3 * sl, sm.slot2[sl], sm.stage + k);
+            schur_edge(hpl_row(d, ch.e0 + k), hpl_stride(d), sm.slot3 + 3 * sl, sm.slot2[sl], sm.stage + k);
         }
         __syncthreads();
         pose_reduce<kStageRows>(sm.pptr, ch, sm.stage, np, acc);
@@ -451,10 +456,10 @@ __device__ __forceinline__ void unit_pass_a(const Dev& d, const uint32_t unit, c
         const uint32_t n = ch.e1 - ch.e0, ns = ch.s1 - ch.s0;
         const uint32_t k0 = threadIdx.x, k1 = threadIdx.x + kThreads;
         uint32_t pl0 = 0, pl1 = 0; double2 a0 = {}, a1 = {}, a2 = {}, b0 = {}, b1 = {}, b2 = {};
-        if (k0 < n) { const double2* hp = reinterpret_cast<const double2*>(d.hpl + 6ull * (ch.e0 + k0));
-            pl0 = d.lm_packed[ch.e0 + k0] >> 16; a0 = hp[0]; a1 = hp[1]; a2 = hp[2]; }
-        if (k1 < n) { const double2* hp = reinterpret_cast<const double2*>(d.hpl + 6ull * (ch.e0 + k1));
-            pl1 = d.lm_packed[ch.e0 + k1] >> 16; b0 = hp[0]; b1 = hp[1]; b2 = hp[2]; }
+        if (k0 < n) { const double2* hp = hpl_row(d, ch.e0 + k0);
+            pl0 = d.lm_packed[ch.e0 + k0] >> 16; a0 = hp[0]; a1 = hp[hpl_stride(d)]; a2 = hp[2 * hpl_stride(d)]; }
+        if (k1 < n) { const double2* hp = hpl_row(d, ch.e0 + k1);
+            pl1 = d.lm_packed[ch.e0 + k1] >> 16; b0 = hp[0]; b1 = hp[hpl_stride(d)]; b2 = hp[2 * hpl_stride(d)]; }
         for (uint32_t k = threadIdx.x; k < n; k += kThreads) sm.sedge[k] = d.slot_edge[ch.e0 + k];
         stage_sptr(d, sm, ch);
         __syncthreads();
@@ -501,10 +506,10 @@ __device__ __forceinline__ double unit_pass_b(const Dev& d, const uint32_t unit,
         const uint32_t n = ch.e1 - ch.e0, ns = ch.s1 - ch.s0;
         const uint32_t k0 = threadIdx.x, k1 = threadIdx.x + kThreads;
         uint32_t sl0 = 0, sl1 = 0; double2 a0 = {}, a1 = {}, a2 = {}, b0 = {}, b1 = {}, b2 = {};
-        if (k0 < n) { const double2* hp = reinterpret_cast<const double2*>(d.hpl + 6ull * (ch.e0 + k0));
-            sl0 = d.lm_packed[ch.e0 + k0] & 0xffffu; a0 = hp[0]; a1 = hp[1]; a2 = hp[2]; }
-        if (k1 < n) { const double2* hp = reinterpret_cast<const double2*>(d.hpl + 6ull * (ch.e0 + k1));
-            sl1 = d.lm_packed[ch.e0 + k1] & 0xffffu; b0 = hp[0]; b1 = hp[1]; b2 = hp[2]; }
+        if (k0 < n) { const double2* hp = hpl_row(d, ch.e0 + k0);
+            sl0 = d.lm_packed[ch.e0 + k0] & 0xffffu; a0 = hp[0]; a1 = hp[hpl_stride(d)]; a2 = hp[2 * hpl_stride(d)]; }
+        if (k1 < n) { const double2* hp = hpl_row(d, ch.e0 + k1);
+            sl1 = d.lm_packed[ch.e0 + k1] & 0xffffu; b0 = hp[0]; b1 = hp[hpl_stride(d)]; b2 = hp[2 * hpl_stride(d)]; }
         for (uint32_t s = threadIdx.x; s < ns; s += kThreads) {
             const uint32_t l = d.slot_lm[ch.s0 + s];
             const double2 w = reinterpret_cast<const double2*>(d.w_sum)[l];
@@ -634,8 +639,8 @@ __global__ void k_coarse_C(const Dev d) {                                  // th
     for (uint32_t q = d.aslot_ptr[sidx]; q < d.aslot_ptr[sidx + 1]; ++q) {
         const uint32_t e = d.aslot_edge[q];
         const double2 zo = d.zoff[d.edge_pose[e]];
-        const double2* h = reinterpret_cast<const double2*>(d.hpl + 6ull * e);
-        const double2 h0 = h[0], h1 = h[1], h2 = h[2];
+        const double2* h = hpl_row(d, e);
+        const double2 h0 = h[0], h1 = h[hpl_stride(d)], h2 = h[2 * hpl_stride(d)];
         c[0] += h0.x; c[1] += h1.x; c[2] += zo.x * h0.x + zo.y * h1.x + h2.x;
         c[3] += h0.y; c[4] += h1.y; c[5] += zo.x * h0.y + zo.y * h1.y + h2.y;
     }
@@ -1010,8 +1015,8 @@ void launch_linearize(const Dev& d, cudaStream_t s) {
     { const char* e = getenv("TSB_STREAM_MIN_UNITS"); if (e) min_units = (uint32_t)atoi(e);      // tests force either path
       e = getenv("TSB_NO_STREAM"); no_stream = e && e[0] == '1'; }
     if (g_stream_blocks > 0 && !no_stream && d.nBlocks >= min_units && d.nBlocks) {
-        k_linearize_stream<<<g_stream_blocks, kLsThreads, kLsSmemBytes, s>>>(d); ++g_launches;
-        nparts = (uint32_t)g_stream_blocks;
+        k_linearize_stream<<<g_stream_blocks, kLsThreads, kLsSmemBytes, s>>>(d); nparts = (uint32_t)g_stream_blocks;
+        ++g_launches;
     } else if (d.nBlocks) { k_linearize<<<d.nBlocks, kThreads, LayLin::bytes, s>>>(d); ++g_launches; }
     k_reduce2_to<<<1, 1024, 0, s>>>(d.part2, nob, d.part, nparts, d.scal + S_CHI2); ++g_launches;
 }

@@ -178,7 +178,7 @@ __global__ void __launch_bounds__(kLsThreads, 2) k_linearize_stream(const Dev d)
 
         // ---- per-edge linearisation, products staged in `rows`, Hpl written once ------------------------------
         if (tid < n) { const uint32_t q = pk[tid];
-            rho_sum += lm_edge(pose[q >> 16], slot2[q & 0xffffu], z0, w0, reinterpret_cast<double2*>(d.hpl + 6ull * (cur.e0 + tid)), rows + tid); }
+            rho_sum += lm_edge(pose[q >> 16], slot2[q & 0xffffu], z0, w0, hpl_row(d, cur.e0 + tid), hpl_stride(d), rows + tid); }
         __syncthreads();
 
         // ---- pose side: one (pose, row) item per thread sums its row segment ----------------------------------

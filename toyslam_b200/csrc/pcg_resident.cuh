@@ -162,9 +162,9 @@ __global__ void __launch_bounds__(kResThreads, 1) k_pcg_resident(const Dev d) {
     double* pp[2] = {d.p, d.sp};                              // p of all poses, double-buffered across iterations
 
     // ---- once per solve: everything this block owns goes to shared memory ------------------------------------
-    for (uint32_t i = tid; i < 6 * ne; i += kResThreads) s.hplP[i] = d.hpl[6ull * e0 + i];
+    for (uint32_t i = tid; i < 6 * ne; i += kResThreads) { const uint32_t k = i / 6, q = i - 6 * k; s.hplP[i] = reinterpret_cast<const double*>(hpl_row(d, e0 + k) + (q >> 1) * hpl_stride(d))[q & 1u]; }
     for (uint32_t i = tid; i < ne; i += kResThreads) s.elm[i] = d.edge_lm[e0 + i];
-    for (uint32_t i = tid; i < 6 * nk; i += kResThreads) { const uint32_t k = i / 6; s.hplL[i] = d.hpl[6ull * d.lmo_edge[k0 + k] + (i - 6 * k)]; }
+    for (uint32_t i = tid; i < 6 * nk; i += kResThreads) { const uint32_t k = i / 6, q = i - 6 * k; s.hplL[i] = reinterpret_cast<const double*>(hpl_row(d, d.lmo_edge[k0 + k]) + (q >> 1) * hpl_stride(d))[q & 1u]; }
     for (uint32_t k = tid; k < nk; k += kResThreads) s.epos[k] = d.edge_pose[d.lmo_edge[k0 + k]];
     for (uint32_t i = tid; i <= np; i += kResThreads) s.eptr[i] = d.pose_ptr[p0 + i] - e0;
     for (uint32_t i = tid; i <= nl; i += kResThreads) s.lptr[i] = d.lmo_ptr[l0 + i] - k0;
