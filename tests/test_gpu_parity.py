@@ -238,6 +238,35 @@ def test_resident_pcg_matches_streaming_pcg(gpu, monkeypatch):
     assert res[0][2] < res[2][2]            # the coarse level pays for itself
 
 
+def test_context_reuse_across_requests_is_bit_reproducible(gpu):
+    """The server keeps one context for every request (ConnectionHandler.h:18-20 rebuilds everything instead); device
+    memory is recycled between graphs.  A -> B (larger) -> A -> C (smaller) -> A on one context: every run of A
+    must reproduce the first one bit for bit (nothing may depend on what a buffer held before)."""
+    from toyslam_b200 import synth
+    pa = synth.to_payload(synth.make_config("c2", scale=0.05, seed=11))
+    pb = synth.to_payload(synth.make_config("c3", scale=0.02, seed=12))
+    pc = load_golden("g_small")["request"].tobytes()
+    g = gpu(iterations=4, pcg_tol=1e-13, pcg_max_iters=20000, enable_exits=False)
+    runs = []
+    for payload in (pa, pb, pa, pc, pa):
+        g.load_wire(payload)
+        rep, per = g.optimize()
+        state = g.state()
+        g.linearize()                                   # H, b at the final state
+        runs.append((np.array([p.chi2 for p in per]), state, g.system(), payload is pa))
+    first = runs[0]
+    for r in runs[1:]:
+        if not r[3]:
+            continue
+        assert np.array_equal(first[0], r[0])
+        assert np.array_equal(first[1][0], r[1][0]) and np.array_equal(first[1][1], r[1][1])
+        for k in first[2]:
+            assert np.array_equal(first[2][k], r[2][k]), k
+    fresh = gpu(iterations=4, pcg_tol=1e-13, pcg_max_iters=20000, enable_exits=False); fresh.load_wire(pa)
+    rep, per = fresh.optimize()
+    assert np.array_equal(first[0], np.array([p.chi2 for p in per]))
+
+
 def test_phased_pcg_path_matches_persistent(gpu, monkeypatch):
     """world == 1 normally runs the persistent cooperative PCG kernel; the one-launch-per-phase path
     (used when collectives sit between the phases) must give the same answer."""

@@ -28,7 +28,10 @@ struct tsb_ctx {
     int world = 1, rank = 0;                              // effective for the loaded graph: (1, 0) when replicated
     ResidentPlan rp;                                      // rp.nb > 0: this graph runs the shared-memory-resident PCG kernel
     Dev d{};
-    std::vector<void*> allocs;
+    // device memory of the loaded graph: bump-allocated from a few large blocks that outlive the graph, so a server
+    // that optimises one request after another stops calling cudaMalloc / cudaFree after the first request
+    std::vector<std::pair<char*, size_t>> arena;          // (base, capacity)
+    size_t arena_blk = 0, arena_off = 0, arena_used = 0;
     double4* pose0 = nullptr; double2* lm0 = nullptr;     // state as loaded (tsb_reset_state)
     double* tmp_xyt = nullptr;                            // 3 * (nP + nG) scratch
     double* h_scal = nullptr; int* h_flags = nullptr;     // pinned
@@ -53,18 +56,34 @@ namespace {
     do { cudaError_t e_ = (call); if (e_ != cudaSuccess) {                                         \
         c->err = std::string(#call) + ": " + cudaGetErrorString(e_); return TSB_ECUDA; } } while (0)
 
+void release_arena(tsb_ctx* c) {
+    for (auto& b : c->arena) cudaFree(b.first);
+    c->arena.clear(); c->arena_blk = c->arena_off = 0;
+}
 void free_graph(tsb_ctx* c) {
-    for (void* p : c->allocs) cudaFree(p);
-    c->allocs.clear(); c->d = Dev{}; c->loaded = c->linearized = c->solved = false;
+    // a graph that needed several blocks: give them back so that the next one gets a single block of the full size
+    if (c->arena.size() > 1) { cudaStreamSynchronize(c->stream); release_arena(c); }
+    c->arena_blk = c->arena_off = 0;
+    c->d = Dev{}; c->loaded = c->linearized = c->solved = false;
     c->pose0 = nullptr; c->lm0 = nullptr; c->tmp_xyt = nullptr; c->cwork = nullptr; c->cwork_len = 0; c->coarse_age = -1;
 }
 
 template <typename T> int dalloc(tsb_ctx* c, T*& out, size_t n) {
-    void* p = nullptr;
     // 64 B of slack: the streaming kernels copy from addresses aligned down / sizes rounded up to 16 B
-    if (cudaMalloc(&p, std::max<size_t>(n, 1) * sizeof(T) + 64) != cudaSuccess) {
-        cudaGetLastError(); c->err = "cudaMalloc failed (" + std::to_string(n * sizeof(T)) + " bytes)"; return TSB_ENOMEM; }
-    c->allocs.push_back(p); out = (T*)p; return TSB_OK;
+    const size_t bytes = (std::max<size_t>(n, 1) * sizeof(T) + 64 + 255) & ~size_t(255);
+    while (c->arena_blk < c->arena.size() && c->arena_off + bytes > c->arena[c->arena_blk].second) { ++c->arena_blk; c->arena_off = 0; }
+    if (c->arena_blk == c->arena.size()) {
+        // first block: what the previous graph used (plus headroom); later blocks double the total
+        size_t total = 0; for (auto& b : c->arena) total += b.second;
+        const size_t cap = std::max(bytes, std::max<size_t>(c->arena.empty() ? c->arena_used + c->arena_used / 8 : total, size_t(16) << 20));
+        void* p = nullptr;
+        if (cudaMalloc(&p, cap) != cudaSuccess) {
+            cudaGetLastError(); c->err = "cudaMalloc failed (" + std::to_string(cap) + " bytes)"; return TSB_ENOMEM; }
+        c->arena.emplace_back((char*)p, cap); c->arena_off = 0;
+    }
+    out = (T*)(c->arena[c->arena_blk].first + c->arena_off); c->arena_off += bytes;
+    { size_t used = c->arena_off; for (size_t i = 0; i < c->arena_blk; ++i) used += c->arena[i].second; c->arena_used = std::max(c->arena_used, used); }
+    return TSB_OK;
 }
 template <typename T, typename U> int upload(tsb_ctx* c, const U*& out, const std::vector<T>& v) {
     static_assert(sizeof(T) == sizeof(U) || sizeof(U) % sizeof(T) == 0, "layout");
@@ -356,7 +375,7 @@ int tsb_nccl_unique_id(void* out128) {
 void tsb_destroy(tsb_ctx* c) {
     if (!c) return;
     cudaSetDevice(c->cfg.device);
-    free_graph(c);
+    free_graph(c); release_arena(c);
     if (c->comm) ncclCommDestroy(c->comm);
     if (c->solver) cusolverDnDestroy(c->solver);
     if (c->h_scal) cudaFreeHost(c->h_scal);
