@@ -82,6 +82,18 @@ def make_workload(name, seed=0):
     return synth.to_payload(g), synth.counts(g)
 
 
+def host_threads(omp_default):
+    """Threads for the CPU arm: every core this process may run on.  torchrun exports OMP_NUM_THREADS=1 when the
+    variable is unset, which would otherwise cut the reference arm to one thread at N > 1; TSB_REF_THREADS overrides."""
+    env = os.environ.get("TSB_REF_THREADS")
+    if env:
+        return max(1, int(env))
+    try:
+        return max(omp_default, len(os.sched_getaffinity(0)))
+    except AttributeError:
+        return max(omp_default, os.cpu_count() or 1)
+
+
 def run_reference(args):
     """CPU arm: sparse restatement of the reference algorithm (oracle tier T2), all host threads."""
     rank = int(os.environ.get("RANK", "0"))
@@ -89,7 +101,7 @@ def run_reference(args):
         return
     from oracle.oracle import OracleGraph, max_threads
     payload, c = make_workload(args.workload)
-    threads = max_threads()
+    threads = host_threads(max_threads())
     sample_iters = args.ref_iters
     times = []
     for s in range(args.warmup + args.steps):
@@ -128,7 +140,7 @@ def main():
     ap.add_argument("--lin-reps", type=int, default=20)
     args = ap.parse_args()
     if args.workload is None:
-        args.workload = "c2"          # BASELINE configs[1] at every N, so the per-N lines are comparable (strong scaling)
+        args.workload = "c2"          # BASELINE configs[1] at every N, so the per-N lines are comparable
     if args.impl == "reference":
         return run_reference(args)
 
@@ -161,6 +173,19 @@ def main():
     # pinned host copies of request and reply for the end-to-end leg
     req = torch.frombuffer(bytearray(payload), dtype=torch.uint8).pin_memory()
     counts = opt.load_wire_ptr(req.data_ptr(), req.numel())
+    # N > 1 and the request fits ONE GPU (the library would run it replicated: same answer on every rank, no speed-up):
+    # the N GPUs of the box then serve N requests at once -- one process per GPU, each with its own graph of this
+    # config (seed = rank) and a context without a communicator; no data-path collective.  `opt_n` (the world = N
+    # context) is kept for the single-request numbers reported beside the aggregate.
+    opt_n, req_n, independent = None, None, False
+    if world > 1 and counts.replicated == 1:
+        independent = True
+        opt_n, req_n = opt, req
+        payload, c = make_workload(args.workload, seed=rank)
+        opt = GraphOptimizerGpu(iterations=GN_ITERS, device=local, rank=0, world=1, nccl_id=None,
+                                pcg_tol=args.pcg_tol, pcg_max_iters=args.pcg_max, enable_exits=False)
+        req = torch.frombuffer(bytearray(payload), dtype=torch.uint8).pin_memory()
+        counts = opt.load_wire_ptr(req.data_ptr(), req.numel())
     reply = torch.empty(opt.reply_size(), dtype=torch.uint8).pin_memory()
     flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
 
@@ -193,7 +218,8 @@ def main():
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     dev_ms = float(t.item())
-    value = GN_ITERS / (dev_ms * 1e-3)
+    n_req = world if independent else 1                      # requests in flight: units = n_req x GN_ITERS per step
+    value = n_req * GN_ITERS / (dev_ms * 1e-3)
 
     # ---- linearize roofline at this workload (K1 + K2a + K2b), CUDA events inside the library ------------
     lin = []
@@ -228,13 +254,14 @@ def main():
     resident_kernel = counts.pcg_path == 1
     line = {
         "metric": "gn_iterations_per_s", "value": value, "unit": "iter/s", "n_gpus": world, "steps": args.steps,
-        "warmup": args.warmup, "ms_per_step": dev_ms, "higher_is_better": True, "scaling": "strong" if world > 1 else "weak",
+        "warmup": args.warmup, "ms_per_step": dev_ms, "higher_is_better": True,
+        "scaling": "strong" if world > 1 and not independent else "weak",
         "vs_baseline": None, "dtype": "f64", "data": "synthetic",
         "config": {"workload": f"{args.workload}: P={c['P']} L={c['L']} Eo={c['Eo']} El={c['El']}, {GN_ITERS} GN iterations/step, exits off",
                    "pcg_tol": args.pcg_tol, "pcg_iters_per_gn": pcg_total / GN_ITERS, "l2": "flushed between timed steps (256 MiB write)",
                    "wall_ms_per_step": 1e3 * wall / args.steps},
-        "edges_linearized_per_s": n_edges / (lin_ms * 1e-3),
-        "e2e": {"value": GN_ITERS / e2e_s, "unit": "iter/s", "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
+        "edges_linearized_per_s": n_req * n_edges / (lin_ms * 1e-3),
+        "e2e": {"value": n_req * GN_ITERS / e2e_s, "unit": "iter/s", "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
                 "ms_per_step": 1e3 * e2e_s},
         "gpu_launches": int(launches),
         "clocks": clk.summary(),
@@ -256,35 +283,47 @@ def main():
                                       "schur_prep_and_coarse_setup": (ms_sol - ms_pcg) / GN_ITERS, "coarse_refreshes_per_step": refreshes},
     }
 
-    replicated = counts.replicated == 1
-    line["config"]["parallelism"] = ("single GPU" if world == 1 else
-                                     f"replicated x{world}: the graph fits one GPU's shared-memory-resident PCG kernel, every rank solves it whole "
-                                     "without collectives (sharding a latency-bound 20 MB problem over NVLink only adds latency; see `sharded`)"
-                                     if replicated else f"edge-sharded over {world} ranks, NCCL all-reduces")
-    # ---- world > 1: the same workload forced through the edge-sharded NCCL path, for the record --------------------
-    if world > 1 and replicated:
-        os.environ["TSB_FORCE_SHARD"] = "1"
-        opt.load_wire_ptr(req.data_ptr(), req.numel())
-        step_resident()
-        barrier()
-        sh = [step_resident()[0] for _ in range(max(1, args.steps - 1))]
-        barrier()
-        ts = torch.tensor([sum(r.ms_total for r in sh) / len(sh)], dtype=torch.float64, device="cuda")
-        dist.all_reduce(ts, op=dist.ReduceOp.MAX)
-        line["sharded"] = {"value": GN_ITERS / (float(ts.item()) * 1e-3), "unit": "iter/s", "ms_per_step": float(ts.item()),
-                           "pcg_iters_per_gn": sum(r.pcg_iters_total for r in sh) / len(sh) / GN_ITERS,
-                           "note": "contiguous pose ranges per rank, per-rank coarse spaces, 3 NCCL all-reduces per PCG iteration"}
+    line["config"]["parallelism"] = (
+        "single GPU" if world == 1 else
+        f"{world} independent requests, one per GPU (this config fits one GPU's shared-memory-resident PCG kernel and is "
+        "latency-bound: sharding it over NVLink only adds collective latency, see `single_request`); one process per GPU, "
+        "graphs of the same config with seed = rank, no data-path collective; value = all ranks' GN iterations / slowest rank"
+        if independent else f"one request edge-sharded over {world} ranks, NCCL all-reduces")
+    # ---- world > 1: ONE request on the N GPUs, for the record: replicated (what the library does by default for a
+    # graph of this size) and forced through the edge-sharded NCCL path ---------------------------------------------
+    if independent:
+        def step_n():
+            opt_n.reset_state()
+            return opt_n.optimize(GN_ITERS)[0]
+        single = {}
+        for mode in ("replicated", "sharded"):
+            if mode == "sharded":
+                os.environ["TSB_FORCE_SHARD"] = "1"
+                opt_n.load_wire_ptr(req_n.data_ptr(), req_n.numel())
+            step_n()
+            barrier()
+            sh = [step_n() for _ in range(max(1, args.steps - 1))]
+            barrier()
+            ts = torch.tensor([sum(r.ms_total for r in sh) / len(sh)], dtype=torch.float64, device="cuda")
+            dist.all_reduce(ts, op=dist.ReduceOp.MAX)
+            single[mode] = {"value": GN_ITERS / (float(ts.item()) * 1e-3), "unit": "iter/s", "ms_per_step": float(ts.item()),
+                            "pcg_iters_per_gn": sum(r.pcg_iters_total for r in sh) / len(sh) / GN_ITERS}
+        os.environ.pop("TSB_FORCE_SHARD", None)
+        single["replicated"]["note"] = "every rank solves the whole graph, bit-identical results, no collective"
+        single["sharded"]["note"] = "contiguous pose ranges per rank, per-rank coarse spaces, 3 NCCL all-reduces per PCG iteration"
+        line["single_request"] = single
+    opt_c4 = opt_n if independent else opt                    # the 1M-pose graph is edge-sharded over the ranks
 
     # ---- the north-star size (1M poses / 20M edges) for the linearize roofline, single GPU only ---------------
     if not args.no_c4 and args.workload != "c4":
         try:
             p4, c4 = make_workload("c4")
             r4 = torch.frombuffer(bytearray(p4), dtype=torch.uint8)
-            opt.load_wire_ptr(r4.data_ptr(), r4.numel())
+            opt_c4.load_wire_ptr(r4.data_ptr(), r4.numel())
             del p4
             l4 = []
             for i in range(8):
-                st = opt.linearize()
+                st = opt_c4.linearize()
                 if i >= 3:
                     l4.append(st.ms_linearize)
             ms4 = float(np.median(l4)); B4, _ = algorithmic_bytes(c4)
@@ -301,7 +340,7 @@ def main():
     if world == 1 and rank == 0:
         from oracle.oracle import OracleGraph, max_threads
         o = OracleGraph(payload)
-        th = max_threads()
+        th = host_threads(max_threads())
         t0 = time.perf_counter()
         o.optimize_sparse(args.ref_iters, False, args.pcg_tol, args.pcg_max, th)
         dt = time.perf_counter() - t0
@@ -311,6 +350,8 @@ def main():
     if rank == 0:
         print(json.dumps(line), flush=True)
     opt.close()
+    if opt_n is not None:
+        opt_n.close()
     if world > 1:
         dist.destroy_process_group()
 

@@ -136,7 +136,7 @@ int upload_graph(tsb_ctx* c) {
     // system and solver vectors
     TRY(dalloc(c, d.hpl, 6ull * d.nE)); TRY(dalloc(c, d.hoo, 3ull * d.nO));
     TRY(dalloc(c, d.hpp, 6ull * d.nP)); TRY(dalloc(c, d.bp, 3ull * d.nP)); TRY(dalloc(c, d.pose_od, 6ull * d.nP));
-    TRY(dalloc(c, d.lm_part, 5ull * d.nSlots)); TRY(dalloc(c, d.lm_sum, 5ull * g.L));
+    TRY(dalloc(c, d.lm_part, 5ull * d.nSlots)); TRY(dalloc(c, d.lm_sum, 5ull * g.L + 1));     // + chi2, so that one all-reduce carries both when world > 1
     TRY(dalloc(c, d.hll, 3ull * g.L)); TRY(dalloc(c, d.hinv, 3ull * g.L)); TRY(dalloc(c, d.bl, 2ull * g.L));
     TRY(dalloc(c, d.minv, 6ull * d.nP)); TRY(dalloc(c, d.rhs, 3ull * d.nP));
     TRY(dalloc(c, d.x, 3ull * d.nP)); TRY(dalloc(c, d.r, 3ull * d.nP)); TRY(dalloc(c, d.z, 3ull * d.nP));
@@ -152,6 +152,9 @@ int upload_graph(tsb_ctx* c) {
     d.nSeg = (d.nP + 31) / 32;
     TRY(upload(c, d.agg_ptr, s.agg_ptr)); TRY(upload(c, d.pose_agg, s.pose_agg));
     d.res_nb = c->rp.nb;
+    d.lm_sum_chi2 = c->world > 1 ? 1u : 0u;
+    { const char* e = std::getenv("TSB_RES_CGSYNC");                  // 1: cooperative-groups grid.sync() in the resident kernel
+      if (d.res_nb && !(e && e[0] == '1')) TRY(dalloc(c, d.gbar, (size_t)1)); }
     if (d.res_nb) {
         TRY(upload(c, d.res_pose_cut, c->rp.pose_cut)); TRY(upload(c, d.res_lm_cut, c->rp.lm_cut)); TRY(upload(c, d.res_agg_cut, c->rp.agg_cut));
         TRY(upload(c, d.lmo_ptr, c->rp.lmo_ptr)); TRY(upload(c, d.lmo_edge, c->rp.lmo_edge)); TRY(upload(c, d.edge_lm, c->rp.edge_lm));
@@ -213,8 +216,7 @@ int enqueue_linearize(tsb_ctx* c) {
     launch_linearize(c->d, c->stream);
     if (c->world <= 1) { launch_lm_sum(c->d, true, c->stream); return TSB_OK; }     // sum + finalize in one kernel
     launch_lm_sum(c->d, false, c->stream);
-    TRY(allreduce(c, c->d.lm_sum, 5ull * c->g.L));
-    TRY(allreduce(c, c->d.scal + S_CHI2, 1));
+    TRY(allreduce(c, c->d.lm_sum, 5ull * c->g.L + 1));         // landmark sums and chi2 (k_lm_finalize moves it to scal)
     launch_lm_finalize(c->d, c->stream);
     return TSB_OK;
 }

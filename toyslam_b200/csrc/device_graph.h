@@ -27,6 +27,7 @@ struct Dev {
     const uint32_t* lm_packed;  // (pose - chunk.p0) << 16 | slot - chunk.s0
     const double2* le_z;        // landmark in the sensor frame (r cos b, r sin b)
     const double2* le_w;        // information diagonal
+    uint32_t* gbar;             // grid-barrier counter of the resident PCG kernel (zeroed before each launch); null: cg grid.sync
     double* hpl;                // A^T W B (3x2) per LM edge, as three planes of nE double2: row r of edge e at 2*(r*nE+e)
     const uint32_t* pose_ptr;   // nP + 1
     const ChunkDesc* chunks;
@@ -48,6 +49,7 @@ struct Dev {
     double* hpp;                // 6 per pose (00 01 02 11 12 22), prior included
     double* bp;                 // 3 per pose
     double* lm_part;            // 5 per slot: partial (Hll 00 01 11, b_l 0 1)
+    uint32_t lm_sum_chi2;       // world > 1: chi2 is written to lm_sum[5 L] (one all-reduce for both)
     double* lm_sum;             // 5 per landmark: sum over this rank's slots (all-reduced when world > 1)
     double* hll;                // 3 per landmark
     double* hinv;               // 3 per landmark: inverse of Hll (prior included)

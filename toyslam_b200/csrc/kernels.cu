@@ -334,6 +334,7 @@ __global__ void __launch_bounds__(kThreads) k_lm_sum(const Dev d) {
 
 __global__ void k_lm_finalize(const Dev d) {
     const uint32_t l = blockIdx.x * blockDim.x + threadIdx.x;
+    if (l == 0 && d.lm_sum_chi2) d.scal[S_CHI2] = d.lm_sum[5ull * d.L];
     if (l >= d.L) return;
     const double* a = d.lm_sum + 5ull * l;
     lm_finalize_one(d, l, a[0], a[1], a[2], a[3], a[4]);
@@ -1018,7 +1019,8 @@ void launch_linearize(const Dev& d, cudaStream_t s) {
         k_linearize_stream<<<g_stream_blocks, kLsThreads, kLsSmemBytes, s>>>(d); nparts = (uint32_t)g_stream_blocks;
         ++g_launches;
     } else if (d.nBlocks) { k_linearize<<<d.nBlocks, kThreads, LayLin::bytes, s>>>(d); ++g_launches; }
-    k_reduce2_to<<<1, 1024, 0, s>>>(d.part2, nob, d.part, nparts, d.scal + S_CHI2); ++g_launches;
+    // sharded: this rank's chi2 rides at the end of lm_sum through the landmark all-reduce
+    k_reduce2_to<<<1, 1024, 0, s>>>(d.part2, nob, d.part, nparts, d.lm_sum_chi2 ? d.lm_sum + 5ull * d.L : d.scal + S_CHI2); ++g_launches;
 }
 void launch_lm_sum(const Dev& d, bool finalize, cudaStream_t s) {
     if (!d.L) return;
@@ -1027,7 +1029,7 @@ void launch_lm_sum(const Dev& d, bool finalize, cudaStream_t s) {
     ++g_launches;
 }
 void launch_lm_finalize(const Dev& d, cudaStream_t s) {
-    if (d.L) { k_lm_finalize<<<cdiv(d.L, kThreads), kThreads, 0, s>>>(d); ++g_launches; }
+    if (d.L || d.lm_sum_chi2) { k_lm_finalize<<<d.L ? cdiv(d.L, kThreads) : 1u, kThreads, 0, s>>>(d); ++g_launches; }
 }
 void launch_schur_prep(const Dev& d, cudaStream_t s) {
     set_attrs();
@@ -1075,6 +1077,7 @@ int resident_blocks_available() {
 bool launch_pcg_resident(const Dev& d, cudaStream_t s) {
     if (!d.res_nb || (int)d.res_nb != resident_blocks_available()) return false;
     Dev dd = d; void* args[] = {&dd};
+    if (dd.gbar) cudaMemsetAsync(dd.gbar, 0, sizeof(uint32_t), s);
     const cudaError_t e = cudaLaunchCooperativeKernel((void*)k_pcg_resident, dim3(d.res_nb), dim3(kResThreads), args, kResSmemBytes, s);
     if (e != cudaSuccess) { cudaGetLastError(); return false; }
     ++g_launches;

@@ -146,10 +146,27 @@ __device__ __forceinline__ void res_landmarks(const Dev& d, const ResSm& s, cons
     }
 }
 
+// Grid barrier of the resident kernel (all blocks are co-resident: cooperative launch).  One counter that only
+// grows: block b's thread 0 adds 1 with release semantics and polls with acquire loads until the counter reaches
+// (barriers so far) x (blocks); bar.sync on both sides extends the ordering to the whole block.  About half the
+// latency of cg::grid_group::sync() here (no second fence, no flip-bit arithmetic); d.gbar == nullptr falls back to it.
+__device__ __forceinline__ void res_gsync(cg::grid_group& grid, uint32_t* ctr, uint32_t& target) {
+    if (!ctr) { grid.sync(); return; }
+    target += gridDim.x;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        asm volatile("red.release.gpu.global.add.u32 [%0], %1;" ::"l"(ctr), "r"(1u) : "memory");
+        uint32_t v;
+        do { asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(ctr) : "memory"); } while (v < target);
+    }
+    __syncthreads();
+}
+
 __global__ void __launch_bounds__(kResThreads, 1) k_pcg_resident(const Dev d) {
     extern __shared__ __align__(32) unsigned char smem_raw[];
     const ResSm s = res_carve(smem_raw);
     cg::grid_group grid = cg::this_grid();
+    uint32_t gtarget = 0;
     const uint32_t tid = threadIdx.x, b = blockIdx.x, nb = gridDim.x;
     const uint32_t p0 = d.res_pose_cut[b], np = d.res_pose_cut[b + 1] - p0;
     const uint32_t l0 = d.res_lm_cut[b], nl = d.res_lm_cut[b + 1] - l0;
@@ -198,10 +215,10 @@ __global__ void __launch_bounds__(kResThreads, 1) k_pcg_resident(const Dev d) {
     __syncthreads();
     // coarse residual Z^T r: this block's aggregates -> global, then every block keeps the whole vector
     if (coarse) res_restrict(s, s.r, s.aptr, na, d.yc + 3 * a0);
-    grid.sync();
+    res_gsync(grid, d.gbar, gtarget);
     if (coarse) { for (uint32_t k = tid; k < nc; k += kResThreads) s.rc[k] = d.yc[k]; __syncthreads(); }
     res_finish(d, s, coarse, p0, np, a0, na);
-    grid.sync();
+    res_gsync(grid, d.gbar, gtarget);
 
     double rz = 0, rz0 = 0, rz_last = 0;
     int it = 0, cur = 0;
@@ -240,7 +257,7 @@ __global__ void __launch_bounds__(kResThreads, 1) k_pcg_resident(const Dev d) {
         }
         cur ^= 1;
         RTICK(0);
-        grid.sync();
+        res_gsync(grid, d.gbar, gtarget);
         RTICK(1);
         // ---- phase 2: y = S p for the own poses, p'y and Z^T y ---------------------------------------------------
         const uint32_t pl = tid / 3, q = tid - 3 * pl;
@@ -275,7 +292,7 @@ __global__ void __launch_bounds__(kResThreads, 1) k_pcg_resident(const Dev d) {
         if (tid == 0) d.part[b] = t;
         if (coarse) res_restrict(s, s.y, s.aptr, na, d.cdot + 3 * a0);
         RTICK(2);
-        grid.sync();
+        res_gsync(grid, d.gbar, gtarget);
         RTICK(3);
         // ---- phase 3: alpha, x, r, coarse residual by recurrence, z and r'z ----------------------------------------
         const double alpha = rz / res_total(d.part, nb, s.red);
@@ -289,7 +306,7 @@ __global__ void __launch_bounds__(kResThreads, 1) k_pcg_resident(const Dev d) {
         res_finish(d, s, coarse, p0, np, a0, na);
         ++it;
         RTICK(4);
-        grid.sync();
+        res_gsync(grid, d.gbar, gtarget);
         RTICK(5);
     }
     if (timing) for (int q = 0; q < 16; ++q) d.dbg[q] = tacc[q];
@@ -297,6 +314,6 @@ __global__ void __launch_bounds__(kResThreads, 1) k_pcg_resident(const Dev d) {
     // ---- results: delta_p, the PCG scalars, landmark back-substitution delta_l = Hll^-1 (b_l - Hpl^T delta_p) ----
     if (tid < 3 * np) d.x[3ull * p0 + tid] = s.x[tid];
     if (b == 0 && tid == 0) { d.scal[S_RZ0] = rz0; d.scal[S_RZ] = rz_last; d.flags[F_ITERS] = it; d.flags[F_DONE] = 1; }
-    grid.sync();
+    res_gsync(grid, d.gbar, gtarget);
     res_landmarks<1>(d, s, d.x, nullptr, 0.0, l0, nl);
 }
