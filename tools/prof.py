@@ -14,7 +14,16 @@ a = ap.parse_args()
 t0 = time.time()
 payload = synth.to_payload(synth.make_config(a.workload, scale=a.scale))
 t1 = time.time()
-g = GraphOptimizerGpu(iterations=a.gn, pcg_tol=1e-12, pcg_max_iters=a.pcg, enable_exits=False)
+rank, world = int(os.environ.get("RANK", "0")), int(os.environ.get("WORLD_SIZE", "1"))
+nccl_id = None
+if world > 1:                      # torchrun: one process per GPU, the graph is edge-sharded over the ranks
+    import torch, torch.distributed as dist
+    torch.cuda.set_device(int(os.environ.get("LOCAL_RANK", "0")))
+    dist.init_process_group("nccl", device_id=torch.device("cuda", int(os.environ.get("LOCAL_RANK", "0"))))
+    from toyslam_b200 import dist as tdist
+    nccl_id = tdist.broadcast_unique_id(rank)
+g = GraphOptimizerGpu(iterations=a.gn, device=int(os.environ.get("LOCAL_RANK", "0")), rank=rank, world=world, nccl_id=nccl_id,
+                      pcg_tol=1e-12, pcg_max_iters=a.pcg, enable_exits=False)
 c = g.load_wire(payload)
 t2 = time.time()
 print(f"gen {t1 - t0:.1f}s load {t2 - t1:.1f}s P={c.n_pose} L={c.n_lm} El={c.n_lmedge} chunks={c.n_chunks} blocks={c.n_blocks} slots={c.n_slots}")

@@ -213,11 +213,31 @@ int fetch_scalars(tsb_ctx* c) {
 // K1 + K2.  world > 1: every rank linearises the LM edges of its poses; the per-landmark partial
 // (Hll, b_l) sums and chi2 are summed over ranks before the landmark blocks are inverted.
 int enqueue_linearize(tsb_ctx* c) {
+    static const bool timing = [] { const char* e = std::getenv("TSB_LIN_TIMING"); return e && e[0] == '1'; }();
+    cudaEvent_t ev[5] = {};
+    auto mark = [&](int i) { if (timing) { cudaEventCreate(&ev[i]); cudaEventRecord(ev[i], c->stream); } };
+    mark(0);
     launch_linearize(c->d, c->stream);
-    if (c->world <= 1) { launch_lm_sum(c->d, true, c->stream); return TSB_OK; }     // sum + finalize in one kernel
-    launch_lm_sum(c->d, false, c->stream);
-    TRY(allreduce(c, c->d.lm_sum, 5ull * c->g.L + 1));         // landmark sums and chi2 (k_lm_finalize moves it to scal)
-    launch_lm_finalize(c->d, c->stream);
+    mark(1);
+    if (c->world <= 1) launch_lm_sum(c->d, true, c->stream);          // sum + finalize in one kernel
+    else {
+        launch_lm_sum(c->d, false, c->stream);
+        mark(2);
+        TRY(allreduce(c, c->d.lm_sum, 5ull * c->g.L + 1));     // landmark sums and chi2 (k_lm_finalize moves it to scal)
+        mark(3);
+        launch_lm_finalize(c->d, c->stream);
+    }
+    mark(4);
+    if (timing) {
+        cudaEventSynchronize(ev[4]);
+        float a = 0, b = 0, x = 0, f = 0;
+        cudaEventElapsedTime(&a, ev[0], ev[1]);
+        if (c->world > 1) { cudaEventElapsedTime(&b, ev[1], ev[2]); cudaEventElapsedTime(&x, ev[2], ev[3]); cudaEventElapsedTime(&f, ev[3], ev[4]); }
+        else cudaEventElapsedTime(&b, ev[1], ev[4]);
+        std::fprintf(stderr, "[tsb] rank %d linearize: odom+edges+chi2 %.1f us, landmark sums %.1f us, all-reduce %.1f us, finalize %.1f us\n",
+                     c->rank, 1e3 * a, 1e3 * b, 1e3 * x, 1e3 * f);
+        for (auto& e : ev) if (e) cudaEventDestroy(e);
+    }
     return TSB_OK;
 }
 
