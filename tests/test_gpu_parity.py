@@ -219,12 +219,13 @@ def test_streaming_linearize_is_bit_identical(gpu, monkeypatch, case):
 
 def test_resident_pcg_matches_streaming_pcg(gpu, monkeypatch):
     """Small graphs run the shared-memory-resident PCG kernel (3 grid barriers per iteration); it must agree with
-    the general persistent kernel (TSB_NO_RESIDENT=1) and with block-Jacobi only (TSB_COARSE=0)."""
+    the general persistent kernel (TSB_NO_RESIDENT=1), with block-Jacobi only (TSB_COARSE=0) and with the coarse
+    operator inverted by cuSOLVER instead of the cooperative Gauss-Jordan kernel (TSB_COARSE_CUSOLVER=1)."""
     from toyslam_b200 import synth
     payload = synth.to_payload(synth.make_config("c2", scale=0.3, seed=4))
     res = []
-    for env in ({}, {"TSB_NO_RESIDENT": "1"}, {"TSB_COARSE": "0"}):
-        for k in ("TSB_NO_RESIDENT", "TSB_COARSE"):
+    for env in ({}, {"TSB_NO_RESIDENT": "1"}, {"TSB_COARSE": "0"}, {"TSB_COARSE_CUSOLVER": "1"}):
+        for k in ("TSB_NO_RESIDENT", "TSB_COARSE", "TSB_COARSE_CUSOLVER"):
             monkeypatch.delenv(k, raising=False)
         for k, v in env.items():
             monkeypatch.setenv(k, v)
@@ -236,6 +237,8 @@ def test_resident_pcg_matches_streaming_pcg(gpu, monkeypatch):
         assert np.max(np.abs(res[0][0] - other[0]) / res[0][0]) < CHI2_TOL
         assert state_diff(*res[0][1], *other[1]) < STATE_TOL
     assert res[0][2] < res[2][2]            # the coarse level pays for itself
+    # the blocked Gauss-Jordan inverse (k_coarse_invert) and cuSOLVER's potrf + potrs(I) give the same preconditioner
+    assert abs(res[0][2] - res[3][2]) <= max(4, res[3][2] // 50)
 
 
 def test_context_reuse_across_requests_is_bit_reproducible(gpu):

@@ -164,7 +164,7 @@ int upload_graph(tsb_ctx* c) {
     TRY(upload(c, d.cpair_a, s.cpair_a)); TRY(upload(c, d.cpair_b, s.cpair_b)); TRY(upload(c, d.cpair_ptr, s.cpair_ptr));
     TRY(upload(c, d.ctrip, s.ctrip));
     TRY(dalloc(c, d.zoff, d.nP)); TRY(dalloc(c, d.cC, 6ull * d.nAS)); TRY(dalloc(c, d.Ac, (size_t)d.nc * d.nc)); TRY(dalloc(c, d.Ai, (size_t)d.nc * d.nc));
-    TRY(dalloc(c, d.rcp, 3ull * d.nSeg)); TRY(dalloc(c, d.yc, d.nc)); TRY(dalloc(c, d.cdot, d.nc)); TRY(dalloc(c, d.cinfo, (size_t)2));
+    TRY(dalloc(c, d.rcp, 3ull * d.nSeg)); TRY(dalloc(c, d.yc, d.nc)); TRY(dalloc(c, d.cdot, d.nc)); TRY(dalloc(c, d.cinfo, (size_t)2)); TRY(dalloc(c, d.cbar, (size_t)1));
     CU(cudaMemsetAsync(d.cinfo, 0, 8, c->stream));
     if (c->use_coarse && d.nc) {
         int l1 = 0, l2 = 0;
@@ -254,6 +254,16 @@ int run_solve(tsb_ctx* c, bool refresh_coarse = true) {
         if (timing) { for (auto& e : te) cudaEventCreate(&e); cudaEventRecord(te[0], c->stream); }
         launch_coarse_assemble(d, c->stream);
         if (timing) cudaEventRecord(te[1], c->stream);
+        const char* ecs = std::getenv("TSB_COARSE_CUSOLVER");          // 1: cuSOLVER potrf + potrs(I) instead of k_coarse_invert
+        const bool use_cusolver = ecs && ecs[0] == '1';
+        if (!use_cusolver && launch_coarse_invert(d, c->stream)) {
+            if (timing) {
+                cudaEventRecord(te[2], c->stream); cudaEventSynchronize(te[2]);
+                float a = 0, b = 0; cudaEventElapsedTime(&a, te[0], te[1]); cudaEventElapsedTime(&b, te[1], te[2]);
+                std::fprintf(stderr, "[tsb] coarse setup nc=%u: assemble %.3f ms, k_coarse_invert %.3f ms\n", d.nc, a, b);
+                for (auto& ev : te) cudaEventDestroy(ev);
+            }
+        } else {
         if (cusolverDnDpotrf(c->solver, CUBLAS_FILL_MODE_LOWER, (int)d.nc, d.Ac, (int)d.nc, c->cwork, c->cwork_len, d.cinfo) != CUSOLVER_STATUS_SUCCESS) {
             c->err = "cusolverDnDpotrf failed"; return TSB_ECUDA; }
         if (timing) cudaEventRecord(te[2], c->stream);
@@ -267,6 +277,7 @@ int run_solve(tsb_ctx* c, bool refresh_coarse = true) {
             float a = 0, b = 0, e = 0; cudaEventElapsedTime(&a, te[0], te[1]); cudaEventElapsedTime(&b, te[1], te[2]); cudaEventElapsedTime(&e, te[2], te[3]);
             std::fprintf(stderr, "[tsb] coarse setup nc=%u: assemble %.3f ms, potrf %.3f ms, potrs(I) %.3f ms\n", d.nc, a, b, e);
             for (auto& ev : te) cudaEventDestroy(ev);
+        }
         }
     }
     cudaEventRecord(c->ev[4], c->stream);
@@ -548,7 +559,9 @@ int tsb_optimize(tsb_ctx* c, uint32_t iterations, tsb_report* rep, tsb_iter_stat
     const uint64_t launches0 = g_launches;
     const bool exits = c->cfg.enable_exits != 0;
     double prevErr = -1, err = 0; int penalty = 0, code = 0; uint32_t done = 0;
-    c->coarse_age = -1; c->coarse_hold = 0; c->coarse_backoff = 1;   // every request starts from a fresh coarse operator
+    // every request starts from a fresh coarse operator and refreshes it on its first solves: far from the optimum the
+    // Huber weights move so much per step that a one-step-old operator costs ~1.7x the iterations (C2: 240 -> 415)
+    c->coarse_age = -1; c->coarse_hold = 4; c->coarse_backoff = 1;
     int64_t pcg_total = 0; float ms_lin = 0, ms_sol = 0, ms_pcg = 0; const int refreshes0 = c->coarse_refreshes;
     CU(cudaEventRecord(c->ev[3], c->stream));
     for (uint32_t it = 0; it < iterations; ++it) {

@@ -87,6 +87,7 @@ struct Dev {
     double* rcp;                // 3 per segment: Z^T r summed over the segment's 32 poses
     double* yc;                 // nc: coarse correction Ac^-1 (Z^T r)
     double* cdot;               // nc: (Z^T r)_j * yc_j  (the coarse part of r'z)
+    uint32_t* cbar;             // grid-barrier counter of k_coarse_invert
     int* cinfo;                 // potrf / potrs status words
     long long* dbg;             // optional: 8 phase-cycle counters of the persistent PCG kernel (TSB_PCG_TIMING=1)
 };
@@ -98,6 +99,7 @@ void launch_lm_finalize(const Dev& d, cudaStream_t s);          // K2b: Hll, b_l
 void launch_schur_prep(const Dev& d, cudaStream_t s);           // K3: diag(S)^-1 and reduced rhs
 void launch_coarse_assemble(const Dev& d, cudaStream_t s);      // zoff, C, Ac = Z^T S Z (dense, deterministic)
 void launch_coarse_identity(const Dev& d, cudaStream_t s);      // Ai = I (right-hand side of the inverse solve)
+bool launch_coarse_invert(const Dev& d, cudaStream_t s);        // Ai = Ac^-1 + F_COARSE, one cooperative launch (blocked Gauss-Jordan)
 void launch_coarse_finish(const Dev& d, cudaStream_t s);        // set F_COARSE from cinfo
 void launch_pcg_coarse(const Dev& d, int init, cudaStream_t s);           // yc = Ac^-1 Z^T r, cdot (phased path)
 bool launch_pcg_persistent(const Dev& d, cudaStream_t s);     // whole PCG + back-substitution, one cooperative launch

@@ -912,6 +912,7 @@ __global__ void __launch_bounds__(kThreads, 3) k_pcg_persistent(const Dev d) {
 }
 
 #include "pcg_resident.cuh"
+#include "coarse_invert.cuh"
 
 // delta_l = Hll^-1 (b_l - Hpl^T delta_p); w_sum holds Hpl^T delta_p
 __global__ void k_backsub(const Dev d) {
@@ -1056,6 +1057,26 @@ void launch_coarse_assemble(const Dev& d, cudaStream_t s) {
     if (d.nAS) { k_coarse_C<<<cdiv(d.nAS, kThreads), kThreads, 0, s>>>(d); ++g_launches; }
     k_coarse_pose<<<cdiv(d.nA * 32, kThreads), kThreads, 0, s>>>(d); ++g_launches;
     if (d.nPairs) { k_coarse_lm<<<cdiv(d.nPairs, 128), 128, 0, s>>>(d); ++g_launches; }
+}
+// Ai = Ac^-1 and F_COARSE in one cooperative launch; false: not launchable here (the caller uses cuSOLVER)
+bool launch_coarse_invert(const Dev& d, cudaStream_t s) {
+    static int blocks = -1;
+    if (blocks < 0) {
+        int dev = 0, sms = 0, per_sm = 0, coop = 0;
+        cudaGetDevice(&dev);
+        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+        cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, dev);
+        if (cudaFuncSetAttribute(k_coarse_invert, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kCiSmemBytes) != cudaSuccess) cudaGetLastError();
+        else cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_coarse_invert, kCiThreads, kCiSmemBytes);
+        blocks = (coop && per_sm >= 1) ? sms : 0;
+    }
+    const uint32_t nb = (d.nc + 31) / 32;
+    if (!blocks || !d.cbar || !nb || nb > (uint32_t)blocks) return false;
+    Dev dd = d; void* args[] = {&dd};
+    cudaMemsetAsync(dd.cbar, 0, sizeof(uint32_t), s);
+    if (cudaLaunchCooperativeKernel((void*)k_coarse_invert, dim3(blocks), dim3(kCiThreads), args, kCiSmemBytes, s) != cudaSuccess) { cudaGetLastError(); return false; }
+    ++g_launches;
+    return true;
 }
 void launch_coarse_identity(const Dev& d, cudaStream_t s) { k_coarse_identity<<<148 * 4, kThreads, 0, s>>>(d); ++g_launches; }
 void launch_coarse_finish(const Dev& d, cudaStream_t s) { k_coarse_finish<<<1, 32, 0, s>>>(d); ++g_launches; }
