@@ -312,27 +312,43 @@ def main():
         single["replicated"]["note"] = "every rank solves the whole graph, bit-identical results, no collective"
         single["sharded"]["note"] = "contiguous pose ranges per rank, per-rank coarse spaces, 3 NCCL all-reduces per PCG iteration"
         line["single_request"] = single
-    opt_c4 = opt_n if independent else opt                    # the 1M-pose graph is edge-sharded over the ranks
-
-    # ---- the north-star size (1M poses / 20M edges) for the linearize roofline, single GPU only ---------------
+    # ---- the north-star size (1M poses / 20M edges): linearize roofline and a bounded PCG sample --------------------
+    # (its own context, edge-sharded over the N ranks, PCG capped at 30 iterations per solve so the cost is fixed)
     if not args.no_c4 and args.workload != "c4":
         try:
+            _, B_pcg4 = 0, 0
+            id4 = None
+            if world > 1:
+                from toyslam_b200 import dist as tdist
+                id4 = tdist.broadcast_unique_id(rank)
+            opt4 = GraphOptimizerGpu(iterations=1, device=local, rank=rank, world=world, nccl_id=id4,
+                                     pcg_tol=args.pcg_tol, pcg_max_iters=30, enable_exits=False)
             p4, c4 = make_workload("c4")
             r4 = torch.frombuffer(bytearray(p4), dtype=torch.uint8)
-            opt_c4.load_wire_ptr(r4.data_ptr(), r4.numel())
+            opt4.load_wire_ptr(r4.data_ptr(), r4.numel())
             del p4
             l4 = []
             for i in range(8):
-                st = opt_c4.linearize()
+                st = opt4.linearize()
                 if i >= 3:
                     l4.append(st.ms_linearize)
-            ms4 = float(np.median(l4)); B4, _ = algorithmic_bytes(c4)
+            ms4 = float(np.median(l4)); B4, B_pcg4 = algorithmic_bytes(c4)
+            rep4 = [opt4.optimize(1)[0] for _ in range(3)][1:]            # GN iterations with 30 PCG iterations each
+            us_it = 1e3 * sum(r.ms_pcg_total for r in rep4) / max(1, sum(r.pcg_iters_total for r in rep4))
             if world > 1:                                     # edge-sharded over the ranks: the slowest rank counts
-                t4 = torch.tensor([ms4], dtype=torch.float64, device="cuda"); dist.all_reduce(t4, op=dist.ReduceOp.MAX); ms4 = float(t4.item())
-            line["roofline_linearize_c4"] = {"workload": f"c4: P={c4['P']} L={c4['L']} Eo={c4['Eo']} El={c4['El']}", "bound": "hbm",
+                t4 = torch.tensor([ms4, us_it], dtype=torch.float64, device="cuda"); dist.all_reduce(t4, op=dist.ReduceOp.MAX)
+                ms4, us_it = float(t4[0].item()), float(t4[1].item())
+            wl4 = f"c4: P={c4['P']} L={c4['L']} Eo={c4['Eo']} El={c4['El']}"
+            line["roofline_linearize_c4"] = {"workload": wl4, "bound": "hbm",
                                              "achieved": B4 / (ms4 * 1e-3) / 1e9, "peak": peak * world, "unit": "GB/s", "n_gpus": world,
                                              "frac": B4 / (ms4 * 1e-3) / 1e9 / (peak * world), "algorithmic_bytes": B4, "ms": ms4,
                                              "edges_linearized_per_s": (c4["Eo"] + c4["El"]) / (ms4 * 1e-3)}
+            line["roofline_pcg_c4"] = {"workload": wl4, "kernel": "k_pcg_persistent" if world == 1 else "k_pcg_* phases + NCCL all-reduces",
+                                       "bound": "hbm", "achieved": B_pcg4 / (us_it * 1e-6) / 1e9, "peak": peak * world, "unit": "GB/s",
+                                       "n_gpus": world, "frac": B_pcg4 / (us_it * 1e-6) / 1e9 / (peak * world),
+                                       "algorithmic_bytes_per_pcg_iteration": B_pcg4, "us_per_pcg_iteration": us_it,
+                                       "sample": "2 GN iterations x 30 PCG iterations (capped), PCG kernel time only"}
+            opt4.close()
         except Exception as e:                                # never lose the main line to the extra measurement
             line["roofline_linearize_c4"] = {"error": str(e)}
 

@@ -308,28 +308,23 @@ __device__ __forceinline__ void lm_finalize_one(const Dev& d, uint32_t l, double
     d.hinv[3ull * l] = h11 * id; d.hinv[3ull * l + 1] = -h01 * id; d.hinv[3ull * l + 2] = h00 * id;
 }
 
-// Warp per landmark.  Lane (j, comp) = (lane / 5, lane % 5), lanes 0..29: slot partials j, j+6, j+12, ... of the
-// landmark are summed in order (the five components of a slot are one contiguous 40-byte read), then the six
-// strided sums are combined as ((v0+v1)+(v2+v3))+(v4+v5): a fixed order.  FIN (world == 1): finalize in place.
+// Thread per landmark: the slot partials of the landmark (five doubles each, one contiguous 40-byte read) are added
+// in list order, two partials in flight per step.  FIN (world == 1): finalize in place.  (A warp per landmark -- six
+// slots x five components across the lanes -- was latency-bound: ~10 partials per landmark, three dependent loads.)
 template <bool FIN>
 __global__ void __launch_bounds__(kThreads) k_lm_sum(const Dev d) {
-    const uint32_t l = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+    const uint32_t l = blockIdx.x * blockDim.x + threadIdx.x;
     if (l >= d.L) return;
-    const uint32_t j = lane / 5, comp = lane - 5 * j;
-    double a = 0;
-    if (lane < 30) {
-        const uint32_t qe = d.lm_part_ptr[l + 1];
-        for (uint32_t q = d.lm_part_ptr[l] + j; q < qe; q += 6) a += d.lm_part[5ull * d.lm_part_idx[q] + comp];
+    uint32_t q = d.lm_part_ptr[l]; const uint32_t qe = d.lm_part_ptr[l + 1];
+    double a0 = 0, a1 = 0, a2 = 0, a3 = 0, a4 = 0;
+    for (; q + 2 <= qe; q += 2) {
+        const double* u = d.lm_part + 5ull * d.lm_part_idx[q]; const double* v = d.lm_part + 5ull * d.lm_part_idx[q + 1];
+        const double u0 = u[0], u1 = u[1], u2 = u[2], u3 = u[3], u4 = u[4], v0 = v[0], v1 = v[1], v2 = v[2], v3 = v[3], v4 = v[4];
+        a0 += u0; a1 += u1; a2 += u2; a3 += u3; a4 += u4; a0 += v0; a1 += v1; a2 += v2; a3 += v3; a4 += v4;
     }
-    const uint32_t c = lane < 5 ? lane : 0;
-    const double v0 = __shfl_sync(0xffffffffu, a, c), v1 = __shfl_sync(0xffffffffu, a, c + 5), v2 = __shfl_sync(0xffffffffu, a, c + 10);
-    const double v3 = __shfl_sync(0xffffffffu, a, c + 15), v4 = __shfl_sync(0xffffffffu, a, c + 20), v5 = __shfl_sync(0xffffffffu, a, c + 25);
-    const double t = ((v0 + v1) + (v2 + v3)) + (v4 + v5);
-    if (FIN) {
-        const double s0 = __shfl_sync(0xffffffffu, t, 0), s1 = __shfl_sync(0xffffffffu, t, 1), s2 = __shfl_sync(0xffffffffu, t, 2);
-        const double s3 = __shfl_sync(0xffffffffu, t, 3), s4 = __shfl_sync(0xffffffffu, t, 4);
-        if (lane == 0) lm_finalize_one(d, l, s0, s1, s2, s3, s4);
-    } else if (lane < 5) d.lm_sum[5ull * l + lane] = t;
+    if (q < qe) { const double* u = d.lm_part + 5ull * d.lm_part_idx[q]; a0 += u[0]; a1 += u[1]; a2 += u[2]; a3 += u[3]; a4 += u[4]; }
+    if (FIN) lm_finalize_one(d, l, a0, a1, a2, a3, a4);
+    else { double* o = d.lm_sum + 5ull * l; o[0] = a0; o[1] = a1; o[2] = a2; o[3] = a3; o[4] = a4; }
 }
 
 __global__ void k_lm_finalize(const Dev d) {
@@ -539,17 +534,20 @@ __device__ __forceinline__ double unit_pass_b(const Dev& d, const uint32_t unit,
     return block_sum(dot, sm.red);
 }
 
-// landmark-major sum of the slot partials of w = Hpl^T v, one warp per landmark: lane j takes the
-// partials j, j+32, ... in order, then a fixed shuffle tree combines the lanes (deterministic).
-__device__ __forceinline__ double2 lm_w_sum_warp(const Dev& d, uint32_t l) {
-    const uint32_t lane = threadIdx.x & 31;
+// landmark-major sum of the slot partials of w = Hpl^T v, one THREAD per landmark, partials added in list order
+// (deterministic).  A landmark has about ten partials at C3/C4: a warp per landmark left two thirds of its lanes
+// idle and put three dependent global loads (pointer, index, partial) in series per landmark and warp -- 260 us of
+// the 1.26 ms C4 iteration; with a thread per landmark all of them are in flight at once.
+__device__ __forceinline__ double2 lm_w_sum(const Dev& d, uint32_t l) {
+    uint32_t q = d.lm_part_ptr[l]; const uint32_t qe = d.lm_part_ptr[l + 1];
+    const double2* wp = reinterpret_cast<const double2*>(d.w_part);
     double a0 = 0, a1 = 0;
-    for (uint32_t q = d.lm_part_ptr[l] + lane; q < d.lm_part_ptr[l + 1]; q += 32) {
-        const double2 r = reinterpret_cast<const double2*>(d.w_part)[d.lm_part_idx[q]];
-        a0 += r.x; a1 += r.y;
+    for (; q + 4 <= qe; q += 4) {
+        const uint32_t i0 = d.lm_part_idx[q], i1 = d.lm_part_idx[q + 1], i2 = d.lm_part_idx[q + 2], i3 = d.lm_part_idx[q + 3];
+        const double2 r0 = wp[i0], r1 = wp[i1], r2 = wp[i2], r3 = wp[i3];
+        a0 += r0.x; a1 += r0.y; a0 += r1.x; a1 += r1.y; a0 += r2.x; a1 += r2.y; a0 += r3.x; a1 += r3.y;
     }
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) { a0 += __shfl_xor_sync(0xffffffffu, a0, o); a1 += __shfl_xor_sync(0xffffffffu, a1, o); }
+    for (; q < qe; ++q) { const double2 r = wp[d.lm_part_idx[q]]; a0 += r.x; a1 += r.y; }
     return make_double2(a0, a1);
 }
 
@@ -750,16 +748,13 @@ __global__ void __launch_bounds__(kThreads) k_pcg_pass_a(const Dev d) {
     const Sm sm = Sm::make<LayA>(smem_raw);
     unit_pass_a<MODE>(d, blockIdx.x, sm, MODE == 0 ? d.scal[S_BETA] : 0.0, MODE == 0 && d.flags[F_COARSE] != 0);
 }
-// landmark-major sum of the slot partials (warp per landmark); used where w must exist as an array:
+// landmark-major sum of the slot partials (thread per landmark); used where w must exist as an array:
 // before the all-reduce over ranks (world > 1) and before the back-substitution
 __global__ void k_pcg_mid(const Dev d, int mode) {
     if (mode == 0 && d.flags[F_DONE]) return;
-    const uint32_t gtid = blockIdx.x * blockDim.x + threadIdx.x, gw = gtid >> 5, nw = (gridDim.x * blockDim.x) >> 5;
-    for (uint32_t l = gw; l < d.L; l += nw) {
-        const double2 w = lm_w_sum_warp(d, l);
-        if ((threadIdx.x & 31) == 0) reinterpret_cast<double2*>(d.w_sum)[l] = w;
-    }
-    if (mode == 0) for (uint32_t p = gtid; p < d.nP; p += gridDim.x * blockDim.x) hpp_apply(d, p, d.sp + 3ull * p);
+    const uint32_t gtid = blockIdx.x * blockDim.x + threadIdx.x, gsz = gridDim.x * blockDim.x;
+    for (uint32_t l = gtid; l < d.L; l += gsz) reinterpret_cast<double2*>(d.w_sum)[l] = lm_w_sum(d, l);
+    if (mode == 0) for (uint32_t p = gtid; p < d.nP; p += gsz) hpp_apply(d, p, d.sp + 3ull * p);
 }
 __global__ void __launch_bounds__(kThreads) k_pcg_pass_b(const Dev d) {
     if (d.flags[F_DONE]) return;
@@ -860,10 +855,7 @@ __global__ void __launch_bounds__(kThreads, 3) k_pcg_persistent(const Dev d) {
             TICK(0);
             grid.sync();
             TICK(1);
-            for (uint32_t l = gtid >> 5; l < d.L; l += gsz >> 5) {
-                const double2 w = lm_w_sum_warp(d, l);
-                if ((threadIdx.x & 31) == 0) reinterpret_cast<double2*>(d.w_sum)[l] = w;
-            }
+            for (uint32_t l = gtid; l < d.L; l += gsz) reinterpret_cast<double2*>(d.w_sum)[l] = lm_w_sum(d, l);
             for (uint32_t p = gtid; p < d.nP; p += gsz) hpp_apply(d, p, d.sp + 3ull * p);
             TICK(2);
             grid.sync();
@@ -901,13 +893,11 @@ __global__ void __launch_bounds__(kThreads, 3) k_pcg_persistent(const Dev d) {
     grid.sync();
     for (uint32_t u = blockIdx.x; u < d.nBlocks; u += nb) unit_pass_a<1>(d, u, sm, 0.0, false);
     grid.sync();
-    for (uint32_t l = gtid >> 5; l < d.L; l += gsz >> 5) {
-        const double2 w = lm_w_sum_warp(d, l);
-        if ((threadIdx.x & 31) == 0) {
-            const double t0 = d.bl[2ull * l] - w.x, t1 = d.bl[2ull * l + 1] - w.y;
-            const double* hi = d.hinv + 3ull * l;
-            d.dl[2ull * l] = hi[0] * t0 + hi[1] * t1; d.dl[2ull * l + 1] = hi[1] * t0 + hi[2] * t1;
-        }
+    for (uint32_t l = gtid; l < d.L; l += gsz) {
+        const double2 w = lm_w_sum(d, l);
+        const double t0 = d.bl[2ull * l] - w.x, t1 = d.bl[2ull * l + 1] - w.y;
+        const double* hi = d.hinv + 3ull * l;
+        d.dl[2ull * l] = hi[0] * t0 + hi[1] * t1; d.dl[2ull * l + 1] = hi[1] * t0 + hi[2] * t1;
     }
 }
 
@@ -1025,8 +1015,8 @@ void launch_linearize(const Dev& d, cudaStream_t s) {
 }
 void launch_lm_sum(const Dev& d, bool finalize, cudaStream_t s) {
     if (!d.L) return;
-    if (finalize) k_lm_sum<true><<<cdiv(d.L, kThreads / 32), kThreads, 0, s>>>(d);
-    else k_lm_sum<false><<<cdiv(d.L, kThreads / 32), kThreads, 0, s>>>(d);
+    if (finalize) k_lm_sum<true><<<cdiv(d.L, kThreads), kThreads, 0, s>>>(d);
+    else k_lm_sum<false><<<cdiv(d.L, kThreads), kThreads, 0, s>>>(d);
     ++g_launches;
 }
 void launch_lm_finalize(const Dev& d, cudaStream_t s) {
@@ -1118,7 +1108,7 @@ void launch_pcg_pass_a(const Dev& d, int mode, cudaStream_t s) {
     ++g_launches;
 }
 void launch_pcg_mid(const Dev& d, int mode, cudaStream_t s) {
-    uint32_t nb = cdiv(d.L, kThreads / 32);
+    uint32_t nb = cdiv(d.L, kThreads);
     if (mode == 0 && cdiv(d.nP, kThreads) > nb) nb = cdiv(d.nP, kThreads);
     if (nb > 148 * 8) nb = 148 * 8;
     if (nb) { k_pcg_mid<<<nb, kThreads, 0, s>>>(d, mode); ++g_launches; }
