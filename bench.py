@@ -343,7 +343,9 @@ def main():
                                              "achieved": B4 / (ms4 * 1e-3) / 1e9, "peak": peak * world, "unit": "GB/s", "n_gpus": world,
                                              "frac": B4 / (ms4 * 1e-3) / 1e9 / (peak * world), "algorithmic_bytes": B4, "ms": ms4,
                                              "edges_linearized_per_s": (c4["Eo"] + c4["El"]) / (ms4 * 1e-3)}
-            line["roofline_pcg_c4"] = {"workload": wl4, "kernel": "k_pcg_persistent" if world == 1 else "k_pcg_* phases + NCCL all-reduces",
+            path4 = {0: "k_pcg_persistent", 1: "k_pcg_resident", 2: "k_pcg_* phases + NCCL all-reduces",
+                     3: "k_pcg_stream (persistent cooperative kernel, edge passes through a 3-stage TMA ring)"}[opt4.refresh_counts().pcg_path]
+            line["roofline_pcg_c4"] = {"workload": wl4, "kernel": path4,
                                        "bound": "hbm", "achieved": B_pcg4 / (us_it * 1e-6) / 1e9, "peak": peak * world, "unit": "GB/s",
                                        "n_gpus": world, "frac": B_pcg4 / (us_it * 1e-6) / 1e9 / (peak * world),
                                        "algorithmic_bytes_per_pcg_iteration": B_pcg4, "us_per_pcg_iteration": us_it,

@@ -66,7 +66,7 @@ typedef struct tsb_counts {
     uint32_t pose_begin, pose_end;                            /* canonical pose range owned by this rank */
     uint32_t n_lmedge_local, n_odom_local;                    /* edges linearised by this rank          */
     uint32_t n_chunks, n_blocks, n_slots;                     /* assembly structure of this rank        */
-    uint32_t pcg_path;                                        /* 0 persistent kernel, 1 shared-memory-resident kernel, 2 one launch per phase (+ NCCL) */
+    uint32_t pcg_path;                                        /* 0 persistent kernel, 1 shared-memory-resident kernel, 2 one launch per phase (+ NCCL), 3 streamed persistent kernel */
     uint32_t replicated;                                      /* 1: world > 1 but the graph is solved whole on every rank (it fits one GPU's resident kernel) */
     uint32_t n_aggregates;                                    /* coarse space of the two-level preconditioner (this rank) */
 } tsb_counts;

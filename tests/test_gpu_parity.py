@@ -241,6 +241,29 @@ def test_resident_pcg_matches_streaming_pcg(gpu, monkeypatch):
     assert abs(res[0][2] - res[3][2]) <= max(4, res[3][2] // 50)
 
 
+def test_streamed_pcg_matches_persistent_kernel(gpu, monkeypatch):
+    """HBM-sized graphs on one GPU run k_pcg_stream (edge passes through the TMA ring, register prefetch); forced on
+    a small graph it must agree with the block-synchronous persistent kernel: same edge-pass arithmetic, only p'Sp
+    is summed per block instead of per unit."""
+    from toyslam_b200 import synth
+    payload = synth.to_payload(synth.make_config("c3", scale=0.04, seed=9))
+    res = []
+    for env in ({"TSB_NO_STREAM": "1"}, {"TSB_STREAM_MIN_UNITS": "1"}):
+        for k in ("TSB_NO_STREAM", "TSB_STREAM_MIN_UNITS"):
+            monkeypatch.delenv(k, raising=False)
+        monkeypatch.setenv("TSB_NO_RESIDENT", "1")
+        for k, v in env.items():
+            monkeypatch.setenv(k, v)
+        g = gpu(iterations=4, pcg_tol=1e-13, pcg_max_iters=20000, enable_exits=False); g.load_wire(payload)
+        rep, per = g.optimize()
+        assert all(p.pcg_rel_residual <= 1e-13 for p in per)
+        res.append((np.array([p.chi2 for p in per]), g.state(), rep.pcg_iters_total, g.refresh_counts().pcg_path))
+    assert res[0][3] == 0 and res[1][3] == 3
+    assert np.max(np.abs(res[0][0] - res[1][0]) / res[0][0]) < CHI2_TOL
+    assert state_diff(*res[0][1], *res[1][1]) < STATE_TOL
+    assert abs(res[0][2] - res[1][2]) <= max(4, res[0][2] // 50)
+
+
 def test_context_reuse_across_requests_is_bit_reproducible(gpu):
     """The server keeps one context for every request (ConnectionHandler.h:18-20 rebuilds everything instead); device
     memory is recycled between graphs.  A -> B (larger) -> A -> C (smaller) -> A on one context: every run of A

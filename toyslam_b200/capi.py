@@ -137,6 +137,11 @@ class GraphOptimizerGpu:
         c = Counts(); self._ck(self.L.tsb_get_counts(self.h, C.byref(c))); self.counts = c
         return c
 
+    def refresh_counts(self):
+        """counts again (pcg_path reports the path the LAST solve took)"""
+        c = Counts(); self._ck(self.L.tsb_get_counts(self.h, C.byref(c))); self.counts = c
+        return c
+
     def load_wire_ptr(self, ptr, nbytes):
         """payload already in (pinned) host memory at address `ptr`"""
         self._ck(self.L.tsb_load_wire(self.h, C.c_void_p(ptr), C.c_uint32(nbytes)))

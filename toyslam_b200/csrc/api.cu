@@ -37,6 +37,7 @@ struct tsb_ctx {
     double* h_scal = nullptr; int* h_flags = nullptr;     // pinned
     bool loaded = false, linearized = false, solved = false;
     uint32_t part_cap = 0;
+    bool pcg_streamed = false;                            // the last solve ran k_pcg_stream
     bool force_phased = false;                            // TSB_PCG_PHASED=1: one launch per PCG phase (the multi-GPU path)
     uint64_t h2d = 0, d2h = 0;                            // bytes copied since the last tsb_load_*
     ncclComm_t comm = nullptr;                            // world > 1: one communicator, collectives on `stream`
@@ -154,7 +155,7 @@ int upload_graph(tsb_ctx* c) {
     d.res_nb = c->rp.nb;
     d.lm_sum_chi2 = c->world > 1 ? 1u : 0u;
     { const char* e = std::getenv("TSB_RES_CGSYNC");                  // 1: cooperative-groups grid.sync() in the resident kernel
-      if (d.res_nb && !(e && e[0] == '1')) TRY(dalloc(c, d.gbar, (size_t)1)); }
+      if (!(e && e[0] == '1')) TRY(dalloc(c, d.gbar, (size_t)1)); }
     if (d.res_nb) {
         TRY(upload(c, d.res_pose_cut, c->rp.pose_cut)); TRY(upload(c, d.res_lm_cut, c->rp.lm_cut)); TRY(upload(c, d.res_agg_cut, c->rp.agg_cut));
         TRY(upload(c, d.lmo_ptr, c->rp.lmo_ptr)); TRY(upload(c, d.lmo_edge, c->rp.lmo_edge)); TRY(upload(c, d.edge_lm, c->rp.edge_lm));
@@ -296,6 +297,26 @@ int run_solve(tsb_ctx* c, bool refresh_coarse = true) {
         cudaEventRecord(c->ev[5], c->stream);
         return TSB_OK;
     }
+    // single GPU, HBM-sized graph: streamed persistent kernel, then the back-substitution by the phased kernels
+    if (c->world <= 1 && !c->force_phased && launch_pcg_stream(d, c->stream)) {
+        c->pcg_streamed = true;
+        if (d.dbg) {
+            long long t[8]; int its = 0;
+            CU(cudaMemcpyAsync(t, d.dbg, sizeof(t), cudaMemcpyDeviceToHost, c->stream));
+            CU(cudaMemcpyAsync(&its, d.flags + F_ITERS, 4, cudaMemcpyDeviceToHost, c->stream));
+            CU(cudaStreamSynchronize(c->stream));
+            const char* nm[8] = {"pass_a", "sync", "mid", "sync", "pass_b", "sync", "update", "sync+coarse"};
+            std::fprintf(stderr, "[tsb] streamed PCG, %d iterations, SM cycles per iteration (block 0):", its);
+            for (int q = 0; q < 8; ++q) std::fprintf(stderr, " %s=%lld", nm[q], its ? t[q] / its : 0);
+            std::fprintf(stderr, "\n");
+        }
+        launch_pcg_pass_a(d, 1, c->stream);
+        launch_pcg_mid(d, 1, c->stream);
+        launch_backsub(d, c->stream);
+        cudaEventRecord(c->ev[5], c->stream);
+        return TSB_OK;
+    }
+    c->pcg_streamed = false;
     // single GPU: the whole PCG and the back-substitution run in one persistent cooperative kernel
     if (c->world <= 1 && !c->force_phased && launch_pcg_persistent(d, c->stream)) {
         if (d.dbg) {
@@ -496,7 +517,7 @@ int tsb_get_counts(const tsb_ctx* c, tsb_counts* o) {
     o->dim = 3 * c->g.P + 2 * c->g.L; o->pose_begin = c->st.pose_begin; o->pose_end = c->st.pose_end;
     o->n_lmedge_local = c->d.nE; o->n_odom_local = c->d.nOwned;
     o->n_chunks = c->d.nChunks; o->n_blocks = c->d.nBlocks; o->n_slots = c->d.nSlots;
-    o->pcg_path = c->d.res_nb ? 1u : (c->world <= 1 && !c->force_phased ? 0u : 2u);
+    o->pcg_path = c->d.res_nb ? 1u : c->pcg_streamed ? 3u : (c->world <= 1 && !c->force_phased ? 0u : 2u);
     o->replicated = (c->cfg.world > 1 && c->world == 1) ? 1u : 0u; o->n_aggregates = c->d.nA;
     return TSB_OK;
 }

@@ -99,6 +99,7 @@ void launch_lm_finalize(const Dev& d, cudaStream_t s);          // K2b: Hll, b_l
 void launch_schur_prep(const Dev& d, cudaStream_t s);           // K3: diag(S)^-1 and reduced rhs
 void launch_coarse_assemble(const Dev& d, cudaStream_t s);      // zoff, C, Ac = Z^T S Z (dense, deterministic)
 void launch_coarse_identity(const Dev& d, cudaStream_t s);      // Ai = I (right-hand side of the inverse solve)
+bool launch_pcg_stream(const Dev& d, cudaStream_t s);           // streamed persistent PCG (no back-substitution)
 bool launch_coarse_invert(const Dev& d, cudaStream_t s);        // Ai = Ac^-1 + F_COARSE, one cooperative launch (blocked Gauss-Jordan)
 void launch_coarse_finish(const Dev& d, cudaStream_t s);        // set F_COARSE from cinfo
 void launch_pcg_coarse(const Dev& d, int init, cudaStream_t s);           // yc = Ac^-1 Z^T r, cdot (phased path)

@@ -903,6 +903,7 @@ __global__ void __launch_bounds__(kThreads, 3) k_pcg_persistent(const Dev d) {
 
 #include "pcg_resident.cuh"
 #include "coarse_invert.cuh"
+#include "pcg_stream.cuh"
 
 // delta_l = Hll^-1 (b_l - Hpl^T delta_p); w_sum holds Hpl^T delta_p
 __global__ void k_backsub(const Dev d) {
@@ -1037,6 +1038,30 @@ bool launch_pcg_persistent(const Dev& d, cudaStream_t s) {
     Dev dd = d; void* args[] = {&dd};
     const cudaError_t e = cudaLaunchCooperativeKernel((void*)k_pcg_persistent, dim3(grid), dim3(kThreads), args, LayPcg::bytes, s);
     if (e != cudaSuccess) { cudaGetLastError(); return false; }
+    ++g_launches;
+    return true;
+}
+// HBM-sized graphs on one GPU: the streamed variant of the persistent kernel (>= 4 units per resident block);
+// leaves the landmark back-substitution to the caller (launch_pcg_pass_a<1>, launch_pcg_mid, launch_backsub)
+bool launch_pcg_stream(const Dev& d, cudaStream_t s) {
+    static int blocks = -1;
+    if (blocks < 0) {
+        int dev = 0, sms = 0, per_sm = 0, coop = 0;
+        cudaGetDevice(&dev);
+        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+        cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, dev);
+        if (cudaFuncSetAttribute(k_pcg_stream, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kPsSmemBytes) != cudaSuccess) cudaGetLastError();
+        else cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_pcg_stream, kPsThreads, kPsSmemBytes);
+        blocks = coop ? sms * per_sm : 0;
+    }
+    uint32_t min_units = 4u * (uint32_t)blocks;
+    { const char* e = getenv("TSB_STREAM_MIN_UNITS"); if (e) min_units = (uint32_t)atoi(e);
+      e = getenv("TSB_NO_STREAM"); if (e && e[0] == '1') return false; }
+    if (blocks <= 0 || !d.gbar || !d.nBlocks || d.nBlocks < min_units) return false;
+    Dev dd = d; void* args[] = {&dd};
+    cudaMemsetAsync(dd.gbar, 0, sizeof(uint32_t), s);
+    const uint32_t grid = d.nBlocks < (uint32_t)blocks ? d.nBlocks : (uint32_t)blocks;
+    if (cudaLaunchCooperativeKernel((void*)k_pcg_stream, dim3(grid), dim3(kPsThreads), args, kPsSmemBytes, s) != cudaSuccess) { cudaGetLastError(); return false; }
     ++g_launches;
     return true;
 }

@@ -53,7 +53,7 @@ __device__ __forceinline__ void bulk_g2s(uint32_t dst, const void* src, uint32_t
 
 // Producer (one thread): arm the stage's barrier and start the bulk copies of chunk `ch`.
 // Sources are aligned down / sizes rounded up to 16 B (every device array carries 64 B of slack).
-__device__ __forceinline__ void ls_issue(const Dev& d, const ChunkDesc& ch, unsigned char* stage, uint32_t bar) {
+__device__ __forceinline__ void ls_issue(const Dev& d, const ChunkDesc& ch, unsigned char* stage, uint32_t bar, bool with_pose = true) {
     const uint32_t n = ch.e1 - ch.e0, ns = ch.s1 - ch.s0, np = ch.p1 - ch.p0;
     const uint32_t e4 = ch.e0 & ~3u, e8 = ch.e0 & ~7u, s4 = ch.s0 & ~3u, p4 = ch.p0 & ~3u;
     const uint32_t bPk = n ? (((ch.e1 - e4) + 3u) & ~3u) * 4u : 0u;
@@ -61,7 +61,7 @@ __device__ __forceinline__ void ls_issue(const Dev& d, const ChunkDesc& ch, unsi
     const uint32_t bSl = ns ? (((ch.s1 - s4) + 3u) & ~3u) * 4u : 0u;
     const uint32_t bSp = (((ch.s1 + 1 - s4) + 3u) & ~3u) * 4u;
     const uint32_t bPp = (((ch.p1 + 1 - p4) + 3u) & ~3u) * 4u;
-    const uint32_t bPose = np * 32u;
+    const uint32_t bPose = with_pose ? np * 32u : 0u;
     const uint32_t s = smem_u32(stage);
     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");      // the stage was last read through the generic proxy
     mbar_expect_tx(bar, bPk + bSe + bSl + bSp + bPp + bPose);
@@ -69,7 +69,7 @@ __device__ __forceinline__ void ls_issue(const Dev& d, const ChunkDesc& ch, unsi
     if (ns) bulk_g2s(s + kLsSl, d.slot_lm + s4, bSl, bar);
     bulk_g2s(s + kLsSp, d.slot_ptr + s4, bSp, bar);
     bulk_g2s(s + kLsPp, d.pose_ptr + p4, bPp, bar);
-    if (np) bulk_g2s(s + kLsPose, d.pose + ch.p0, bPose, bar);
+    if (bPose) bulk_g2s(s + kLsPose, d.pose + ch.p0, bPose, bar);
 }
 
 constexpr int kLsThreads = 512;         // one LM edge per thread; 2 blocks (32 warps) per SM at <= 64 registers
