@@ -143,6 +143,57 @@ def test_synthetic_matches_sparse_oracle(gpu, cfg, scale):
     assert state_diff(*g.state(), *o.state()) < STATE_TOL
 
 
+@pytest.mark.parametrize("path", ["default", "no_resident", "streamed"])
+def test_pose_with_more_edges_than_a_chunk(gpu, monkeypatch, path):
+    """A pose that observes more landmarks than a chunk holds (> 512 LM edges) is split over several chunks: its
+    row sums are carried from chunk to chunk in every kernel (unit, streamed, resident).  24 poses x 650 edges."""
+    from oracle.oracle import OracleGraph
+    from toyslam_b200 import synth
+    payload = synth.to_payload(synth.make_graph(24, 800, 650, "manhattan", seed=3))
+    for k in ("TSB_NO_RESIDENT", "TSB_STREAM_MIN_UNITS", "TSB_NO_STREAM"):
+        monkeypatch.delenv(k, raising=False)
+    if path != "default":
+        monkeypatch.setenv("TSB_NO_RESIDENT", "1")
+    if path == "streamed":
+        monkeypatch.setenv("TSB_STREAM_MIN_UNITS", "1")
+    o = OracleGraph(payload)
+    traj, its, code = o.optimize_sparse(5, False, tol=1e-14, max_pcg=20000, threads=0)
+    g = gpu(iterations=5, pcg_tol=1e-14, pcg_max_iters=20000, enable_exits=False); c = g.load_wire(payload)
+    assert c.n_chunks > c.n_blocks >= 24                 # every pose is a unit of two chunks
+    rep, per = g.optimize()
+    got = np.array([p.chi2 for p in per])
+    assert np.max(np.abs(got - traj) / np.abs(traj)) < CHI2_TOL
+    assert state_diff(*g.state(), *o.state()) < STATE_TOL
+    if path == "streamed":
+        assert g.refresh_counts().pcg_path == 3
+
+
+@pytest.mark.parametrize("kind", ["empty", "one_fixed_pose", "odom_only_streamed"])
+def test_degenerate_graphs(gpu, monkeypatch, kind):
+    """Empty request, a single fixed pose without edges, and an ODOM-only chain through the streamed kernels: no
+    crash, state and reply as the oracle's."""
+    from oracle.oracle import OracleGraph
+    from toyslam_b200 import synth, wire
+    for k in ("TSB_NO_RESIDENT", "TSB_STREAM_MIN_UNITS", "TSB_NO_STREAM"):
+        monkeypatch.delenv(k, raising=False)
+    z = lambda *shape, dt=np.float32: np.zeros(shape, dt)
+    if kind == "empty":
+        payload = wire.encode_request(z(0, dt=np.uint32), z(0, 3), z(0, dt=np.uint32), z(0, 2), z(0, 2, dt=np.uint32), z(0, 9), z(0, 3),
+                                      z(0, 2, dt=np.uint32), z(0, 2), z(0, 2), z(0, dt=np.uint32))
+    elif kind == "one_fixed_pose":
+        payload = wire.encode_request(np.array([7], np.uint32), np.array([[1.0, 2.0, 0.5]], np.float32), z(0, dt=np.uint32), z(0, 2),
+                                      z(0, 2, dt=np.uint32), z(0, 9), z(0, 3), z(0, 2, dt=np.uint32), z(0, 2), z(0, 2), np.array([7], np.uint32))
+    else:
+        payload = load_golden("g_odom_only")["request"].tobytes()
+        monkeypatch.setenv("TSB_NO_RESIDENT", "1"); monkeypatch.setenv("TSB_STREAM_MIN_UNITS", "1")
+    o = OracleGraph(payload); o.optimize_dense(3, True)
+    g = gpu(iterations=3, pcg_tol=1e-14); g.load_wire(payload); g.optimize()
+    a, b = wire.decode_reply(g.reply()), wire.decode_reply(o.reply())
+    assert set(a["vertices"]) == set(b["vertices"]) and a["fixed"] == b["fixed"] and len(a["edges"]) == len(b["edges"])
+    for vid, (t, v) in a["vertices"].items():
+        assert t == b["vertices"][vid][0] and np.allclose(v, b["vertices"][vid][1], rtol=0, atol=2e-6)
+
+
 def test_reply_matches_oracle_reply(gpu):
     from oracle.oracle import OracleGraph
     from toyslam_b200 import wire
