@@ -350,14 +350,18 @@ def test_phased_pcg_path_matches_persistent(gpu, monkeypatch):
     from toyslam_b200 import synth
     payload = synth.to_payload(synth.make_config("c2", scale=0.1, seed=2))
     res = []
-    for phased in ("0", "1"):
+    for phased, stream in (("0", None), ("1", None), ("1", "1")):      # the last: phased with the streamed edge-pass kernels
         monkeypatch.setenv("TSB_PCG_PHASED", phased)
+        monkeypatch.delenv("TSB_STREAM_MIN_UNITS", raising=False)
+        if stream:
+            monkeypatch.setenv("TSB_STREAM_MIN_UNITS", stream)
         g = gpu(iterations=5, pcg_tol=1e-14, pcg_max_iters=20000, enable_exits=False); g.load_wire(payload)
         rep, per = g.optimize()
         res.append((np.array([p.chi2 for p in per]), g.state(), rep.kernel_launches))
     assert res[0][2] < res[1][2]
-    assert np.max(np.abs(res[0][0] - res[1][0]) / res[0][0]) < CHI2_TOL
-    assert state_diff(*res[0][1], *res[1][1]) < STATE_TOL
+    for other in res[1:]:
+        assert np.max(np.abs(res[0][0] - other[0]) / res[0][0]) < CHI2_TOL
+        assert state_diff(*res[0][1], *other[1]) < STATE_TOL
 
 
 def test_two_ranks_match_one_rank(gpu):

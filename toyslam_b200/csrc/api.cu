@@ -347,8 +347,8 @@ int run_solve(tsb_ctx* c, bool refresh_coarse = true) {
             TRY(allreduce(c, d.w_sum, nx));
             launch_unpack_ghost(d, d.p, c->stream);
             launch_pcg_hpp(d, c->stream);                      // sp = Hpp p + ODOM part (needs the ghost p)
-            launch_pcg_pass_b(d, c->stream);
-            launch_pcg_psp(d, c->stream);
+            const uint32_t nparts = launch_pcg_pass_b(d, c->stream);
+            launch_pcg_psp(d, nparts, c->stream);
             TRY(allreduce(c, d.scal + S_PSP, 1));
             launch_pcg_alpha(d, c->stream);
             launch_pcg_update(d, c->stream);

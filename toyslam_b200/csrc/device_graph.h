@@ -109,11 +109,11 @@ int resident_blocks_available();                              // SM count if the
 void launch_pcg_init(const Dev& d, cudaStream_t s);
 void launch_pcg_pass_a(const Dev& d, int mode, cudaStream_t s); // mode 0: v = p (with p = z + beta p fused), 1: v = x
 void launch_pcg_mid(const Dev& d, int mode, cudaStream_t s);   // w = sum of slot partials; mode 0 also sp = Hpp p + ODOM part
-void launch_pcg_pass_b(const Dev& d, cudaStream_t s);
+uint32_t launch_pcg_pass_b(const Dev& d, cudaStream_t s);      // returns the number of p'Sp partials left in d.part
 void launch_pcg_hpp(const Dev& d, cudaStream_t s);              // sp = Hpp p + ODOM part (pose-parallel)
 void launch_pack_boundary(const Dev& d, const double* vec, cudaStream_t s);   // own boundary entries of vec -> d.bnd, zeros elsewhere
 void launch_unpack_ghost(const Dev& d, double* vec, cudaStream_t s);          // d.bnd -> ghost entries of vec
-void launch_pcg_psp(const Dev& d, cudaStream_t s);              // local p'Sp -> scal[S_PSP]
+void launch_pcg_psp(const Dev& d, uint32_t nparts, cudaStream_t s);              // local p'Sp -> scal[S_PSP]
 void launch_pcg_alpha(const Dev& d, cudaStream_t s);
 void launch_pcg_update(const Dev& d, cudaStream_t s);
 void launch_pcg_rznew(const Dev& d, cudaStream_t s);            // local r'z -> scal[S_RZNEW]

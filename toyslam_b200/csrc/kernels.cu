@@ -763,10 +763,10 @@ __global__ void __launch_bounds__(kThreads) k_pcg_pass_b(const Dev d) {
     const double t = unit_pass_b(d, blockIdx.x, sm);
     if (threadIdx.x == 0) d.part[blockIdx.x] = t;
 }
-__global__ void k_pcg_psp(const Dev d) {          // local part of p'Sp (all-reduced over ranks before k_pcg_alpha)
+__global__ void k_pcg_psp(const Dev d, uint32_t nparts) {   // local part of p'Sp (all-reduced over ranks before k_pcg_alpha)
     if (d.flags[F_DONE]) return;
     __shared__ double red[32];
-    const double psp = reduce_all(d.part, d.nBlocks, red);
+    const double psp = reduce_all(d.part, nparts, red);
     if (threadIdx.x == 0) d.scal[S_PSP] = psp;
 }
 __global__ void k_pcg_alpha(const Dev d) {
@@ -1125,6 +1125,23 @@ void launch_pcg_init(const Dev& d, cudaStream_t s) {
     launch_pcg_coarse(d, 1, s);
     k_pcg_init_scal<<<1, 1024, 0, s>>>(d, nb); ++g_launches;
 }
+// grid of the stand-alone streamed pass B (2 blocks per SM) when this graph is large enough for it, else 0
+static uint32_t ps_phase_grid(const Dev& d) {
+    static int blocks = -1;
+    if (blocks < 0) {
+        int dev = 0, sms = 0, pb = 0;
+        cudaGetDevice(&dev);
+        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+        if (cudaFuncSetAttribute(k_ps_pass_b, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kPsSmemBytes) != cudaSuccess) cudaGetLastError();
+        else cudaOccupancyMaxActiveBlocksPerMultiprocessor(&pb, k_ps_pass_b, kPsThreads, kPsSmemBytes);
+        blocks = sms * pb;
+    }
+    uint32_t min_units = 4u * (uint32_t)(blocks > 0 ? blocks : 0);
+    { const char* e = getenv("TSB_STREAM_MIN_UNITS"); if (e) min_units = (uint32_t)atoi(e);
+      e = getenv("TSB_NO_STREAM"); if (e && e[0] == '1') return 0; }
+    if (blocks <= 0 || !d.nBlocks || d.nBlocks < min_units) return 0;
+    return d.nBlocks < (uint32_t)blocks ? d.nBlocks : (uint32_t)blocks;
+}
 void launch_pcg_pass_a(const Dev& d, int mode, cudaStream_t s) {
     set_attrs();
     if (!d.nBlocks) return;
@@ -1138,9 +1155,17 @@ void launch_pcg_mid(const Dev& d, int mode, cudaStream_t s) {
     if (nb > 148 * 8) nb = 148 * 8;
     if (nb) { k_pcg_mid<<<nb, kThreads, 0, s>>>(d, mode); ++g_launches; }
 }
-void launch_pcg_pass_b(const Dev& d, cudaStream_t s) {
+// returns the number of p'Sp partials it leaves in d.part (for launch_pcg_psp)
+uint32_t launch_pcg_pass_b(const Dev& d, cudaStream_t s) {
     set_attrs();
-    if (d.nBlocks) { k_pcg_pass_b<<<d.nBlocks, kThreads, LayB::bytes, s>>>(d); ++g_launches; }
+    if (!d.nBlocks) return 0;
+    if (const uint32_t g = ps_phase_grid(d)) {
+        if (d.L) { k_ps_w_to_u<<<cdiv(d.L, kThreads), kThreads, 0, s>>>(d); ++g_launches; }
+        k_ps_pass_b<<<g, kPsThreads, kPsSmemBytes, s>>>(d); ++g_launches;
+        return g;
+    }
+    k_pcg_pass_b<<<d.nBlocks, kThreads, LayB::bytes, s>>>(d); ++g_launches;
+    return d.nBlocks;
 }
 void launch_pcg_hpp(const Dev& d, cudaStream_t s) {
     if (d.nP) { k_pcg_hpp<<<cdiv(d.nP, kThreads), kThreads, 0, s>>>(d); ++g_launches; }
@@ -1151,7 +1176,7 @@ void launch_pack_boundary(const Dev& d, const double* vec, cudaStream_t s) {
 void launch_unpack_ghost(const Dev& d, double* vec, cudaStream_t s) {
     if (d.nG) { k_unpack_ghost<<<cdiv(d.nG, kThreads), kThreads, 0, s>>>(d, vec); ++g_launches; }
 }
-void launch_pcg_psp(const Dev& d, cudaStream_t s) { k_pcg_psp<<<1, 1024, 0, s>>>(d); ++g_launches; }
+void launch_pcg_psp(const Dev& d, uint32_t nparts, cudaStream_t s) { k_pcg_psp<<<1, 1024, 0, s>>>(d, nparts); ++g_launches; }
 void launch_pcg_alpha(const Dev& d, cudaStream_t s) { k_pcg_alpha<<<1, 1, 0, s>>>(d); ++g_launches; }
 void launch_pcg_update(const Dev& d, cudaStream_t s) {
     const uint32_t nb = cdiv(d.nP, kThreads);

@@ -43,10 +43,8 @@ __device__ __forceinline__ void ps_issue(const Dev& d, const ChunkDesc& ch, unsi
     const double2* hp = hpl_row(d, ch.e0); const size_t hs = hpl_stride(d);
     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
     mbar_expect_tx(bar, bPk + bSe + bPp + bSp + bSl + 3 * bH);
-    if (n) {
-        bulk_g2s(s + kPsPk, d.lm_packed + e4, bPk, bar);
-        bulk_g2s(s + kPsH, hp, bH, bar); bulk_g2s(s + kPsH + 16 * kChunkEdges, hp + hs, bH, bar); bulk_g2s(s + kPsH + 32 * kChunkEdges, hp + 2 * hs, bH, bar);
-    }
+    if (bPk) bulk_g2s(s + kPsPk, d.lm_packed + e4, bPk, bar);
+    if (bH) { bulk_g2s(s + kPsH, hp, bH, bar); bulk_g2s(s + kPsH + 16 * kChunkEdges, hp + hs, bH, bar); bulk_g2s(s + kPsH + 32 * kChunkEdges, hp + 2 * hs, bH, bar); }
     if (bSe) bulk_g2s(s + kPsIx1, d.slot_edge + e8, bSe, bar);
     if (bPp) bulk_g2s(s + kPsIx1, d.pose_ptr + p4, bPp, bar);
     if (bSp) bulk_g2s(s + kPsIx2, d.slot_ptr + s4, bSp, bar);
@@ -269,4 +267,35 @@ __global__ void __launch_bounds__(kPsThreads, 2) k_pcg_stream(const Dev d) {
         if (timing) for (int q = 0; q < 8; ++q) d.dbg[q] = tacc[q];
     }
 #undef TICK
+}
+
+// ---- pass B as a stand-alone kernel: the sharded (world > 1) path runs one launch per phase with NCCL all-reduces in
+// between.  (Pass A as a stand-alone kernel faulted in the TMA refill of the Hpl planes on the B200 -- the same inlined
+// code runs inside k_pcg_stream -- and is left on the block-synchronous kernel until that is understood.) ------------
+__device__ __forceinline__ void ps_block_range(const Dev& d, unsigned char* smem, uint32_t& cb, uint32_t& ce) {
+    const uint32_t nb = gridDim.x;
+    const uint32_t u_lo = (uint32_t)((uint64_t)d.nBlocks * blockIdx.x / nb), u_hi = (uint32_t)((uint64_t)d.nBlocks * (blockIdx.x + 1) / nb);
+    cb = d.blk_chunk_ptr[u_lo]; ce = d.blk_chunk_ptr[u_hi];
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < kLsStages; ++s) mbar_init(smem_u32(smem + kPsBar) + 8 * s, 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncthreads();
+}
+// w_sum holds w = Hpl^T p summed over slots and ranks: u = Hll^-1 w in place, as ps_pass_b gathers it
+__global__ void __launch_bounds__(kThreads) k_ps_w_to_u(const Dev d) {
+    if (d.flags[F_DONE]) return;
+    const uint32_t l = blockIdx.x * blockDim.x + threadIdx.x;
+    if (l >= d.L) return;
+    double2* ws = reinterpret_cast<double2*>(d.w_sum);
+    const double2 w = ws[l]; const double* hi = d.hinv + 3ull * l;
+    ws[l] = make_double2(hi[0] * w.x + hi[1] * w.y, hi[1] * w.x + hi[2] * w.y);
+}
+__global__ void __launch_bounds__(kPsThreads, 2) k_ps_pass_b(const Dev d) {
+    if (d.flags[F_DONE]) return;
+    extern __shared__ __align__(32) unsigned char smem_raw[];
+    uint32_t cb, ce, kbase = 0;
+    ps_block_range(d, smem_raw, cb, ce);
+    const double t = block_sum(ps_pass_b(d, smem_raw, cb, ce, kbase), reinterpret_cast<double*>(smem_raw + kPsRed));
+    if (threadIdx.x == 0) d.part[blockIdx.x] = t;
 }
