@@ -159,12 +159,18 @@ int upload_graph(tsb_ctx* c) {
     if (d.res_nb) {
         TRY(upload(c, d.res_pose_cut, c->rp.pose_cut)); TRY(upload(c, d.res_lm_cut, c->rp.lm_cut)); TRY(upload(c, d.res_agg_cut, c->rp.agg_cut));
         TRY(upload(c, d.lmo_ptr, c->rp.lmo_ptr)); TRY(upload(c, d.lmo_edge, c->rp.lmo_edge)); TRY(upload(c, d.edge_lm, c->rp.edge_lm));
+        // TSB_SMOOTHER=1: dense smoother blocks (sblock_smoother.cuh) instead of the 3x3 pose blocks as the fine level of the
+        // resident kernel's preconditioner.  Off by default: 2.4x fewer PCG iterations on the first solves of C2 but 1.6x the
+        // time per iteration (the inverses stream from L2), a net loss over a 50-iteration request
+        { const char* e = std::getenv("TSB_SMOOTHER");
+          if (e && e[0] == '1') TRY(dalloc(c, d.sbinv, (size_t)d.res_nb * kSbPerBlock * (3 * kSbCap) * (3 * kSbCap))); }
     }
     TRY(upload(c, d.edge_pose, s.edge_pose)); TRY(upload(c, d.aslot_lm, s.aslot_lm)); TRY(upload(c, d.aslot_agg, s.aslot_agg));
     TRY(upload(c, d.aslot_ptr, s.aslot_ptr)); TRY(upload(c, d.aslot_edge, s.aslot_edge));
     TRY(upload(c, d.cpair_a, s.cpair_a)); TRY(upload(c, d.cpair_b, s.cpair_b)); TRY(upload(c, d.cpair_ptr, s.cpair_ptr));
     TRY(upload(c, d.ctrip, s.ctrip));
     TRY(dalloc(c, d.zoff, d.nP)); TRY(dalloc(c, d.cC, 6ull * d.nAS)); TRY(dalloc(c, d.Ac, (size_t)d.nc * d.nc)); TRY(dalloc(c, d.Ai, (size_t)d.nc * d.nc));
+    if (d.nc > 3 * kCoarseMaxAgg) TRY(dalloc(c, d.rcs, (size_t)kCoarseScratchBlocks * d.nc));
     TRY(dalloc(c, d.rcp, 3ull * d.nSeg)); TRY(dalloc(c, d.yc, d.nc)); TRY(dalloc(c, d.cdot, d.nc)); TRY(dalloc(c, d.cinfo, (size_t)2)); TRY(dalloc(c, d.cbar, (size_t)1));
     CU(cudaMemsetAsync(d.cinfo, 0, 8, c->stream));
     if (c->use_coarse && d.nc) {
@@ -246,6 +252,7 @@ int enqueue_linearize(tsb_ctx* c) {
 int run_solve(tsb_ctx* c, bool refresh_coarse = true) {
     const Dev& d = c->d;
     launch_schur_prep(d, c->stream);
+    if (d.res_nb && d.sbinv && !launch_sb_build(d, c->stream)) { c->err = "smoother-block kernel could not be launched"; return TSB_ECUDA; }
     if (c->use_coarse && d.nc && (refresh_coarse || c->coarse_age < 0)) {
         c->coarse_age = 0; ++c->coarse_refreshes;
         // coarse operator Ac = Z^T S Z of this rank's poses, inverted explicitly so that the PCG applies it as a
@@ -256,7 +263,8 @@ int run_solve(tsb_ctx* c, bool refresh_coarse = true) {
         launch_coarse_assemble(d, c->stream);
         if (timing) cudaEventRecord(te[1], c->stream);
         const char* ecs = std::getenv("TSB_COARSE_CUSOLVER");          // 1: cuSOLVER potrf + potrs(I) instead of k_coarse_invert
-        const bool use_cusolver = ecs && ecs[0] == '1';
+        // k_coarse_invert wins at C2 size (0.55 vs 1.32 ms at nc = 888) but scales worse: 26.8 vs 14.4 ms at nc = 4689
+        const bool use_cusolver = (ecs && ecs[0] == '1') || (d.nc > 2304 && !(ecs && ecs[0] == '0'));
         if (!use_cusolver && launch_coarse_invert(d, c->stream)) {
             if (timing) {
                 cudaEventRecord(te[2], c->stream); cudaEventSynchronize(te[2]);

@@ -10,6 +10,7 @@ constexpr int kThreads = 256;          // threads per block of the chunked kerne
 #ifndef TSB_HPL_PLANES
 #define TSB_HPL_PLANES 1              // Hpl as three planes of nE double2 (1) or 3x2 per edge (0)
 #endif
+constexpr uint32_t kCoarseScratchBlocks = 3 * kCoarseMaxAggLarge / (kThreads / 32);   // blocks that can own coarse rows (one row per warp at least)
 constexpr int kStageRows = 9;          // values staged per LM edge
 constexpr int kStageStride = kChunkEdges + 1;   // odd stride in doubles: rows land in different banks
 
@@ -80,11 +81,13 @@ struct Dev {
     uint32_t res_nb;
     const uint32_t* res_pose_cut; const uint32_t* res_lm_cut; const uint32_t* res_agg_cut;
     const uint32_t* lmo_ptr; const uint32_t* lmo_edge; const uint32_t* edge_lm;
+    double* sbinv;              // res_nb x kSbPerBlock dense symmetric inverses (kSbLD^2 each) of the smoother blocks; null: 3x3 pose blocks (minv)
     double2* zoff;              // per pose: (-(y - cy), x - cx) about its aggregate's centroid -> third column of Z_i
     double* cC;                 // 6 per aslot: sum of Hpl_e^T Z_i (2x3 row-major)
     double* Ac;                 // nc x nc: Z^T S Z, overwritten by its Cholesky factor
     double* Ai;                 // nc x nc: (Z^T S Z)^-1, applied as a dense mat-vec by the PCG
     double* rcp;                // 3 per segment: Z^T r summed over the segment's 32 poses
+    double* rcs;                // nc > 3 kCoarseMaxAgg only: kCoarseScratchBlocks x nc, block b's copy of Z^T r in coarse_phase
     double* yc;                 // nc: coarse correction Ac^-1 (Z^T r)
     double* cdot;               // nc: (Z^T r)_j * yc_j  (the coarse part of r'z)
     uint32_t* cbar;             // grid-barrier counter of k_coarse_invert
@@ -104,6 +107,7 @@ bool launch_coarse_invert(const Dev& d, cudaStream_t s);        // Ai = Ac^-1 + 
 void launch_coarse_finish(const Dev& d, cudaStream_t s);        // set F_COARSE from cinfo
 void launch_pcg_coarse(const Dev& d, int init, cudaStream_t s);           // yc = Ac^-1 Z^T r, cdot (phased path)
 bool launch_pcg_persistent(const Dev& d, cudaStream_t s);     // whole PCG + back-substitution, one cooperative launch
+bool launch_sb_build(const Dev& d, cudaStream_t s);           // smoother-block inverses of the resident kernel (needs minv, hinv: after launch_schur_prep)
 bool launch_pcg_resident(const Dev& d, cudaStream_t s);       // same, Hpl resident in shared memory (needs d.res_nb > 0)
 int resident_blocks_available();                              // SM count if the resident kernel can be co-scheduled, else 0
 void launch_pcg_init(const Dev& d, cudaStream_t s);

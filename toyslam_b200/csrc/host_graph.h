@@ -96,7 +96,11 @@ constexpr uint32_t kResPoseCap = 96;      // poses per block
 constexpr uint32_t kResLmCap = 64;        // landmarks per block
 constexpr uint32_t kResAggCap = 4;        // aggregates per block
 constexpr uint32_t kResOdomCap = 384;     // ODOM neighbour entries per block
-constexpr uint32_t kCoarseMaxAgg = 512;   // upper bound on aggregates per rank (coarse matrix is dense: (3*512)^2 doubles)
+constexpr uint32_t kSbCap = 48;           // poses per smoother block of the resident kernel (dense 144 x 144 inverse)
+constexpr uint32_t kSbPerBlock = 2;       // smoother blocks per resident block
+constexpr uint32_t kCoarseMaxAgg = 512;   // aggregates whose coarse residual (3 doubles each) fits the shared memory the PCG kernels set aside for it
+constexpr uint32_t kCoarseMaxAggLarge = 2048;   // upper bound on aggregates per rank (the coarse matrix is dense: (3*2048)^2 doubles = 302 MB);
+                                                // above kCoarseMaxAgg the coarse residual lives in per-block global scratch (Dev::rcs)
 
 constexpr uint32_t kChunkEdges = 512;   // LM edges staged per chunk
 constexpr uint32_t kBlockPoses = 128;   // poses per thread block (upper bound)

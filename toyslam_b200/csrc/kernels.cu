@@ -585,18 +585,59 @@ __device__ __forceinline__ double pose_step(const Dev& d, uint32_t i, bool valid
 }
 
 // Coarse level: yc = Ac^-1 (Z^T r) with Z^T r summed from the segment partials, and cdot_j = (Z^T r)_j yc_j.
-// Rows are dealt to warps (`gwarp` of `nwarps`); rc_s is block shared memory for nc doubles.
-__device__ __forceinline__ void coarse_phase(const Dev& d, uint32_t gwarp, uint32_t nwarps, double* rc_s) {
-    const uint32_t spa = d.aggK >> 5, nc = d.nc;
-    for (uint32_t k = threadIdx.x; k < nc; k += blockDim.x) {
-        const uint32_t a = k / 3, q = k % 3, s0 = a * spa, s1 = min(d.nSeg, s0 + spa);
-        double t = 0;
+// Rows are dealt to warps (`gwarp` of `nwarps`); rc_smem is block shared memory for 3 kCoarseMaxAgg doubles; larger
+// coarse spaces (HBM-sized graphs: up to kCoarseMaxAggLarge aggregates) keep the block's copy of Z^T r in its own
+// slice of d.rcs (global, L1/L2-resident: written and read by this block only).
+// (Z^T r)_k for coarse unknown k: the segment partials of its aggregate added in segment order
+__device__ __forceinline__ double coarse_restrict(const Dev& d, uint32_t k) {
+    const uint32_t spa = d.aggK >> 5, a = k / 3, q = k % 3, s0 = a * spa, s1 = min(d.nSeg, s0 + spa);
+    double t = 0;
 #pragma unroll 8
-        for (uint32_t sg = s0; sg < s1; ++sg) t += d.rcp[3ull * sg + q];
-        rc_s[k] = t;
+    for (uint32_t sg = s0; sg < s1; ++sg) t += d.rcp[3ull * sg + q];
+    return t;
+}
+// `shared_rc`: Z^T r was left in d.rcs[0 .. nc) by a preceding launch (k_pcg_restrict, phased path, large coarse spaces)
+__device__ __forceinline__ void coarse_phase(const Dev& d, uint32_t gwarp, uint32_t nwarps, double* rc_smem, bool shared_rc = false) {
+    const uint32_t nc = d.nc;
+    double* rc_s = nc <= 3 * kCoarseMaxAgg ? rc_smem : shared_rc ? d.rcs : d.rcs + (size_t)blockIdx.x * nc;
+    if (!(shared_rc && nc > 3 * kCoarseMaxAgg)) {
+        for (uint32_t k = threadIdx.x; k < nc; k += blockDim.x) rc_s[k] = coarse_restrict(d, k);
+        __syncthreads();
     }
-    __syncthreads();
     const uint32_t lane = threadIdx.x & 31;
+    if (nc > 3 * kCoarseMaxAgg) {
+        // Large coarse space (Ai = 100-300 MB, streamed from HBM every iteration): a warp per row leaves one 47 KB row
+        // behind a handful of loads in flight (C4: 190 us for 275 MB).  Here a whole block takes four rows at a time,
+        // every thread with 4 x nc / blockDim independent loads; warp xor tree, then the warps' partials in warp order.
+        const uint32_t wpb = blockDim.x >> 5, warp = threadIdx.x >> 5;
+        const uint32_t nblk = min(nwarps / wpb, (nc + wpb - 1) / wpb), bidx = gwarp / wpb;      // blocks that own coarse rows
+        double* red = rc_smem;                                   // shared memory is free in this mode (rc_s is global)
+        for (uint32_t j0 = 4 * bidx; j0 < nc; j0 += 4 * nblk) {
+            const uint32_t nr = min(4u, nc - j0);
+            const double* r0 = d.Ai + (size_t)j0 * nc;
+            const double* r1 = r0 + (nr > 1 ? nc : 0); const double* r2 = r0 + (nr > 2 ? 2 * (size_t)nc : 0); const double* r3 = r0 + (nr > 3 ? 3 * (size_t)nc : 0);
+            double t0 = 0, t1 = 0, t2 = 0, t3 = 0;
+#pragma unroll 2
+            for (uint32_t k = threadIdx.x; k < nc; k += blockDim.x) {
+                const double c = rc_s[k];
+                t0 += r0[k] * c; t1 += r1[k] * c; t2 += r2[k] * c; t3 += r3[k] * c;
+            }
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) {
+                t0 += __shfl_xor_sync(0xffffffffu, t0, o); t1 += __shfl_xor_sync(0xffffffffu, t1, o);
+                t2 += __shfl_xor_sync(0xffffffffu, t2, o); t3 += __shfl_xor_sync(0xffffffffu, t3, o);
+            }
+            if (lane == 0) { red[4 * warp] = t0; red[4 * warp + 1] = t1; red[4 * warp + 2] = t2; red[4 * warp + 3] = t3; }
+            __syncthreads();
+            if (threadIdx.x < nr) {
+                double t = 0;
+                for (uint32_t w = 0; w < wpb; ++w) t += red[4 * w + threadIdx.x];
+                d.yc[j0 + threadIdx.x] = t; d.cdot[j0 + threadIdx.x] = t * rc_s[j0 + threadIdx.x];
+            }
+            __syncthreads();
+        }
+        return;
+    }
     for (uint32_t j = gwarp; j < nc; j += nwarps) {
         const double* row = d.Ai + (size_t)j * nc;
         double t0 = 0, t1 = 0;
@@ -730,7 +771,13 @@ __global__ void k_pcg_init(const Dev d) {
 __global__ void __launch_bounds__(kThreads) k_pcg_coarse(const Dev d, int init) {
     if (!d.flags[F_COARSE] || (!init && d.flags[F_DONE])) return;
     __shared__ double rc_s[3 * kCoarseMaxAgg];
-    coarse_phase(d, (blockIdx.x * blockDim.x + threadIdx.x) >> 5, (gridDim.x * blockDim.x) >> 5, rc_s);
+    coarse_phase(d, (blockIdx.x * blockDim.x + threadIdx.x) >> 5, (gridDim.x * blockDim.x) >> 5, rc_s, true);
+}
+// large coarse spaces, phased path: Z^T r once into d.rcs instead of once per block of k_pcg_coarse
+__global__ void k_pcg_restrict(const Dev d, int init) {
+    if (!d.flags[F_COARSE] || (!init && d.flags[F_DONE])) return;
+    const uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k < d.nc) d.rcs[k] = coarse_restrict(d, k);
 }
 __global__ void k_pcg_init_scal(const Dev d, uint32_t nparts) {
     __shared__ double red[32];
@@ -901,6 +948,7 @@ __global__ void __launch_bounds__(kThreads, 3) k_pcg_persistent(const Dev d) {
     }
 }
 
+#include "sblock_smoother.cuh"
 #include "pcg_resident.cuh"
 #include "coarse_invert.cuh"
 #include "pcg_stream.cuh"
@@ -1096,7 +1144,13 @@ bool launch_coarse_invert(const Dev& d, cudaStream_t s) {
 void launch_coarse_identity(const Dev& d, cudaStream_t s) { k_coarse_identity<<<148 * 4, kThreads, 0, s>>>(d); ++g_launches; }
 void launch_coarse_finish(const Dev& d, cudaStream_t s) { k_coarse_finish<<<1, 32, 0, s>>>(d); ++g_launches; }
 void launch_pcg_coarse(const Dev& d, int init, cudaStream_t s) {
-    if (d.nc) { k_pcg_coarse<<<cdiv(d.nc, kThreads / 32), kThreads, 0, s>>>(d, init); ++g_launches; }
+    if (!d.nc) return;
+    if (d.nc > 3 * kCoarseMaxAgg) {          // block-per-4-rows mat-vec: one block per SM-slot is enough, the rows stream from HBM
+        k_pcg_restrict<<<cdiv(d.nc, kThreads), kThreads, 0, s>>>(d, init); ++g_launches;
+        k_pcg_coarse<<<min(cdiv(d.nc, kThreads / 32), 148u * 4u), kThreads, 0, s>>>(d, init); ++g_launches;   // grid <= cdiv(nc, warps per block): see nblk in coarse_phase
+        return;
+    }
+    k_pcg_coarse<<<cdiv(d.nc, kThreads / 32), kThreads, 0, s>>>(d, init); ++g_launches;
 }
 static int g_res_blocks = -1;      // SM count if k_pcg_resident can be co-scheduled with one block per SM, else 0
 int resident_blocks_available() {
@@ -1109,6 +1163,14 @@ int resident_blocks_available() {
     else cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_pcg_resident, kResThreads, kResSmemBytes);
     g_res_blocks = (coop && per_sm >= 1) ? sms : 0;
     return g_res_blocks;
+}
+bool launch_sb_build(const Dev& d, cudaStream_t s) {
+    static int ok = -1;
+    if (ok < 0) ok = cudaFuncSetAttribute(k_sb_build, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSbSmemBytes) == cudaSuccess ? 1 : 0;
+    if (!ok) { cudaGetLastError(); return false; }
+    if (!d.res_nb || !d.sbinv) return false;
+    k_sb_build<<<d.res_nb * kSbPerBlock, kSbThreads, kSbSmemBytes, s>>>(d); ++g_launches;
+    return true;
 }
 bool launch_pcg_resident(const Dev& d, cudaStream_t s) {
     if (!d.res_nb || (int)d.res_nb != resident_blocks_available()) return false;

@@ -146,6 +146,43 @@ __device__ __forceinline__ void res_landmarks(const Dev& d, const ResSm& s, cons
     }
 }
 
+// z_j = blockdiag_sb(S)^-1 r for the block's poses (sblock_smoother.cuh): dense symmetric mat-vec per sblock, the
+// matrix streamed from L2 (column-major == row-major, so the threads of a warp -- consecutive rows -- read
+// consecutive words).  Every row is split over G thread groups so that all 1024 threads have loads in flight; the
+// partial sums are added in group order (deterministic).  `part` = G x 3 np doubles of scratch (s.rows).
+__device__ __forceinline__ void res_smooth(const Dev& d, const ResSm& s, uint32_t np) {
+    const uint32_t tid = threadIdx.x, nrows = 3 * np;
+    if (nrows == 0) return;
+    const uint32_t G = min(8u, (uint32_t)kResThreads / nrows);
+    const uint32_t g = tid / nrows, row = tid - g * nrows;
+    double* part = s.rows;
+    if (g < G) {
+        const uint32_t pl = row / 3;
+        uint32_t ls, n; sb_range(np, 0, ls, n);
+        uint32_t q = 0;
+        if (pl >= n) { q = 1; sb_range(np, 1, ls, n); }
+        const uint32_t dim = 3 * n, lr = row - 3 * ls;
+        const uint32_t c0 = dim * g / G, c1 = dim * (g + 1) / G;
+        const double* mat = d.sbinv + ((size_t)blockIdx.x * kSbPerBlock + q) * kSbLD * kSbLD + lr;
+        const double* rv = s.r + 3 * ls;
+        double t0 = 0, t1 = 0, t2 = 0, t3 = 0;
+        uint32_t c = c0;
+        for (; c + 4 <= c1; c += 4) {
+            const double m0 = mat[(size_t)c * kSbLD], m1 = mat[(size_t)(c + 1) * kSbLD], m2 = mat[(size_t)(c + 2) * kSbLD], m3 = mat[(size_t)(c + 3) * kSbLD];
+            t0 += m0 * rv[c]; t1 += m1 * rv[c + 1]; t2 += m2 * rv[c + 2]; t3 += m3 * rv[c + 3];
+        }
+        for (; c < c1; ++c) t0 += mat[(size_t)c * kSbLD] * rv[c];
+        part[g * nrows + row] = (t0 + t1) + (t2 + t3);
+    }
+    __syncthreads();
+    if (tid < nrows) {
+        double z = 0;
+        for (uint32_t k = 0; k < G; ++k) z += part[k * nrows + tid];
+        s.zf[tid] = z;
+    }
+    __syncthreads();
+}
+
 // Grid barrier of the resident kernel (all blocks are co-resident: cooperative launch).  One counter that only
 // grows: block b's thread 0 adds 1 with release semantics and polls with acquire loads until the counter reaches
 // (barriers so far) x (blocks); bar.sync on both sides extends the ordering to the whole block.  About half the
@@ -210,9 +247,10 @@ __global__ void __launch_bounds__(kResThreads, 1) k_pcg_resident(const Dev d) {
             const uint32_t k = d.od_in_edge[q];
             s.onb_idx[n] = d.od_a[k]; s.onb_h[3 * n] = d.hoo[3ull * k]; s.onb_h[3 * n + 1] = d.hoo[3ull * k + 1]; s.onb_h[3 * n + 2] = d.hoo[3ull * k + 2];
         }
-        sym3_mul(s.minv + 6 * tid, s.r[3 * tid], s.r[3 * tid + 1], s.r[3 * tid + 2], s.zf[3 * tid], s.zf[3 * tid + 1], s.zf[3 * tid + 2]);
+        if (!d.sbinv) sym3_mul(s.minv + 6 * tid, s.r[3 * tid], s.r[3 * tid + 1], s.r[3 * tid + 2], s.zf[3 * tid], s.zf[3 * tid + 1], s.zf[3 * tid + 2]);
     }
     __syncthreads();
+    if (d.sbinv) res_smooth(d, s, np);
     // coarse residual Z^T r: this block's aggregates -> global, then every block keeps the whole vector
     if (coarse) res_restrict(s, s.r, s.aptr, na, d.yc + 3 * a0);
     res_gsync(grid, d.gbar, gtarget);
@@ -300,8 +338,11 @@ __global__ void __launch_bounds__(kResThreads, 1) k_pcg_resident(const Dev d) {
         if (coarse) for (uint32_t k = tid; k < nc; k += kResThreads) s.rc[k] -= alpha * d.cdot[k];
         if (tid < 3 * np) { s.x[tid] += alpha * s.p[tid]; s.r[tid] -= alpha * s.y[tid]; }
         __syncthreads();
-        if (tid < np) sym3_mul(s.minv + 6 * tid, s.r[3 * tid], s.r[3 * tid + 1], s.r[3 * tid + 2], s.zf[3 * tid], s.zf[3 * tid + 1], s.zf[3 * tid + 2]);
-        __syncthreads();
+        if (d.sbinv) res_smooth(d, s, np);
+        else {
+            if (tid < np) sym3_mul(s.minv + 6 * tid, s.r[3 * tid], s.r[3 * tid + 1], s.r[3 * tid + 2], s.zf[3 * tid], s.zf[3 * tid + 1], s.zf[3 * tid + 2]);
+            __syncthreads();
+        }
         RTICK(13);
         res_finish(d, s, coarse, p0, np, a0, na);
         ++it;

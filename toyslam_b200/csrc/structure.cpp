@@ -214,7 +214,7 @@ void build_structure(const HostGraph& g, uint32_t rank, uint32_t world, Structur
         }
         if (!resident) {
             uint32_t K = 32;
-            if (nP > 32ull * kCoarseMaxAgg) K = 32 * (uint32_t)((nP + 32ull * kCoarseMaxAgg - 1) / (32ull * kCoarseMaxAgg));
+            if (nP > 32ull * kCoarseMaxAggLarge) K = 32 * (uint32_t)((nP + 32ull * kCoarseMaxAggLarge - 1) / (32ull * kCoarseMaxAggLarge));
             s.agg_K = K; s.nA = (nP + K - 1) / K;
             s.agg_ptr.resize(s.nA + 1);
             for (uint32_t a = 0; a <= s.nA; ++a) s.agg_ptr[a] = std::min<uint64_t>(nP, (uint64_t)a * K);
