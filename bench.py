@@ -270,7 +270,12 @@ def main():
         "roofline": {"kernel": ("k_pcg_resident (whole PCG solve in one cooperative launch, Hpl resident in shared memory)" if resident_kernel else
                                 "k_pcg_persistent (whole PCG solve in one cooperative launch)" if world == 1 else "k_pcg_* phases + NCCL all-reduces"),
                      "bound": "hbm", "achieved": B_pcg / (pcg_ms * 1e-3) / 1e9, "peak": peak, "peak_kind": peak_kind, "unit": "GB/s",
-                     "frac": B_pcg / (pcg_ms * 1e-3) / 1e9 / peak, "traffic": None,
+                     "frac": B_pcg / (pcg_ms * 1e-3) / 1e9 / peak,
+                     # DRAM bytes of one k_pcg_resident launch (= one solve) from the ncu --set full capture summarised in
+                     # profiles/r1_pcg_resident_c2_v2_ncu_summary.csv (17.38 MB read + 0.22 MB written): far below the
+                     # algorithmic bytes because both orders of Hpl stay in shared memory for the whole solve
+                     "traffic": 17.6e6 if (resident_kernel and args.workload == "c2") else None,
+                     "traffic_source": "profiles/r1_pcg_resident_c2_v2_ncu_summary.csv" if (resident_kernel and args.workload == "c2") else None,
                      "algorithmic_bytes_per_launch": B_pcg * pcg_total / GN_ITERS, "algorithmic_bytes_per_pcg_iteration": B_pcg,
                      "launch_ms": ms_pcg / GN_ITERS, "pcg_iterations_per_launch": pcg_total / GN_ITERS,
                      "share_of_step": ms_pcg / dev_ms,
@@ -342,6 +347,9 @@ def main():
             line["roofline_linearize_c4"] = {"workload": wl4, "bound": "hbm",
                                              "achieved": B4 / (ms4 * 1e-3) / 1e9, "peak": peak * world, "unit": "GB/s", "n_gpus": world,
                                              "frac": B4 / (ms4 * 1e-3) / 1e9 / (peak * world), "algorithmic_bytes": B4, "ms": ms4,
+                                             # dram read + write of k_linearize_stream + k_lm_sum + k_odom at N=1, ncu --set full
+                                             # (profiles/r1_lin_c4_planes_ncu_summary.csv): 1 865 + 113 + 128 MB
+                                             "traffic": 2.106e9 if world == 1 else None,
                                              "edges_linearized_per_s": (c4["Eo"] + c4["El"]) / (ms4 * 1e-3)}
             path4 = {0: "k_pcg_persistent", 1: "k_pcg_resident", 2: "k_pcg_* phases + NCCL all-reduces",
                      3: "k_pcg_stream (persistent cooperative kernel, edge passes through a 3-stage TMA ring)"}[opt4.refresh_counts().pcg_path]

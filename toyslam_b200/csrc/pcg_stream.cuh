@@ -189,6 +189,36 @@ __device__ __forceinline__ double ps_pass_b(const Dev& d, unsigned char* smem, u
     return dot;
 }
 
+// Pose-vector step of k_pcg_stream: pose_step over this block's 512-pose windows.  With a large coarse space
+// (nc > 3 kCoarseMaxAgg) whose aggregates nest in a window (aggK / 32 divides 16: C3 K = 64, C4 K = 512) the block also
+// sums the segment partials it has just written into Z^T r of its aggregates (d.rcs[0 .. nc), same segment order as
+// coarse_restrict), so that coarse_phase need not restrict 3 nSeg values once per block (C4: 296 x 750 KB of L2 reads
+// per PCG iteration).  Returns whether d.rcs holds Z^T r.
+template <bool INIT>
+__device__ __forceinline__ bool ps_pose_phase(const Dev& d, double alpha, bool coarse, double& dot) {
+    const uint32_t nP32 = (d.nP + 31u) & ~31u, gsz = gridDim.x * kPsThreads, spa = d.aggK >> 5;
+    const bool agg = coarse && d.nc > 3 * kCoarseMaxAgg && spa >= 1 && spa <= 16 && 16 % spa == 0;
+    dot = 0;
+    for (uint32_t base = blockIdx.x * kPsThreads; base < nP32; base += gsz) {
+        const uint32_t i = base + threadIdx.x;
+        if (i < nP32) dot += pose_step<INIT>(d, i, i < d.nP, alpha, coarse);
+        if (agg) {
+            __syncthreads();                                  // this block's rcp entries of the window are written
+            const uint32_t seg0 = base >> 5, k = threadIdx.x;  // k = (aggregate in window, component)
+            if (k < 3 * (16 / spa)) {
+                const uint32_t a = seg0 / spa + k / 3, q = k % 3;
+                if (a < d.nA) {
+                    const uint32_t s0 = a * spa, s1 = min(d.nSeg, s0 + spa);
+                    double t = 0;
+                    for (uint32_t sg = s0; sg < s1; ++sg) t += d.rcp[3ull * sg + q];
+                    d.rcs[3ull * a + q] = t;
+                }
+            }
+        }
+    }
+    return agg;
+}
+
 __global__ void __launch_bounds__(kPsThreads, 2) k_pcg_stream(const Dev d) {
     extern __shared__ __align__(32) unsigned char smem_raw[];
     double* red = reinterpret_cast<double*>(smem_raw + kPsRed);
@@ -204,15 +234,14 @@ __global__ void __launch_bounds__(kPsThreads, 2) k_pcg_stream(const Dev d) {
     }
     __syncthreads();
     const bool coarse = d.flags[F_COARSE] != 0;
-    const uint32_t nP32 = (d.nP + 31u) & ~31u;
     const bool crow = coarse && blockIdx.x * (kPsThreads / 32) < d.nc;
     double dot = 0;
-    for (uint32_t i = gtid; i < nP32; i += gsz) dot += pose_step<true>(d, i, i < d.nP, 0.0, coarse);
+    const bool rc_shared = ps_pose_phase<true>(d, 0.0, coarse, dot);
     double t = block_sum(dot, red);
     if (tid == 0) d.part[blockIdx.x] = t;
     res_gsync(grid, d.gbar, gtarget);
     if (coarse) {
-        if (crow) coarse_phase(d, gtid >> 5, gsz >> 5, rc_s);
+        if (crow) coarse_phase(d, gtid >> 5, gsz >> 5, rc_s, rc_shared);
         res_gsync(grid, d.gbar, gtarget);
     }
     double rz0 = reduce_all(d.part, nb, red);
@@ -245,14 +274,13 @@ __global__ void __launch_bounds__(kPsThreads, 2) k_pcg_stream(const Dev d) {
             res_gsync(grid, d.gbar, gtarget);
             TICK(5);
             const double alpha = rz / reduce_all(d.part2, nb, red);
-            dot = 0;
-            for (uint32_t i = gtid; i < nP32; i += gsz) dot += pose_step<false>(d, i, i < d.nP, alpha, coarse);
+            ps_pose_phase<false>(d, alpha, coarse, dot);
             t = block_sum(dot, red);
             if (tid == 0) d.part[blockIdx.x] = t;
             TICK(6);
             res_gsync(grid, d.gbar, gtarget);
             if (coarse) {
-                if (crow) coarse_phase(d, gtid >> 5, gsz >> 5, rc_s);
+                if (crow) coarse_phase(d, gtid >> 5, gsz >> 5, rc_s, rc_shared);
                 res_gsync(grid, d.gbar, gtarget);
             }
             TICK(7);
