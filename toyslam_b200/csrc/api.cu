@@ -48,6 +48,8 @@ struct tsb_ctx {
     // the coarse inverse is reused across GN iterations while it keeps working (any SPD M is a valid
     // preconditioner; a stale one only costs iterations): refreshed on the first solve of a request, when the
     // PCG needs > 1.25x the iterations it took right after the last refresh, or after `coarse_max_age` solves
+    int sb_mode = 0;                                      // smoother blocks: 0 never, 1 always, 2 adaptive (default)
+    double* sbinv_buf = nullptr;                          // Dev::sbinv is this buffer or null, solve by solve
     int coarse_age = -1, coarse_ref_iters = 0, coarse_max_age = 16, coarse_refreshes = 0, coarse_hold = 0, coarse_backoff = 1;
 };
 
@@ -66,7 +68,7 @@ void free_graph(tsb_ctx* c) {
     if (c->arena.size() > 1) { cudaStreamSynchronize(c->stream); release_arena(c); }
     c->arena_blk = c->arena_off = 0;
     c->d = Dev{}; c->loaded = c->linearized = c->solved = false;
-    c->pose0 = nullptr; c->lm0 = nullptr; c->tmp_xyt = nullptr; c->cwork = nullptr; c->cwork_len = 0; c->coarse_age = -1;
+    c->pose0 = nullptr; c->lm0 = nullptr; c->tmp_xyt = nullptr; c->cwork = nullptr; c->cwork_len = 0; c->coarse_age = -1; c->sbinv_buf = nullptr;
 }
 
 template <typename T> int dalloc(tsb_ctx* c, T*& out, size_t n) {
@@ -159,11 +161,14 @@ int upload_graph(tsb_ctx* c) {
     if (d.res_nb) {
         TRY(upload(c, d.res_pose_cut, c->rp.pose_cut)); TRY(upload(c, d.res_lm_cut, c->rp.lm_cut)); TRY(upload(c, d.res_agg_cut, c->rp.agg_cut));
         TRY(upload(c, d.lmo_ptr, c->rp.lmo_ptr)); TRY(upload(c, d.lmo_edge, c->rp.lmo_edge)); TRY(upload(c, d.edge_lm, c->rp.edge_lm));
-        // TSB_SMOOTHER=1: dense smoother blocks (sblock_smoother.cuh) instead of the 3x3 pose blocks as the fine level of the
-        // resident kernel's preconditioner.  Off by default: 2.4x fewer PCG iterations on the first solves of C2 but 1.6x the
-        // time per iteration (the inverses stream from L2), a net loss over a 50-iteration request
+        // Dense smoother blocks (sblock_smoother.cuh) instead of the 3x3 pose blocks as the fine level of the resident
+        // kernel's preconditioner: 2.4x fewer PCG iterations on the first solves of C2 but ~1.27x the time per iteration
+        // (the inverses stream from L2), and little gain once the Huber weights have settled.  Default: adaptive per
+        // request (tsb_optimize); TSB_SMOOTHER=1 always, TSB_SMOOTHER=0 never.
         { const char* e = std::getenv("TSB_SMOOTHER");
-          if (e && e[0] == '1') TRY(dalloc(c, d.sbinv, (size_t)d.res_nb * kSbPerBlock * (3 * kSbCap) * (3 * kSbCap))); }
+          c->sb_mode = e && e[0] == '0' ? 0 : e && e[0] == '1' ? 1 : 2;
+          if (c->sb_mode) TRY(dalloc(c, c->sbinv_buf, (size_t)d.res_nb * kSbPerBlock * (3 * kSbCap) * (3 * kSbCap)));
+          d.sbinv = c->sb_mode ? c->sbinv_buf : nullptr; }
     }
     TRY(upload(c, d.edge_pose, s.edge_pose)); TRY(upload(c, d.aslot_lm, s.aslot_lm)); TRY(upload(c, d.aslot_agg, s.aslot_agg));
     TRY(upload(c, d.aslot_ptr, s.aslot_ptr)); TRY(upload(c, d.aslot_edge, s.aslot_edge));
@@ -249,7 +254,8 @@ int enqueue_linearize(tsb_ctx* c) {
 }
 
 // Schur preparation + PCG + landmark back-substitution; leaves delta in d.x / d.dl
-int run_solve(tsb_ctx* c, bool refresh_coarse = true) {
+int run_solve(tsb_ctx* c, bool refresh_coarse = true, bool smoother = true) {
+    c->d.sbinv = (smoother && c->d.res_nb && c->sb_mode) ? c->sbinv_buf : nullptr;      // this solve's fine level
     const Dev& d = c->d;
     launch_schur_prep(d, c->stream);
     if (d.res_nb && d.sbinv && !launch_sb_build(d, c->stream)) { c->err = "smoother-block kernel could not be launched"; return TSB_ECUDA; }
@@ -592,6 +598,7 @@ int tsb_optimize(tsb_ctx* c, uint32_t iterations, tsb_report* rep, tsb_iter_stat
     // Huber weights move so much per step that a one-step-old operator costs ~1.7x the iterations (C2: 240 -> 415)
     c->coarse_age = -1; c->coarse_hold = 4; c->coarse_backoff = 1;
     int64_t pcg_total = 0; float ms_lin = 0, ms_sol = 0, ms_pcg = 0; const int refreshes0 = c->coarse_refreshes;
+    bool sb_on = true; int sb_last_iters = 0;
     CU(cudaEventRecord(c->ev[3], c->stream));
     for (uint32_t it = 0; it < iterations; ++it) {
         CU(cudaEventRecord(c->ev[0], c->stream));
@@ -620,7 +627,14 @@ int tsb_optimize(tsb_ctx* c, uint32_t iterations, tsb_report* rep, tsb_iter_stat
             if (c->coarse_age == 2) { c->coarse_hold = c->coarse_backoff; c->coarse_backoff = std::min(2 * c->coarse_backoff, 16); }
             else c->coarse_backoff = std::max(1, c->coarse_backoff / 2);
         }
-        TRY(run_solve(c, refresh));
+        // Fine level of the resident kernel, adaptive mode: a request starts with the dense smoother blocks; every sixth
+        // solve is a probe with the 3x3 pose blocks (and a fresh coarse operator), and once the probe is cheaper -- an
+        // iteration with smoother blocks costs ~1.27x one without (C2, measured) -- the request stays with the 3x3 blocks.
+        // Iteration counts only: deterministic.
+        bool use_sb = c->sb_mode == 1 || (c->sb_mode == 2 && sb_on);
+        const bool sb_probe = c->sb_mode == 2 && sb_on && c->d.res_nb && it > 0 && it % 6 == 0;
+        if (sb_probe) { use_sb = false; refresh = true; }
+        TRY(run_solve(c, refresh, use_sb));
         CU(cudaEventRecord(c->ev[2], c->stream));
         TRY(enqueue_update(c));
         TRY(fetch_scalars(c));
@@ -631,6 +645,8 @@ int tsb_optimize(tsb_ctx* c, uint32_t iterations, tsb_report* rep, tsb_iter_stat
         CU(cudaEventElapsedTime(&a, c->ev[0], c->ev[1])); CU(cudaEventElapsedTime(&b, c->ev[1], c->ev[2]));
         { float p_ = 0; CU(cudaEventElapsedTime(&p_, c->ev[4], c->ev[5])); ms_pcg += p_; }
         ms_lin += a; ms_sol += b; pcg_total += c->h_flags[F_ITERS]; ++done;
+        if (sb_probe && 100 * c->h_flags[F_ITERS] < 127 * sb_last_iters) sb_on = false;
+        if (use_sb) sb_last_iters = c->h_flags[F_ITERS];
         if (c->coarse_age == 0) c->coarse_ref_iters = c->h_flags[F_ITERS];
         ++c->coarse_age;
         if (per_iter) { tsb_iter_stats& s = per_iter[it]; s.chi2 = err; s.delta_norm = dnorm; s.pcg_iters = c->h_flags[F_ITERS];

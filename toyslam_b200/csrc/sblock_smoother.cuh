@@ -4,8 +4,10 @@
 // An sblock is the EXACT diagonal block of the Schur complement S = Hpp - Hpl Hll^-1 Hpl^T over its poses (consecutive
 // poses see the same landmarks, so it is dense), inverted explicitly; the PCG applies it as a dense mat-vec.
 // C2, first solve: 247 PCG iterations with 3x3 blocks -> 101 with sblocks (tools/precond_proto.py --schwarz predicted 102),
-// but 36 us instead of 23 us per iteration (24 MB of inverses stream from L2 per iteration) and only 113 -> 100 iterations
-// averaged over a 50-iteration request: opt-in (TSB_SMOOTHER=1), see DESIGN.md section 4.
+// at ~1.27x the time per iteration (24 MB of inverses stream from L2 per iteration) plus this kernel (0.31 ms); once the
+// Huber weights have settled the iteration counts meet (113 vs 100 averaged over a 50-iteration request), so
+// tsb_optimize starts a request with sblocks and drops them when a probe solve with 3x3 blocks is cheaper
+// (TSB_SMOOTHER=1 / 0: always / never).  C2, 50 GN iterations: 420 -> 441 GN it/s.
 //
 // Resident block b (poses [res_pose_cut[b], res_pose_cut[b+1])) is cut into msb = ceil(np / kSbCap) <= kSbPerBlock
 // equal sblocks; sblock q of block b is stored at sbinv + (b kSbPerBlock + q) kSbLD^2, leading dimension kSbLD,
@@ -15,14 +17,19 @@
 //   1. assembly in shared memory: thread per pose pair (i <= j): Hpp diagonal / ODOM blocks, minus the landmark
 //      terms found by merging the two poses' edge lists (sorted by landmark).  One thread per entry block, fixed
 //      order: deterministic, no atomics.
-//   2. in-place Gauss-Jordan without pivoting (the block is SPD); a non-positive pivot falls back to the 3x3
-//      pose blocks of d.minv for this sblock.
+//   2. Gauss-Jordan without pivoting (the block is SPD) with the matrix in REGISTERS: thread (ty, tx) of 16 x 32 owns
+//      rows ty + 16 a, columns tx + 32 b (9 x 5 tile); per pivot the owners publish row k (scaled) and column k through
+//      double-buffered shared memory, one block barrier per pivot.  (The first version kept the matrix in shared
+//      memory: 75 % of its 474 us were short-scoreboard stalls of the n^3 update loop, profiles/r1_sb_build_c2_source.txt.)
+//      A non-positive pivot falls back to the 3x3 pose blocks of d.minv for this sblock.
 //   3. symmetrised write to global memory.
 // Included inside the anonymous namespace of kernels.cu.
 
 constexpr uint32_t kSbLD = 3 * kSbCap;
-constexpr int kSbThreads = 1024;
-constexpr size_t kSbSmemBytes = sizeof(double) * ((size_t)kSbLD * (kSbLD + 1) + 2 * kSbLD + 8);
+constexpr int kSbThreads = 512;          // 16 x 32 threads, each owns a 9 x 5 register tile of the (padded) block during the inversion
+constexpr uint32_t kSbColPad = 160;      // columns covered by 32 lanes x 5
+constexpr size_t kSbSmemBytes = sizeof(double) * ((size_t)kSbLD * (kSbLD + 1) + 2 * kSbLD + 2 * kSbColPad + 8);
+static_assert(kSbLD <= 16 * 9 && kSbLD <= kSbColPad, "register tile of the Gauss-Jordan step");
 static_assert(kResPoseCap <= kSbPerBlock * kSbCap, "a resident block's poses must fit its sblocks");
 
 // pose range [ls, ls + n) (block-local) of sblock q of a resident block with np poses
@@ -40,13 +47,16 @@ __global__ void __launch_bounds__(kSbThreads, 1) k_sb_build(const Dev d) {
     uint32_t ls, n; sb_range(np, q, ls, n);
     if (n == 0) return;
     const uint32_t ps = p0 + ls, dim = 3 * n, ld = dim + 1;
-    double* colk = A + (size_t)kSbLD * (kSbLD + 1); double* rowk = colk + kSbLD;
-    int* bad = reinterpret_cast<int*>(rowk + kSbLD);
+    double* colk = A + (size_t)kSbLD * (kSbLD + 1); double* rowk = colk + 2 * kSbLD;      // two buffers each
+    double* sh_ip = rowk + 2 * kSbColPad; int* bad = reinterpret_cast<int*>(sh_ip + 2);
     if (tid == 0) *bad = 0;
     // ---- 1. assembly ------------------------------------------------------------------------------------------
-    for (uint32_t t = tid; t < n * n; t += kSbThreads) {
-        const uint32_t i = t / n, j = t - i * n;
-        if (j < i) continue;
+    // pose pairs i <= j: rows r and n - 1 - r of the upper triangle together hold n + 1 pairs
+    for (uint32_t t = tid; t < ((n + 1) / 2) * (n + 1); t += kSbThreads) {
+        const uint32_t r = t / (n + 1), c = t - r * (n + 1);
+        uint32_t i, j;
+        if (c < n - r) { i = r; j = r + c; }
+        else { i = n - 1 - r; j = i + (c - (n - r)); if (i == r) continue; }
         const uint32_t pi = ps + i, pj = ps + j;
         double m[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0};
         if (i == j) { const double* H = d.hpp + 6ull * pi; m[0] = H[0]; m[1] = m[3] = H[1]; m[2] = m[6] = H[2]; m[4] = H[3]; m[5] = m[7] = H[4]; m[8] = H[5]; }
@@ -89,22 +99,67 @@ __global__ void __launch_bounds__(kSbThreads, 1) k_sb_build(const Dev d) {
             }
     }
     __syncthreads();
-    // ---- 2. in-place Gauss-Jordan, no pivoting -----------------------------------------------------------------
-    for (uint32_t k = 0; k < dim; ++k) {
-        const double piv = A[(size_t)k * ld + k];
-        if (!(piv > 0) || !(piv < 1e300)) { if (tid == 0) *bad = 1; break; }      // same value in every thread: uniform branch
-        const double ip = 1.0 / piv;
-        for (uint32_t i = tid; i < dim; i += kSbThreads) { colk[i] = A[(size_t)i * ld + k]; rowk[i] = A[(size_t)k * ld + i] * ip; }
-        __syncthreads();
-        for (uint32_t t = tid; t < dim * dim; t += kSbThreads) {
-            const uint32_t i = t / dim, j = t - i * dim;
-            double v;
-            if (i == k) v = (j == k) ? ip : rowk[j];
-            else if (j == k) v = -colk[i] * ip;
-            else v = A[(size_t)i * ld + j] - colk[i] * rowk[j];
-            A[(size_t)i * ld + j] = v;
+    // ---- 2. Gauss-Jordan, no pivoting, matrix in registers ------------------------------------------------------
+    {
+        const uint32_t ty = tid >> 5, tx = tid & 31;
+        double R[9][5];
+#pragma unroll
+        for (int a = 0; a < 9; ++a)
+#pragma unroll
+            for (int b = 0; b < 5; ++b) {
+                const uint32_t i = ty + 16 * a, j = tx + 32 * b;
+                R[a][b] = (i < dim && j < dim) ? A[(size_t)i * ld + j] : (i == j ? 1.0 : 0.0);     // identity padding stays inert
+            }
+#pragma unroll
+        for (int a0 = 0; a0 < 9; ++a0) {
+            if (16u * a0 >= dim) break;
+            const int b0 = a0 >> 1;                                  // k / 32 for k = 16 a0 + kk, kk < 16
+#pragma unroll 1
+            for (uint32_t kk = 0; kk < 16; ++kk) {
+                const uint32_t k = 16u * a0 + kk;
+                if (k >= dim) break;
+                double* ck = colk + (k & 1u) * kSbLD; double* rk = rowk + (k & 1u) * kSbColPad;
+                if (ty == kk) {                                      // this warp owns row k; lane k % 32 holds the pivot
+                    const double piv = __shfl_sync(0xffffffffu, R[a0][b0], k & 31u);
+                    const double ipv = 1.0 / piv;
+                    if (tx == 0) { sh_ip[k & 1u] = ipv; if (!(piv > 0) || !(piv < 1e300)) *bad = 1; }
+#pragma unroll
+                    for (int b = 0; b < 5; ++b) rk[tx + 32 * b] = R[a0][b] * ipv;
+                }
+                if (tx == (k & 31u)) {
+#pragma unroll
+                    for (int a = 0; a < 9; ++a) ck[ty + 16 * a] = R[a][b0];
+                }
+                __syncthreads();
+                const double ipv = sh_ip[k & 1u];
+                double rj[5];
+#pragma unroll
+                for (int b = 0; b < 5; ++b) rj[b] = rk[tx + 32 * b];
+#pragma unroll
+                for (int a = 0; a < 9; ++a) {
+                    if (16u * a >= dim) break;                       // tiles beyond the block are identity padding (block-uniform)
+                    const uint32_t i = ty + 16 * a;
+                    const double ci = ck[i];
+#pragma unroll
+                    for (int b = 0; b < 5; ++b) {
+                        if (32u * b >= dim) break;
+                        const uint32_t j = tx + 32 * b;
+                        double v = R[a][b] - ci * rj[b];
+                        if (j == k) v = -ci * ipv;
+                        if (i == k) v = (j == k) ? ipv : rj[b];
+                        R[a][b] = v;
+                    }
+                }
+            }
         }
         __syncthreads();
+#pragma unroll
+        for (int a = 0; a < 9; ++a)
+#pragma unroll
+            for (int b = 0; b < 5; ++b) {
+                const uint32_t i = ty + 16 * a, j = tx + 32 * b;
+                if (i < dim && j < dim) A[(size_t)i * ld + j] = R[a][b];
+            }
     }
     __syncthreads();
     // ---- 3. publish ------------------------------------------------------------------------------------------------
@@ -122,8 +177,7 @@ __global__ void __launch_bounds__(kSbThreads, 1) k_sb_build(const Dev d) {
         }
         return;
     }
-    for (uint32_t t = tid; t < dim * dim; t += kSbThreads) {
-        const uint32_t i = t / dim, j = t - i * dim;
-        out[(size_t)i * kSbLD + j] = 0.5 * (A[(size_t)i * ld + j] + A[(size_t)j * ld + i]);
-    }
+    for (uint32_t i = tid >> 5; i < dim; i += kSbThreads / 32)
+        for (uint32_t j = tid & 31; j < dim; j += 32)
+            out[(size_t)i * kSbLD + j] = 0.5 * (A[(size_t)i * ld + j] + A[(size_t)j * ld + i]);
 }
