@@ -629,7 +629,8 @@ int tsb_optimize(tsb_ctx* c, uint32_t iterations, tsb_report* rep, tsb_iter_stat
         }
         // Fine level of the resident kernel, adaptive mode: a request starts with the dense smoother blocks; every sixth
         // solve is a probe with the 3x3 pose blocks (and a fresh coarse operator), and once the probe is cheaper -- an
-        // iteration with smoother blocks costs ~1.27x one without (C2, measured) -- the request stays with the 3x3 blocks.
+        // iteration with smoother blocks costs ~1.27x one without and k_sb_build ~17.5 iterations (C2, measured) -- the
+        // request stays with the 3x3 blocks.
         // Iteration counts only: deterministic.
         bool use_sb = c->sb_mode == 1 || (c->sb_mode == 2 && sb_on);
         const bool sb_probe = c->sb_mode == 2 && sb_on && c->d.res_nb && it > 0 && it % 6 == 0;
@@ -645,7 +646,7 @@ int tsb_optimize(tsb_ctx* c, uint32_t iterations, tsb_report* rep, tsb_iter_stat
         CU(cudaEventElapsedTime(&a, c->ev[0], c->ev[1])); CU(cudaEventElapsedTime(&b, c->ev[1], c->ev[2]));
         { float p_ = 0; CU(cudaEventElapsedTime(&p_, c->ev[4], c->ev[5])); ms_pcg += p_; }
         ms_lin += a; ms_sol += b; pcg_total += c->h_flags[F_ITERS]; ++done;
-        if (sb_probe && 100 * c->h_flags[F_ITERS] < 127 * sb_last_iters) sb_on = false;
+        if (sb_probe && 100 * c->h_flags[F_ITERS] < 127 * sb_last_iters + 1750) sb_on = false;
         if (use_sb) sb_last_iters = c->h_flags[F_ITERS];
         if (c->coarse_age == 0) c->coarse_ref_iters = c->h_flags[F_ITERS];
         ++c->coarse_age;
