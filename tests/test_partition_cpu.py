@@ -58,3 +58,14 @@ dist.destroy_process_group()
                         "--master-addr", "127.0.0.1", "--master-port", "29731", str(script)],
                        capture_output=True, text=True, timeout=240, env=env)
     assert r.returncode == 0 and "W2 OK" in r.stdout, r.stdout[-2000:] + r.stderr[-2000:]
+
+
+def test_coarse_aggregates_of_large_graphs():
+    """Graphs beyond the resident kernel: aggregates of 32 poses up to 2 048 aggregates (65 536 poses), then
+    32 ceil(P / 65 536) poses per aggregate (structure.cpp; kCoarseMaxAggLarge in host_graph.h)."""
+    from toyslam_b200 import synth, capi
+    for scale, k in ((0.05, 32), (0.1, 64), (0.2, 128)):
+        payload = synth.to_payload(synth.make_config("c5", scale=scale, seed=1))
+        c, _, _, _ = capi.host_plan(payload, 0, 1)
+        assert c.n_aggregates == -(-c.n_pose // k), (c.n_pose, c.n_aggregates, k)
+        assert c.n_aggregates <= 2048

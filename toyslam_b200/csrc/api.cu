@@ -514,6 +514,7 @@ int tsb_host_plan(const void* payload, uint32_t nbytes, int32_t rank, int32_t wo
     o->dim = 3 * g.P + 2 * g.L; o->pose_begin = st.pose_begin; o->pose_end = st.pose_end;
     o->n_lmedge_local = (uint32_t)st.lm_perm.size(); o->n_odom_local = st.n_od_owned;
     o->n_chunks = (uint32_t)st.chunks.size(); o->n_blocks = (uint32_t)st.blk_chunk_ptr.size() - 1; o->n_slots = (uint32_t)st.slot_lm.size();
+    o->n_aggregates = st.nA;
     if (n_ghost) *n_ghost = st.nG;
     if (n_boundary) *n_boundary = (uint32_t)st.boundary.size();
     if (structure_hash) {            // FNV-1a over the rank-independent parts (cuts, boundary list): must agree on all ranks
