@@ -271,11 +271,12 @@ def main():
                                 "k_pcg_persistent (whole PCG solve in one cooperative launch)" if world == 1 else "k_pcg_* phases + NCCL all-reduces"),
                      "bound": "hbm", "achieved": B_pcg / (pcg_ms * 1e-3) / 1e9, "peak": peak, "peak_kind": peak_kind, "unit": "GB/s",
                      "frac": B_pcg / (pcg_ms * 1e-3) / 1e9 / peak,
-                     # DRAM bytes of one k_pcg_resident launch (= one solve) from the ncu --set full capture summarised in
-                     # profiles/r1_pcg_resident_c2_v2_ncu_summary.csv (17.38 MB read + 0.22 MB written): far below the
-                     # algorithmic bytes because both orders of Hpl stay in shared memory for the whole solve
-                     "traffic": 17.6e6 if (resident_kernel and args.workload == "c2") else None,
-                     "traffic_source": "profiles/r1_pcg_resident_c2_v2_ncu_summary.csv" if (resident_kernel and args.workload == "c2") else None,
+                     # DRAM bytes of one k_pcg_resident launch (= one solve) from the ncu --set full captures summarised in
+                     # profiles/r1_pcg_resident_c2_v3_ncu_summary.csv (first solve, smoother blocks: 44.3 MB read + 1.2 MB
+                     # written, 24.5 MB of it the smoother inverses read once into L2) and ..._v2_... (3x3 blocks: 17.6 MB):
+                     # far below the algorithmic bytes because both orders of Hpl stay in shared memory for the whole solve
+                     "traffic": 45.5e6 if (resident_kernel and args.workload == "c2") else None,
+                     "traffic_source": "profiles/r1_pcg_resident_c2_v3_ncu_summary.csv" if (resident_kernel and args.workload == "c2") else None,
                      "algorithmic_bytes_per_launch": B_pcg * pcg_total / GN_ITERS, "algorithmic_bytes_per_pcg_iteration": B_pcg,
                      "launch_ms": ms_pcg / GN_ITERS, "pcg_iterations_per_launch": pcg_total / GN_ITERS,
                      "share_of_step": ms_pcg / dev_ms,
@@ -357,6 +358,10 @@ def main():
                                        "bound": "hbm", "achieved": B_pcg4 / (us_it * 1e-6) / 1e9, "peak": peak * world, "unit": "GB/s",
                                        "n_gpus": world, "frac": B_pcg4 / (us_it * 1e-6) / 1e9 / (peak * world),
                                        "algorithmic_bytes_per_pcg_iteration": B_pcg4, "us_per_pcg_iteration": us_it,
+                                       # k_pcg_stream at N=1, ncu --set full (profiles/r1_pcg_stream_c4_v2_ncu_summary.csv):
+                                       # 17.11 GB read + 1.19 GB written in a 6-iteration launch; B_pcg + the 275 MB dense
+                                       # coarse inverse = 2.79 GB per iteration
+                                       "traffic_per_pcg_iteration": 3.05e9 if world == 1 else None,
                                        "sample": "2 GN iterations x 30 PCG iterations (capped), PCG kernel time only"}
             opt4.close()
         except Exception as e:                                # never lose the main line to the extra measurement
