@@ -124,6 +124,14 @@ int upload_graph(tsb_ctx* c) {
     TRY(upload(c, d.lm_part_ptr, s.lm_part_ptr)); TRY(upload(c, d.lm_part_idx, s.lm_part_idx));
     TRY(upload(c, d.od_a, s.od_a)); TRY(upload(c, d.od_b, s.od_b)); TRY(upload(c, d.od_zinv, oz)); TRY(upload(c, d.od_w, ow));
     TRY(upload(c, d.od_out_ptr, s.od_out_ptr)); TRY(upload(c, d.od_in_ptr, s.od_in_ptr)); TRY(upload(c, d.od_in_edge, s.od_in_edge));
+    { std::vector<uint32_t> nb(4ull * d.nP, 0xFFFFFFFFu);
+      for (uint32_t p = 0; p < d.nP; ++p) {
+          const uint32_t no = s.od_out_ptr[p + 1] - s.od_out_ptr[p], ni = s.od_in_ptr[p + 1] - s.od_in_ptr[p];
+          if (no > 1 || ni > 1) { nb[4ull * p] = 0xFFFFFFFEu; continue; }
+          if (no) { const uint32_t k = s.od_out_ptr[p]; nb[4ull * p] = s.od_b[k]; nb[4ull * p + 1] = k; }
+          if (ni) { const uint32_t k = s.od_in_edge[s.od_in_ptr[p]]; nb[4ull * p + 2] = s.od_a[k]; nb[4ull * p + 3] = k; }
+      }
+      TRY(upload(c, d.od_nb, nb)); }
     TRY(upload(c, d.fixed_pose_count, s.fixed_pose_count)); TRY(upload(c, d.fixed_lm_count, s.fixed_lm_count));
     // state: local poses then ghosts
     const uint32_t nPG = d.nP + d.nG;

@@ -43,6 +43,8 @@ struct Dev {
     const double* od_zinv;      // 6 per edge
     const double* od_w;         // 3 per edge
     const uint32_t* od_out_ptr; const uint32_t* od_in_ptr; const uint32_t* od_in_edge;
+    const uint4* od_nb;         // per pose with <= 1 out- and <= 1 in-edge (a chain): (out pose, out edge, in pose, in edge), 0xFFFFFFFF = none;
+                                // x == 0xFFFFFFFE: general pose, walk the CSR lists.  Saves two dependent loads per pose in S p
     double* hoo;                // 3 per edge: diagonal of the (i,j) block = -W
     const uint32_t* fixed_pose_count; const uint32_t* fixed_lm_count;
     // assembled system

@@ -476,6 +476,15 @@ __device__ __forceinline__ void unit_pass_a(const Dev& d, const uint32_t unit, c
 __device__ __forceinline__ void hpp_apply(const Dev& d, uint32_t p, double* out) {
     const double v0 = d.p[3ull * p], v1 = d.p[3ull * p + 1], v2 = d.p[3ull * p + 2];
     double y0, y1, y2; sym3_mul(d.hpp + 6ull * p, v0, v1, v2, y0, y1, y2);
+    const uint4 nb = d.od_nb[p];
+    if (nb.x != 0xFFFFFFFEu) {                 // chain pose: both neighbours known after ONE load (same order of additions)
+        if (nb.x != 0xFFFFFFFFu) { const double* h = d.hoo + 3ull * nb.y; const double* q = d.p + 3ull * nb.x;
+            y0 += h[0] * q[0]; y1 += h[1] * q[1]; y2 += h[2] * q[2]; }
+        if (nb.z != 0xFFFFFFFFu) { const double* h = d.hoo + 3ull * nb.w; const double* q = d.p + 3ull * nb.z;
+            y0 += h[0] * q[0]; y1 += h[1] * q[1]; y2 += h[2] * q[2]; }
+        out[0] = y0; out[1] = y1; out[2] = y2;
+        return;
+    }
     for (uint32_t k = d.od_out_ptr[p]; k < d.od_out_ptr[p + 1]; ++k) {
         const double* h = d.hoo + 3ull * k; const double* q = d.p + 3ull * d.od_b[k];
         y0 += h[0] * q[0]; y1 += h[1] * q[1]; y2 += h[2] * q[2];
