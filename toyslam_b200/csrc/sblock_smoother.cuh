@@ -4,7 +4,7 @@
 // An sblock is the EXACT diagonal block of the Schur complement S = Hpp - Hpl Hll^-1 Hpl^T over its poses (consecutive
 // poses see the same landmarks, so it is dense), inverted explicitly; the PCG applies it as a dense mat-vec.
 // C2, first solve: 247 PCG iterations with 3x3 blocks -> 101 with sblocks (tools/precond_proto.py --schwarz predicted 102),
-// at ~1.27x the time per iteration (24 MB of inverses stream from L2 per iteration) plus this kernel (0.31 ms); once the
+// at ~1.27x the time per iteration (24 MB of inverses stream from L2 per iteration) plus this kernel (0.26 ms); once the
 // Huber weights have settled the iteration counts meet (113 vs 100 averaged over a 50-iteration request), so
 // tsb_optimize starts a request with sblocks and drops them when a probe solve with 3x3 blocks is cheaper
 // (TSB_SMOOTHER=1 / 0: always / never).  C2, 50 GN iterations: 420 -> 441 GN it/s.
@@ -143,10 +143,11 @@ __global__ void __launch_bounds__(kSbThreads, 1) k_sb_build(const Dev d) {
 #pragma unroll
                     for (int b = 0; b < 5; ++b) {
                         if (32u * b >= dim) break;
-                        const uint32_t j = tx + 32 * b;
+                        // row k lives in tile row a0 of warp kk, column k in tile column b0 of lane k % 32: a, a0, b, b0 are
+                        // compile-time in the unrolled loops, so only 1/9 and 1/5 of the tile entries carry the selects
                         double v = R[a][b] - ci * rj[b];
-                        if (j == k) v = -ci * ipv;
-                        if (i == k) v = (j == k) ? ipv : rj[b];
+                        if (b == b0 && tx == (k & 31u)) v = -ci * ipv;
+                        if (a == a0 && ty == kk) v = (b == b0 && tx == (k & 31u)) ? ipv : rj[b];
                         R[a][b] = v;
                     }
                 }
