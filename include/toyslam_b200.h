@@ -69,6 +69,7 @@ typedef struct tsb_counts {
     uint32_t pcg_path;                                        /* 0 persistent kernel, 1 shared-memory-resident kernel, 2 one launch per phase (+ NCCL), 3 streamed persistent kernel */
     uint32_t replicated;                                      /* 1: world > 1 but the graph is solved whole on every rank (it fits one GPU's resident kernel) */
     uint32_t n_aggregates;                                    /* coarse space of the two-level preconditioner (this rank) */
+    uint32_t n_ml_levels, n_ml_top;                           /* multilevel hierarchy of the streamed PCG: levels, nodes of the dense top level */
 } tsb_counts;
 
 typedef struct tsb_iter_stats {
@@ -90,6 +91,9 @@ typedef struct tsb_report {
     float ms_linearize_total, ms_solve_total;
     float ms_pcg_total;        /* part of ms_solve_total spent in the PCG itself (the persistent kernel when world == 1) */
     int32_t coarse_refreshes;  /* how many solves rebuilt the coarse operator of the two-level preconditioner */
+    int32_t pcg_not_converged; /* solves that hit pcg_max_iters or ended with a non-finite residual (the step is then inexact) */
+    int32_t coarse_failures;   /* solves whose dense coarse operator could not be inverted (they ran with block-Jacobi only) */
+    int32_t singular_blocks;   /* GN iterations in which an unconstrained vertex (singular 2x2 / 3x3 block) was held at delta = 0 */
 } tsb_report;
 
 /* world > 1: rank 0 calls this once and ships the 128 bytes to every rank (e.g. over torch.distributed or MPI) */

@@ -60,12 +60,16 @@ dist.destroy_process_group()
     assert r.returncode == 0 and "W2 OK" in r.stdout, r.stdout[-2000:] + r.stderr[-2000:]
 
 
-def test_coarse_aggregates_of_large_graphs():
-    """Graphs beyond the resident kernel: aggregates of 32 poses up to 2 048 aggregates (65 536 poses), then
-    32 ceil(P / 65 536) poses per aggregate (structure.cpp; kCoarseMaxAggLarge in host_graph.h)."""
+def test_multilevel_hierarchy_of_large_graphs():
+    """Graphs beyond the resident kernel get the multilevel hierarchy (structure.cpp build_hierarchy): ratio 4 per
+    level, a final ratio of 2 where 4 would leave the dense top level under half of kMlTopDefault = 1024 nodes."""
     from toyslam_b200 import synth, capi
-    for scale, k in ((0.05, 32), (0.1, 64), (0.2, 128)):
+    for scale in (0.02, 0.05, 0.2):
         payload = synth.to_payload(synth.make_config("c5", scale=scale, seed=1))
         c, _, _, _ = capi.host_plan(payload, 0, 1)
-        assert c.n_aggregates == -(-c.n_pose // k), (c.n_pose, c.n_aggregates, k)
-        assert c.n_aggregates <= 2048
+        n, levels = c.n_pose, 0
+        while levels == 0 or n > 1024:
+            ratio = 2 if (levels > 0 and (n + 1) // 2 <= 1024) else 4
+            n = -(-n // ratio); levels += 1
+        assert (c.n_ml_levels, c.n_ml_top) == (levels, n), (c.n_pose, c.n_ml_levels, c.n_ml_top, levels, n)
+        assert 512 < c.n_ml_top <= 1024 or levels == 1

@@ -39,7 +39,7 @@ class GraphSoa(C.Structure):
 class Counts(C.Structure):
     _fields_ = [(n, C.c_uint32) for n in ("n_pose", "n_lm", "n_odom", "n_lmedge", "n_fixed", "dim", "pose_begin",
                                           "pose_end", "n_lmedge_local", "n_odom_local", "n_chunks", "n_blocks", "n_slots",
-                                          "pcg_path", "replicated", "n_aggregates")]
+                                          "pcg_path", "replicated", "n_aggregates", "n_ml_levels", "n_ml_top")]
 
 
 class IterStats(C.Structure):
@@ -51,7 +51,8 @@ class Report(C.Structure):
     _fields_ = [("iterations_run", C.c_int32), ("exit_code", C.c_int32), ("final_chi2", C.c_double),
                 ("pcg_iters_total", C.c_int64), ("kernel_launches", C.c_int64), ("ms_total", C.c_float),
                 ("ms_linearize_total", C.c_float), ("ms_solve_total", C.c_float), ("ms_pcg_total", C.c_float),
-                ("coarse_refreshes", C.c_int32)]
+                ("coarse_refreshes", C.c_int32), ("pcg_not_converged", C.c_int32), ("coarse_failures", C.c_int32),
+                ("singular_blocks", C.c_int32)]
 
 
 _lib = None

@@ -5,7 +5,6 @@
 #include "device_graph.h"
 
 #include <nccl.h>
-#include <cusolverDn.h>
 
 #include <cmath>
 #include <cstdio>
@@ -41,10 +40,10 @@ struct tsb_ctx {
     bool force_phased = false;                            // TSB_PCG_PHASED=1: one launch per PCG phase (the multi-GPU path)
     uint64_t h2d = 0, d2h = 0;                            // bytes copied since the last tsb_load_*
     ncclComm_t comm = nullptr;                            // world > 1: one communicator, collectives on `stream`
-    // two-level preconditioner: dense coarse operator factored and inverted with cuSOLVER (potrf + potrs against I)
+    // coarse levels of the preconditioner (two-level aggregates for the resident kernel, multilevel hierarchy for the
+    // streamed one): the dense top operator is inverted by k_coarse_invert
     bool use_coarse = true;                               // TSB_COARSE=0: block-Jacobi only
-    cusolverDnHandle_t solver = nullptr;
-    double* cwork = nullptr; int cwork_len = 0;
+    uint32_t ml_top = kMlTopDefault;                      // TSB_ML_TOP: nodes of the hierarchy's top level; TSB_ML=0: two-level aggregates everywhere
     // the coarse inverse is reused across GN iterations while it keeps working (any SPD M is a valid
     // preconditioner; a stale one only costs iterations): refreshed on the first solve of a request, when the
     // PCG needs > 1.25x the iterations it took right after the last refresh, or after `coarse_max_age` solves
@@ -68,7 +67,7 @@ void free_graph(tsb_ctx* c) {
     if (c->arena.size() > 1) { cudaStreamSynchronize(c->stream); release_arena(c); }
     c->arena_blk = c->arena_off = 0;
     c->d = Dev{}; c->loaded = c->linearized = c->solved = false;
-    c->pose0 = nullptr; c->lm0 = nullptr; c->tmp_xyt = nullptr; c->cwork = nullptr; c->cwork_len = 0; c->coarse_age = -1; c->sbinv_buf = nullptr;
+    c->pose0 = nullptr; c->lm0 = nullptr; c->tmp_xyt = nullptr; c->coarse_age = -1; c->sbinv_buf = nullptr;
 }
 
 template <typename T> int dalloc(tsb_ctx* c, T*& out, size_t n) {
@@ -182,17 +181,33 @@ int upload_graph(tsb_ctx* c) {
     TRY(upload(c, d.aslot_ptr, s.aslot_ptr)); TRY(upload(c, d.aslot_edge, s.aslot_edge));
     TRY(upload(c, d.cpair_a, s.cpair_a)); TRY(upload(c, d.cpair_b, s.cpair_b)); TRY(upload(c, d.cpair_ptr, s.cpair_ptr));
     TRY(upload(c, d.ctrip, s.ctrip));
+    // multilevel hierarchy (streamed PCG): structure arrays and per-level vectors
+    d.mlLv = (uint32_t)s.ml.size(); d.mlLocal = s.ml_local; d.mlWin = (d.nP + kMlWindow - 1) / kMlWindow; d.mlCdot = d.nc;
+    if (d.mlLv) {
+        d.nc = 3 * s.ml.back().n; d.mlCdot = d.nc;
+        for (uint32_t l = 0; l < d.mlLv; ++l) {
+            const MlLevel& h = s.ml[l]; MlDev& m = d.ml[l];
+            m.n = h.n; m.ratio = h.ratio; m.spacing = h.spacing; m.nnz = (uint32_t)h.edge_lm.size();
+            m.slots = (kMlWindow + h.spacing - 1) / h.spacing + 2; m.cdot_off = 0;
+            TRY(upload(c, m.node_ptr, h.node_ptr)); TRY(upload(c, m.edge_lm, h.edge_lm)); TRY(upload(c, m.ref_ptr, h.ref_ptr)); TRY(upload(c, m.ref, h.ref));
+            TRY(dalloc(c, m.C, 6ull * m.nnz)); TRY(dalloc(c, m.dinv, 6ull * m.n)); TRY(dalloc(c, m.m, 3ull * m.n)); TRY(dalloc(c, m.g, 3ull * m.n + 3));
+            if (l >= d.mlLocal) TRY(dalloc(c, m.wpart, 3ull * d.mlWin * m.slots));
+            if (l >= d.mlLocal && l + 1 < d.mlLv) { m.cdot_off = d.mlCdot; d.mlCdot += m.n; }
+        }
+        // landmark-major CSR over the top level's coarse edges (k_ml_top)
+        const MlLevel& t = s.ml.back();
+        std::vector<uint32_t> tp(g.L + 1, 0), te(t.edge_lm.size()), tn(t.edge_lm.size());
+        for (uint32_t l : t.edge_lm) tp[l + 1]++;
+        for (uint32_t l = 0; l < g.L; ++l) tp[l + 1] += tp[l];
+        { std::vector<uint32_t> c2(tp.begin(), tp.end() - 1);
+          for (uint32_t K = 0; K < t.n; ++K) for (uint32_t e = t.node_ptr[K]; e < t.node_ptr[K + 1]; ++e) { const uint32_t at = c2[t.edge_lm[e]]++; te[at] = e; tn[at] = K; } }
+        TRY(upload(c, d.tl_ptr, tp)); TRY(upload(c, d.tl_edge, te)); TRY(upload(c, d.tl_node, tn));
+        TRY(dalloc(c, d.r2, 3ull * d.nP));
+    }
     TRY(dalloc(c, d.zoff, d.nP)); TRY(dalloc(c, d.cC, 6ull * d.nAS)); TRY(dalloc(c, d.Ac, (size_t)d.nc * d.nc)); TRY(dalloc(c, d.Ai, (size_t)d.nc * d.nc));
     if (d.nc > 3 * kCoarseMaxAgg) TRY(dalloc(c, d.rcs, (size_t)kCoarseScratchBlocks * d.nc));
-    TRY(dalloc(c, d.rcp, 3ull * d.nSeg)); TRY(dalloc(c, d.yc, d.nc)); TRY(dalloc(c, d.cdot, d.nc)); TRY(dalloc(c, d.cinfo, (size_t)2)); TRY(dalloc(c, d.cbar, (size_t)1));
+    TRY(dalloc(c, d.rcp, 3ull * d.nSeg)); TRY(dalloc(c, d.yc, d.nc + 3ull)); TRY(dalloc(c, d.cdot, (size_t)std::max(d.mlCdot, d.nc))); TRY(dalloc(c, d.cinfo, (size_t)2)); TRY(dalloc(c, d.cbar, (size_t)1));
     CU(cudaMemsetAsync(d.cinfo, 0, 8, c->stream));
-    if (c->use_coarse && d.nc) {
-        int l1 = 0, l2 = 0;
-        if (cusolverDnDpotrf_bufferSize(c->solver, CUBLAS_FILL_MODE_LOWER, (int)d.nc, d.Ac, (int)d.nc, &l1) != CUSOLVER_STATUS_SUCCESS) {
-            c->err = "cusolverDnDpotrf_bufferSize failed"; return TSB_ECUDA; }
-        c->cwork_len = std::max(l1, l2);
-        TRY(dalloc(c, c->cwork, (size_t)c->cwork_len));
-    }
     // partial-sum scratch: one entry per unit, per 256 vertices, or per block of a persistent kernel (<= 8 per SM)
     c->part_cap = std::max<uint32_t>(std::max<uint32_t>(d.nBlocks, (std::max(d.nP, g.L) + kThreads - 1) / kThreads) + 1, 4096);
     TRY(dalloc(c, d.part, c->part_cap)); TRY(dalloc(c, d.part2, c->part_cap));
@@ -269,38 +284,20 @@ int run_solve(tsb_ctx* c, bool refresh_coarse = true, bool smoother = true) {
     if (d.res_nb && d.sbinv && !launch_sb_build(d, c->stream)) { c->err = "smoother-block kernel could not be launched"; return TSB_ECUDA; }
     if (c->use_coarse && d.nc && (refresh_coarse || c->coarse_age < 0)) {
         c->coarse_age = 0; ++c->coarse_refreshes;
-        // coarse operator Ac = Z^T S Z of this rank's poses, inverted explicitly so that the PCG applies it as a
-        // dense mat-vec; a failed factorisation (cinfo != 0) turns the coarse level off for this solve on the device
-        cudaEvent_t te[4] = {nullptr, nullptr, nullptr, nullptr};
+        // coarse operator (two-level: Ac = Z^T S Z of the aggregates; multilevel: C_l, blockdiag(S_l)^-1 and the dense top
+        // operator), inverted explicitly so that the PCG applies it as a dense mat-vec; a failed inversion (non-positive
+        // pivot) turns the coarse levels off for this solve on the device (F_COARSE = 0)
+        cudaEvent_t te[3] = {nullptr, nullptr, nullptr};
         const bool timing = d.dbg != nullptr;
         if (timing) { for (auto& e : te) cudaEventCreate(&e); cudaEventRecord(te[0], c->stream); }
-        launch_coarse_assemble(d, c->stream);
+        if (d.mlLv) launch_ml_setup(d, c->stream); else launch_coarse_assemble(d, c->stream);
         if (timing) cudaEventRecord(te[1], c->stream);
-        const char* ecs = std::getenv("TSB_COARSE_CUSOLVER");          // 1: cuSOLVER potrf + potrs(I) instead of k_coarse_invert
-        // k_coarse_invert wins at C2 size (0.55 vs 1.32 ms at nc = 888) but scales worse: 26.8 vs 14.4 ms at nc = 4689
-        const bool use_cusolver = (ecs && ecs[0] == '1') || (d.nc > 2304 && !(ecs && ecs[0] == '0'));
-        if (!use_cusolver && launch_coarse_invert(d, c->stream)) {
-            if (timing) {
-                cudaEventRecord(te[2], c->stream); cudaEventSynchronize(te[2]);
-                float a = 0, b = 0; cudaEventElapsedTime(&a, te[0], te[1]); cudaEventElapsedTime(&b, te[1], te[2]);
-                std::fprintf(stderr, "[tsb] coarse setup nc=%u: assemble %.3f ms, k_coarse_invert %.3f ms\n", d.nc, a, b);
-                for (auto& ev : te) cudaEventDestroy(ev);
-            }
-        } else {
-        if (cusolverDnDpotrf(c->solver, CUBLAS_FILL_MODE_LOWER, (int)d.nc, d.Ac, (int)d.nc, c->cwork, c->cwork_len, d.cinfo) != CUSOLVER_STATUS_SUCCESS) {
-            c->err = "cusolverDnDpotrf failed"; return TSB_ECUDA; }
-        if (timing) cudaEventRecord(te[2], c->stream);
-        // inverse = solve against the identity (two triangular solves with nc right-hand sides); potri was 3.5x slower
-        launch_coarse_identity(d, c->stream);
-        if (cusolverDnDpotrs(c->solver, CUBLAS_FILL_MODE_LOWER, (int)d.nc, (int)d.nc, d.Ac, (int)d.nc, d.Ai, (int)d.nc, d.cinfo + 1) != CUSOLVER_STATUS_SUCCESS) {
-            c->err = "cusolverDnDpotrs failed"; return TSB_ECUDA; }
-        launch_coarse_finish(d, c->stream);
+        if (!launch_coarse_invert(d, c->stream)) { c->err = "coarse inverse kernel could not be launched (nc = " + std::to_string(d.nc) + ")"; return TSB_ECUDA; }
         if (timing) {
-            cudaEventRecord(te[3], c->stream); cudaEventSynchronize(te[3]);
-            float a = 0, b = 0, e = 0; cudaEventElapsedTime(&a, te[0], te[1]); cudaEventElapsedTime(&b, te[1], te[2]); cudaEventElapsedTime(&e, te[2], te[3]);
-            std::fprintf(stderr, "[tsb] coarse setup nc=%u: assemble %.3f ms, potrf %.3f ms, potrs(I) %.3f ms\n", d.nc, a, b, e);
+            cudaEventRecord(te[2], c->stream); cudaEventSynchronize(te[2]);
+            float a = 0, b = 0; cudaEventElapsedTime(&a, te[0], te[1]); cudaEventElapsedTime(&b, te[1], te[2]);
+            std::fprintf(stderr, "[tsb] coarse setup nc=%u (%u levels): assemble %.3f ms, k_coarse_invert %.3f ms\n", d.nc, d.mlLv, a, b);
             for (auto& ev : te) cudaEventDestroy(ev);
-        }
         }
     }
     cudaEventRecord(c->ev[4], c->stream);
@@ -339,6 +336,7 @@ int run_solve(tsb_ctx* c, bool refresh_coarse = true, bool smoother = true) {
         return TSB_OK;
     }
     c->pcg_streamed = false;
+    if (d.mlLv) { c->err = "streamed PCG kernel could not be launched"; return TSB_ECUDA; }      // the hierarchy has no other consumer
     // single GPU: the whole PCG and the back-substitution run in one persistent cooperative kernel
     if (c->world <= 1 && !c->force_phased && launch_pcg_persistent(d, c->stream)) {
         if (d.dbg) {
@@ -428,8 +426,8 @@ int tsb_create(const tsb_config* cfg, tsb_ctx** out) {
     for (auto& ev : c->ev) if ((e = cudaEventCreate(&ev)) != cudaSuccess) return fail("cudaEventCreate", e);
     if ((e = cudaMallocHost((void**)&c->h_scal, sizeof(double) * S_COUNT)) != cudaSuccess) return fail("cudaMallocHost", e);
     if ((e = cudaMallocHost((void**)&c->h_flags, sizeof(int) * F_COUNT)) != cudaSuccess) return fail("cudaMallocHost", e);
-    if (cusolverDnCreate(&c->solver) != CUSOLVER_STATUS_SUCCESS || cusolverDnSetStream(c->solver, c->stream) != CUSOLVER_STATUS_SUCCESS) {
-        g_create_error = "cusolverDnCreate failed"; delete c; return TSB_ECUDA; }
+    { const char* e = std::getenv("TSB_ML"); if (e && e[0] == '0') c->ml_top = 0; }
+    { const char* e = std::getenv("TSB_ML_TOP"); if (e && std::atoi(e) >= 8) c->ml_top = std::min<uint32_t>((uint32_t)std::atoi(e), kMlTopMax); }
     if (c->cfg.world > 1) {
         ncclUniqueId id; std::memcpy(&id, cfg->nccl_id, sizeof(id));
         const ncclResult_t r = ncclCommInitRank(&c->comm, c->cfg.world, id, c->cfg.rank);
@@ -453,7 +451,6 @@ void tsb_destroy(tsb_ctx* c) {
     cudaSetDevice(c->cfg.device);
     free_graph(c); release_arena(c);
     if (c->comm) ncclCommDestroy(c->comm);
-    if (c->solver) cusolverDnDestroy(c->solver);
     if (c->h_scal) cudaFreeHost(c->h_scal);
     if (c->h_flags) cudaFreeHost(c->h_flags);
     for (auto& ev : c->ev) if (ev) cudaEventDestroy(ev);
@@ -479,7 +476,11 @@ int tsb_load_wire(tsb_ctx* c, const void* payload, uint32_t nbytes) {
         build_structure(c->g, 0, 1, c->st, res_nb, &c->rp);
         if (c->rp.nb > 0) { c->world = 1; c->rank = 0; return upload_graph(c); }
     }
-    build_structure(c->g, (uint32_t)c->rank, (uint32_t)c->world, c->st, c->world <= 1 ? res_nb : 0, &c->rp);
+    // graphs beyond the resident kernel run the streamed PCG with the multilevel hierarchy (one GPU; the sharded path
+    // and TSB_PCG_PHASED=1 / TSB_ML=0 keep the two-level aggregates)
+    const char* ns = std::getenv("TSB_NO_STREAM");
+    const uint32_t ml_top = (c->world <= 1 && c->use_coarse && !c->force_phased && !(ns && ns[0] == '1')) ? c->ml_top : 0;
+    build_structure(c->g, (uint32_t)c->rank, (uint32_t)c->world, c->st, c->world <= 1 ? res_nb : 0, &c->rp, ml_top);
     return upload_graph(c);
 }
 
@@ -516,13 +517,14 @@ int tsb_host_plan(const void* payload, uint32_t nbytes, int32_t rank, int32_t wo
     if (!payload || !o || world < 1 || rank < 0 || rank >= world) return TSB_EINVAL;
     HostGraph g; Structure st; std::string err;
     if (!parse_wire((const uint8_t*)payload, nbytes, g, err)) { g_create_error = err; return TSB_EPARSE; }
-    build_structure(g, (uint32_t)rank, (uint32_t)world, st);
+    build_structure(g, (uint32_t)rank, (uint32_t)world, st, 0, nullptr, world <= 1 ? kMlTopDefault : 0);
     std::memset(o, 0, sizeof(*o));
     o->n_pose = g.P; o->n_lm = g.L; o->n_odom = g.Eo; o->n_lmedge = g.El; o->n_fixed = (uint32_t)g.fixed.size();
     o->dim = 3 * g.P + 2 * g.L; o->pose_begin = st.pose_begin; o->pose_end = st.pose_end;
     o->n_lmedge_local = (uint32_t)st.lm_perm.size(); o->n_odom_local = st.n_od_owned;
     o->n_chunks = (uint32_t)st.chunks.size(); o->n_blocks = (uint32_t)st.blk_chunk_ptr.size() - 1; o->n_slots = (uint32_t)st.slot_lm.size();
     o->n_aggregates = st.nA;
+    o->n_ml_levels = (uint32_t)st.ml.size(); o->n_ml_top = st.ml.empty() ? 0 : st.ml.back().n;
     if (n_ghost) *n_ghost = st.nG;
     if (n_boundary) *n_boundary = (uint32_t)st.boundary.size();
     if (structure_hash) {            // FNV-1a over the rank-independent parts (cuts, boundary list): must agree on all ranks
@@ -542,6 +544,7 @@ int tsb_get_counts(const tsb_ctx* c, tsb_counts* o) {
     o->n_chunks = c->d.nChunks; o->n_blocks = c->d.nBlocks; o->n_slots = c->d.nSlots;
     o->pcg_path = c->d.res_nb ? 1u : c->pcg_streamed ? 3u : (c->world <= 1 && !c->force_phased ? 0u : 2u);
     o->replicated = (c->cfg.world > 1 && c->world == 1) ? 1u : 0u; o->n_aggregates = c->d.nA;
+    o->n_ml_levels = c->d.mlLv; o->n_ml_top = c->d.mlLv ? c->d.ml[c->d.mlLv - 1].n : 0;
     return TSB_OK;
 }
 
@@ -608,6 +611,9 @@ int tsb_optimize(tsb_ctx* c, uint32_t iterations, tsb_report* rep, tsb_iter_stat
     c->coarse_age = -1; c->coarse_hold = 4; c->coarse_backoff = 1;
     int64_t pcg_total = 0; float ms_lin = 0, ms_sol = 0, ms_pcg = 0; const int refreshes0 = c->coarse_refreshes;
     bool sb_on = true; int sb_last_iters = 0;
+    int not_conv = 0, coarse_fail = 0, singular = 0;
+    const int maxit = c->cfg.pcg_max_iters > 0 ? c->cfg.pcg_max_iters : 4000;
+    CU(cudaMemsetAsync(c->d.flags + F_SING, 0, sizeof(int), c->stream));
     CU(cudaEventRecord(c->ev[3], c->stream));
     for (uint32_t it = 0; it < iterations; ++it) {
         CU(cudaEventRecord(c->ev[0], c->stream));
@@ -650,6 +656,11 @@ int tsb_optimize(tsb_ctx* c, uint32_t iterations, tsb_report* rep, tsb_iter_stat
         TRY(fetch_scalars(c));
         CU(cudaGetLastError());
         err = c->h_scal[S_CHI2];
+        // the solve is only as good as its PCG: count the ones that stopped at the cap or lost the residual
+        const bool bad_pcg = c->h_flags[F_ITERS] >= maxit || !std::isfinite(c->h_scal[S_RZ]);
+        if (bad_pcg) { ++not_conv; if (c->cfg.verbose) std::printf("warning: PCG stopped after %d iterations, residual %g\n", c->h_flags[F_ITERS], c->h_scal[S_RZ]); }
+        if (c->use_coarse && c->d.nc && !c->h_flags[F_COARSE]) ++coarse_fail;
+        if (c->h_flags[F_SING]) { ++singular; CU(cudaMemsetAsync(c->d.flags + F_SING, 0, sizeof(int), c->stream)); }
         const double dnorm = std::sqrt(c->h_scal[S_DELTA2] + c->h_scal[S_DELTA2L]);
         float a = 0, b = 0;
         CU(cudaEventElapsedTime(&a, c->ev[0], c->ev[1])); CU(cudaEventElapsedTime(&b, c->ev[1], c->ev[2]));
@@ -672,6 +683,7 @@ int tsb_optimize(tsb_ctx* c, uint32_t iterations, tsb_report* rep, tsb_iter_stat
     if (rep) { rep->iterations_run = (int32_t)done; rep->exit_code = code; rep->final_chi2 = err; rep->pcg_iters_total = pcg_total;
         rep->kernel_launches = (int64_t)(g_launches - launches0); rep->ms_linearize_total = ms_lin; rep->ms_solve_total = ms_sol;
         rep->ms_pcg_total = ms_pcg; rep->coarse_refreshes = c->coarse_refreshes - refreshes0;
+        rep->pcg_not_converged = not_conv; rep->coarse_failures = coarse_fail; rep->singular_blocks = singular;
         CU(cudaEventElapsedTime(&rep->ms_total, c->ev[3], c->ev[2])); }
     return TSB_OK;
 }

@@ -10,14 +10,26 @@ constexpr int kThreads = 256;          // threads per block of the chunked kerne
 #ifndef TSB_HPL_PLANES
 #define TSB_HPL_PLANES 1              // Hpl as three planes of nE double2 (1) or 3x2 per edge (0)
 #endif
-constexpr uint32_t kCoarseScratchBlocks = 3 * kCoarseMaxAggLarge / (kThreads / 32);   // blocks that can own coarse rows (one row per warp at least)
+constexpr uint32_t kCoarseScratchBlocks = 1024;   // upper bound on the blocks of a persistent PCG kernel (each owns a scratch row of nc doubles in Dev::rcs)
 constexpr int kStageRows = 9;          // values staged per LM edge
 constexpr int kStageStride = kChunkEdges + 1;   // odd stride in doubles: rows land in different banks
 
 // scalars kept on the device (index into Dev::scal)
 enum Scal { S_CHI2 = 0, S_RZ0, S_RZ, S_PSP, S_ALPHA, S_BETA, S_DELTA2, S_DELTA2L, S_TOL2, S_RZNEW, S_COUNT };
 // integer flags (index into Dev::flags)
-enum Flag { F_DONE = 0, F_ITERS, F_MAXIT, F_COARSE, F_COUNT };   // F_COARSE: 1 = coarse inverse valid for this solve
+enum Flag { F_DONE = 0, F_ITERS, F_MAXIT, F_COARSE, F_SING, F_COUNT };   // F_COARSE: 1 = coarse inverse valid for this solve; F_SING: a singular vertex block was zeroed
+
+// one level of the multilevel hierarchy (host_graph.h MlLevel) on the device
+struct MlDev {
+    uint32_t n, ratio, spacing, nnz;
+    uint32_t slots, cdot_off;                 // upper levels: partial sums per window; first entry of the level in Dev::cdot
+    const uint32_t* node_ptr; const uint32_t* edge_lm; const uint32_t* ref_ptr; const uint32_t* ref;
+    double* C;                                // C_l = Z^T Hpl: three planes of nnz double2, like Dev::hpl
+    double* dinv;                             // 6 per node: inverse of the diagonal block of S_l (not on the top level)
+    double* m;                                // 3 per node: restricted residual as (force x, force y, moment about the origin)
+    double* g;                                // 3 per node: correction (e_x + Y e_t, e_y - X e_t, e_t), prolongated with scalar hat weights
+    double* wpart;                            // upper levels: nWin x slots x 3 partial sums of m
+};
 
 struct Dev {
     uint32_t nP, nG, L, nE, nO, nOwned, nChunks, nBlocks, nSlots;
@@ -95,6 +107,12 @@ struct Dev {
     uint32_t* cbar;             // grid-barrier counter of k_coarse_invert
     int* cinfo;                 // potrf / potrs status words
     long long* dbg;             // optional: 8 phase-cycle counters of the persistent PCG kernel (TSB_PCG_TIMING=1)
+    // multilevel preconditioner of the streamed PCG (mlLv > 0): M^-1 = blockdiag(S)^-1 + sum_l Z_l blockdiag(S_l)^-1 Z_l^T
+    //   + Z_top S_top^-1 Z_top^T; the top level uses Ac / Ai / yc / cdot above with nc = 3 * ml[mlLv - 1].n
+    uint32_t mlLv, mlLocal, mlWin, mlCdot;   // levels, window-local levels, restriction windows, entries of cdot
+    const uint32_t* tl_ptr; const uint32_t* tl_edge; const uint32_t* tl_node;   // landmark-major CSR over the top level's coarse edges
+    double* r2;                 // second residual buffer (the restriction recomputes halo poses: r ping-pongs between r and r2)
+    MlDev ml[kMlMaxLevels];
 };
 
 // kernel launchers (kernels.cu).  All take the launching stream.
@@ -103,10 +121,9 @@ void launch_lm_sum(const Dev& d, bool finalize, cudaStream_t s);   // K2a: landm
 void launch_lm_finalize(const Dev& d, cudaStream_t s);          // K2b: Hll, b_l, prior, Hll^-1; chi2
 void launch_schur_prep(const Dev& d, cudaStream_t s);           // K3: diag(S)^-1 and reduced rhs
 void launch_coarse_assemble(const Dev& d, cudaStream_t s);      // zoff, C, Ac = Z^T S Z (dense, deterministic)
-void launch_coarse_identity(const Dev& d, cudaStream_t s);      // Ai = I (right-hand side of the inverse solve)
+void launch_ml_setup(const Dev& d, cudaStream_t s);             // multilevel: C_l, blockdiag(S_l)^-1, dense top operator into Ac
 bool launch_pcg_stream(const Dev& d, cudaStream_t s);           // streamed persistent PCG (no back-substitution)
 bool launch_coarse_invert(const Dev& d, cudaStream_t s);        // Ai = Ac^-1 + F_COARSE, one cooperative launch (blocked Gauss-Jordan)
-void launch_coarse_finish(const Dev& d, cudaStream_t s);        // set F_COARSE from cinfo
 void launch_pcg_coarse(const Dev& d, int init, cudaStream_t s);           // yc = Ac^-1 Z^T r, cdot (phased path)
 bool launch_pcg_persistent(const Dev& d, cudaStream_t s);     // whole PCG + back-substitution, one cooperative launch
 bool launch_sb_build(const Dev& d, cudaStream_t s);           // smoother-block inverses of the resident kernel (needs minv, hinv: after launch_schur_prep)

@@ -37,6 +37,23 @@ void encode_reply(const HostGraph& g, const double* pose_xyt, const double* lm_x
 
 struct ChunkDesc { uint32_t e0, e1, p0, p1, s0, s1, block, flags; };
 
+// ---- multilevel coarse hierarchy of the streamed PCG (HBM-sized graphs) -----------------------------------------
+// Level l >= 1 has one node per `spacing` consecutive local poses (node K sits at local pose K * spacing); a vector on
+// level l is interpolated to the poses LINEARLY along the trajectory (hat functions) as rigid-body motions about the
+// node's pose.  The landmarks are kept on every level, so S_l = App_l - C_l Hll^-1 C_l^T is the Galerkin operator
+// Z^T S Z and C_l (one 3x2 block per distinct (node, landmark) pair: a "coarse edge") is a weighted sum of the blocks
+// of the level below.  All integer structure; built once per request.
+constexpr uint32_t kMlMaxLevels = 10;
+constexpr uint32_t kMlWindow = 448;     // poses whose residual one block restricts at a time (7 x 64) + 64 halo poses = 512 threads
+constexpr uint32_t kMlHalo = 64;
+struct MlLevel {
+    uint32_t n = 0, ratio = 4, spacing = 4;      // nodes, nodes of the level below per node interval, poses per node interval
+    std::vector<uint32_t> node_ptr;              // n + 1 offsets into edge_lm: coarse edges of a node, landmark ascending
+    std::vector<uint32_t> edge_lm;               // landmark of each coarse edge
+    std::vector<uint32_t> ref_ptr;               // nnz + 1 offsets into ref
+    std::vector<uint32_t> ref;                   // child edge index (level below; level 1: LM edge in assembly order) << 4 | (child - ratio * K + 7)
+};
+
 // Assembly structure of one rank (all integer; compared bit-exactly in tests).
 struct Structure {
     uint32_t pose_begin = 0, pose_end = 0;   // canonical pose range owned by this rank
@@ -79,6 +96,9 @@ struct Structure {
     std::vector<uint32_t> aslot_ptr, aslot_edge;    // nAS + 1 offsets into aslot_edge (assembly edge index, ascending)
     std::vector<uint32_t> cpair_a, cpair_b, cpair_ptr;   // coarse block pairs (a, b) sharing a landmark; offsets into ctrip
     std::vector<uint32_t> ctrip;             // 2 per triple: (aslot of a, aslot of b) with the same landmark, landmark ascending
+    // ---- multilevel hierarchy (replaces the aggregates above for graphs that run the streamed PCG) -------------------
+    std::vector<MlLevel> ml;                 // ml[0] = level 1; the last level is solved exactly (dense inverse)
+    uint32_t ml_local = 0;                   // levels 1..ml_local are restricted inside a window (ratio 4, spacing <= 64)
 };
 // ---- resident plan (world == 1, graphs whose Hpl fits the shared memory of the whole GPU) -----------------
 // One block per SM owns a contiguous pose range with all its LM edges (assembly order) and a contiguous landmark
@@ -99,15 +119,20 @@ constexpr uint32_t kResOdomCap = 384;     // ODOM neighbour entries per block
 constexpr uint32_t kSbCap = 48;           // poses per smoother block of the resident kernel (dense 144 x 144 inverse)
 constexpr uint32_t kSbPerBlock = 2;       // smoother blocks per resident block
 constexpr uint32_t kCoarseMaxAgg = 512;   // aggregates whose coarse residual (3 doubles each) fits the shared memory the PCG kernels set aside for it
-constexpr uint32_t kCoarseMaxAggLarge = 2048;   // upper bound on aggregates per rank (the coarse matrix is dense: (3*2048)^2 doubles = 302 MB);
-                                                // above kCoarseMaxAgg the coarse residual lives in per-block global scratch (Dev::rcs)
+constexpr uint32_t kCoarseMaxAggLarge = 768;    // upper bound on aggregates per rank of the two-level method (dense coarse matrix, inverted by
+                                                // k_coarse_invert: nc <= 4736); above kCoarseMaxAgg the coarse residual lives in per-block global
+                                                // scratch (Dev::rcs).  HBM-sized graphs use the multilevel hierarchy (MlLevel) instead
+constexpr uint32_t kMlTopDefault = 1024;        // nodes of the exactly-solved top level of the hierarchy (nc = 3072: 75 MB inverse)
+constexpr uint32_t kMlTopMax = 1536;            // k_coarse_invert handles nc <= 32 * 148
 
 constexpr uint32_t kChunkEdges = 512;   // LM edges staged per chunk
 constexpr uint32_t kBlockPoses = 128;   // poses per thread block (upper bound)
 
 // resident_blocks > 0 (world == 1): try to lay the graph out for the shared-memory-resident PCG kernel with that many
 // blocks; `rp.nb` stays 0 when it does not fit and the uniform aggregates (agg_K) are used instead
+// ml_top > 0: a graph that does not fit the resident plan gets the multilevel hierarchy (top level <= ml_top nodes)
+// instead of the uniform aggregates
 void build_structure(const HostGraph& g, uint32_t rank, uint32_t world, Structure& s, uint32_t resident_blocks = 0,
-                     ResidentPlan* rp = nullptr);
+                     ResidentPlan* rp = nullptr, uint32_t ml_top = 0);
 
 }  // namespace tsb

@@ -97,6 +97,20 @@ __device__ __forceinline__ double reduce_all(const double* part, uint32_t n, dou
     return r;
 }
 
+// guarded inverse of a symmetric 3x3 block (00 01 02 11 12 22); a singular / non-finite block gives the zero block:
+// that vertex then takes no correction from this level (the dense QR of the reference leaves such unknowns at zero)
+__device__ __forceinline__ bool sym3_inverse(const double s00, const double s01, const double s02, const double s11, const double s12,
+                                             const double s22, double* M) {
+    const double c00 = s11 * s22 - s12 * s12, c01 = s02 * s12 - s01 * s22, c02 = s01 * s12 - s02 * s11;
+    const double det = s00 * c00 + s01 * c01 + s02 * c02;
+    const double scale = fabs(s00 * s11 * s22);
+    if (!(det > 1e-13 * scale) || !isfinite(det)) { M[0] = M[1] = M[2] = M[3] = M[4] = M[5] = 0; return false; }
+    const double id = 1.0 / det;
+    M[0] = c00 * id; M[1] = c01 * id; M[2] = c02 * id;
+    M[3] = (s00 * s22 - s02 * s02) * id; M[4] = (s01 * s02 - s00 * s12) * id; M[5] = (s00 * s11 - s01 * s01) * id;
+    return true;
+}
+
 // Huber on chi2 with delta = 1.5 (OptimizerCpu.h:36-46)
 __device__ __forceinline__ void robustify(double chi2, double& rho, double& w) {
     if (chi2 <= 2.25) { rho = chi2; w = 1.0; }
@@ -304,7 +318,12 @@ __device__ __forceinline__ void lm_finalize_one(const Dev& d, uint32_t l, double
     const double h00 = a0 + prior, h01 = a1, h11 = a2 + prior;
     d.hll[3ull * l] = h00; d.hll[3ull * l + 1] = h01; d.hll[3ull * l + 2] = h11;
     d.bl[2ull * l] = -a3; d.bl[2ull * l + 1] = -a4;               // b_l -= B^T W e
-    const double id = 1.0 / (h00 * h11 - h01 * h01);
+    // a landmark without (effective) observations has a singular block: it keeps delta = 0, as the rank-revealing QR of
+    // the reference leaves an unconstrained unknown (SolverEigen.h:20); counted in tsb_report.singular_blocks
+    const double det = h00 * h11 - h01 * h01;
+    if (!(det > 1e-13 * fabs(h00 * h11)) || !isfinite(det)) {
+        d.hinv[3ull * l] = 0; d.hinv[3ull * l + 1] = 0; d.hinv[3ull * l + 2] = 0; d.flags[F_SING] = 1; return; }
+    const double id = 1.0 / det;
     d.hinv[3ull * l] = h11 * id; d.hinv[3ull * l + 1] = -h01 * id; d.hinv[3ull * l + 2] = h00 * id;
 }
 
@@ -401,12 +420,8 @@ __global__ void __launch_bounds__(kThreads, 3) k_schur_prep(const Dev d) {
         const uint32_t p = p0 + i;
         const double* H = d.hpp + 6ull * p;
         const double s00 = H[0] - a[0], s01 = H[1] - a[1], s02 = H[2] - a[2], s11 = H[3] - a[3], s12 = H[4] - a[4], s22 = H[5] - a[5];
-        // symmetric 3x3 inverse by cofactors
-        const double c00 = s11 * s22 - s12 * s12, c01 = s02 * s12 - s01 * s22, c02 = s01 * s12 - s02 * s11;
-        const double id = 1.0 / (s00 * c00 + s01 * c01 + s02 * c02);
-        double* M = d.minv + 6ull * p;
-        M[0] = c00 * id; M[1] = c01 * id; M[2] = c02 * id;
-        M[3] = (s00 * s22 - s02 * s02) * id; M[4] = (s01 * s02 - s00 * s12) * id; M[5] = (s00 * s11 - s01 * s01) * id;
+        // symmetric 3x3 inverse by cofactors; an unconstrained pose (no edge, not fixed) gets the zero block: delta = 0
+        if (!sym3_inverse(s00, s01, s02, s11, s12, s22, d.minv + 6ull * p)) d.flags[F_SING] = 1;
         d.rhs[3ull * p] = d.bp[3ull * p] - a[6]; d.rhs[3ull * p + 1] = d.bp[3ull * p + 1] - a[7]; d.rhs[3ull * p + 2] = d.bp[3ull * p + 2] - a[8];
     }
 }
@@ -606,13 +621,10 @@ __device__ __forceinline__ double coarse_restrict(const Dev& d, uint32_t k) {
     return t;
 }
 // `shared_rc`: Z^T r was left in d.rcs[0 .. nc) by a preceding launch (k_pcg_restrict, phased path, large coarse spaces)
-__device__ __forceinline__ void coarse_phase(const Dev& d, uint32_t gwarp, uint32_t nwarps, double* rc_smem, bool shared_rc = false) {
+// yc = Ai rc_s and cdot_j = yc_j rc_s_j; rc_s holds the coarse residual (shared memory for nc <= 3 kCoarseMaxAgg, else a
+// global scratch row); rc_smem: the block's shared scratch (reduction space in the large mode)
+__device__ __forceinline__ void coarse_matvec(const Dev& d, uint32_t gwarp, uint32_t nwarps, const double* rc_s, double* rc_smem) {
     const uint32_t nc = d.nc;
-    double* rc_s = nc <= 3 * kCoarseMaxAgg ? rc_smem : shared_rc ? d.rcs : d.rcs + (size_t)blockIdx.x * nc;
-    if (!(shared_rc && nc > 3 * kCoarseMaxAgg)) {
-        for (uint32_t k = threadIdx.x; k < nc; k += blockDim.x) rc_s[k] = coarse_restrict(d, k);
-        __syncthreads();
-    }
     const uint32_t lane = threadIdx.x & 31;
     if (nc > 3 * kCoarseMaxAgg) {
         // Large coarse space (Ai = 100-300 MB, streamed from HBM every iteration): a warp per row leaves one 47 KB row
@@ -660,6 +672,15 @@ __device__ __forceinline__ void coarse_phase(const Dev& d, uint32_t gwarp, uint3
         if (lane == 0) { d.yc[j] = t; d.cdot[j] = t * rc_s[j]; }
     }
     __syncthreads();
+}
+__device__ __forceinline__ void coarse_phase(const Dev& d, uint32_t gwarp, uint32_t nwarps, double* rc_smem, bool shared_rc = false) {
+    const uint32_t nc = d.nc;
+    double* rc_s = nc <= 3 * kCoarseMaxAgg ? rc_smem : shared_rc ? d.rcs : d.rcs + (size_t)blockIdx.x * nc;
+    if (!(shared_rc && nc > 3 * kCoarseMaxAgg)) {
+        for (uint32_t k = threadIdx.x; k < nc; k += blockDim.x) rc_s[k] = coarse_restrict(d, k);
+        __syncthreads();
+    }
+    coarse_matvec(d, gwarp, nwarps, rc_s, rc_smem);
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -757,16 +778,6 @@ __global__ void k_coarse_lm(const Dev d) {
     for (int r = 0; r < 3; ++r)
 #pragma unroll
         for (int c = 0; c < 3; ++c) blk[(size_t)r * d.nc + c] -= acc[3 * r + c];
-}
-
-__global__ void k_coarse_identity(const Dev d) {
-    const size_t n = d.nc, tot = n * n;
-    for (size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x; idx < tot; idx += (size_t)gridDim.x * blockDim.x)
-        d.Ai[idx] = (idx / n == idx % n) ? 1.0 : 0.0;
-}
-// after potrf + potrs: publish whether the coarse inverse is usable for this solve
-__global__ void k_coarse_finish(const Dev d) {
-    if (threadIdx.x == 0) d.flags[F_COARSE] = (d.cinfo[0] == 0 && d.cinfo[1] == 0) ? 1 : 0;
 }
 
 // ---- one launch per phase (used when collectives sit between the phases, world > 1) -------------------
@@ -960,6 +971,7 @@ __global__ void __launch_bounds__(kThreads, 3) k_pcg_persistent(const Dev d) {
 #include "sblock_smoother.cuh"
 #include "pcg_resident.cuh"
 #include "coarse_invert.cuh"
+#include "mlevel.cuh"
 #include "pcg_stream.cuh"
 
 // delta_l = Hll^-1 (b_l - Hpl^T delta_p); w_sum holds Hpl^T delta_p
@@ -1113,8 +1125,8 @@ bool launch_pcg_stream(const Dev& d, cudaStream_t s) {
     }
     uint32_t min_units = 4u * (uint32_t)blocks;
     { const char* e = getenv("TSB_STREAM_MIN_UNITS"); if (e) min_units = (uint32_t)atoi(e);
-      e = getenv("TSB_NO_STREAM"); if (e && e[0] == '1') return false; }
-    if (blocks <= 0 || !d.gbar || !d.nBlocks || d.nBlocks < min_units) return false;
+      e = getenv("TSB_NO_STREAM"); if (e && e[0] == '1' && !d.mlLv) return false; }
+    if (blocks <= 0 || !d.gbar || !d.nBlocks || (d.nBlocks < min_units && !d.mlLv)) return false;     // a graph with the multilevel hierarchy always streams
     Dev dd = d; void* args[] = {&dd};
     cudaMemsetAsync(dd.gbar, 0, sizeof(uint32_t), s);
     const uint32_t grid = d.nBlocks < (uint32_t)blocks ? d.nBlocks : (uint32_t)blocks;
@@ -1130,7 +1142,21 @@ void launch_coarse_assemble(const Dev& d, cudaStream_t s) {
     k_coarse_pose<<<cdiv(d.nA * 32, kThreads), kThreads, 0, s>>>(d); ++g_launches;
     if (d.nPairs) { k_coarse_lm<<<cdiv(d.nPairs, 128), 128, 0, s>>>(d); ++g_launches; }
 }
-// Ai = Ac^-1 and F_COARSE in one cooperative launch; false: not launchable here (the caller uses cuSOLVER)
+// multilevel setup (mlevel.cuh): C_l level by level, blockdiag(S_l)^-1 below the top, the dense top operator into Ac
+void launch_ml_setup(const Dev& d, cudaStream_t s) {
+    if (!d.mlLv) return;
+    static size_t top_smem = 0;
+    for (uint32_t l = 0; l < d.mlLv; ++l) {
+        const uint32_t nb = cdiv(d.ml[l].n * 32, 256);
+        if (l == 0) k_ml_C<true><<<nb, 256, 0, s>>>(d, 0); else k_ml_C<false><<<nb, 256, 0, s>>>(d, (int)l);
+        ++g_launches;
+        if (l + 1 < d.mlLv) { k_ml_D<<<nb, 256, 0, s>>>(d, (int)l); ++g_launches; }
+    }
+    const size_t smem = sizeof(double) * 3 * d.nc;
+    if (smem > top_smem) { cudaFuncSetAttribute(k_ml_top, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); top_smem = smem; }
+    k_ml_top<<<d.ml[d.mlLv - 1].n, kMlTopThreads, smem, s>>>(d, d.tl_ptr, d.tl_edge, d.tl_node); ++g_launches;
+}
+// Ai = Ac^-1 and F_COARSE in one cooperative launch; false: not launchable here
 bool launch_coarse_invert(const Dev& d, cudaStream_t s) {
     static int blocks = -1;
     if (blocks < 0) {
@@ -1150,8 +1176,6 @@ bool launch_coarse_invert(const Dev& d, cudaStream_t s) {
     ++g_launches;
     return true;
 }
-void launch_coarse_identity(const Dev& d, cudaStream_t s) { k_coarse_identity<<<148 * 4, kThreads, 0, s>>>(d); ++g_launches; }
-void launch_coarse_finish(const Dev& d, cudaStream_t s) { k_coarse_finish<<<1, 32, 0, s>>>(d); ++g_launches; }
 void launch_pcg_coarse(const Dev& d, int init, cudaStream_t s) {
     if (!d.nc) return;
     if (d.nc > 3 * kCoarseMaxAgg) {          // block-per-4-rows mat-vec: one block per SM-slot is enough, the rows stream from HBM

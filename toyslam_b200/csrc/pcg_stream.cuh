@@ -79,6 +79,14 @@ __device__ __forceinline__ void ps_pass_a(const Dev& d, unsigned char* smem, uin
     // dependent global loads (aggregate -> yc), which inside the chunk loop stalled the block once per chunk
     {
         const uint32_t p_lo = cur.p0, p_hi = d.chunks[ce - 1].p1;
+        if (coarse && d.mlLv) {         // multilevel: one thread per pose gathers the hat-weighted node corrections of every level
+            for (uint32_t i = p_lo + tid; i < p_hi; i += kPsThreads) {
+                const double4 ps = d.pose[i];
+                double c0, c1, c2; ml_prolong(d, i, ps.x, ps.y, c0, c1, c2);
+                double* pp = d.p + 3ull * i; const double* zz = d.z + 3ull * i;
+                pp[0] = (zz[0] + c0) + beta * pp[0]; pp[1] = (zz[1] + c1) + beta * pp[1]; pp[2] = (zz[2] + c2) + beta * pp[2];
+            }
+        } else
         for (uint32_t i = tid; i < 3 * (p_hi - p_lo); i += kPsThreads) d.p[3ull * p_lo + i] = ps_pnew(d, p_lo, i, beta, coarse);
     }
     __syncthreads();
@@ -234,18 +242,25 @@ __global__ void __launch_bounds__(kPsThreads, 2) k_pcg_stream(const Dev d) {
     }
     __syncthreads();
     const bool coarse = d.flags[F_COARSE] != 0;
+    const bool ml = coarse && d.mlLv > 0;                            // multilevel preconditioner (mlevel.cuh)
     const bool crow = coarse && blockIdx.x * (kPsThreads / 32) < d.nc;
+    const uint32_t ncdot = ml ? d.mlCdot : d.nc;
+    double* ml_sm = reinterpret_cast<double*>(smem_raw + kPsRing);   // the ring is idle during the pose phase
+    double* rbuf[2] = {d.r, ml ? d.r2 : d.r};
     double dot = 0;
-    const bool rc_shared = ps_pose_phase<true>(d, 0.0, coarse, dot);
+    bool rc_shared = false;
+    if (ml) dot = ml_pose_phase<true>(d, ml_sm, 0.0, rbuf[0], rbuf[0]);
+    else rc_shared = ps_pose_phase<true>(d, 0.0, coarse, dot);
     double t = block_sum(dot, red);
     if (tid == 0) d.part[blockIdx.x] = t;
     res_gsync(grid, d.gbar, gtarget);
     if (coarse) {
-        if (crow) coarse_phase(d, gtid >> 5, gsz >> 5, rc_s, rc_shared);
+        if (ml) ml_coarse_phase(d, gtid, gsz, rc_s, crow);
+        else if (crow) coarse_phase(d, gtid >> 5, gsz >> 5, rc_s, rc_shared);
         res_gsync(grid, d.gbar, gtarget);
     }
     double rz0 = reduce_all(d.part, nb, red);
-    if (coarse) rz0 += reduce_all(d.cdot, d.nc, red);
+    if (coarse) rz0 += reduce_all(d.cdot, ncdot, red);
     double rz = rz0, beta = 0;
     const double tol2 = d.scal[S_TOL2]; const int maxit = d.flags[F_MAXIT];
     int it = 0;
@@ -274,18 +289,20 @@ __global__ void __launch_bounds__(kPsThreads, 2) k_pcg_stream(const Dev d) {
             res_gsync(grid, d.gbar, gtarget);
             TICK(5);
             const double alpha = rz / reduce_all(d.part2, nb, red);
-            ps_pose_phase<false>(d, alpha, coarse, dot);
+            if (ml) dot = ml_pose_phase<false>(d, ml_sm, alpha, rbuf[it & 1], rbuf[(it + 1) & 1]);
+            else ps_pose_phase<false>(d, alpha, coarse, dot);
             t = block_sum(dot, red);
             if (tid == 0) d.part[blockIdx.x] = t;
             TICK(6);
             res_gsync(grid, d.gbar, gtarget);
             if (coarse) {
-                if (crow) coarse_phase(d, gtid >> 5, gsz >> 5, rc_s, rc_shared);
+                if (ml) ml_coarse_phase(d, gtid, gsz, rc_s, crow);
+                else if (crow) coarse_phase(d, gtid >> 5, gsz >> 5, rc_s, rc_shared);
                 res_gsync(grid, d.gbar, gtarget);
             }
             TICK(7);
             double rz_new = reduce_all(d.part, nb, red);
-            if (coarse) rz_new += reduce_all(d.cdot, d.nc, red);
+            if (coarse) rz_new += reduce_all(d.cdot, ncdot, red);
             beta = rz_new / rz; rz = rz_new; ++it;
             if (!(rz_new > tol2 * rz0) || it >= maxit) break;
         }

@@ -9,10 +9,90 @@
 
 #include <algorithm>
 #include <numeric>
+#ifdef _OPENMP
+#include <omp.h>
+#endif
 
 namespace tsb {
 
-void build_structure(const HostGraph& g, uint32_t rank, uint32_t world, Structure& s, uint32_t resident_blocks, ResidentPlan* rp) {
+namespace {
+
+// One level of the hierarchy from the level below (child nodes with their landmark-sorted edge lists).
+// Parent K interpolates to the children ratio*K - (ratio-1) .. ratio*K + (ratio-1); its coarse edges are the distinct
+// landmarks of those children, each with the list of child edges it sums (ascending child edge index).
+void build_ml_level(const std::vector<uint32_t>& cptr, const std::vector<uint32_t>& clm, uint32_t ratio, uint32_t spacing, MlLevel& lv) {
+    const uint32_t nc = (uint32_t)cptr.size() - 1, n = (nc + ratio - 1) / ratio;
+    lv.n = n; lv.ratio = ratio; lv.spacing = spacing;
+    lv.node_ptr.assign(n + 1, 0);
+    int nt = 1;
+#ifdef _OPENMP
+    nt = omp_get_max_threads();
+#endif
+    nt = std::max(1, std::min<int>(nt, (int)(n / 64 + 1)));
+    std::vector<std::vector<uint32_t>> t_lm(nt), t_cnt(nt), t_ref(nt);
+    std::vector<uint32_t> t_lo(nt + 1);
+    for (int t = 0; t <= nt; ++t) t_lo[t] = (uint32_t)((uint64_t)n * t / nt);
+#pragma omp parallel for num_threads(nt) schedule(static, 1)
+    for (int t = 0; t < nt; ++t) {
+        std::vector<uint64_t> tmp;
+        auto& olm = t_lm[t]; auto& ocnt = t_cnt[t]; auto& oref = t_ref[t];
+        for (uint32_t K = t_lo[t]; K < t_lo[t + 1]; ++K) {
+            const uint32_t k_lo = ratio * K >= ratio - 1 ? ratio * K - (ratio - 1) : 0;
+            const uint32_t k_hi = std::min<uint64_t>(nc - 1, (uint64_t)ratio * K + ratio - 1);
+            tmp.clear();
+            for (uint32_t k = k_lo; k <= k_hi; ++k)
+                for (uint32_t e = cptr[k]; e < cptr[k + 1]; ++e)
+                    tmp.push_back(((uint64_t)clm[e] << 32) | ((uint64_t)e << 4) | (uint64_t)(k + 7 - ratio * K));
+            std::sort(tmp.begin(), tmp.end());
+            uint32_t ne = 0;
+            for (size_t q = 0; q < tmp.size(); ++q) {
+                const uint32_t l = (uint32_t)(tmp[q] >> 32);
+                if (q == 0 || l != (uint32_t)(tmp[q - 1] >> 32)) { olm.push_back(l); ocnt.push_back(0); ++ne; }
+                ocnt.back()++; oref.push_back((uint32_t)tmp[q]);
+            }
+            lv.node_ptr[K + 1] = ne;
+        }
+    }
+    for (uint32_t K = 0; K < n; ++K) lv.node_ptr[K + 1] += lv.node_ptr[K];
+    const uint32_t nnz = lv.node_ptr[n];
+    lv.edge_lm.resize(nnz); lv.ref_ptr.assign(nnz + 1, 0);
+    size_t nref = 0; for (int t = 0; t < nt; ++t) nref += t_ref[t].size();
+    lv.ref.resize(nref);
+    std::vector<size_t> e_off(nt + 1, 0), r_off(nt + 1, 0);
+    for (int t = 0; t < nt; ++t) { e_off[t + 1] = e_off[t] + t_lm[t].size(); r_off[t + 1] = r_off[t] + t_ref[t].size(); }
+#pragma omp parallel for num_threads(nt) schedule(static, 1)
+    for (int t = 0; t < nt; ++t) {
+        std::copy(t_lm[t].begin(), t_lm[t].end(), lv.edge_lm.begin() + e_off[t]);
+        std::copy(t_ref[t].begin(), t_ref[t].end(), lv.ref.begin() + r_off[t]);
+        size_t r = r_off[t];
+        for (size_t q = 0; q < t_cnt[t].size(); ++q) { r += t_cnt[t][q]; lv.ref_ptr[e_off[t] + q + 1] = (uint32_t)r; }
+    }
+}
+
+// Hierarchy over the nP local poses: ratio 4 per level (a final ratio of 2 where 4 would leave the exactly-solved top
+// level with fewer than top_max / 2 nodes); no level at all for graphs with <= 64 poses (block-Jacobi is enough there).
+void build_hierarchy(Structure& s, const std::vector<uint32_t>& elm, uint32_t top_max) {
+    s.ml.clear(); s.ml_local = 0;
+    s.ml.reserve(kMlMaxLevels);                  // the loop keeps pointers into the previous level
+    const uint32_t nP = s.nP;
+    if (nP <= 64 || top_max < 8) return;
+    uint32_t n = nP, spacing = 1;
+    const std::vector<uint32_t>* cptr = &s.pose_ptr; const std::vector<uint32_t>* clm = &elm;
+    bool first = true;
+    while ((first || n > top_max) && s.ml.size() < kMlMaxLevels) {
+        const uint32_t ratio = (!first && (n + 1) / 2 <= top_max) ? 2u : 4u;
+        spacing *= ratio;
+        s.ml.emplace_back();
+        build_ml_level(*cptr, *clm, ratio, spacing, s.ml.back());
+        if (ratio == 4 && spacing <= kMlHalo && s.ml_local + 1 == s.ml.size()) s.ml_local = (uint32_t)s.ml.size();
+        n = s.ml.back().n; cptr = &s.ml.back().node_ptr; clm = &s.ml.back().edge_lm; first = false;
+    }
+}
+
+}  // namespace
+
+void build_structure(const HostGraph& g, uint32_t rank, uint32_t world, Structure& s, uint32_t resident_blocks, ResidentPlan* rp,
+                     uint32_t ml_top) {
     s = Structure();
     const uint32_t P = g.P, L = g.L;
     // ---- pose partition: contiguous ranges balanced by edge work --------------------------------
@@ -212,13 +292,23 @@ void build_structure(const HostGraph& g, uint32_t rank, uint32_t world, Structur
                 }
             } else *rp = ResidentPlan();
         }
-        if (!resident) {
+        if (!resident && ml_top > 0) {
+            // streamed PCG: multilevel hierarchy instead of the uniform aggregates (no aslots, no block pairs)
+            build_hierarchy(s, elm, ml_top);
+            s.agg_K = 32; s.nA = 0; s.agg_ptr.assign(1, 0);
+            s.aslot_ptr.push_back(0); s.cpair_ptr.push_back(0);
+            s.edge_pose.resize(nE);
+            for (uint32_t p = 0; p < nP; ++p) for (uint32_t k = s.pose_ptr[p]; k < s.pose_ptr[p + 1]; ++k) s.edge_pose[k] = p;
+        }
+        const bool use_ml = !resident && ml_top > 0;
+        if (!resident && !use_ml) {
             uint32_t K = 32;
             if (nP > 32ull * kCoarseMaxAggLarge) K = 32 * (uint32_t)((nP + 32ull * kCoarseMaxAggLarge - 1) / (32ull * kCoarseMaxAggLarge));
             s.agg_K = K; s.nA = (nP + K - 1) / K;
             s.agg_ptr.resize(s.nA + 1);
             for (uint32_t a = 0; a <= s.nA; ++a) s.agg_ptr[a] = std::min<uint64_t>(nP, (uint64_t)a * K);
         }
+        if (!use_ml) {
         s.pose_agg.resize(nP);
         for (uint32_t a = 0; a < s.nA; ++a) for (uint32_t p = s.agg_ptr[a]; p < s.agg_ptr[a + 1]; ++p) s.pose_agg[p] = a;
         s.edge_pose.resize(nE);
@@ -273,6 +363,7 @@ void build_structure(const HostGraph& g, uint32_t rank, uint32_t world, Structur
                 s.ctrip[2 * at] = ss[t].first; s.ctrip[2 * at + 1] = ss[t].second;
             }
             q0 = q1;
+        }
         }
     }
     // ---- fixed vertices ---------------------------------------------------------------------------
