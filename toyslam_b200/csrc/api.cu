@@ -40,6 +40,9 @@ struct tsb_ctx {
     bool force_phased = false;                            // TSB_PCG_PHASED=1: one launch per PCG phase (the multi-GPU path)
     uint64_t h2d = 0, d2h = 0;                            // bytes copied since the last tsb_load_*
     ncclComm_t comm = nullptr;                            // world > 1: one communicator, collectives on `stream`
+    // peer exchange over NVLink (device_graph.h XDev): this rank's region, the peers' regions opened through CUDA IPC
+    char* xreg = nullptr; size_t xbytes = 0; char* xpeer[kXMaxWorld] = {}; uint64_t xseq = 0, xlaunch = 0;
+    bool use_p2p = true;                                  // TSB_P2P=0: NCCL collectives between phase launches (round-1 path)
     // coarse levels of the preconditioner (two-level aggregates for the resident kernel, multilevel hierarchy for the
     // streamed one): the dense top operator is inverted by k_coarse_invert
     bool use_coarse = true;                               // TSB_COARSE=0: block-Jacobi only
@@ -97,11 +100,38 @@ template <typename T, typename U> int upload(tsb_ctx* c, const U*& out, const st
 }
 #define TRY(x) do { if (int rc_ = (x)) return rc_; } while (0)
 
+int x_ensure(tsb_ctx* c, size_t bytes);
+
 int upload_graph(tsb_ctx* c) {
     const HostGraph& g = c->g; const Structure& s = c->st; Dev& d = c->d;
     d.nP = s.nP; d.nG = s.nG; d.L = g.L; d.nE = (uint32_t)s.lm_perm.size(); d.nO = (uint32_t)s.od_local.size();
     d.nOwned = s.n_od_owned; d.nChunks = (uint32_t)s.chunks.size(); d.nBlocks = (uint32_t)s.blk_chunk_ptr.size() - 1;
     d.nSlots = (uint32_t)s.slot_lm.size();
+    // peer exchange (sharded, one process per GPU): region layout -- identical on every rank -- and the peers' mappings
+    d.xc = XDev{};
+    if (c->world > 1 && c->use_p2p) {
+        if (s.nG > kXMaxGhost) { c->err = "peer exchange: too many ghost poses (general ODOM graphs across a cut need TSB_P2P=0)"; return TSB_EINVAL; }
+        XDev& x = d.xc;
+        x.world = (uint32_t)c->world; x.rank = (uint32_t)c->rank; x.slice = (g.L + x.world - 1) / x.world; if (!x.slice) x.slice = 1;
+        auto al = [](size_t v) { return (v + 255) & ~size_t(255); };
+        size_t o = 0;
+        x.o_flags = o; o = al(o + 8ull * kXPoints * kXMaxWorld);
+        x.o_scal = o; o = al(o + 8ull * 16 * kXMaxWorld);
+        x.o_ghost = o; o = al(o + 8ull * 3 * kXMaxGhost);
+        x.o_lm5 = o; o = al(o + 8ull * 5 * x.world * x.slice);
+        x.o_hll = o; o = al(o + 8ull * 3 * g.L + 64);
+        x.o_hinv = o; o = al(o + 8ull * 3 * g.L + 64);
+        x.o_bl = o; o = al(o + 8ull * 2 * g.L + 64);
+        x.o_w = o; o = al(o + 8ull * 2 * x.world * x.slice);
+        x.o_u = o; o = al(o + 8ull * 2 * g.L + 64);
+        x.o_dl = o; o = al(o + 8ull * 2 * g.L + 64);
+        x.o_top = o; o = al(o + 8ull * (3 * 4096 + 4 * kXMaxWorld));
+        TRY(x_ensure(c, o));
+        for (int r = 0; r < c->world; ++r) x.peer[r] = c->xpeer[r];
+        x.nExp = (uint32_t)(s.x_exp.size() / 3);
+        TRY(upload(c, x.exp, s.x_exp)); TRY(upload(c, x.lm_mask, s.lm_mask));
+    }
+    const bool xp = d.xc.world > 1;
     // per-edge data gathered into assembly order
     std::vector<double> z(2ull * d.nE), w(2ull * d.nE);
     for (uint32_t k = 0; k < d.nE; ++k) {
@@ -147,22 +177,30 @@ int upload_graph(tsb_ctx* c) {
     TRY(dalloc(c, d.hpl, 6ull * d.nE)); TRY(dalloc(c, d.hoo, 3ull * d.nO));
     TRY(dalloc(c, d.hpp, 6ull * d.nP)); TRY(dalloc(c, d.bp, 3ull * d.nP)); TRY(dalloc(c, d.pose_od, 6ull * d.nP));
     TRY(dalloc(c, d.lm_part, 5ull * d.nSlots)); TRY(dalloc(c, d.lm_sum, 5ull * g.L + 1));     // + chi2, so that one all-reduce carries both when world > 1
-    TRY(dalloc(c, d.hll, 3ull * g.L)); TRY(dalloc(c, d.hinv, 3ull * g.L)); TRY(dalloc(c, d.bl, 2ull * g.L));
+    if (xp) {     // written by the landmark's owner rank: they live in the exchange region
+        d.hll = reinterpret_cast<double*>(c->xreg + d.xc.o_hll); d.hinv = reinterpret_cast<double*>(c->xreg + d.xc.o_hinv); d.bl = reinterpret_cast<double*>(c->xreg + d.xc.o_bl);
+    } else { TRY(dalloc(c, d.hll, 3ull * g.L)); TRY(dalloc(c, d.hinv, 3ull * g.L)); TRY(dalloc(c, d.bl, 2ull * g.L)); }
     TRY(dalloc(c, d.minv, 6ull * d.nP)); TRY(dalloc(c, d.rhs, 3ull * d.nP));
     TRY(dalloc(c, d.x, 3ull * d.nP)); TRY(dalloc(c, d.r, 3ull * d.nP)); TRY(dalloc(c, d.z, 3ull * d.nP));
     TRY(dalloc(c, d.p, 3ull * nPG)); TRY(dalloc(c, d.sp, 3ull * d.nP));
     TRY(dalloc(c, d.w_part, 2ull * d.nSlots)); d.nBnd = (uint32_t)s.boundary.size();
+    if (xp) {     // u = Hll^-1 w is pushed by the owners, ghost-pose values by their owners
+        d.w_sum = reinterpret_cast<double*>(c->xreg + d.xc.o_u); d.bnd = reinterpret_cast<double*>(c->xreg + d.xc.o_ghost); d.nBnd = d.nG;
+        std::vector<uint32_t> ident(d.nG); for (uint32_t q = 0; q < d.nG; ++q) ident[q] = q;
+        TRY(upload(c, d.bnd_local, ident)); TRY(upload(c, d.ghost_bnd_slot, ident));
+    } else {
     TRY(dalloc(c, d.w_sum, 2ull * g.L + 3ull * d.nBnd + 8)); d.bnd = d.w_sum + 2ull * g.L;
     { std::vector<uint32_t> bl(d.nBnd, 0xFFFFFFFFu);
       for (size_t k = 0; k < s.own_bnd_slot.size(); ++k) bl[s.own_bnd_slot[k]] = s.own_bnd_pose[k];
       TRY(upload(c, d.bnd_local, bl)); TRY(upload(c, d.ghost_bnd_slot, s.ghost_bnd_slot)); }
-    TRY(dalloc(c, d.dl, 2ull * g.L));
+    }
+    if (xp) d.dl = reinterpret_cast<double*>(c->xreg + d.xc.o_dl); else TRY(dalloc(c, d.dl, 2ull * g.L));
     // coarse space
     d.aggK = s.agg_K; d.nA = s.nA; d.nc = 3 * s.nA; d.nAS = (uint32_t)s.aslot_lm.size(); d.nPairs = (uint32_t)s.cpair_a.size();
     d.nSeg = (d.nP + 31) / 32;
     TRY(upload(c, d.agg_ptr, s.agg_ptr)); TRY(upload(c, d.pose_agg, s.pose_agg));
     d.res_nb = c->rp.nb;
-    d.lm_sum_chi2 = c->world > 1 ? 1u : 0u;
+    d.lm_sum_chi2 = (c->world > 1 && !xp) ? 1u : 0u;
     { const char* e = std::getenv("TSB_RES_CGSYNC");                  // 1: cooperative-groups grid.sync() in the resident kernel
       if (!(e && e[0] == '1')) TRY(dalloc(c, d.gbar, (size_t)1)); }
     if (d.res_nb) {
@@ -237,6 +275,43 @@ int allreduce(tsb_ctx* c, double* buf, size_t n) {
     return TSB_OK;
 }
 
+// Exchange region of at least `bytes` on every rank (collective: all ranks pass the same size).  Allocated with
+// cudaMalloc (CUDA IPC needs a plain allocation), zeroed, and opened on the peers: handles travel through NCCL.
+int x_ensure(tsb_ctx* c, size_t bytes) {
+    if (bytes <= c->xbytes) return TSB_OK;
+    CU(cudaStreamSynchronize(c->stream));
+    for (int r = 0; r < c->cfg.world; ++r) if (r != c->cfg.rank && c->xpeer[r]) { cudaIpcCloseMemHandle(c->xpeer[r]); c->xpeer[r] = nullptr; }
+    if (c->xreg) { cudaFree(c->xreg); c->xreg = nullptr; c->xbytes = 0; }
+    bytes = std::max(bytes + bytes / 4, size_t(32) << 20);
+    CU(cudaMalloc((void**)&c->xreg, bytes));
+    CU(cudaMemsetAsync(c->xreg, 0, bytes, c->stream));
+    cudaIpcMemHandle_t h;
+    CU(cudaIpcGetMemHandle(&h, c->xreg));
+    static_assert(sizeof(cudaIpcMemHandle_t) == 64, "ipc handle size");
+    char* hb = nullptr;
+    CU(cudaMalloc((void**)&hb, 64 * (size_t)c->cfg.world));
+    CU(cudaMemcpyAsync(hb + 64 * (size_t)c->cfg.rank, &h, 64, cudaMemcpyHostToDevice, c->stream));
+    const ncclResult_t r = ncclAllGather(hb + 64 * (size_t)c->cfg.rank, hb, 64, ncclChar, c->comm, c->stream);
+    if (r != ncclSuccess) { cudaFree(hb); c->err = std::string("ncclAllGather: ") + ncclGetErrorString(r); return TSB_ENCCL; }
+    std::vector<cudaIpcMemHandle_t> all(c->cfg.world);
+    CU(cudaMemcpyAsync(all.data(), hb, 64 * (size_t)c->cfg.world, cudaMemcpyDeviceToHost, c->stream));
+    CU(cudaStreamSynchronize(c->stream));
+    cudaFree(hb);
+    for (int q = 0; q < c->cfg.world; ++q) {
+        if (q == c->cfg.rank) { c->xpeer[q] = c->xreg; continue; }
+        const cudaError_t e = cudaIpcOpenMemHandle((void**)&c->xpeer[q], all[q], cudaIpcMemLazyEnablePeerAccess);
+        if (e != cudaSuccess) { c->err = std::string("cudaIpcOpenMemHandle (peer exchange needs one process per GPU with peer access): ") + cudaGetErrorString(e); return TSB_ECUDA; }
+    }
+    c->xbytes = bytes; c->xseq = 0; c->xlaunch = 0;           // flags are zero everywhere: every rank memset before it entered the all-gather
+    return TSB_OK;
+}
+inline bool p2p(const tsb_ctx* c) { return c->world > 1 && c->d.xc.world > 1; }
+// all-to-all "step done" over the peers' flag rows: publish after everything enqueued so far, wait for every peer
+void x_sync(tsb_ctx* c, uint32_t point) {
+    ++c->xseq;
+    launch_x_signal_wait(c->d, point, c->xseq, c->stream);
+}
+
 int fetch_scalars(tsb_ctx* c) {
     CU(cudaMemcpyAsync(c->h_scal, c->d.scal, sizeof(double) * S_COUNT, cudaMemcpyDeviceToHost, c->stream));
     CU(cudaMemcpyAsync(c->h_flags, c->d.flags, sizeof(int) * F_COUNT, cudaMemcpyDeviceToHost, c->stream));
@@ -255,7 +330,18 @@ int enqueue_linearize(tsb_ctx* c) {
     launch_linearize(c->d, c->stream);
     mark(1);
     if (c->world <= 1) launch_lm_sum(c->d, true, c->stream);          // sum + finalize in one kernel
-    else {
+    else if (p2p(c)) {
+        // owner-computes over NVLink: every rank pushes the sums of the landmarks it touches to their owners (+ its chi2),
+        // the owner adds them in rank order, inverts and pushes Hll / Hll^-1 / b_l back to every rank
+        launch_x_lm5_push(c->d, c->stream);
+        launch_x_scal_push(c->d, 0, c->d.scal + S_CHI2, c->stream);
+        mark(2);
+        x_sync(c, XP_LM5);
+        launch_x_lm5_own(c->d, c->stream);
+        launch_x_scal_sum(c->d, 0, c->d.scal + S_CHI2, c->stream);
+        x_sync(c, XP_HINV);
+        mark(3);
+    } else {
         launch_lm_sum(c->d, false, c->stream);
         mark(2);
         TRY(allreduce(c, c->d.lm_sum, 5ull * c->g.L + 1));     // landmark sums and chi2 (k_lm_finalize moves it to scal)
@@ -317,7 +403,8 @@ int run_solve(tsb_ctx* c, bool refresh_coarse = true, bool smoother = true) {
         return TSB_OK;
     }
     // single GPU, HBM-sized graph: streamed persistent kernel, then the back-substitution by the phased kernels
-    if (c->world <= 1 && !c->force_phased && launch_pcg_stream(d, c->stream)) {
+    if (p2p(c)) c->d.xc.seq = (uint64_t)(++c->xlaunch) << 32;      // flag values of this launch: the same on every rank
+    if ((c->world <= 1 || p2p(c)) && !c->force_phased && launch_pcg_stream(d, c->stream)) {
         c->pcg_streamed = true;
         if (d.dbg) {
             long long t[8]; int its = 0;
@@ -330,12 +417,18 @@ int run_solve(tsb_ctx* c, bool refresh_coarse = true, bool smoother = true) {
             std::fprintf(stderr, "\n");
         }
         launch_pcg_pass_a(d, 1, c->stream);
+        if (p2p(c)) {          // Hpl^T delta_p summed over ranks by the landmark's owner, delta_l pushed back to every rank
+            launch_x_w_push(d, c->stream); x_sync(c, XP_BW);
+            launch_x_backsub_own(d, c->stream); x_sync(c, XP_BU);
+        } else {
         launch_pcg_mid(d, 1, c->stream);
         launch_backsub(d, c->stream);
+        }
         cudaEventRecord(c->ev[5], c->stream);
         return TSB_OK;
     }
     c->pcg_streamed = false;
+    if (p2p(c)) { c->err = "streamed PCG kernel could not be launched (peer exchange)"; return TSB_ECUDA; }
     if (d.mlLv) { c->err = "streamed PCG kernel could not be launched"; return TSB_ECUDA; }      // the hierarchy has no other consumer
     // single GPU: the whole PCG and the back-substitution run in one persistent cooperative kernel
     if (c->world <= 1 && !c->force_phased && launch_pcg_persistent(d, c->stream)) {
@@ -392,6 +485,15 @@ int run_solve(tsb_ctx* c, bool refresh_coarse = true, bool smoother = true) {
 // K5: damped update of poses and landmarks; ghost poses follow their owners
 int enqueue_update(tsb_ctx* c) {
     const Dev& d = c->d;
+    if (p2p(c)) {
+        launch_x_push_ghost(d, d.x, c->stream);                // delta of the boundary poses -> the ranks that hold them as ghosts
+        x_sync(c, XP_GHOST);
+        launch_update_state(d, 0.2, c->stream);
+        launch_x_scal_push(d, 1, d.scal + S_DELTA2, c->stream);    // ||delta_pose||^2 summed over ranks in rank order
+        x_sync(c, XP_MISC);
+        launch_x_scal_sum(d, 1, d.scal + S_DELTA2, c->stream);
+        return TSB_OK;
+    }
     launch_pack_boundary(d, d.x, c->stream);
     TRY(allreduce(c, d.bnd, 3ull * d.nBnd));
     launch_update_state(d, 0.2, c->stream);                    // OptimizerCpu.h:159-165
@@ -426,6 +528,8 @@ int tsb_create(const tsb_config* cfg, tsb_ctx** out) {
     for (auto& ev : c->ev) if ((e = cudaEventCreate(&ev)) != cudaSuccess) return fail("cudaEventCreate", e);
     if ((e = cudaMallocHost((void**)&c->h_scal, sizeof(double) * S_COUNT)) != cudaSuccess) return fail("cudaMallocHost", e);
     if ((e = cudaMallocHost((void**)&c->h_flags, sizeof(int) * F_COUNT)) != cudaSuccess) return fail("cudaMallocHost", e);
+    { const char* e = std::getenv("TSB_P2P"); c->use_p2p = !(e && e[0] == '0'); }
+    if (cfg->world > (int)kXMaxWorld) { g_create_error = "tsb_create: world > 8 is not supported"; delete c; return TSB_EINVAL; }
     { const char* e = std::getenv("TSB_ML"); if (e && e[0] == '0') c->ml_top = 0; }
     { const char* e = std::getenv("TSB_ML_TOP"); if (e && std::atoi(e) >= 8) c->ml_top = std::min<uint32_t>((uint32_t)std::atoi(e), kMlTopMax); }
     if (c->cfg.world > 1) {
@@ -450,6 +554,8 @@ void tsb_destroy(tsb_ctx* c) {
     if (!c) return;
     cudaSetDevice(c->cfg.device);
     free_graph(c); release_arena(c);
+    for (int r = 0; r < c->cfg.world; ++r) if (r != c->cfg.rank && c->xpeer[r]) cudaIpcCloseMemHandle(c->xpeer[r]);
+    if (c->xreg) cudaFree(c->xreg);
     if (c->comm) ncclCommDestroy(c->comm);
     if (c->h_scal) cudaFreeHost(c->h_scal);
     if (c->h_flags) cudaFreeHost(c->h_flags);
@@ -479,7 +585,7 @@ int tsb_load_wire(tsb_ctx* c, const void* payload, uint32_t nbytes) {
     // graphs beyond the resident kernel run the streamed PCG with the multilevel hierarchy (one GPU; the sharded path
     // and TSB_PCG_PHASED=1 / TSB_ML=0 keep the two-level aggregates)
     const char* ns = std::getenv("TSB_NO_STREAM");
-    const uint32_t ml_top = (c->world <= 1 && c->use_coarse && !c->force_phased && !(ns && ns[0] == '1')) ? c->ml_top : 0;
+    const uint32_t ml_top = ((c->world <= 1 || c->use_p2p) && c->use_coarse && !c->force_phased && !(ns && ns[0] == '1')) ? c->ml_top : 0;
     build_structure(c->g, (uint32_t)c->rank, (uint32_t)c->world, c->st, c->world <= 1 ? res_nb : 0, &c->rp, ml_top);
     return upload_graph(c);
 }

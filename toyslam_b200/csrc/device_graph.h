@@ -19,6 +19,22 @@ enum Scal { S_CHI2 = 0, S_RZ0, S_RZ, S_PSP, S_ALPHA, S_BETA, S_DELTA2, S_DELTA2L
 // integer flags (index into Dev::flags)
 enum Flag { F_DONE = 0, F_ITERS, F_MAXIT, F_COARSE, F_SING, F_COUNT };   // F_COARSE: 1 = coarse inverse valid for this solve; F_SING: a singular vertex block was zeroed
 
+// Peer exchange over NVLink (world > 1, one process per GPU).  Every rank owns an "exchange region" (one cudaMalloc,
+// opened on the peers through CUDA IPC) with the SAME layout on all ranks; a rank WRITES into its peers' regions and only
+// ever READS its own (push model: every wait polls local memory).  Flags are 64-bit sequence numbers, one row per
+// exchange point and source rank; the data of a step is written first, fenced at system scope, then the flag.
+constexpr uint32_t kXMaxWorld = 8, kXPoints = 16, kXMaxGhost = 16;
+enum XPoint { XP_LM5 = 0, XP_HINV, XP_GHOST, XP_W, XP_U, XP_PSP, XP_TOP, XP_MISC, XP_BW, XP_BU, XP_COUNT };   // XP_W .. XP_TOP: inside the PCG kernel
+struct XDev {
+    uint32_t world, rank, slice, nExp;     // slice: landmarks owned per rank (owner(l) = l / slice); nExp: export entries
+    uint64_t seq;                          // flag value base of this launch (the host advances it identically on all ranks)
+    char* peer[kXMaxWorld];                // region of every rank as mapped here (peer[rank] = own region)
+    size_t o_flags, o_scal, o_ghost, o_lm5, o_hll, o_hinv, o_bl, o_w, o_u, o_dl, o_top;   // byte offsets inside a region
+    const uint32_t* exp;                   // 3 per export entry: local pose, destination rank, ghost slot there
+    const uint8_t* lm_mask;                // per landmark: bit r set = rank r has LM edges to it
+    uint32_t top_off, top_total;           // this rank's first node / all nodes of the global top level
+};
+
 // one level of the multilevel hierarchy (host_graph.h MlLevel) on the device
 struct MlDev {
     uint32_t n, ratio, spacing, nnz;
@@ -111,6 +127,7 @@ struct Dev {
     //   + Z_top S_top^-1 Z_top^T; the top level uses Ac / Ai / yc / cdot above with nc = 3 * ml[mlLv - 1].n
     uint32_t mlLv, mlLocal, mlWin, mlCdot;   // levels, window-local levels, restriction windows, entries of cdot
     const uint32_t* tl_ptr; const uint32_t* tl_edge; const uint32_t* tl_node;   // landmark-major CSR over the top level's coarse edges
+    XDev xc;                    // peer exchange (xc.world <= 1: none)
     double* r2;                 // second residual buffer (the restriction recomputes halo poses: r ping-pongs between r and r2)
     MlDev ml[kMlMaxLevels];
 };
@@ -146,6 +163,15 @@ void launch_backsub(const Dev& d, cudaStream_t s);              // delta_l = Hll
 void launch_update_state(const Dev& d, double step, cudaStream_t s);   // K5 + ||delta||^2 (ghost poses take delta from d.bnd)
 void launch_init_pose(const double* xyt, uint32_t n, double4* out, cudaStream_t s);
 void launch_read_pose(const double4* pose, uint32_t n, double* xyt, cudaStream_t s);
+// peer exchange between separately launched kernels (xchg.cuh)
+void launch_x_signal_wait(const Dev& d, uint32_t point, uint64_t value, cudaStream_t s);   // publish `value`, then wait for every peer's
+void launch_x_lm5_push(const Dev& d, cudaStream_t s);          // landmark sums of this rank -> the owners' receive buffers
+void launch_x_lm5_own(const Dev& d, cudaStream_t s);           // owners: sum in rank order, finalize, push Hll / Hll^-1 / b_l to all
+void launch_x_push_ghost(const Dev& d, const double* vec, cudaStream_t s);   // boundary-pose entries of vec -> ghost buffers of the peers
+void launch_x_w_push(const Dev& d, cudaStream_t s);            // back-substitution: this rank's Hpl^T delta_p per touched landmark -> owners
+void launch_x_backsub_own(const Dev& d, cudaStream_t s);       // owners: delta_l = Hll^-1 (b_l - sum over ranks), pushed to every rank
+void launch_x_scal_push(const Dev& d, uint32_t slot, const double* src, cudaStream_t s);
+void launch_x_scal_sum(const Dev& d, uint32_t slot, double* dst, cudaStream_t s);
 size_t linearize_smem_bytes();
 extern uint64_t g_launches;   // kernels launched by this library since load
 

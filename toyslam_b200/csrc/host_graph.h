@@ -65,6 +65,10 @@ struct Structure {
     std::vector<uint32_t> boundary;          // canonical pose index, ascending
     std::vector<uint32_t> own_bnd_slot, own_bnd_pose;   // slots of `boundary` owned here and their local pose index
     std::vector<uint32_t> ghost_bnd_slot;    // per ghost pose: its slot in `boundary`
+    // peer exchange (world > 1): poses of this rank that are ghosts elsewhere, and which ranks touch each landmark
+    std::vector<uint32_t> x_exp;             // 3 per entry: local pose, destination rank, ghost slot on that rank
+    std::vector<uint8_t> lm_mask;            // L: bit r set = rank r owns a pose with an LM edge to the landmark
+    std::vector<uint32_t> top_nodes;         // world > 1: nodes of every rank's top level (global top = concatenation)
     // LM edges of local poses, assembly order = sorted by (pose, landmark, request index)
     std::vector<uint32_t> le_local;          // request-order indices (into HostGraph::le_*) of the local LM edges
     std::vector<uint32_t> lm_perm;           // assembly k -> index into le_local

@@ -971,6 +971,7 @@ __global__ void __launch_bounds__(kThreads, 3) k_pcg_persistent(const Dev d) {
 #include "sblock_smoother.cuh"
 #include "pcg_resident.cuh"
 #include "coarse_invert.cuh"
+#include "xchg.cuh"
 #include "mlevel.cuh"
 #include "pcg_stream.cuh"
 
@@ -1125,8 +1126,8 @@ bool launch_pcg_stream(const Dev& d, cudaStream_t s) {
     }
     uint32_t min_units = 4u * (uint32_t)blocks;
     { const char* e = getenv("TSB_STREAM_MIN_UNITS"); if (e) min_units = (uint32_t)atoi(e);
-      e = getenv("TSB_NO_STREAM"); if (e && e[0] == '1' && !d.mlLv) return false; }
-    if (blocks <= 0 || !d.gbar || !d.nBlocks || (d.nBlocks < min_units && !d.mlLv)) return false;     // a graph with the multilevel hierarchy always streams
+      e = getenv("TSB_NO_STREAM"); if (e && e[0] == '1' && !d.mlLv && d.xc.world <= 1) return false; }
+    if (blocks <= 0 || !d.gbar || !d.nBlocks || (d.nBlocks < min_units && !d.mlLv && d.xc.world <= 1)) return false;     // the multilevel hierarchy and the peer exchange always stream
     Dev dd = d; void* args[] = {&dd};
     cudaMemsetAsync(dd.gbar, 0, sizeof(uint32_t), s);
     const uint32_t grid = d.nBlocks < (uint32_t)blocks ? d.nBlocks : (uint32_t)blocks;
@@ -1291,6 +1292,19 @@ void launch_update_state(const Dev& d, double step, cudaStream_t s) {
     k_reduce_to<<<1, 1024, 0, s>>>(d.part, nb, d.scal + S_DELTA2); ++g_launches;
     k_reduce_to<<<1, 1024, 0, s>>>(d.part2, nb, d.scal + S_DELTA2L); ++g_launches;
 }
+void launch_x_signal_wait(const Dev& d, uint32_t point, uint64_t value, cudaStream_t s) {
+    k_x_signal<<<1, 1, 0, s>>>(d, point, (unsigned long long)value); ++g_launches;
+    k_x_wait<<<1, 1, 0, s>>>(d, point, (unsigned long long)value); ++g_launches;
+}
+void launch_x_lm5_push(const Dev& d, cudaStream_t s) { if (d.L) { k_x_lm5_push<<<cdiv(d.L, kThreads), kThreads, 0, s>>>(d); ++g_launches; } }
+void launch_x_lm5_own(const Dev& d, cudaStream_t s) { k_x_lm5_own<<<cdiv(d.xc.slice, kThreads), kThreads, 0, s>>>(d); ++g_launches; }
+void launch_x_push_ghost(const Dev& d, const double* vec, cudaStream_t s) {
+    if (d.xc.nExp) { k_x_push_ghost<<<cdiv(d.xc.nExp, kThreads), kThreads, 0, s>>>(d, vec); ++g_launches; }
+}
+void launch_x_w_push(const Dev& d, cudaStream_t s) { if (d.L) { k_x_w_push<<<cdiv(d.L, kThreads), kThreads, 0, s>>>(d); ++g_launches; } }
+void launch_x_backsub_own(const Dev& d, cudaStream_t s) { k_x_backsub_own<<<cdiv(d.xc.slice, kThreads), kThreads, 0, s>>>(d); ++g_launches; }
+void launch_x_scal_push(const Dev& d, uint32_t slot, const double* src, cudaStream_t s) { k_x_scal_push<<<1, 1, 0, s>>>(d, slot, src); ++g_launches; }
+void launch_x_scal_sum(const Dev& d, uint32_t slot, double* dst, cudaStream_t s) { k_x_scal_sum<<<1, 1, 0, s>>>(d, slot, dst); ++g_launches; }
 void launch_init_pose(const double* xyt, uint32_t n, double4* out, cudaStream_t s) {
     if (n) { k_init_pose<<<cdiv(n, kThreads), kThreads, 0, s>>>(xyt, n, out); ++g_launches; }
 }

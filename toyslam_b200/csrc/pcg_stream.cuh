@@ -259,8 +259,13 @@ __global__ void __launch_bounds__(kPsThreads, 2) k_pcg_stream(const Dev d) {
         else if (crow) coarse_phase(d, gtid >> 5, gsz >> 5, rc_s, rc_shared);
         res_gsync(grid, d.gbar, gtarget);
     }
+    // world > 1 (peer exchange, xchg.cuh): the ranks' parts of every scalar are added in rank order -- every rank sees
+    // the same bits and takes the same branches
+    const bool xp = d.xc.world > 1;
+    unsigned long long xv = d.xc.seq;
     double rz0 = reduce_all(d.part, nb, red);
     if (coarse) rz0 += reduce_all(d.cdot, ncdot, red);
+    if (xp) rz0 = x_scalar_sum(d, 3, XP_TOP, ++xv, rz0);
     double rz = rz0, beta = 0;
     const double tol2 = d.scal[S_TOL2]; const int maxit = d.flags[F_MAXIT];
     int it = 0;
@@ -275,6 +280,14 @@ __global__ void __launch_bounds__(kPsThreads, 2) k_pcg_stream(const Dev d) {
             TICK(0);
             res_gsync(grid, d.gbar, gtarget);
             TICK(1);
+            if (xp) {             // landmark sums across ranks: partial w -> owner, owner adds in rank order, u = Hll^-1 w -> every toucher
+                x_w_push(d, gtid, gsz);
+                x_gsync(grid, d, gtarget, XP_W, ++xv);
+                x_u_own(d, gtid, gsz);
+                for (uint32_t p = gtid; p < d.nP; p += gsz) hpp_apply(d, p, d.sp + 3ull * p);
+                TICK(2);
+                x_gsync(grid, d, gtarget, XP_U, ++xv);
+            } else {
             for (uint32_t l = gtid; l < d.L; l += gsz) {          // u_l = Hll^-1 w_l straight away: pass B then gathers it raw
                 const double2 w = lm_w_sum(d, l); const double* hi = d.hinv + 3ull * l;
                 reinterpret_cast<double2*>(d.w_sum)[l] = make_double2(hi[0] * w.x + hi[1] * w.y, hi[1] * w.x + hi[2] * w.y);
@@ -282,13 +295,16 @@ __global__ void __launch_bounds__(kPsThreads, 2) k_pcg_stream(const Dev d) {
             for (uint32_t p = gtid; p < d.nP; p += gsz) hpp_apply(d, p, d.sp + 3ull * p);
             TICK(2);
             res_gsync(grid, d.gbar, gtarget);
+            }
             TICK(3);
             t = block_sum(ps_pass_b(d, smem_raw, cb, ce, kbase), red);
             if (tid == 0) d.part2[blockIdx.x] = t;
             TICK(4);
             res_gsync(grid, d.gbar, gtarget);
             TICK(5);
-            const double alpha = rz / reduce_all(d.part2, nb, red);
+            double psp = reduce_all(d.part2, nb, red);
+            if (xp) psp = x_scalar_sum(d, 2, XP_PSP, ++xv, psp);
+            const double alpha = rz / psp;
             if (ml) dot = ml_pose_phase<false>(d, ml_sm, alpha, rbuf[it & 1], rbuf[(it + 1) & 1]);
             else ps_pose_phase<false>(d, alpha, coarse, dot);
             t = block_sum(dot, red);
@@ -303,6 +319,7 @@ __global__ void __launch_bounds__(kPsThreads, 2) k_pcg_stream(const Dev d) {
             TICK(7);
             double rz_new = reduce_all(d.part, nb, red);
             if (coarse) rz_new += reduce_all(d.cdot, ncdot, red);
+            if (xp) rz_new = x_scalar_sum(d, 3, XP_TOP, ++xv, rz_new);
             beta = rz_new / rz; rz = rz_new; ++it;
             if (!(rz_new > tol2 * rz0) || it >= maxit) break;
         }

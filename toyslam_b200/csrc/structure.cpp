@@ -240,6 +240,20 @@ void build_structure(const HostGraph& g, uint32_t rank, uint32_t world, Structur
             if (local(s.boundary[k])) { s.own_bnd_slot.push_back(k); s.own_bnd_pose.push_back(s.boundary[k] - pb); }
         for (uint32_t gp : s.ghost_pose)
             s.ghost_bnd_slot.push_back((uint32_t)(std::lower_bound(s.boundary.begin(), s.boundary.end(), gp) - s.boundary.begin()));
+        // peer exchange: every rank's ghost list (sorted, unique) -> where this rank's boundary poses go
+        std::vector<std::vector<uint32_t>> gl(world);
+        for (uint32_t e = 0; e < g.Eo; ++e) {
+            const uint32_t oi = owner(g.od_i[e]), oj = owner(g.od_j[e]);
+            if (oi != oj) { gl[oj].push_back(g.od_i[e]); gl[oi].push_back(g.od_j[e]); }
+        }
+        for (uint32_t r = 0; r < world; ++r) {
+            std::sort(gl[r].begin(), gl[r].end()); gl[r].erase(std::unique(gl[r].begin(), gl[r].end()), gl[r].end());
+            if (r == rank) continue;
+            for (uint32_t k = 0; k < gl[r].size(); ++k)
+                if (local(gl[r][k])) { s.x_exp.push_back(gl[r][k] - pb); s.x_exp.push_back(r); s.x_exp.push_back(k); }
+        }
+        s.lm_mask.assign(L, 0);
+        for (uint32_t e = 0; e < g.El; ++e) s.lm_mask[g.le_l[e]] |= (uint8_t)(1u << owner(g.le_i[e]));
     }
     // ---- coarse space: aggregates of agg_K consecutive local poses ------------------------------------
     {
