@@ -4,8 +4,11 @@
   python bench.py [--gpus N] [--steps K] [--warmup W] [--workload c2|c3|c4|c5] [--impl ours|reference]
 
 A "step" is one optimisation request: 50 Gauss-Newton iterations (early exits disabled so all 50
-run) on one synthetic Manhattan-world graph (toyslam_b200/synth.py, seed 0).  At N=1 the default
-workload is BASELINE configs[1] (10k poses / 2k landmarks / 150k LM edges).
+run) on one synthetic Manhattan-world graph (toyslam_b200/synth.py, seed 0).  The default workload at
+every N is BASELINE configs[2] (C3: 100k poses / 20k landmarks / 2M LM edges), the largest config a
+50-iteration request finishes in seconds on; with --gpus N the ONE request is edge-sharded over the N
+ranks ("scaling": "strong") and the line carries parity_vs_n1.  C4 (1M poses / 20M edges, sharded the
+same way) and C2 (N independent replicas) are reported as side keys.
   value : GN iterations/s with the graph resident in HBM (state reset device-to-device each step)
   e2e   : the same through the C ABI with host buffers: tsb_load_wire (parse + H2D) ->
           tsb_optimize -> tsb_write_reply (D2H + encode), payload in pinned host memory
@@ -95,7 +98,10 @@ def host_threads(omp_default):
 
 
 def run_reference(args):
-    """CPU arm: sparse restatement of the reference algorithm (oracle tier T2), all host threads."""
+    """CPU arm: sparse restatement of the reference algorithm (oracle tier T2), all host threads, on the SAME workload.
+    A step is a bounded sample: `--ref-iters` GN iterations from the start of the request, with the block-Jacobi PCG of
+    each stopped after `--ref-pcg-cap` iterations (to convergence it needs thousands at C3: minutes per GN iteration).
+    The value is therefore an UPPER bound on the CPU arm's throughput, i.e. GPU / CPU ratios built on it are lower bounds."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
@@ -103,27 +109,129 @@ def run_reference(args):
     payload, c = make_workload(args.workload)
     threads = host_threads(max_threads())
     sample_iters = args.ref_iters
-    times = []
+    times, its_seen = [], []
     for s in range(args.warmup + args.steps):
         o = OracleGraph(payload)
         t0 = time.perf_counter()
-        traj, its, _ = o.optimize_sparse(sample_iters, False, args.pcg_tol, args.pcg_max, threads)
+        traj, its, _ = o.optimize_sparse(sample_iters, False, args.pcg_tol, args.ref_pcg_cap, threads)
         dt = time.perf_counter() - t0
         if s >= args.warmup:
-            times.append(dt)
+            times.append(dt); its_seen.append(float(np.mean(its)))
     t = float(np.mean(times))
     val = sample_iters / t
     line = {"impl": "reference", "metric": "gn_iterations_per_s", "value": val, "unit": "iter/s", "n_gpus": args.gpus,
-            "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * t, "higher_is_better": True, "scaling": "weak",
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * t, "higher_is_better": True, "scaling": "strong",
             "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-            "config": {"workload": f"{args.workload}: P={c['P']} L={c['L']} Eo={c['Eo']} El={c['El']}",
-                       "gn_iterations_per_step_sampled": sample_iters, "pcg_tol": args.pcg_tol},
+            "config": {"workload": f"{args.workload}: P={c['P']} L={c['L']} Eo={c['Eo']} El={c['El']}, {GN_ITERS} GN iterations/step, exits off",
+                       "gn_iterations_per_step_sampled": sample_iters, "pcg_tol": args.pcg_tol, "pcg_cap": args.ref_pcg_cap,
+                       "pcg_iters_per_gn": float(np.mean(its_seen))},
             "cpu_baseline": {"value": val, "unit": "iter/s", "cores": threads, "kind": "port",
-                             "sample": f"first {sample_iters} of {GN_ITERS} GN iterations per step, sparse Schur+PCG restatement "
+                             "sample": f"first {sample_iters} of {GN_ITERS} GN iterations per step, PCG stopped after {args.ref_pcg_cap} iterations per GN iteration "
+                                       "(upper bound on the CPU throughput: block-Jacobi needs thousands to reach 1e-12 at this size); sparse Schur+PCG restatement "
                                        "of OptimizerCpu (reference C++ unbuildable here: Eigen/Boost absent; dense H impossible at this size)"},
             "e2e": {"value": val, "unit": "iter/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "edges_linearized_per_s_incl_solve": (c["Eo"] + c["El"]) * val}
     print(json.dumps(line), flush=True)
+
+
+def measure_request(opt, torch, dist, world, steps, warmup, flush, local):
+    """`warmup` untimed + `steps` timed requests of GN_ITERS iterations on the loaded graph (state reset on the device
+    before each).  Device time by the library's CUDA events on its own stream, MAX over ranks; clocks sampled meanwhile."""
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def step():
+        opt.reset_state()
+        return opt.optimize(GN_ITERS)[0]
+
+    for _ in range(warmup):
+        step()
+    reps = []
+    barrier()
+    with ClockSampler(local) as clk:
+        t0 = time.perf_counter()
+        for _ in range(steps):
+            flush.fill_(1)                                   # L2 flush between timed steps
+            torch.cuda.synchronize()
+            reps.append(step())
+        barrier()
+        wall = time.perf_counter() - t0
+    n = len(reps)
+    out = {"ms": sum(r.ms_total for r in reps) / n, "launches": sum(r.kernel_launches for r in reps),
+           "pcg": sum(r.pcg_iters_total for r in reps) / n, "ms_lin": sum(r.ms_linearize_total for r in reps) / n,
+           "ms_sol": sum(r.ms_solve_total for r in reps) / n, "ms_pcg": sum(r.ms_pcg_total for r in reps) / n,
+           "refreshes": sum(r.coarse_refreshes for r in reps) / n, "not_converged": sum(r.pcg_not_converged for r in reps),
+           "coarse_failures": sum(r.coarse_failures for r in reps), "wall_ms": 1e3 * wall / n, "clocks": clk.summary()}
+    t = torch.tensor([out["ms"]], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    out["ms"] = float(t.item())
+    return out
+
+
+def parity_vs_one_rank(args, payload, opt, torch, dist, rank, world, local, iters=4):
+    """The sharded request against the same request on ONE GPU (rank 0 runs it), `iters` GN iterations from the loaded
+    state: relative chi2 trajectory error and state error (relative to max(1, |value|))."""
+    from toyslam_b200.capi import GraphOptimizerGpu
+    opt.reset_state()
+    _, per = opt.optimize(iters)
+    chi = np.array([p.chi2 for p in per]); ps, ls = opt.state()
+    res = torch.zeros(3, dtype=torch.float64, device="cuda")
+    if rank == 0:
+        one = GraphOptimizerGpu(iterations=iters, device=local, pcg_tol=args.pcg_tol, pcg_max_iters=args.pcg_max, enable_exits=False)
+        one.load_wire(payload)
+        rep1, per1 = one.optimize(iters)
+        chi1 = np.array([p.chi2 for p in per1]); ps1, ls1 = one.state()
+        d = ps - ps1; d[:, 2] = np.arctan2(np.sin(d[:, 2]), np.cos(d[:, 2]))
+        e_st = max(float((np.abs(d) / np.maximum(1.0, np.abs(ps1))).max()), float((np.abs(ls - ls1) / np.maximum(1.0, np.abs(ls1))).max()) if len(ls) else 0.0)
+        res[0] = float(np.max(np.abs(chi - chi1) / chi1)); res[1] = e_st
+        res[2] = float(sum(p.pcg_iters for p in per1)) / iters
+        one.close()
+    dist.broadcast(res, 0)
+    return {"chi2_rel": float(res[0].item()), "state_rel": float(res[1].item()), "gn_iterations": iters,
+            "pcg_iters_per_gn_n1": float(res[2].item()), "pcg_iters_per_gn": float(sum(p.pcg_iters for p in per)) / iters,
+            "tolerance": {"chi2_rel": 1e-8, "state_rel": 1e-8}}
+
+
+def kernel_sample(args, name, torch, dist, rank, world, local, nccl_id_fn, gn=2, lin_reps=6):
+    """Side measurement on another config (sharded over the ranks like the headline): linearize time (K1+K2, CUDA events in
+    the library), time per PCG iteration inside the PCG kernel, and `gn` full GN iterations to the PCG tolerance."""
+    from toyslam_b200.capi import GraphOptimizerGpu
+    payload, c = make_workload(name)
+    opt = GraphOptimizerGpu(iterations=gn, device=local, rank=rank, world=world, nccl_id=nccl_id_fn(), pcg_tol=args.pcg_tol,
+                            pcg_max_iters=args.pcg_max, enable_exits=False)
+    buf = torch.frombuffer(bytearray(payload), dtype=torch.uint8)
+    t0 = time.perf_counter(); cnt = opt.load_wire_ptr(buf.data_ptr(), buf.numel()); load_s = time.perf_counter() - t0
+    del payload
+    lin = []
+    for i in range(lin_reps + 2):
+        st = opt.linearize()
+        if i >= 2:
+            lin.append(st.ms_linearize)
+    rep, per = opt.optimize(gn)
+    vals = torch.tensor([float(np.median(lin)), rep.ms_total, rep.ms_pcg_total], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(vals, op=dist.ReduceOp.MAX)
+    ms_lin, ms_tot, ms_pcg = (float(v) for v in vals.tolist())
+    B_lin, B_pcg = algorithmic_bytes(c)
+    peak, _ = peaks()
+    its = max(1, rep.pcg_iters_total)
+    path = {0: "k_pcg_persistent", 1: "k_pcg_resident", 2: "k_pcg_* phases + NCCL", 3: "k_pcg_stream"}[cnt.pcg_path]
+    out = {"workload": f"{name}: P={c['P']} L={c['L']} Eo={c['Eo']} El={c['El']}", "n_gpus": world, "sharded": world > 1,
+           "gn_iterations_per_s": gn / (ms_tot * 1e-3), "gn_iterations_sampled": gn, "ms_per_gn_iteration": ms_tot / gn,
+           "pcg_iters_per_gn": rep.pcg_iters_total / gn, "pcg_not_converged": rep.pcg_not_converged,
+           "ml_levels": cnt.n_ml_levels, "ml_top_nodes": cnt.n_ml_top, "load_wire_s": load_s,
+           "linearize": {"kernel": "k_odom + k_linearize_stream + landmark sums", "bound": "hbm", "ms": ms_lin, "algorithmic_bytes": B_lin,
+                         "achieved": B_lin / (ms_lin * 1e-3) / 1e9, "peak": peak * world, "unit": "GB/s",
+                         "frac": B_lin / (ms_lin * 1e-3) / 1e9 / (peak * world), "traffic": None,
+                         "edges_linearized_per_s": (c["Eo"] + c["El"]) / (ms_lin * 1e-3)},
+           "pcg_iteration": {"kernel": path, "bound": "hbm", "us": 1e3 * ms_pcg / its, "algorithmic_bytes": B_pcg,
+                             "achieved": B_pcg / (ms_pcg / its * 1e-3) / 1e9, "peak": peak * world, "unit": "GB/s",
+                             "frac": B_pcg / (ms_pcg / its * 1e-3) / 1e9 / (peak * world), "traffic": None}}
+    opt.close()
+    return out
 
 
 def main():
@@ -131,16 +239,16 @@ def main():
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=3)
     ap.add_argument("--warmup", type=int, default=3)
-    ap.add_argument("--workload", default=None)
+    ap.add_argument("--workload", default="c3", help="headline workload (c2..c5); one request, edge-sharded over the ranks at N > 1")
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--pcg-tol", type=float, default=1e-12)
     ap.add_argument("--pcg-max", type=int, default=20000)
-    ap.add_argument("--ref-iters", type=int, default=2, help="GN iterations per step sampled by the CPU arm")
-    ap.add_argument("--no-c4", action="store_true", help="skip the extra 1M-pose linearize roofline measurement")
+    ap.add_argument("--ref-iters", type=int, default=1, help="GN iterations per sample of the CPU arm")
+    ap.add_argument("--ref-pcg-cap", type=int, default=300, help="PCG iterations per GN iteration after which the CPU arm's solve is stopped")
+    ap.add_argument("--no-c4", action="store_true", help="skip the side measurement at the north-star size (1M poses / 20M edges)")
+    ap.add_argument("--no-c2", action="store_true", help="skip the C2 side measurement (N independent replicas)")
     ap.add_argument("--lin-reps", type=int, default=20)
     args = ap.parse_args()
-    if args.workload is None:
-        args.workload = "c2"          # BASELINE configs[1] at every N, so the per-N lines are comparable
     if args.impl == "reference":
         return run_reference(args)
 
@@ -152,86 +260,51 @@ def main():
     if not torch.cuda.is_available():
         raise SystemExit("bench.py needs a CUDA device (no CPU fallback in the product path)")
     torch.cuda.set_device(local)
-    nccl_id = None
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
-        from toyslam_b200 import dist as tdist
-        nccl_id = tdist.broadcast_unique_id(rank)
     assert world == args.gpus, f"--gpus {args.gpus} but WORLD_SIZE={world}"
+
+    def new_id():
+        if world == 1:
+            return None
+        from toyslam_b200 import dist as tdist
+        return tdist.broadcast_unique_id(rank)
 
     def barrier():
         if world > 1:
             dist.barrier()
         torch.cuda.synchronize()
 
+    os.environ["TSB_FORCE_SHARD"] = "1"          # the headline request is ONE request on N GPUs, never N replicas
     payload, c = make_workload(args.workload)
     n_edges = c["Eo"] + c["El"]
     B_lin, B_pcg = algorithmic_bytes(c)
     peak, peak_kind = peaks()
-    opt = GraphOptimizerGpu(iterations=GN_ITERS, device=local, rank=rank, world=world, nccl_id=nccl_id,
+    opt = GraphOptimizerGpu(iterations=GN_ITERS, device=local, rank=rank, world=world, nccl_id=new_id(),
                             pcg_tol=args.pcg_tol, pcg_max_iters=args.pcg_max, enable_exits=False)
-    # pinned host copies of request and reply for the end-to-end leg
-    req = torch.frombuffer(bytearray(payload), dtype=torch.uint8).pin_memory()
+    req = torch.frombuffer(bytearray(payload), dtype=torch.uint8).pin_memory()       # pinned request / reply for the end-to-end leg
     counts = opt.load_wire_ptr(req.data_ptr(), req.numel())
-    # N > 1 and the request fits ONE GPU (the library would run it replicated: same answer on every rank, no speed-up):
-    # the N GPUs of the box then serve N requests at once -- one process per GPU, each with its own graph of this
-    # config (seed = rank) and a context without a communicator; no data-path collective.  `opt_n` (the world = N
-    # context) is kept for the single-request numbers reported beside the aggregate.
-    opt_n, req_n, independent = None, None, False
-    if world > 1 and counts.replicated == 1:
-        independent = True
-        opt_n, req_n = opt, req
-        payload, c = make_workload(args.workload, seed=rank)
-        opt = GraphOptimizerGpu(iterations=GN_ITERS, device=local, rank=0, world=1, nccl_id=None,
-                                pcg_tol=args.pcg_tol, pcg_max_iters=args.pcg_max, enable_exits=False)
-        req = torch.frombuffer(bytearray(payload), dtype=torch.uint8).pin_memory()
-        counts = opt.load_wire_ptr(req.data_ptr(), req.numel())
     reply = torch.empty(opt.reply_size(), dtype=torch.uint8).pin_memory()
     flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
 
-    # ---- resident leg: value ------------------------------------------------------------------------
-    def step_resident():
-        opt.reset_state()
-        rep, per = opt.optimize(GN_ITERS)
-        return rep, per
+    # ---- resident leg: value ------------------------------------------------------------------------------------
+    m = measure_request(opt, torch, dist, world, args.steps, args.warmup, flush, local)
+    value = GN_ITERS / (m["ms"] * 1e-3)
+    pcg_ms = m["ms_pcg"] / max(m["pcg"], 1)                  # device time per PCG iteration inside the PCG kernel
 
-    for _ in range(args.warmup):
-        step_resident()
-    reps = []
-    barrier()
-    with ClockSampler(local) as clk:
-        t0 = time.perf_counter()
-        for _ in range(args.steps):
-            flush.fill_(1)                                   # L2 flush between timed steps
-            torch.cuda.synchronize()
-            reps.append(step_resident())
-        barrier()
-        wall = time.perf_counter() - t0
-    dev_ms = sum(r.ms_total for r, _ in reps) / args.steps
-    launches = sum(r.kernel_launches for r, _ in reps)
-    pcg_total = sum(r.pcg_iters_total for r, _ in reps) / args.steps
-    ms_lin = sum(r.ms_linearize_total for r, _ in reps) / args.steps / GN_ITERS
-    ms_sol = sum(r.ms_solve_total for r, _ in reps) / args.steps
-    ms_pcg = sum(r.ms_pcg_total for r, _ in reps) / args.steps       # the PCG proper (one persistent kernel per solve at N=1)
-    refreshes = sum(r.coarse_refreshes for r, _ in reps) / args.steps
-    t = torch.tensor([dev_ms], dtype=torch.float64, device="cuda")
-    if world > 1:
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    dev_ms = float(t.item())
-    n_req = world if independent else 1                      # requests in flight: units = n_req x GN_ITERS per step
-    value = n_req * GN_ITERS / (dev_ms * 1e-3)
-
-    # ---- linearize roofline at this workload (K1 + K2a + K2b), CUDA events inside the library ------------
+    # ---- linearize (K1 + K2) at this workload, CUDA events inside the library ---------------------------------------
     lin = []
     for i in range(args.lin_reps + 3):
         flush.fill_(1); torch.cuda.synchronize()
         st = opt.linearize()
         if i >= 3:
             lin.append(st.ms_linearize)
-    lin_ms = float(np.median(lin))
-    pcg_ms = ms_pcg / max(pcg_total, 1)                      # device time per PCG iteration inside the PCG kernel(s)
+    tl = torch.tensor([float(np.median(lin))], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(tl, op=dist.ReduceOp.MAX)
+    lin_ms = float(tl.item())
 
-    # ---- end-to-end leg -----------------------------------------------------------------------------
+    # ---- end-to-end leg: host request bytes -> tsb_load_wire (parse, structure, H2D) -> optimize -> reply bytes (D2H) ----
     def step_e2e():
         opt.load_wire_ptr(req.data_ptr(), req.numel())
         rep, _ = opt.optimize(GN_ITERS)
@@ -251,138 +324,92 @@ def main():
         dist.all_reduce(te, op=dist.ReduceOp.MAX)
     e2e_s = float(te.item())
 
-    resident_kernel = counts.pcg_path == 1
+    path = {0: "k_pcg_persistent (whole PCG solve in one cooperative launch)", 1: "k_pcg_resident (whole solve in one cooperative launch, Hpl resident in shared memory)",
+            2: "k_pcg_* phases + NCCL all-reduces", 3: "k_pcg_stream (whole PCG solve in one persistent cooperative launch: edge passes through a 3-stage TMA ring, "
+            "multilevel preconditioner" + (", landmark sums / top-level residual / dot products exchanged over NVLink peer memory" if world > 1 else "") + ")"}[counts.pcg_path]
     line = {
         "metric": "gn_iterations_per_s", "value": value, "unit": "iter/s", "n_gpus": world, "steps": args.steps,
-        "warmup": args.warmup, "ms_per_step": dev_ms, "higher_is_better": True,
-        "scaling": "strong" if world > 1 and not independent else "weak",
+        "warmup": args.warmup, "ms_per_step": m["ms"], "higher_is_better": True, "scaling": "strong",
         "vs_baseline": None, "dtype": "f64", "data": "synthetic",
         "config": {"workload": f"{args.workload}: P={c['P']} L={c['L']} Eo={c['Eo']} El={c['El']}, {GN_ITERS} GN iterations/step, exits off",
-                   "pcg_tol": args.pcg_tol, "pcg_iters_per_gn": pcg_total / GN_ITERS, "l2": "flushed between timed steps (256 MiB write)",
-                   "wall_ms_per_step": 1e3 * wall / args.steps},
-        "edges_linearized_per_s": n_req * n_edges / (lin_ms * 1e-3),
-        "e2e": {"value": n_req * GN_ITERS / e2e_s, "unit": "iter/s", "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
-                "ms_per_step": 1e3 * e2e_s},
-        "gpu_launches": int(launches),
-        "clocks": clk.summary(),
-        # dominant kernel of the step (profiles/: > 90 % of the C2 step): the persistent PCG kernel, one launch per solve.
-        # algorithmic bytes per launch = B_pcg x the PCG iterations of that solve; duration by CUDA events around the launch.
-        "roofline": {"kernel": ("k_pcg_resident (whole PCG solve in one cooperative launch, Hpl resident in shared memory)" if resident_kernel else
-                                "k_pcg_persistent (whole PCG solve in one cooperative launch)" if world == 1 else "k_pcg_* phases + NCCL all-reduces"),
-                     "bound": "hbm", "achieved": B_pcg / (pcg_ms * 1e-3) / 1e9, "peak": peak, "peak_kind": peak_kind, "unit": "GB/s",
-                     "frac": B_pcg / (pcg_ms * 1e-3) / 1e9 / peak,
-                     # DRAM bytes of one k_pcg_resident launch (= one solve) from the ncu --set full captures summarised in
-                     # profiles/r1_pcg_resident_c2_v3_ncu_summary.csv (first solve, smoother blocks: 44.3 MB read + 1.2 MB
-                     # written, 24.5 MB of it the smoother inverses read once into L2) and ..._v2_... (3x3 blocks: 17.6 MB):
-                     # far below the algorithmic bytes because both orders of Hpl stay in shared memory for the whole solve
-                     "traffic": 45.5e6 if (resident_kernel and args.workload == "c2") else None,
-                     "traffic_source": "profiles/r1_pcg_resident_c2_v3_ncu_summary.csv" if (resident_kernel and args.workload == "c2") else None,
-                     "algorithmic_bytes_per_launch": B_pcg * pcg_total / GN_ITERS, "algorithmic_bytes_per_pcg_iteration": B_pcg,
-                     "launch_ms": ms_pcg / GN_ITERS, "pcg_iterations_per_launch": pcg_total / GN_ITERS,
-                     "share_of_step": ms_pcg / dev_ms,
-                     "note": "working set (%.0f MB) is L2-resident at this size: latency-bound, not HBM-bound" % (B_pcg / 1e6) if B_pcg < 100e6 else ""},
-        "roofline_linearize": {"kernel": "k_odom + k_linearize[_stream] + k_lm_sum", "bound": "hbm",
-                               "achieved": B_lin / (lin_ms * 1e-3) / 1e9, "peak": peak, "unit": "GB/s",
-                               "frac": B_lin / (lin_ms * 1e-3) / 1e9 / peak, "algorithmic_bytes": B_lin, "ms": lin_ms,
-                               "note": "working set is L2-resident at this size" if B_lin < 100e6 else ""},
-        "solve_breakdown_ms_per_gn": {"linearize": ms_lin, "solve_total": ms_sol / GN_ITERS, "pcg": ms_pcg / GN_ITERS,
-                                      "schur_prep_and_coarse_setup": (ms_sol - ms_pcg) / GN_ITERS, "coarse_refreshes_per_step": refreshes},
+                   "pcg_tol": args.pcg_tol, "pcg_iters_per_gn": m["pcg"] / GN_ITERS, "l2": "flushed between timed steps (256 MiB write)",
+                   "wall_ms_per_step": m["wall_ms"], "pcg_not_converged": m["not_converged"], "coarse_failures": m["coarse_failures"],
+                   "preconditioner": f"{counts.n_ml_levels}-level hierarchy, dense top level of {counts.n_ml_top} nodes per rank" if counts.n_ml_levels else f"two-level, {counts.n_aggregates} aggregates",
+                   "parallelism": "single GPU" if world == 1 else
+                   f"ONE request edge-sharded over {world} ranks (contiguous pose ranges, one process per GPU): landmark sums by owner-computes "
+                   "pushes over NVLink peer memory inside the persistent PCG kernel, global dense top level of the preconditioner replicated"},
+        "edges_linearized_per_s": n_edges / (lin_ms * 1e-3),
+        "e2e": {"value": GN_ITERS / e2e_s, "unit": "iter/s", "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h), "ms_per_step": 1e3 * e2e_s},
+        "gpu_launches": int(m["launches"]),
+        "clocks": m["clocks"],
+        # dominant kernel of the step: the PCG kernel, one launch per solve.  Algorithmic bytes per launch = B_pcg x the PCG
+        # iterations of that solve; duration from CUDA events around the launch on the library's stream.
+        "roofline": {"kernel": path, "bound": "hbm", "achieved": B_pcg / (pcg_ms * 1e-3) / 1e9, "peak": peak * world, "peak_kind": peak_kind,
+                     "unit": "GB/s", "frac": B_pcg / (pcg_ms * 1e-3) / 1e9 / (peak * world), "traffic": None,
+                     "traffic_note": "not measured in this run; ncu --set full summaries of the same kernel: profiles/",
+                     "algorithmic_bytes_per_launch": B_pcg * m["pcg"] / GN_ITERS, "algorithmic_bytes_per_pcg_iteration": B_pcg,
+                     "launch_ms": m["ms_pcg"] / GN_ITERS, "pcg_iterations_per_launch": m["pcg"] / GN_ITERS, "us_per_pcg_iteration": 1e3 * pcg_ms,
+                     "share_of_step": m["ms_pcg"] / m["ms"]},
+        "roofline_linearize": {"kernel": "k_odom + k_linearize[_stream] + landmark sums", "bound": "hbm",
+                               "achieved": B_lin / (lin_ms * 1e-3) / 1e9, "peak": peak * world, "unit": "GB/s",
+                               "frac": B_lin / (lin_ms * 1e-3) / 1e9 / (peak * world), "algorithmic_bytes": B_lin, "ms": lin_ms, "traffic": None},
+        "solve_breakdown_ms_per_gn": {"linearize": m["ms_lin"] / GN_ITERS, "solve_total": m["ms_sol"] / GN_ITERS, "pcg": m["ms_pcg"] / GN_ITERS,
+                                      "schur_prep_and_coarse_setup": (m["ms_sol"] - m["ms_pcg"]) / GN_ITERS, "coarse_refreshes_per_step": m["refreshes"]},
     }
+    # ---- N > 1: the sharded request against the same request on one GPU, in this run -----------------------------------
+    if world > 1:
+        try:
+            line["parity_vs_n1"] = parity_vs_one_rank(args, payload, opt, torch, dist, rank, world, local)
+        except Exception as e:
+            line["parity_vs_n1"] = {"error": str(e)}
+    opt.close()
+    del opt
 
-    line["config"]["parallelism"] = (
-        "single GPU" if world == 1 else
-        f"{world} independent requests, one per GPU (this config fits one GPU's shared-memory-resident PCG kernel and is "
-        "latency-bound: sharding it over NVLink only adds collective latency, see `single_request`); one process per GPU, "
-        "graphs of the same config with seed = rank, no data-path collective; value = all ranks' GN iterations / slowest rank"
-        if independent else f"one request edge-sharded over {world} ranks, NCCL all-reduces")
-    # ---- world > 1: ONE request on the N GPUs, for the record: replicated (what the library does by default for a
-    # graph of this size) and forced through the edge-sharded NCCL path ---------------------------------------------
-    if independent:
-        def step_n():
-            opt_n.reset_state()
-            return opt_n.optimize(GN_ITERS)[0]
-        single = {}
-        for mode in ("replicated", "sharded"):
-            if mode == "sharded":
-                os.environ["TSB_FORCE_SHARD"] = "1"
-                opt_n.load_wire_ptr(req_n.data_ptr(), req_n.numel())
-            step_n()
-            barrier()
-            sh = [step_n() for _ in range(max(1, args.steps - 1))]
-            barrier()
-            ts = torch.tensor([sum(r.ms_total for r in sh) / len(sh)], dtype=torch.float64, device="cuda")
-            dist.all_reduce(ts, op=dist.ReduceOp.MAX)
-            single[mode] = {"value": GN_ITERS / (float(ts.item()) * 1e-3), "unit": "iter/s", "ms_per_step": float(ts.item()),
-                            "pcg_iters_per_gn": sum(r.pcg_iters_total for r in sh) / len(sh) / GN_ITERS}
-        os.environ.pop("TSB_FORCE_SHARD", None)
-        single["replicated"]["note"] = "every rank solves the whole graph, bit-identical results, no collective"
-        single["sharded"]["note"] = "contiguous pose ranges per rank, per-rank coarse spaces, 3 NCCL all-reduces per PCG iteration"
-        line["single_request"] = single
-    # ---- the north-star size (1M poses / 20M edges): linearize roofline and a bounded PCG sample --------------------
-    # (its own context, edge-sharded over the N ranks, PCG capped at 30 iterations per solve so the cost is fixed)
+    # ---- the north-star size (C4: 1M poses / 20M edges), sharded the same way: kernels against the roofline and full GN iterations
     if not args.no_c4 and args.workload != "c4":
         try:
-            _, B_pcg4 = 0, 0
-            id4 = None
-            if world > 1:
-                from toyslam_b200 import dist as tdist
-                id4 = tdist.broadcast_unique_id(rank)
-            opt4 = GraphOptimizerGpu(iterations=1, device=local, rank=rank, world=world, nccl_id=id4,
-                                     pcg_tol=args.pcg_tol, pcg_max_iters=30, enable_exits=False)
-            p4, c4 = make_workload("c4")
-            r4 = torch.frombuffer(bytearray(p4), dtype=torch.uint8)
-            opt4.load_wire_ptr(r4.data_ptr(), r4.numel())
-            del p4
-            l4 = []
-            for i in range(8):
-                st = opt4.linearize()
-                if i >= 3:
-                    l4.append(st.ms_linearize)
-            ms4 = float(np.median(l4)); B4, B_pcg4 = algorithmic_bytes(c4)
-            rep4 = [opt4.optimize(1)[0] for _ in range(3)][1:]            # GN iterations with 30 PCG iterations each
-            us_it = 1e3 * sum(r.ms_pcg_total for r in rep4) / max(1, sum(r.pcg_iters_total for r in rep4))
-            if world > 1:                                     # edge-sharded over the ranks: the slowest rank counts
-                t4 = torch.tensor([ms4, us_it], dtype=torch.float64, device="cuda"); dist.all_reduce(t4, op=dist.ReduceOp.MAX)
-                ms4, us_it = float(t4[0].item()), float(t4[1].item())
-            wl4 = f"c4: P={c4['P']} L={c4['L']} Eo={c4['Eo']} El={c4['El']}"
-            line["roofline_linearize_c4"] = {"workload": wl4, "bound": "hbm",
-                                             "achieved": B4 / (ms4 * 1e-3) / 1e9, "peak": peak * world, "unit": "GB/s", "n_gpus": world,
-                                             "frac": B4 / (ms4 * 1e-3) / 1e9 / (peak * world), "algorithmic_bytes": B4, "ms": ms4,
-                                             # dram read + write of k_linearize_stream + k_lm_sum + k_odom at N=1, ncu --set full
-                                             # (profiles/r1_lin_c4_planes_ncu_summary.csv): 1 865 + 113 + 128 MB
-                                             "traffic": 2.106e9 if world == 1 else None,
-                                             "edges_linearized_per_s": (c4["Eo"] + c4["El"]) / (ms4 * 1e-3)}
-            path4 = {0: "k_pcg_persistent", 1: "k_pcg_resident", 2: "k_pcg_* phases + NCCL all-reduces",
-                     3: "k_pcg_stream (persistent cooperative kernel, edge passes through a 3-stage TMA ring)"}[opt4.refresh_counts().pcg_path]
-            line["roofline_pcg_c4"] = {"workload": wl4, "kernel": path4,
-                                       "bound": "hbm", "achieved": B_pcg4 / (us_it * 1e-6) / 1e9, "peak": peak * world, "unit": "GB/s",
-                                       "n_gpus": world, "frac": B_pcg4 / (us_it * 1e-6) / 1e9 / (peak * world),
-                                       "algorithmic_bytes_per_pcg_iteration": B_pcg4, "us_per_pcg_iteration": us_it,
-                                       # k_pcg_stream at N=1, ncu --set full (profiles/r1_pcg_stream_c4_v2_ncu_summary.csv):
-                                       # 17.11 GB read + 1.19 GB written in a 6-iteration launch; B_pcg + the 275 MB dense
-                                       # coarse inverse = 2.79 GB per iteration
-                                       "traffic_per_pcg_iteration": 3.05e9 if world == 1 else None,
-                                       "sample": "2 GN iterations x 30 PCG iterations (capped), PCG kernel time only"}
-            opt4.close()
-        except Exception as e:                                # never lose the main line to the extra measurement
-            line["roofline_linearize_c4"] = {"error": str(e)}
+            line["c4"] = kernel_sample(args, "c4", torch, dist, rank, world, local, new_id, gn=2)
+        except Exception as e:                                # never lose the main line to a side measurement
+            line["c4"] = {"error": str(e)}
+    # ---- C2 (fits one GPU's shared-memory-resident kernel; latency-bound): N independent requests, one per GPU ------------
+    if not args.no_c2 and args.workload != "c2":
+        try:
+            os.environ.pop("TSB_FORCE_SHARD", None)
+            p2, c2 = make_workload("c2", seed=rank)
+            o2 = GraphOptimizerGpu(iterations=GN_ITERS, device=local, pcg_tol=args.pcg_tol, pcg_max_iters=args.pcg_max, enable_exits=False)
+            o2.load_wire(p2)
+            m2 = measure_request(o2, torch, dist, world, 2, 1, flush, local)
+            line["c2_replicas"] = {"workload": f"c2: P={c2['P']} L={c2['L']} El={c2['El']}, one request per GPU (seed = rank), no collective",
+                                   "gn_iterations_per_s_aggregate": world * GN_ITERS / (m2["ms"] * 1e-3), "ms_per_request": m2["ms"],
+                                   "pcg_iters_per_gn": m2["pcg"] / GN_ITERS, "scaling": "weak",
+                                   "note": "L2/shared-memory-resident working set: latency-bound, no HBM roofline fraction is quoted for it"}
+            o2.close()
+        except Exception as e:
+            line["c2_replicas"] = {"error": str(e)}
 
-    # ---- CPU baseline on the host cores of this box (rank 0, N=1 only) ----------------------------------------
+    # ---- CPU baseline on the host cores of this box (rank 0, N=1 only): the oracle's sparse tier on the SAME graph,
+    # sampled at the start of the request and from the state the GPU run reached after half of it --------------------------
     if world == 1 and rank == 0:
-        from oracle.oracle import OracleGraph, max_threads
-        o = OracleGraph(payload)
-        th = host_threads(max_threads())
-        t0 = time.perf_counter()
-        o.optimize_sparse(args.ref_iters, False, args.pcg_tol, args.pcg_max, th)
-        dt = time.perf_counter() - t0
-        line["cpu_baseline"] = {"value": args.ref_iters / dt, "unit": "iter/s", "cores": th, "kind": "port",
-                                "sample": f"first {args.ref_iters} of {GN_ITERS} GN iterations of the same graph, sparse Schur+PCG "
-                                          "restatement of OptimizerCpu (oracle tier T2, OpenMP)"}
+        try:
+            from oracle.oracle import OracleGraph, max_threads
+            th = host_threads(max_threads())
+            o = OracleGraph(payload)
+            t0 = time.perf_counter(); _, its0, _ = o.optimize_sparse(args.ref_iters, False, args.pcg_tol, args.ref_pcg_cap, th); dt0 = time.perf_counter() - t0
+            g = GraphOptimizerGpu(iterations=GN_ITERS // 2, device=local, pcg_tol=args.pcg_tol, pcg_max_iters=args.pcg_max, enable_exits=False)
+            g.load_wire(payload); g.optimize(GN_ITERS // 2); ps, ls = g.state(); g.close()
+            o.set_state(ps, ls)
+            t0 = time.perf_counter(); _, its1, _ = o.optimize_sparse(args.ref_iters, False, args.pcg_tol, args.ref_pcg_cap, th); dt1 = time.perf_counter() - t0
+            line["cpu_baseline"] = {"value": 2 * args.ref_iters / (dt0 + dt1), "unit": "iter/s", "cores": th, "kind": "port",
+                                    "sample": f"GN iterations 0..{args.ref_iters - 1} and {GN_ITERS // 2}..{GN_ITERS // 2 + args.ref_iters - 1} of the same {args.workload} request "
+                                              f"(the second sample starts from the state the GPU run reached), PCG stopped after {args.ref_pcg_cap} iterations per GN iteration (an upper bound on the CPU "
+                                              "throughput: to 1e-12 block-Jacobi needs thousands), sparse Schur + block-Jacobi PCG restatement of OptimizerCpu "
+                                              "(oracle tier T2, OpenMP); the reference C++ needs Eigen/Boost (absent) and a dense dim x dim H",
+                                    "s_per_gn_iteration": {"start": dt0 / args.ref_iters, "mid": dt1 / args.ref_iters},
+                                    "pcg_iters_per_gn": {"start": float(np.mean(its0)), "mid": float(np.mean(its1))}}
+        except Exception as e:
+            line["cpu_baseline"] = {"error": str(e)}
     if rank == 0:
         print(json.dumps(line), flush=True)
-    opt.close()
-    if opt_n is not None:
-        opt_n.close()
     if world > 1:
         dist.destroy_process_group()
 

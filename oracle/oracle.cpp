@@ -756,6 +756,45 @@ double orc_linearize_sparse(void* h, int reps, int threads) {
     for (int r = 0; r < reps; ++r) err = sparse_linearize(g, s);
     return err;
 }
+// True residual of a candidate step against the oracle's own linearisation at the oracle's current state:
+//   || H delta - b ||_2 / || b ||_2  over the FULL system (poses and landmarks, nothing eliminated), one sparse mat-vec.
+// Used by the parity tests at sizes where no dense solve exists (OptimizerCpu.h:82-156 assembles this H and b).
+double orc_residual_sparse(void* h, const double* dp, const double* dl, int threads, double* chi2) {
+#ifdef _OPENMP
+    if (threads > 0) omp_set_num_threads(threads);
+#endif
+    Graph& g = *(Graph*)h;
+    Sparse s; sparse_init(g, s);
+    const double err = sparse_linearize(g, s);
+    if (chi2) *chi2 = err;
+    const long P = (long)s.P, L = (long)s.L;
+    double rr = 0, bb = 0;
+#pragma omp parallel for reduction(+ : rr, bb) schedule(static)
+    for (long i = 0; i < P; ++i) {
+        const double* H = &s.Hpp[9 * i]; const double* pv = &dp[3 * i];
+        double y[3];
+        for (int r = 0; r < 3; ++r) y[r] = H[3 * r] * pv[0] + H[3 * r + 1] * pv[1] + H[3 * r + 2] * pv[2] - s.bp[3 * i + r];
+        for (uint32_t q = s.oo_ptr[i]; q < s.oo_ptr[i + 1]; ++q) { const uint32_t k = s.oo_edge[q];
+            const double* pj = &dp[3 * (size_t)g.od_j[k]]; for (int d = 0; d < 3; ++d) y[d] -= s.od_inf[3 * k + d] * pj[d]; }
+        for (uint32_t q = s.oi_ptr[i]; q < s.oi_ptr[i + 1]; ++q) { const uint32_t k = s.oi_edge[q];
+            const double* pj = &dp[3 * (size_t)g.od_i[k]]; for (int d = 0; d < 3; ++d) y[d] -= s.od_inf[3 * k + d] * pj[d]; }
+        for (uint32_t q = s.pose_ptr[i]; q < s.pose_ptr[i + 1]; ++q) { const uint32_t k = s.pose_edge[q];
+            const double* hh = &s.Hpl[6 * (size_t)k]; const double* u = &dl[2 * (size_t)g.lm_l[k]];
+            y[0] += hh[0] * u[0] + hh[1] * u[1]; y[1] += hh[2] * u[0] + hh[3] * u[1]; y[2] += hh[4] * u[0] + hh[5] * u[1]; }
+        for (int r = 0; r < 3; ++r) { rr += y[r] * y[r]; bb += s.bp[3 * i + r] * s.bp[3 * i + r]; }
+    }
+#pragma omp parallel for reduction(+ : rr, bb) schedule(static)
+    for (long l = 0; l < L; ++l) {
+        const double* hl = &s.Hll[4 * l]; const double* u = &dl[2 * l];
+        double t0 = hl[0] * u[0] + hl[1] * u[1] - s.bl[2 * l], t1 = hl[2] * u[0] + hl[3] * u[1] - s.bl[2 * l + 1];
+        for (uint32_t q = s.lm_ptr[l]; q < s.lm_ptr[l + 1]; ++q) { const uint32_t k = s.lm_edge[q];
+            const double* hh = &s.Hpl[6 * (size_t)k]; const double* pv = &dp[3 * (size_t)g.lm_i[k]];
+            t0 += hh[0] * pv[0] + hh[2] * pv[1] + hh[4] * pv[2]; t1 += hh[1] * pv[0] + hh[3] * pv[1] + hh[5] * pv[2]; }
+        rr += t0 * t0 + t1 * t1; bb += s.bl[2 * l] * s.bl[2 * l] + s.bl[2 * l + 1] * s.bl[2 * l + 1];
+    }
+    return bb > 0 ? std::sqrt(rr / bb) : std::sqrt(rr);
+}
+
 int orc_max_threads() {
 #ifdef _OPENMP
     return omp_get_max_threads();

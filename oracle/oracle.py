@@ -97,6 +97,14 @@ class OracleGraph:
                                        C.c_int(max_pcg), C.c_int(threads), _p(traj), _p(its), C.byref(code))
         return traj[:n].copy(), its[:n].copy(), code.value
 
+    def residual_sparse(self, delta_pose, delta_lm, threads=0):
+        """(||H delta - b|| / ||b||, chi2) of the full system linearised at the oracle's current state"""
+        dp = np.ascontiguousarray(delta_pose, np.float64); dl = np.ascontiguousarray(delta_lm, np.float64)
+        chi2 = C.c_double(0)
+        self.L.orc_residual_sparse.restype = C.c_double
+        r = self.L.orc_residual_sparse(self.h, _p(dp), _p(dl), C.c_int(threads), C.byref(chi2))
+        return float(r), chi2.value
+
     def linearize_sparse(self, reps=1, threads=0):
         return float(self.L.orc_linearize_sparse(self.h, C.c_int(reps), C.c_int(threads)))
 

@@ -344,6 +344,33 @@ def test_multilevel_pcg_matches_two_level_and_block_jacobi(gpu, monkeypatch, sca
     assert res[0][2] < res[1][2] and 4 * res[0][2] < res[4][2], [r[2] for r in res]
 
 
+@pytest.mark.parametrize("cfg", ["c3", "c5", "c4"])
+def test_full_size_solve_has_a_small_true_residual(gpu, cfg):
+    """Configs 3, 4, 5 at FULL size, where no dense solve and no converged CPU run exist: the step the streamed PCG
+    kernel returns (poses and back-substituted landmarks) is fed to the oracle's own sparse linearisation of the same
+    state, which evaluates the true residual || H delta - b || / || b || of the full system (one CPU mat-vec) and chi2.
+    Checked at the loaded state and again at the state three GN iterations later."""
+    from oracle.oracle import OracleGraph
+    from toyslam_b200 import synth
+    payload = synth.to_payload(synth.make_config(cfg, seed=0))
+    g = gpu(iterations=3, pcg_tol=1e-12, pcg_max_iters=30000, enable_exits=False)
+    c = g.load_wire(payload)
+    assert c.pcg_path in (0, 3) and c.n_ml_levels >= 3
+    o = OracleGraph(payload)
+    for stage in range(2):
+        st = g.linearize(); s2 = g.solve()
+        dp, dl = g.delta()
+        res, chi2 = o.residual_sparse(dp, dl)
+        assert abs(st.chi2 - chi2) <= 1e-11 * chi2, (cfg, stage, st.chi2, chi2)
+        assert res <= 1e-10, (cfg, stage, res, s2.pcg_iters, s2.pcg_rel_residual)
+        if stage == 0:
+            rep, per = g.optimize(3)
+            assert rep.pcg_not_converged == 0 and rep.coarse_failures == 0
+            assert per[-1].chi2 < per[0].chi2
+            o.set_state(*g.state())
+    g.close()
+
+
 def test_streamed_pcg_matches_persistent_kernel(gpu, monkeypatch):
     """HBM-sized graphs on one GPU run k_pcg_stream (edge passes through the TMA ring, register prefetch); forced on
     a small graph it must agree with the block-synchronous persistent kernel: same edge-pass arithmetic, only p'Sp

@@ -42,6 +42,7 @@ struct tsb_ctx {
     ncclComm_t comm = nullptr;                            // world > 1: one communicator, collectives on `stream`
     // peer exchange over NVLink (device_graph.h XDev): this rank's region, the peers' regions opened through CUDA IPC
     char* xreg = nullptr; size_t xbytes = 0; char* xpeer[kXMaxWorld] = {}; uint64_t xseq = 0, xlaunch = 0;
+    std::vector<uint32_t> gt_ecnt, gt_eoff;               // coarse edges of every rank's top level (global top lists)
     bool use_p2p = true;                                  // TSB_P2P=0: NCCL collectives between phase launches (round-1 path)
     // coarse levels of the preconditioner (two-level aggregates for the resident kernel, multilevel hierarchy for the
     // streamed one): the dense top operator is inverted by k_coarse_invert
@@ -101,6 +102,7 @@ template <typename T, typename U> int upload(tsb_ctx* c, const U*& out, const st
 #define TRY(x) do { if (int rc_ = (x)) return rc_; } while (0)
 
 int x_ensure(tsb_ctx* c, size_t bytes);
+int x_gatherv_u32(tsb_ctx* c, const std::vector<uint32_t>& mine, std::vector<std::vector<uint32_t>>& all);
 
 int upload_graph(tsb_ctx* c) {
     const HostGraph& g = c->g; const Structure& s = c->st; Dev& d = c->d;
@@ -222,7 +224,13 @@ int upload_graph(tsb_ctx* c) {
     // multilevel hierarchy (streamed PCG): structure arrays and per-level vectors
     d.mlLv = (uint32_t)s.ml.size(); d.mlLocal = s.ml_local; d.mlWin = (d.nP + kMlWindow - 1) / kMlWindow; d.mlCdot = d.nc;
     if (d.mlLv) {
-        d.nc = 3 * s.ml.back().n; d.mlCdot = d.nc;
+        // the exactly-solved top level: this rank's last level, or (sharded) the last levels of all ranks concatenated
+        const MlLevel& t = s.ml.back();
+        uint32_t top_total = t.n; d.xc.top_off = 0;
+        if (xp) { top_total = 0; for (int r = 0; r < c->world; ++r) { if (r == c->rank) d.xc.top_off = top_total; top_total += s.top_nodes[r]; } }
+        d.xc.top_total = top_total;
+        if (top_total > 4096) { c->err = "multilevel hierarchy: global top level too large"; return TSB_EINVAL; }
+        d.nc = 3 * top_total; d.mlCdot = d.nc;
         for (uint32_t l = 0; l < d.mlLv; ++l) {
             const MlLevel& h = s.ml[l]; MlDev& m = d.ml[l];
             m.n = h.n; m.ratio = h.ratio; m.spacing = h.spacing; m.nnz = (uint32_t)h.edge_lm.size();
@@ -232,14 +240,33 @@ int upload_graph(tsb_ctx* c) {
             if (l >= d.mlLocal) TRY(dalloc(c, m.wpart, 3ull * d.mlWin * m.slots));
             if (l >= d.mlLocal && l + 1 < d.mlLv) { m.cdot_off = d.mlCdot; d.mlCdot += m.n; }
         }
-        // landmark-major CSR over the top level's coarse edges (k_ml_top)
-        const MlLevel& t = s.ml.back();
-        std::vector<uint32_t> tp(g.L + 1, 0), te(t.edge_lm.size()), tn(t.edge_lm.size());
-        for (uint32_t l : t.edge_lm) tp[l + 1]++;
+        // global top lists: per node the landmark-sorted coarse edges; sharded: every rank's (counts, landmarks) gathered
+        std::vector<uint32_t> gptr, glm;
+        c->gt_ecnt.assign(c->world, 0); c->gt_eoff.assign(c->world + 1, 0);
+        if (!xp) { gptr = t.node_ptr; glm = t.edge_lm; c->gt_ecnt[0] = (uint32_t)glm.size(); c->gt_eoff[1] = c->gt_ecnt[0]; }
+        else {
+            std::vector<uint32_t> cnt(t.n);
+            for (uint32_t K = 0; K < t.n; ++K) cnt[K] = t.node_ptr[K + 1] - t.node_ptr[K];
+            std::vector<std::vector<uint32_t>> acnt, alm;
+            TRY(x_gatherv_u32(c, cnt, acnt)); TRY(x_gatherv_u32(c, t.edge_lm, alm));
+            gptr.push_back(0);
+            for (int r = 0; r < c->world; ++r) {
+                if (acnt[r].size() != s.top_nodes[r]) { c->err = "multilevel hierarchy: ranks disagree on the top level"; return TSB_EINVAL; }
+                for (uint32_t v : acnt[r]) gptr.push_back(gptr.back() + v);
+                glm.insert(glm.end(), alm[r].begin(), alm[r].end());
+                c->gt_ecnt[r] = (uint32_t)alm[r].size(); c->gt_eoff[r + 1] = c->gt_eoff[r] + c->gt_ecnt[r];
+            }
+        }
+        d.gt_nnz = (uint32_t)glm.size();
+        // landmark-major CSR over the (global) top-level coarse edges (k_ml_top)
+        std::vector<uint32_t> tp(g.L + 1, 0), te(glm.size()), tn(glm.size());
+        for (uint32_t l : glm) tp[l + 1]++;
         for (uint32_t l = 0; l < g.L; ++l) tp[l + 1] += tp[l];
         { std::vector<uint32_t> c2(tp.begin(), tp.end() - 1);
-          for (uint32_t K = 0; K < t.n; ++K) for (uint32_t e = t.node_ptr[K]; e < t.node_ptr[K + 1]; ++e) { const uint32_t at = c2[t.edge_lm[e]]++; te[at] = e; tn[at] = K; } }
+          for (uint32_t K = 0; K < top_total; ++K) for (uint32_t e = gptr[K]; e < gptr[K + 1]; ++e) { const uint32_t at = c2[glm[e]]++; te[at] = e; tn[at] = K; } }
         TRY(upload(c, d.tl_ptr, tp)); TRY(upload(c, d.tl_edge, te)); TRY(upload(c, d.tl_node, tn));
+        if (xp) { TRY(upload(c, d.gt_node_ptr, gptr)); TRY(upload(c, d.gt_edge_lm, glm)); TRY(dalloc(c, d.gtC, 6ull * d.gt_nnz)); }
+        else { d.gt_node_ptr = d.ml[d.mlLv - 1].node_ptr; d.gt_edge_lm = d.ml[d.mlLv - 1].edge_lm; d.gtC = d.ml[d.mlLv - 1].C; }
         TRY(dalloc(c, d.r2, 3ull * d.nP));
     }
     TRY(dalloc(c, d.zoff, d.nP)); TRY(dalloc(c, d.cC, 6ull * d.nAS)); TRY(dalloc(c, d.Ac, (size_t)d.nc * d.nc)); TRY(dalloc(c, d.Ai, (size_t)d.nc * d.nc));
@@ -303,6 +330,33 @@ int x_ensure(tsb_ctx* c, size_t bytes) {
         if (e != cudaSuccess) { c->err = std::string("cudaIpcOpenMemHandle (peer exchange needs one process per GPU with peer access): ") + cudaGetErrorString(e); return TSB_ECUDA; }
     }
     c->xbytes = bytes; c->xseq = 0; c->xlaunch = 0;           // flags are zero everywhere: every rank memset before it entered the all-gather
+    return TSB_OK;
+}
+// load-time gather of one uint32 list per rank (collective; NCCL on the compute stream)
+int x_gatherv_u32(tsb_ctx* c, const std::vector<uint32_t>& mine, std::vector<std::vector<uint32_t>>& all) {
+    const int W = c->cfg.world, R = c->cfg.rank;
+    unsigned long long* dcnt = nullptr;
+    CU(cudaMalloc((void**)&dcnt, 8 * (size_t)W));
+    const unsigned long long n = mine.size();
+    CU(cudaMemcpyAsync(dcnt + R, &n, 8, cudaMemcpyHostToDevice, c->stream));
+    if (ncclAllGather(dcnt + R, dcnt, 1, ncclUint64, c->comm, c->stream) != ncclSuccess) { cudaFree(dcnt); c->err = "ncclAllGather failed"; return TSB_ENCCL; }
+    std::vector<unsigned long long> cnt(W);
+    CU(cudaMemcpyAsync(cnt.data(), dcnt, 8 * (size_t)W, cudaMemcpyDeviceToHost, c->stream));
+    CU(cudaStreamSynchronize(c->stream));
+    cudaFree(dcnt);
+    std::vector<size_t> off(W + 1, 0);
+    for (int r = 0; r < W; ++r) off[r + 1] = off[r] + cnt[r];
+    uint32_t* buf = nullptr;
+    CU(cudaMalloc((void**)&buf, 4 * std::max<size_t>(off[W], 1)));
+    if (n) CU(cudaMemcpyAsync(buf + off[R], mine.data(), 4 * n, cudaMemcpyHostToDevice, c->stream));
+    for (int r = 0; r < W; ++r)
+        if (cnt[r] && ncclBroadcast(buf + off[r], buf + off[r], cnt[r], ncclUint32, r, c->comm, c->stream) != ncclSuccess) { cudaFree(buf); c->err = "ncclBroadcast failed"; return TSB_ENCCL; }
+    std::vector<uint32_t> flat(off[W]);
+    if (off[W]) CU(cudaMemcpyAsync(flat.data(), buf, 4 * off[W], cudaMemcpyDeviceToHost, c->stream));
+    CU(cudaStreamSynchronize(c->stream));
+    cudaFree(buf);
+    all.assign(W, {});
+    for (int r = 0; r < W; ++r) all[r].assign(flat.begin() + off[r], flat.begin() + off[r + 1]);
     return TSB_OK;
 }
 inline bool p2p(const tsb_ctx* c) { return c->world > 1 && c->d.xc.world > 1; }
@@ -376,7 +430,27 @@ int run_solve(tsb_ctx* c, bool refresh_coarse = true, bool smoother = true) {
         cudaEvent_t te[3] = {nullptr, nullptr, nullptr};
         const bool timing = d.dbg != nullptr;
         if (timing) { for (auto& e : te) cudaEventCreate(&e); cudaEventRecord(te[0], c->stream); }
-        if (d.mlLv) launch_ml_setup(d, c->stream); else launch_coarse_assemble(d, c->stream);
+        if (d.mlLv) {
+            launch_ml_levels(d, c->stream);
+            if (p2p(c)) {      // every rank's top-level C into the global planes (stride gt_nnz), each rank's segment broadcast by its owner
+                const MlDev& t = d.ml[d.mlLv - 1];
+                for (int q = 0; q < 3; ++q)
+                    if (t.nnz) CU(cudaMemcpyAsync(d.gtC + 2ull * ((size_t)q * d.gt_nnz + c->gt_eoff[c->rank]), t.C + 2ull * (size_t)q * t.nnz, 16ull * t.nnz, cudaMemcpyDeviceToDevice, c->stream));
+                for (int r = 0; r < c->world; ++r) for (int q = 0; q < 3; ++q) {
+                    double* seg = d.gtC + 2ull * ((size_t)q * d.gt_nnz + c->gt_eoff[r]);
+                    if (c->gt_ecnt[r] && ncclBroadcast(seg, seg, 2ull * c->gt_ecnt[r], ncclDouble, r, c->comm, c->stream) != ncclSuccess) { c->err = "ncclBroadcast failed"; return TSB_ENCCL; }
+                }
+            }
+            launch_ml_top(d, c->stream);
+            if (p2p(c)) {      // block rows of the dense top operator: every rank assembled its own nodes' rows
+                size_t row = 0;
+                for (int r = 0; r < c->world; ++r) {
+                    const size_t cnt = 3ull * c->st.top_nodes[r] * d.nc;
+                    if (cnt && ncclBroadcast(d.Ac + row, d.Ac + row, cnt, ncclDouble, r, c->comm, c->stream) != ncclSuccess) { c->err = "ncclBroadcast failed"; return TSB_ENCCL; }
+                    row += cnt;
+                }
+            }
+        } else launch_coarse_assemble(d, c->stream);
         if (timing) cudaEventRecord(te[1], c->stream);
         if (!launch_coarse_invert(d, c->stream)) { c->err = "coarse inverse kernel could not be launched (nc = " + std::to_string(d.nc) + ")"; return TSB_ECUDA; }
         if (timing) {
@@ -648,7 +722,7 @@ int tsb_get_counts(const tsb_ctx* c, tsb_counts* o) {
     o->dim = 3 * c->g.P + 2 * c->g.L; o->pose_begin = c->st.pose_begin; o->pose_end = c->st.pose_end;
     o->n_lmedge_local = c->d.nE; o->n_odom_local = c->d.nOwned;
     o->n_chunks = c->d.nChunks; o->n_blocks = c->d.nBlocks; o->n_slots = c->d.nSlots;
-    o->pcg_path = c->d.res_nb ? 1u : c->pcg_streamed ? 3u : (c->world <= 1 && !c->force_phased ? 0u : 2u);
+    o->pcg_path = c->d.res_nb ? 1u : (c->pcg_streamed || c->d.mlLv || c->d.xc.world > 1) ? 3u : (c->world <= 1 && !c->force_phased ? 0u : 2u);
     o->replicated = (c->cfg.world > 1 && c->world == 1) ? 1u : 0u; o->n_aggregates = c->d.nA;
     o->n_ml_levels = c->d.mlLv; o->n_ml_top = c->d.mlLv ? c->d.ml[c->d.mlLv - 1].n : 0;
     return TSB_OK;

@@ -127,6 +127,9 @@ struct Dev {
     //   + Z_top S_top^-1 Z_top^T; the top level uses Ac / Ai / yc / cdot above with nc = 3 * ml[mlLv - 1].n
     uint32_t mlLv, mlLocal, mlWin, mlCdot;   // levels, window-local levels, restriction windows, entries of cdot
     const uint32_t* tl_ptr; const uint32_t* tl_edge; const uint32_t* tl_node;   // landmark-major CSR over the top level's coarse edges
+    // the top level as k_ml_top sees it: world == 1 the last level's own arrays; sharded: the top levels of all ranks
+    // concatenated (node index = xc.top_off + local node), C gathered from the peers before every assembly
+    const uint32_t* gt_node_ptr; const uint32_t* gt_edge_lm; double* gtC; uint32_t gt_nnz;
     XDev xc;                    // peer exchange (xc.world <= 1: none)
     double* r2;                 // second residual buffer (the restriction recomputes halo poses: r ping-pongs between r and r2)
     MlDev ml[kMlMaxLevels];
@@ -138,7 +141,8 @@ void launch_lm_sum(const Dev& d, bool finalize, cudaStream_t s);   // K2a: landm
 void launch_lm_finalize(const Dev& d, cudaStream_t s);          // K2b: Hll, b_l, prior, Hll^-1; chi2
 void launch_schur_prep(const Dev& d, cudaStream_t s);           // K3: diag(S)^-1 and reduced rhs
 void launch_coarse_assemble(const Dev& d, cudaStream_t s);      // zoff, C, Ac = Z^T S Z (dense, deterministic)
-void launch_ml_setup(const Dev& d, cudaStream_t s);             // multilevel: C_l, blockdiag(S_l)^-1, dense top operator into Ac
+void launch_ml_levels(const Dev& d, cudaStream_t s);            // multilevel: C_l and blockdiag(S_l)^-1 level by level
+void launch_ml_top(const Dev& d, cudaStream_t s);               // this rank's block rows of the dense top operator into Ac
 bool launch_pcg_stream(const Dev& d, cudaStream_t s);           // streamed persistent PCG (no back-substitution)
 bool launch_coarse_invert(const Dev& d, cudaStream_t s);        // Ai = Ac^-1 + F_COARSE, one cooperative launch (blocked Gauss-Jordan)
 void launch_pcg_coarse(const Dev& d, int init, cudaStream_t s);           // yc = Ac^-1 Z^T r, cdot (phased path)

@@ -1143,16 +1143,18 @@ void launch_coarse_assemble(const Dev& d, cudaStream_t s) {
     k_coarse_pose<<<cdiv(d.nA * 32, kThreads), kThreads, 0, s>>>(d); ++g_launches;
     if (d.nPairs) { k_coarse_lm<<<cdiv(d.nPairs, 128), 128, 0, s>>>(d); ++g_launches; }
 }
-// multilevel setup (mlevel.cuh): C_l level by level, blockdiag(S_l)^-1 below the top, the dense top operator into Ac
-void launch_ml_setup(const Dev& d, cudaStream_t s) {
-    if (!d.mlLv) return;
-    static size_t top_smem = 0;
+// multilevel setup (mlevel.cuh)
+void launch_ml_levels(const Dev& d, cudaStream_t s) {
     for (uint32_t l = 0; l < d.mlLv; ++l) {
         const uint32_t nb = cdiv(d.ml[l].n * 32, 256);
         if (l == 0) k_ml_C<true><<<nb, 256, 0, s>>>(d, 0); else k_ml_C<false><<<nb, 256, 0, s>>>(d, (int)l);
         ++g_launches;
         if (l + 1 < d.mlLv) { k_ml_D<<<nb, 256, 0, s>>>(d, (int)l); ++g_launches; }
     }
+}
+void launch_ml_top(const Dev& d, cudaStream_t s) {
+    if (!d.mlLv) return;
+    static size_t top_smem = 0;
     const size_t smem = sizeof(double) * 3 * d.nc;
     if (smem > top_smem) { cudaFuncSetAttribute(k_ml_top, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); top_smem = smem; }
     k_ml_top<<<d.ml[d.mlLv - 1].n, kMlTopThreads, smem, s>>>(d, d.tl_ptr, d.tl_edge, d.tl_node); ++g_launches;

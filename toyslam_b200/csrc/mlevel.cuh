@@ -135,14 +135,14 @@ __global__ void __launch_bounds__(kMlTopThreads) k_ml_top(const Dev d, const uin
                                                           const uint32_t* __restrict__ tl_node) {
     extern __shared__ __align__(16) double ml_row[];         // [3][nc]
     const MlDev& lv = d.ml[d.mlLv - 1];
-    const uint32_t K = blockIdx.x, nc = d.nc, tid = threadIdx.x, s = lv.spacing, n = lv.n;
+    const uint32_t K = blockIdx.x, nc = d.nc, tid = threadIdx.x, s = lv.spacing, n = lv.n, off = d.xc.top_off, Kg = off + K;
     for (uint32_t k = tid; k < 3 * nc; k += kMlTopThreads) ml_row[k] = 0;
     __syncthreads();
     const double4 pc = d.pose[(size_t)K * s];
     if (tid < 9) {
         const int r = tid / 3, c = tid % 3;
         uint32_t lo, hi; ml_support(d, K, s, n, lo, hi);
-        double* rowp = ml_row + (size_t)r * nc;
+        double* rowp = ml_row + (size_t)r * nc + 3 * off;     // local node Kp -> column block off + Kp
         for (uint32_t i = lo; i < hi; ++i) {
             const double wi = ml_pose_weight(i, K, s, n);
             const double4 pi = d.pose[i];
@@ -164,7 +164,7 @@ __global__ void __launch_bounds__(kMlTopThreads) k_ml_top(const Dev d, const uin
                 for (uint32_t kk = kb; kk < ke; ++kk) {
                     const uint32_t k = pass == 0 ? kk : d.od_in_edge[kk];
                     const uint32_t j = pass == 0 ? d.od_b[k] : d.od_a[k];
-                    if (j >= d.nP) continue;                              // pose of another rank
+                    if (j >= d.nP) continue;                              // pose of another rank: the cut edge stays out of the top operator
                     const double* h = d.hoo + 3ull * k;
                     const double4 pj = d.pose[j];
                     const uint32_t qj = j / s, remj = j - qj * s;
@@ -181,11 +181,11 @@ __global__ void __launch_bounds__(kMlTopThreads) k_ml_top(const Dev d, const uin
         }
     }
     __syncthreads();
-    // landmark part
-    const double2* C = reinterpret_cast<const double2*>(lv.C);
-    const size_t cs = lv.nnz;
-    for (uint32_t e = lv.node_ptr[K]; e < lv.node_ptr[K + 1]; ++e) {
-        const uint32_t lm = lv.edge_lm[e];
+    // landmark part (global lists: the partner node of a landmark may live on another rank)
+    const double2* C = reinterpret_cast<const double2*>(d.gtC);
+    const size_t cs = d.gt_nnz;
+    for (uint32_t e = d.gt_node_ptr[Kg]; e < d.gt_node_ptr[Kg + 1]; ++e) {
+        const uint32_t lm = d.gt_edge_lm[e];
         const uint32_t t0 = tl_ptr[lm], t1 = tl_ptr[lm + 1];
         bool mine = false;
         for (uint32_t q = t0; q < t1; ++q) if (tl_node[q] % kMlTopThreads == tid) { mine = true; break; }
@@ -208,7 +208,7 @@ __global__ void __launch_bounds__(kMlTopThreads) k_ml_top(const Dev d, const uin
         }
     }
     __syncthreads();
-    double* out = d.Ac + (size_t)(3 * K) * nc;
+    double* out = d.Ac + (size_t)(3 * Kg) * nc;
     for (uint32_t k = tid; k < 3 * nc; k += kMlTopThreads) out[k] = ml_row[k];
 }
 
@@ -228,7 +228,7 @@ __device__ __forceinline__ void ml_prolong(const Dev& d, uint32_t i, double px, 
     {   // top level: e = yc, node position read from the pose array
         const MlDev& lv = d.ml[top];
         const uint32_t q = i / lv.spacing, rem = i - q * lv.spacing;
-        const double* e = d.yc + 3ull * q;
+        const double* e = d.yc + 3ull * (d.xc.top_off + q);
         const double4 c0 = d.pose[(size_t)q * lv.spacing];
         const double g0x = e[0] + c0.y * e[2], g0y = e[1] - c0.x * e[2];
         if (q + 1 >= lv.n || rem == 0) { gx += g0x; gy += g0y; gt += e[2]; }
@@ -391,4 +391,33 @@ __device__ __forceinline__ void ml_coarse_phase(const Dev& d, uint32_t gtid, uin
     }
     __syncthreads();
     coarse_matvec(d, gtid >> 5, gsz >> 5, rc_s, rc_smem);
+}
+
+// Sharded (peer exchange): the same in two steps with the exchange between them.  Step 1: the upper levels of this rank
+// and the corrected top-level residual of this rank's top nodes, pushed into every rank's copy of the global top residual.
+__device__ __forceinline__ void ml_coarse_push(const Dev& d, uint32_t gtid, uint32_t gsz) {
+    const uint32_t Lv = d.mlLv, top = Lv - 1, nloc = d.mlLocal;
+    for (uint32_t l = nloc; l < top; ++l) {
+        const MlDev& lv = d.ml[l];
+        for (uint32_t K = gtid; K < lv.n; K += gsz) {
+            double mx, my, mt; ml_upper_sum(d, lv, K, mx, my, mt);
+            d.cdot[lv.cdot_off + K] = ml_finalize(d, lv, K, mx, my, mt);
+        }
+    }
+    const MlDev& lv = d.ml[top];
+    for (uint32_t K = gtid; K < lv.n; K += gsz) {
+        double mx, my, mt;
+        if (top < nloc) { const double* m = lv.m + 3ull * K; mx = m[0]; my = m[1]; mt = m[2]; }
+        else ml_upper_sum(d, lv, K, mx, my, mt);
+        const double4 pc = d.pose[(size_t)K * lv.spacing];
+        const double r2 = mt + pc.y * mx - pc.x * my;
+        for (uint32_t r = 0; r < d.xc.world; ++r) {
+            double* o = x_ptr(d, r, d.xc.o_top) + 3ull * (d.xc.top_off + K);
+            o[0] = mx; o[1] = my; o[2] = r2;
+        }
+    }
+}
+// Step 2 (after the exchange): yc = Ai r_top with the global top residual read from the own region; the same on every rank
+__device__ __forceinline__ void ml_coarse_top(const Dev& d, uint32_t gtid, uint32_t gsz, double* rc_smem) {
+    coarse_matvec(d, gtid >> 5, gsz >> 5, x_ptr(d, d.xc.rank, d.xc.o_top), rc_smem);
 }

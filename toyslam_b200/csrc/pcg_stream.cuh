@@ -253,19 +253,25 @@ __global__ void __launch_bounds__(kPsThreads, 2) k_pcg_stream(const Dev d) {
     else rc_shared = ps_pose_phase<true>(d, 0.0, coarse, dot);
     double t = block_sum(dot, red);
     if (tid == 0) d.part[blockIdx.x] = t;
-    res_gsync(grid, d.gbar, gtarget);
-    if (coarse) {
-        if (ml) ml_coarse_phase(d, gtid, gsz, rc_s, crow);
-        else if (crow) coarse_phase(d, gtid >> 5, gsz >> 5, rc_s, rc_shared);
-        res_gsync(grid, d.gbar, gtarget);
-    }
     // world > 1 (peer exchange, xchg.cuh): the ranks' parts of every scalar are added in rank order -- every rank sees
-    // the same bits and takes the same branches
+    // the same bits and takes the same branches.  With the hierarchy the top level is GLOBAL: every rank pushes the
+    // residual of its top nodes to all ranks, the dense mat-vec and its part of r'z are replicated.
     const bool xp = d.xc.world > 1;
     unsigned long long xv = d.xc.seq;
-    double rz0 = reduce_all(d.part, nb, red);
-    if (coarse) rz0 += reduce_all(d.cdot, ncdot, red);
-    if (xp) rz0 = x_scalar_sum(d, 3, XP_TOP, ++xv, rz0);
+    res_gsync(grid, d.gbar, gtarget);
+    auto coarse_step = [&]() -> double {
+        if (coarse) {
+            if (ml && xp) { ml_coarse_push(d, gtid, gsz); x_gsync(grid, d, gtarget, XP_TOP, ++xv); if (crow) ml_coarse_top(d, gtid, gsz, rc_s); }
+            else if (ml) ml_coarse_phase(d, gtid, gsz, rc_s, crow);
+            else if (crow) coarse_phase(d, gtid >> 5, gsz >> 5, rc_s, rc_shared);
+            res_gsync(grid, d.gbar, gtarget);
+        }
+        double v = reduce_all(d.part, nb, red);
+        if (ml && xp) { v += reduce_all(d.cdot + d.nc, ncdot - d.nc, red); v = x_scalar_sum(d, 3, XP_TOP, ++xv, v); v += reduce_all(d.cdot, d.nc, red); }
+        else { if (coarse) v += reduce_all(d.cdot, ncdot, red); if (xp) v = x_scalar_sum(d, 3, XP_TOP, ++xv, v); }
+        return v;
+    };
+    double rz0 = coarse_step();
     double rz = rz0, beta = 0;
     const double tol2 = d.scal[S_TOL2]; const int maxit = d.flags[F_MAXIT];
     int it = 0;
@@ -311,15 +317,8 @@ __global__ void __launch_bounds__(kPsThreads, 2) k_pcg_stream(const Dev d) {
             if (tid == 0) d.part[blockIdx.x] = t;
             TICK(6);
             res_gsync(grid, d.gbar, gtarget);
-            if (coarse) {
-                if (ml) ml_coarse_phase(d, gtid, gsz, rc_s, crow);
-                else if (crow) coarse_phase(d, gtid >> 5, gsz >> 5, rc_s, rc_shared);
-                res_gsync(grid, d.gbar, gtarget);
-            }
+            const double rz_new = coarse_step();
             TICK(7);
-            double rz_new = reduce_all(d.part, nb, red);
-            if (coarse) rz_new += reduce_all(d.cdot, ncdot, red);
-            if (xp) rz_new = x_scalar_sum(d, 3, XP_TOP, ++xv, rz_new);
             beta = rz_new / rz; rz = rz_new; ++it;
             if (!(rz_new > tol2 * rz0) || it >= maxit) break;
         }

@@ -71,21 +71,30 @@ void build_ml_level(const std::vector<uint32_t>& cptr, const std::vector<uint32_
 
 // Hierarchy over the nP local poses: ratio 4 per level (a final ratio of 2 where 4 would leave the exactly-solved top
 // level with fewer than top_max / 2 nodes); no level at all for graphs with <= 64 poses (block-Jacobi is enough there).
+// level plan of nP consecutive poses: (ratio, spacing) per level; returns the nodes of the top level (0: no hierarchy)
+uint32_t ml_plan(uint32_t nP, uint32_t top_max, std::vector<std::pair<uint32_t, uint32_t>>* levels = nullptr) {
+    if (levels) levels->clear();
+    if (nP <= 64 || top_max < 8) return 0;
+    uint32_t n = nP, spacing = 1, cnt = 0;
+    bool first = true;
+    while ((first || n > top_max) && cnt < kMlMaxLevels) {
+        const uint32_t ratio = (!first && (n + 1) / 2 <= top_max) ? 2u : 4u;
+        spacing *= ratio; n = (n + ratio - 1) / ratio; ++cnt; first = false;
+        if (levels) levels->emplace_back(ratio, spacing);
+    }
+    return n;
+}
 void build_hierarchy(Structure& s, const std::vector<uint32_t>& elm, uint32_t top_max) {
     s.ml.clear(); s.ml_local = 0;
     s.ml.reserve(kMlMaxLevels);                  // the loop keeps pointers into the previous level
-    const uint32_t nP = s.nP;
-    if (nP <= 64 || top_max < 8) return;
-    uint32_t n = nP, spacing = 1;
+    std::vector<std::pair<uint32_t, uint32_t>> plan;
+    if (!ml_plan(s.nP, top_max, &plan)) return;
     const std::vector<uint32_t>* cptr = &s.pose_ptr; const std::vector<uint32_t>* clm = &elm;
-    bool first = true;
-    while ((first || n > top_max) && s.ml.size() < kMlMaxLevels) {
-        const uint32_t ratio = (!first && (n + 1) / 2 <= top_max) ? 2u : 4u;
-        spacing *= ratio;
+    for (const auto& lv : plan) {
         s.ml.emplace_back();
-        build_ml_level(*cptr, *clm, ratio, spacing, s.ml.back());
-        if (ratio == 4 && spacing <= kMlHalo && s.ml_local + 1 == s.ml.size()) s.ml_local = (uint32_t)s.ml.size();
-        n = s.ml.back().n; cptr = &s.ml.back().node_ptr; clm = &s.ml.back().edge_lm; first = false;
+        build_ml_level(*cptr, *clm, lv.first, lv.second, s.ml.back());
+        if (lv.first == 4 && lv.second <= kMlHalo && s.ml_local + 1 == s.ml.size()) s.ml_local = (uint32_t)s.ml.size();
+        cptr = &s.ml.back().node_ptr; clm = &s.ml.back().edge_lm;
     }
 }
 
@@ -306,15 +315,25 @@ void build_structure(const HostGraph& g, uint32_t rank, uint32_t world, Structur
                 }
             } else *rp = ResidentPlan();
         }
-        if (!resident && ml_top > 0) {
+        // sharded: every rank builds the hierarchy of its own pose range; the top levels of all ranks together form the
+        // exactly-solved global top level (ml_top nodes in total), so every rank needs every rank's node count -- and a
+        // rank too small for a hierarchy switches it off everywhere (the ranks must take the same kernel phases)
+        uint32_t top_rank = ml_top;
+        if (ml_top > 0 && world > 1) {
+            top_rank = std::max<uint32_t>(16, ml_top / world);
+            s.top_nodes.assign(world, 0);
+            for (uint32_t r = 0; r < world; ++r) { s.top_nodes[r] = ml_plan(s.cuts[r + 1] - s.cuts[r], top_rank); if (!s.top_nodes[r]) top_rank = 0; }
+            if (!top_rank) s.top_nodes.clear();
+        }
+        if (!resident && top_rank > 0) {
             // streamed PCG: multilevel hierarchy instead of the uniform aggregates (no aslots, no block pairs)
-            build_hierarchy(s, elm, ml_top);
+            build_hierarchy(s, elm, top_rank);
             s.agg_K = 32; s.nA = 0; s.agg_ptr.assign(1, 0);
             s.aslot_ptr.push_back(0); s.cpair_ptr.push_back(0);
             s.edge_pose.resize(nE);
             for (uint32_t p = 0; p < nP; ++p) for (uint32_t k = s.pose_ptr[p]; k < s.pose_ptr[p + 1]; ++k) s.edge_pose[k] = p;
         }
-        const bool use_ml = !resident && ml_top > 0;
+        const bool use_ml = !resident && top_rank > 0;
         if (!resident && !use_ml) {
             uint32_t K = 32;
             if (nP > 32ull * kCoarseMaxAggLarge) K = 32 * (uint32_t)((nP + 32ull * kCoarseMaxAggLarge - 1) / (32ull * kCoarseMaxAggLarge));
