@@ -148,6 +148,27 @@ int tsb_get_transfer_bytes(const tsb_ctx* ctx, uint64_t* h2d, uint64_t* d2h);
 int tsb_reply_size(tsb_ctx* ctx, uint32_t* nbytes);
 int tsb_write_reply(tsb_ctx* ctx, void* out, uint32_t capacity);
 
+/* ODOM edges without any allocation.  No counterpart in the reference: added for
+ * callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * Evaluates every ODOM edge at the given state with the arithmetic of the pose-parallel ODOM kernel behind
+ * tsb_linearize (EdgeSe2.h:24-38 residual, Huber weight of OptimizerCpu.h:36-46):
+ *   hpp_off[3k..]  diagonal of the (i,j) Hessian block of edge k, = what tsb_read_system returns as hpp_off
+ *   w_e[3k..]      W e of edge k (b_i += W e, b_j -= W e)
+ *   chi2[0]        sum of the robustified edge errors (== tsb_iter_stats.chi2 of an ODOM-only graph)
+ * Every pointer is a DEVICE pointer owned by the caller (poses 3 per pose as x, y, theta; edge_ij 2 per edge, indices
+ * into the pose array; edge_zinv 6 per edge, the top two rows of inverse(Z); edge_w 3 per edge, information diagonal).
+ * `stream` is a cudaStream_t (NULL: the default stream); the call enqueues two kernels and returns without
+ * synchronising.  No context is needed and nothing is allocated or freed: the per-block chi2 partials live in a static
+ * device array of TSB_NOALLOC_MAX_ODOM_EDGES / 256 doubles (32 KB per GPU that loads the library, until exit).  More
+ * edges are rejected with TSB_EINVAL.  The array is shared by all calls in the process and keeps the last call's
+ * contents (every launch overwrites what it reads): calls that overlap on the GPU race on it -- serialise them.
+ * `err` (may be NULL) receives a message of at most err_cap bytes on failure. */
+#define TSB_NOALLOC_MAX_ODOM_EDGES 1048576
+int tsb_odom_linearize_noalloc(int32_t device, void* stream, uint32_t n_pose, uint32_t n_edge,
+                               const double* pose_xytheta, const uint32_t* edge_ij, const double* edge_zinv,
+                               const double* edge_w, double* hpp_off, double* w_e, double* chi2,
+                               char* err, uint32_t err_cap);
+
 #ifdef __cplusplus
 }
 #endif

@@ -20,7 +20,7 @@ LIB_PATH = os.path.join(_HERE, "libtoyslam_b200.so")
 SYMBOLS = ["tsb_nccl_unique_id", "tsb_create", "tsb_destroy", "tsb_last_error", "tsb_load_wire", "tsb_load_soa", "tsb_get_counts", "tsb_host_plan",
            "tsb_reset_state", "tsb_set_state", "tsb_linearize", "tsb_solve", "tsb_optimize", "tsb_read_ids",
            "tsb_read_state", "tsb_read_delta", "tsb_get_transfer_bytes", "tsb_read_system", "tsb_read_structure", "tsb_reply_size",
-           "tsb_write_reply"]
+           "tsb_write_reply", "tsb_odom_linearize_noalloc"]
 
 
 class Config(C.Structure):
@@ -82,6 +82,19 @@ def nccl_unique_id() -> bytes:
     if rc:
         raise TsbError(rc, lib().tsb_last_error(None).decode())
     return buf.raw
+
+
+NOALLOC_MAX_ODOM_EDGES = 1048576
+
+
+def odom_linearize_noalloc(device, stream, n_pose, n_edge, pose_xyt, edge_ij, edge_zinv, edge_w, hpp_off, w_e, chi2):
+    """tsb_odom_linearize_noalloc: every array argument is a DEVICE pointer (int); nothing is allocated.  Raises TsbError."""
+    err = C.create_string_buffer(256)
+    vp = lambda a: C.c_void_p(int(a) if a else None)
+    rc = lib().tsb_odom_linearize_noalloc(C.c_int32(device), vp(stream), C.c_uint32(n_pose), C.c_uint32(n_edge), vp(pose_xyt), vp(edge_ij),
+                                          vp(edge_zinv), vp(edge_w), vp(hpp_off), vp(w_e), vp(chi2), err, C.c_uint32(256))
+    if rc:
+        raise TsbError(rc, err.value.decode())
 
 
 def host_plan(payload: bytes, rank: int, world: int):

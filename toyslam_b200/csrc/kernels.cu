@@ -18,8 +18,10 @@
 // one unit so that the same code serves the one-launch-per-phase kernels and the persistent
 // cooperative PCG kernel.
 #include "device_graph.h"
+#include "../../include/toyslam_b200.h"
 
 #include <cooperative_groups.h>
+#include <cstdio>
 #include <cstdlib>
 namespace cg = cooperative_groups;
 
@@ -1315,3 +1317,101 @@ void launch_read_pose(const double4* pose, uint32_t n, double* xyt, cudaStream_t
 }
 
 }  // namespace tsb
+
+// ------------------------------------------------------------------------------------------------
+// tsb_odom_linearize_noalloc (include/toyslam_b200.h): the ODOM edge kernel for callers that must not allocate.
+// No counterpart in the reference.
+//
+// k_odom leaves one chi2 partial per thread block in context scratch (Dev::part2, from the context's arena) and a
+// second launch adds them in a fixed order.  This variant keeps that scratch in a file-scope device array of
+// kNaMaxBlocks doubles (32 KB, held by every GPU that loads the library until the process exits), so the call needs no
+// context and performs no cudaMalloc / cudaFree: the caller passes device pointers for every input and output.
+// Edge-parallel (one thread per edge, same odom_edge() arithmetic as k_odom); chi2 = block partials added in block order.
+//
+// The array is shared by every call in the process and keeps the previous call's contents.  A launch writes partials
+// [0, blocks) before the reduction reads exactly those, so nothing has to start at zero and stale entries beyond
+// `blocks` are never read.  Calls that overlap on the GPU (different streams, or several host threads) RACE on it:
+// serialise them.
+// ------------------------------------------------------------------------------------------------
+namespace tsb {
+constexpr uint32_t kNaMaxBlocks = 4096;                                   // x kThreads edges = TSB_NOALLOC_MAX_ODOM_EDGES
+constexpr int kNaMaxDevices = 64;
+}
+static __device__ __align__(256) double g_na_scratch[tsb::kNaMaxBlocks];
+static_assert(tsb::kNaMaxBlocks * tsb::kThreads == TSB_NOALLOC_MAX_ODOM_EDGES, "header constant");
+
+namespace tsb {
+namespace {
+
+__global__ void __launch_bounds__(kThreads) k_odom_noalloc(uint32_t nP, uint32_t nE, const double* __restrict__ xyt,
+                                                           const uint32_t* __restrict__ ij, const double* __restrict__ zinv,
+                                                           const double* __restrict__ w, double* __restrict__ hoff,
+                                                           double* __restrict__ we, double* __restrict__ part) {
+    __shared__ double red[32];
+    const uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
+    double rho = 0;
+    if (k < nE) {
+        const uint32_t i = ij[2ull * k], j = ij[2ull * k + 1];
+        double W[3] = {0, 0, 0}, We[3] = {0, 0, 0};
+        if (i < nP && j < nP) {                                           // an edge with an id out of range contributes nothing
+            double4 a, b;
+            {   // CreateTransform2d (Helper.h:6-18), as k_init_pose
+                double sh, ch; sincos(0.5 * xyt[3ull * i + 2], &sh, &ch); const double tz = 2.0 * sh;
+                a = make_double4(xyt[3ull * i], xyt[3ull * i + 1], 1.0 - tz * sh, tz * ch);
+                sincos(0.5 * xyt[3ull * j + 2], &sh, &ch); const double ty = 2.0 * sh;
+                b = make_double4(xyt[3ull * j], xyt[3ull * j + 1], 1.0 - ty * sh, ty * ch);
+            }
+            odom_edge(a, b, zinv + 6ull * k, w + 3ull * k, W, We, rho);
+        }
+        hoff[3ull * k] = -W[0]; hoff[3ull * k + 1] = -W[1]; hoff[3ull * k + 2] = -W[2];     // H_ij = A^T W B, A = -I, B = +I
+        we[3ull * k] = We[0]; we[3ull * k + 1] = We[1]; we[3ull * k + 2] = We[2];
+    }
+    const double t = block_sum(rho, red);
+    if (threadIdx.x == 0) part[blockIdx.x] = t;
+}
+__global__ void k_odom_noalloc_sum(const double* __restrict__ part, uint32_t n, double* __restrict__ chi2) {
+    __shared__ double red[32];
+    const double r = reduce_all(part, n, red);
+    if (threadIdx.x == 0) *chi2 = r;
+}
+
+}  // namespace
+}  // namespace tsb
+
+extern "C" int tsb_odom_linearize_noalloc(int32_t device, void* stream, uint32_t n_pose, uint32_t n_edge,
+                                          const double* pose_xytheta, const uint32_t* edge_ij, const double* edge_zinv,
+                                          const double* edge_w, double* hpp_off, double* w_e, double* chi2,
+                                          char* err, uint32_t err_cap) {
+    using namespace tsb;
+    static double* scratch_of[kNaMaxDevices] = {};       // device address of g_na_scratch, per device ordinal
+    auto fail = [&](int code, const char* msg, const char* detail) {
+        if (err && err_cap) std::snprintf(err, err_cap, "tsb_odom_linearize_noalloc: %s%s%s", msg, detail ? ": " : "", detail ? detail : "");
+        return code;
+    };
+    if (err && err_cap) err[0] = 0;
+    if (n_edge > TSB_NOALLOC_MAX_ODOM_EDGES) {
+        char d[96]; std::snprintf(d, sizeof d, "%u edges, the static scratch holds partials for at most %u", n_edge, (unsigned)TSB_NOALLOC_MAX_ODOM_EDGES);
+        return fail(1 /* TSB_EINVAL */, "too many ODOM edges", d);
+    }
+    if (!chi2 || (n_edge && (!pose_xytheta || !edge_ij || !edge_zinv || !edge_w || !hpp_off || !w_e))) return fail(1, "null pointer", nullptr);
+    if (device < 0 || device >= kNaMaxDevices) return fail(1, "bad device ordinal", nullptr);
+    cudaError_t e = cudaSetDevice(device);
+    if (e != cudaSuccess) return fail(3 /* TSB_ECUDA */, "cudaSetDevice", cudaGetErrorString(e));
+    if (!scratch_of[device]) {
+        // g_na_scratch names a host-side stand-in here: the device address comes from the runtime, once per device
+        double* p = nullptr;
+        e = cudaGetSymbolAddress((void**)&p, g_na_scratch);
+        if (e != cudaSuccess || !p) return fail(3, "cudaGetSymbolAddress", cudaGetErrorString(e));
+        scratch_of[device] = p;
+    }
+    double* part = scratch_of[device];
+    cudaStream_t s = (cudaStream_t)stream;
+    const uint32_t blocks = (n_edge + kThreads - 1) / kThreads;
+    if (blocks) {
+        k_odom_noalloc<<<blocks, kThreads, 0, s>>>(n_pose, n_edge, pose_xytheta, edge_ij, edge_zinv, edge_w, hpp_off, w_e, part); ++g_launches;
+    }
+    k_odom_noalloc_sum<<<1, 1024, 0, s>>>(part, blocks, chi2); ++g_launches;
+    e = cudaGetLastError();
+    if (e != cudaSuccess) return fail(3, "kernel launch", cudaGetErrorString(e));
+    return 0;
+}
