@@ -457,6 +457,9 @@ int run_solve(tsb_ctx* c, bool refresh_coarse = true, bool smoother = true) {
             cudaEventRecord(te[2], c->stream); cudaEventSynchronize(te[2]);
             float a = 0, b = 0; cudaEventElapsedTime(&a, te[0], te[1]); cudaEventElapsedTime(&b, te[1], te[2]);
             std::fprintf(stderr, "[tsb] coarse setup nc=%u (%u levels): assemble %.3f ms, k_coarse_invert %.3f ms\n", d.nc, d.mlLv, a, b);
+            if (d.mlLv) { long long t[8] = {}; cudaMemcpy(t, d.dbg + 8, sizeof(t), cudaMemcpyDeviceToHost);
+                std::fprintf(stderr, "[tsb] k_ml_top, cycles of a middle block (%lld coarse edges): pose part %lld, landmark part %lld (stage edges %lld, stage pairs %lld, "
+                             "own walk of thread 0 %lld, wait for the other owners %lld), write-out %lld\n", t[7], t[0], t[1], t[3], t[4], t[5], t[6], t[2]); }
             for (auto& ev : te) cudaEventDestroy(ev);
         }
     }

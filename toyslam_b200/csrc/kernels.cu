@@ -623,6 +623,11 @@ __device__ __forceinline__ double coarse_restrict(const Dev& d, uint32_t k) {
     return t;
 }
 // `shared_rc`: Z^T r was left in d.rcs[0 .. nc) by a preceding launch (k_pcg_restrict, phased path, large coarse spaces)
+// does this block take part in the dense coarse mat-vec?  Large coarse spaces: every block that gets at least one group
+// of four rows; small ones: blocks whose first warp has a row
+__device__ __forceinline__ bool coarse_row_owner(const Dev& d) {
+    return d.nc > 3 * kCoarseMaxAgg ? 4 * blockIdx.x < d.nc : blockIdx.x * (blockDim.x >> 5) < d.nc;
+}
 // yc = Ai rc_s and cdot_j = yc_j rc_s_j; rc_s holds the coarse residual (shared memory for nc <= 3 kCoarseMaxAgg, else a
 // global scratch row); rc_smem: the block's shared scratch (reduction space in the large mode)
 __device__ __forceinline__ void coarse_matvec(const Dev& d, uint32_t gwarp, uint32_t nwarps, const double* rc_s, double* rc_smem) {
@@ -633,7 +638,7 @@ __device__ __forceinline__ void coarse_matvec(const Dev& d, uint32_t gwarp, uint
         // behind a handful of loads in flight (C4: 190 us for 275 MB).  Here a whole block takes four rows at a time,
         // every thread with 4 x nc / blockDim independent loads; warp xor tree, then the warps' partials in warp order.
         const uint32_t wpb = blockDim.x >> 5, warp = threadIdx.x >> 5;
-        const uint32_t nblk = min(nwarps / wpb, (nc + wpb - 1) / wpb), bidx = gwarp / wpb;      // blocks that own coarse rows
+        const uint32_t nblk = min(nwarps / wpb, (nc + 3) / 4), bidx = gwarp / wpb;      // blocks that own coarse rows: coarse_row_owner()
         double* red = rc_smem;                                   // shared memory is free in this mode (rc_s is global)
         for (uint32_t j0 = 4 * bidx; j0 < nc; j0 += 4 * nblk) {
             const uint32_t nr = min(4u, nc - j0);
@@ -898,7 +903,7 @@ __global__ void __launch_bounds__(kThreads, 3) k_pcg_persistent(const Dev d) {
     const uint32_t nb = gridDim.x, gtid = blockIdx.x * kThreads + threadIdx.x, gsz = nb * kThreads;
     const bool coarse = d.flags[F_COARSE] != 0;
     const uint32_t nP32 = (d.nP + 31u) & ~31u;                      // whole warps take part in the restriction
-    const bool crow = coarse && blockIdx.x * (kThreads / 32) < d.nc;   // this block owns coarse rows
+    const bool crow = coarse && coarse_row_owner(d);   // this block owns coarse rows
     double dot = 0;
     for (uint32_t i = gtid; i < nP32; i += gsz) dot += pose_step<true>(d, i, i < d.nP, 0.0, coarse);
     double t = block_sum(dot, sm.red);
@@ -1185,7 +1190,7 @@ void launch_pcg_coarse(const Dev& d, int init, cudaStream_t s) {
     if (!d.nc) return;
     if (d.nc > 3 * kCoarseMaxAgg) {          // block-per-4-rows mat-vec: one block per SM-slot is enough, the rows stream from HBM
         k_pcg_restrict<<<cdiv(d.nc, kThreads), kThreads, 0, s>>>(d, init); ++g_launches;
-        k_pcg_coarse<<<min(cdiv(d.nc, kThreads / 32), 148u * 4u), kThreads, 0, s>>>(d, init); ++g_launches;   // grid <= cdiv(nc, warps per block): see nblk in coarse_phase
+        k_pcg_coarse<<<min(cdiv(d.nc, 4u), 148u * 4u), kThreads, 0, s>>>(d, init); ++g_launches;   // grid <= groups of four rows: see nblk in coarse_matvec
         return;
     }
     k_pcg_coarse<<<cdiv(d.nc, kThreads / 32), kThreads, 0, s>>>(d, init); ++g_launches;

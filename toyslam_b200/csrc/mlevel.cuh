@@ -136,41 +136,112 @@ __global__ void __launch_bounds__(kMlTopThreads) k_ml_top(const Dev d, const uin
     extern __shared__ __align__(16) double ml_row[];         // [3][nc]
     const MlDev& lv = d.ml[d.mlLv - 1];
     const uint32_t K = blockIdx.x, nc = d.nc, tid = threadIdx.x, s = lv.spacing, n = lv.n, off = d.xc.top_off, Kg = off + K;
+    const bool timing = d.dbg != nullptr && K == n / 2 && tid == 0;      // TSB_PCG_TIMING=1: cycles of one middle block per part
+    long long tk0 = timing ? clock64() : 0;
     for (uint32_t k = tid; k < 3 * nc; k += kMlTopThreads) ml_row[k] = 0;
     __syncthreads();
     const double4 pc = d.pose[(size_t)K * s];
-    if (tid < 9) {
-        const int r = tid / 3, c = tid % 3;
-        uint32_t lo, hi; ml_support(d, K, s, n, lo, hi);
-        double* rowp = ml_row + (size_t)r * nc + 3 * off;     // local node Kp -> column block off + Kp
-        for (uint32_t i = lo; i < hi; ++i) {
-            const double wi = ml_pose_weight(i, K, s, n);
-            const double4 pi = d.pose[i];
-            double a0, a1, a2; zcol(make_double2(-(pi.y - pc.y), pi.x - pc.x), r, a0, a1, a2);
-            // the two nodes pose i interpolates from (one of them is K)
+    // ---- pose part.  Hpp_ii couples node K with the chain neighbours its hat overlaps; an ODOM edge couples it with the
+    // nodes of the other end.  For a chain (and any ODOM edge whose other end lies in K-1 .. K+1) a thread per support
+    // pose adds into 3 x 9 register accumulators [Kp - K + 1][r][c]; warp xor tree, then the warps in order: deterministic.
+    // ODOM edges that reach farther (loop-closure odometry) are walked sequentially by one lane per entry afterwards.
+    __shared__ double ml_red[(kMlTopThreads / 32) * 27];
+    uint32_t lo, hi; ml_support(d, K, s, n, lo, hi);
+    double acc[3][9];
+#pragma unroll
+    for (int q = 0; q < 3; ++q)
+#pragma unroll
+        for (int e = 0; e < 9; ++e) acc[q][e] = 0;
+    int far = 0;
+    // acc[dk] += w * R(zx, zy)^T B R(yx, yy) with R(a, b) = [[1, 0, a], [0, 1, b], [0, 0, 1]], for the target node K + dk - 1
+    auto add = [&](int dk, double w, double zx, double zy, const double* B, double yx, double yy) {
+        double X[9];
+#pragma unroll
+        for (int r = 0; r < 3; ++r) { X[3 * r] = B[3 * r]; X[3 * r + 1] = B[3 * r + 1]; X[3 * r + 2] = yx * B[3 * r] + yy * B[3 * r + 1] + B[3 * r + 2]; }
+#pragma unroll
+        for (int q = 0; q < 3; ++q)
+            if (dk == q) {
+#pragma unroll
+                for (int c = 0; c < 3; ++c) { acc[q][c] += w * X[c]; acc[q][3 + c] += w * X[3 + c]; acc[q][6 + c] += w * (zx * X[c] + zy * X[3 + c] + X[6 + c]); }
+            }
+    };
+    for (uint32_t i = lo + tid; i < hi; i += kMlTopThreads) {
+        const double wi = ml_pose_weight(i, K, s, n);
+        const double4 pi = d.pose[i];
+        const double zx = -(pi.y - pc.y), zy = pi.x - pc.x;
+        {   // Hpp_ii against the (one or two) nodes pose i interpolates from
+            const double* H = d.hpp + 6ull * i;
+            const double B[9] = {H[0], H[1], H[2], H[1], H[3], H[4], H[2], H[4], H[5]};
             const uint32_t q = i / s, rem = i - q * s;
             const bool two = !(q + 1 >= n || rem == 0);
             for (int side = 0; side < (two ? 2 : 1); ++side) {
                 const uint32_t Kp = q + side;
                 const double wp = two ? (side == 0 ? 1.0 - (double)rem / (double)s : (double)rem / (double)s) : 1.0;
                 const double4 pp = d.pose[(size_t)Kp * s];
-                double b0, b1, b2; zcol(make_double2(-(pi.y - pp.y), pi.x - pp.x), c, b0, b1, b2);
-                double y0, y1, y2; sym3_mul(d.hpp + 6ull * i, b0, b1, b2, y0, y1, y2);
-                rowp[3 * Kp + c] += wi * wp * (a0 * y0 + a1 * y1 + a2 * y2);
+                add((int)Kp - (int)K + 1, wi * wp, zx, zy, B, -(pi.y - pp.y), pi.x - pp.x);
             }
-            // ODOM edges of pose i (both directions): block H_ij = diag(hoo)
+        }
+        for (uint32_t pass = 0; pass < 2; ++pass) {        // ODOM edges of pose i, both directions: H_ij = diag(hoo)
+            const uint32_t kb = pass == 0 ? d.od_out_ptr[i] : d.od_in_ptr[i], ke = pass == 0 ? d.od_out_ptr[i + 1] : d.od_in_ptr[i + 1];
+            for (uint32_t kk = kb; kk < ke; ++kk) {
+                const uint32_t k = pass == 0 ? kk : d.od_in_edge[kk];
+                const uint32_t j = pass == 0 ? d.od_b[k] : d.od_a[k];
+                if (j >= d.nP) continue;                              // pose of another rank: the cut edge stays out of the top operator
+                const double* h = d.hoo + 3ull * k;
+                const double B[9] = {h[0], 0, 0, 0, h[1], 0, 0, 0, h[2]};
+                const double4 pj = d.pose[j];
+                const uint32_t qj = j / s, remj = j - qj * s;
+                const bool twoj = !(qj + 1 >= n || remj == 0);
+                for (int side = 0; side < (twoj ? 2 : 1); ++side) {
+                    const uint32_t Kp = qj + side;
+                    if (Kp + 1 < K || Kp > K + 1) { far = 1; continue; }
+                    const double wp = twoj ? (side == 0 ? 1.0 - (double)remj / (double)s : (double)remj / (double)s) : 1.0;
+                    const double4 pp = d.pose[(size_t)Kp * s];
+                    add((int)Kp - (int)K + 1, wi * wp, zx, zy, B, -(pj.y - pp.y), pj.x - pp.x);
+                }
+            }
+        }
+    }
+#pragma unroll
+    for (int q = 0; q < 3; ++q)
+#pragma unroll
+        for (int e = 0; e < 9; ++e) {
+            double v = acc[q][e];
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+            if ((tid & 31) == 0) ml_red[(tid >> 5) * 27 + q * 9 + e] = v;
+        }
+    far = __syncthreads_or(far);
+    if (tid < 27) {
+        const int dk = tid / 9, r = (tid % 9) / 3, c = tid % 3;
+        const long long Kp = (long long)K + dk - 1;
+        if (Kp >= 0 && Kp < (long long)n) {
+            double t = 0;
+            for (int wv = 0; wv < kMlTopThreads / 32; ++wv) t += ml_red[wv * 27 + tid];
+            ml_row[(size_t)r * nc + 3 * (off + (uint32_t)Kp) + c] += t;
+        }
+    }
+    __syncthreads();
+    if (far && tid < 9) {          // far ODOM targets only: one lane per entry, sequential over the support (fixed order)
+        const int r = tid / 3, c = tid % 3;
+        double* rowp = ml_row + (size_t)r * nc + 3 * off;
+        for (uint32_t i = lo; i < hi; ++i) {
+            const double wi = ml_pose_weight(i, K, s, n);
+            const double4 pi = d.pose[i];
+            double a0, a1, a2; zcol(make_double2(-(pi.y - pc.y), pi.x - pc.x), r, a0, a1, a2);
             for (uint32_t pass = 0; pass < 2; ++pass) {
                 const uint32_t kb = pass == 0 ? d.od_out_ptr[i] : d.od_in_ptr[i], ke = pass == 0 ? d.od_out_ptr[i + 1] : d.od_in_ptr[i + 1];
                 for (uint32_t kk = kb; kk < ke; ++kk) {
                     const uint32_t k = pass == 0 ? kk : d.od_in_edge[kk];
                     const uint32_t j = pass == 0 ? d.od_b[k] : d.od_a[k];
-                    if (j >= d.nP) continue;                              // pose of another rank: the cut edge stays out of the top operator
+                    if (j >= d.nP) continue;
                     const double* h = d.hoo + 3ull * k;
                     const double4 pj = d.pose[j];
                     const uint32_t qj = j / s, remj = j - qj * s;
                     const bool twoj = !(qj + 1 >= n || remj == 0);
                     for (int side = 0; side < (twoj ? 2 : 1); ++side) {
                         const uint32_t Kp = qj + side;
+                        if (!(Kp + 1 < K || Kp > K + 1)) continue;
                         const double wp = twoj ? (side == 0 ? 1.0 - (double)remj / (double)s : (double)remj / (double)s) : 1.0;
                         const double4 pp = d.pose[(size_t)Kp * s];
                         double b0, b1, b2; zcol(make_double2(-(pj.y - pp.y), pj.x - pp.x), c, b0, b1, b2);
@@ -181,35 +252,79 @@ __global__ void __launch_bounds__(kMlTopThreads) k_ml_top(const Dev d, const uin
         }
     }
     __syncthreads();
-    // landmark part (global lists: the partner node of a landmark may live on another rank)
+    if (timing) { const long long t = clock64(); d.dbg[8] = t - tk0; tk0 = t; }
+    // ---- landmark part (global lists: the partner node of a landmark may live on another rank).
+    //   Ac[K, Kp] -= sum over landmarks l seen by both of C_{K,l} Hll^-1 C_{Kp,l}^T
+    // Walking the node's coarse edges with four dependent global loads each (landmark -> list -> partner edge -> its C)
+    // by every thread cost 3.4 M cycles per block at C3 (4.5 ms per launch).  Now the edges are staged 256 at a time by a
+    // thread per edge (T = C Hll^-1, list offsets), the (edge, partner) pairs of the batch by a thread per pair, and only
+    // then does the owner of column block Kp (thread Kp mod 256) walk the staged pairs -- reading shared memory, and global
+    // memory only for its own pairs.  Every (row, column) entry still receives its landmarks in ascending order.
+    constexpr uint32_t kPairCap = 3072;
+    __shared__ double sT[kMlTopThreads][6];
+    __shared__ uint32_t s_off[kMlTopThreads + 1], s_t0[kMlTopThreads], sp_e2[kPairCap];
+    __shared__ uint16_t sp_node[kPairCap], sp_el[kPairCap];
     const double2* C = reinterpret_cast<const double2*>(d.gtC);
     const size_t cs = d.gt_nnz;
-    for (uint32_t e = d.gt_node_ptr[Kg]; e < d.gt_node_ptr[Kg + 1]; ++e) {
-        const uint32_t lm = d.gt_edge_lm[e];
-        const uint32_t t0 = tl_ptr[lm], t1 = tl_ptr[lm + 1];
-        bool mine = false;
-        for (uint32_t q = t0; q < t1; ++q) if (tl_node[q] % kMlTopThreads == tid) { mine = true; break; }
-        if (!mine) continue;
-        const double* hi_ = d.hinv + 3ull * lm;
-        const double i00 = hi_[0], i01 = hi_[1], i11 = hi_[2];
-        const double2 r0 = C[e], r1 = C[cs + e], r2 = C[2 * cs + e];
-        const double t00 = r0.x * i00 + r0.y * i01, t01 = r0.x * i01 + r0.y * i11;
-        const double t10 = r1.x * i00 + r1.y * i01, t11 = r1.x * i01 + r1.y * i11;
-        const double t20 = r2.x * i00 + r2.y * i01, t21 = r2.x * i01 + r2.y * i11;
-        for (uint32_t q = t0; q < t1; ++q) {
-            const uint32_t Kp = tl_node[q];
-            if (Kp % kMlTopThreads != tid) continue;
-            const uint32_t e2 = tl_edge[q];
-            const double2 s0 = C[e2], s1 = C[cs + e2], s2 = C[2 * cs + e2];
-            double* o = ml_row + 3 * Kp;
-            o[0] -= t00 * s0.x + t01 * s0.y; o[1] -= t00 * s1.x + t01 * s1.y; o[2] -= t00 * s2.x + t01 * s2.y;
-            o[nc] -= t10 * s0.x + t11 * s0.y; o[nc + 1] -= t10 * s1.x + t11 * s1.y; o[nc + 2] -= t10 * s2.x + t11 * s2.y;
-            o[2 * nc] -= t20 * s0.x + t21 * s0.y; o[2 * nc + 1] -= t20 * s1.x + t21 * s1.y; o[2 * nc + 2] -= t20 * s2.x + t21 * s2.y;
+    const uint32_t e_lo = d.gt_node_ptr[Kg], e_hi = d.gt_node_ptr[Kg + 1];
+    long long tq = 0, tacc[4] = {0, 0, 0, 0};
+#define MLTICK(slot) do { if (timing) { const long long now_ = clock64(); tacc[slot] += now_ - tq; tq = now_; } } while (0)
+    for (uint32_t e_base = e_lo; e_base < e_hi; e_base += kMlTopThreads) {
+        const uint32_t ne = min((uint32_t)kMlTopThreads, e_hi - e_base);
+        uint32_t len = 0;
+        if (timing) tq = clock64();
+        if (tid < ne) {
+            const uint32_t e = e_base + tid, lm = d.gt_edge_lm[e];
+            const uint32_t t0 = tl_ptr[lm]; len = tl_ptr[lm + 1] - t0; s_t0[tid] = t0;
+            const double* hi_ = d.hinv + 3ull * lm;
+            const double i00 = hi_[0], i01 = hi_[1], i11 = hi_[2];
+            const double2 r0 = C[e], r1 = C[cs + e], r2 = C[2 * cs + e];
+            sT[tid][0] = r0.x * i00 + r0.y * i01; sT[tid][1] = r0.x * i01 + r0.y * i11;
+            sT[tid][2] = r1.x * i00 + r1.y * i01; sT[tid][3] = r1.x * i01 + r1.y * i11;
+            sT[tid][4] = r2.x * i00 + r2.y * i01; sT[tid][5] = r2.x * i01 + r2.y * i11;
+        }
+        // exclusive prefix sum of the list lengths: s_off[t] = pairs before edge t of the batch, s_off[ne] = total
+        s_off[tid + 1] = len;
+        if (tid == 0) s_off[0] = 0;
+        __syncthreads();
+        if (tid == 0) for (uint32_t t = 0; t < ne; ++t) s_off[t + 1] += s_off[t];
+        __syncthreads();
+        const uint32_t total = s_off[ne];
+        MLTICK(0);
+        for (uint32_t pb = 0; pb < total; pb += kPairCap) {
+            const uint32_t np = min(kPairCap, total - pb);
+            for (uint32_t pr = tid; pr < np; pr += kMlTopThreads) {
+                const uint32_t gp = pb + pr;
+                uint32_t lo_ = 0, hi_ = ne;                  // last edge el with s_off[el] <= gp
+                while (hi_ - lo_ > 1) { const uint32_t mid = (lo_ + hi_) >> 1; if (s_off[mid] <= gp) lo_ = mid; else hi_ = mid; }
+                const uint32_t q = s_t0[lo_] + (gp - s_off[lo_]);
+                sp_node[pr] = (uint16_t)tl_node[q]; sp_e2[pr] = tl_edge[q]; sp_el[pr] = (uint16_t)lo_;
+            }
+            __syncthreads();
+            MLTICK(1);
+            for (uint32_t pr = 0; pr < np; ++pr) {
+                const uint32_t Kp = sp_node[pr];
+                if ((Kp % kMlTopThreads) != tid) continue;
+                const double* T = sT[sp_el[pr]];
+                const uint32_t e2 = sp_e2[pr];
+                const double2 s0 = C[e2], s1 = C[cs + e2], s2 = C[2 * cs + e2];
+                double* o = ml_row + 3 * Kp;
+                o[0] -= T[0] * s0.x + T[1] * s0.y; o[1] -= T[0] * s1.x + T[1] * s1.y; o[2] -= T[0] * s2.x + T[1] * s2.y;
+                o[nc] -= T[2] * s0.x + T[3] * s0.y; o[nc + 1] -= T[2] * s1.x + T[3] * s1.y; o[nc + 2] -= T[2] * s2.x + T[3] * s2.y;
+                o[2 * nc] -= T[4] * s0.x + T[5] * s0.y; o[2 * nc + 1] -= T[4] * s1.x + T[5] * s1.y; o[2 * nc + 2] -= T[4] * s2.x + T[5] * s2.y;
+            }
+            MLTICK(2);
+            __syncthreads();
+            MLTICK(3);
         }
     }
+    if (timing) { d.dbg[11] = tacc[0]; d.dbg[12] = tacc[1]; d.dbg[13] = tacc[2]; d.dbg[14] = tacc[3]; d.dbg[15] = (long long)(e_hi - e_lo); }
+#undef MLTICK
     __syncthreads();
+    if (timing) { const long long t = clock64(); d.dbg[9] = t - tk0; tk0 = t; }
     double* out = d.Ac + (size_t)(3 * Kg) * nc;
     for (uint32_t k = tid; k < 3 * nc; k += kMlTopThreads) out[k] = ml_row[k];
+    if (timing) d.dbg[10] = clock64() - tk0;
 }
 
 // ---- PCG phases -------------------------------------------------------------------------------------------------------

@@ -243,7 +243,7 @@ __global__ void __launch_bounds__(kPsThreads, 2) k_pcg_stream(const Dev d) {
     __syncthreads();
     const bool coarse = d.flags[F_COARSE] != 0;
     const bool ml = coarse && d.mlLv > 0;                            // multilevel preconditioner (mlevel.cuh)
-    const bool crow = coarse && blockIdx.x * (kPsThreads / 32) < d.nc;
+    const bool crow = coarse && coarse_row_owner(d);
     const uint32_t ncdot = ml ? d.mlCdot : d.nc;
     double* ml_sm = reinterpret_cast<double*>(smem_raw + kPsRing);   // the ring is idle during the pose phase
     double* rbuf[2] = {d.r, ml ? d.r2 : d.r};
@@ -294,7 +294,9 @@ __global__ void __launch_bounds__(kPsThreads, 2) k_pcg_stream(const Dev d) {
                 TICK(2);
                 x_gsync(grid, d, gtarget, XP_U, ++xv);
             } else {
-            for (uint32_t l = gtid; l < d.L; l += gsz) {          // u_l = Hll^-1 w_l straight away: pass B then gathers it raw
+            // landmarks are dealt round-robin over the BLOCKS (landmark l -> block l mod nb): with l = gtid the 20 k landmarks of
+            // C3 all sat on the first 39 blocks while the other 257 waited at the barrier (35 k + 23 k cycles per iteration)
+            for (uint32_t l = blockIdx.x + nb * tid; l < d.L; l += nb * kPsThreads) {          // u_l = Hll^-1 w_l straight away: pass B then gathers it raw
                 const double2 w = lm_w_sum(d, l); const double* hi = d.hinv + 3ull * l;
                 reinterpret_cast<double2*>(d.w_sum)[l] = make_double2(hi[0] * w.x + hi[1] * w.y, hi[1] * w.x + hi[2] * w.y);
             }

@@ -140,7 +140,7 @@ __device__ __forceinline__ double x_scalar_sum(const Dev& d, uint32_t slot, uint
 // landmark phase, step 1: this rank's w = Hpl^T p per touched landmark -> the owner's receive buffer; block 0 also sends
 // the boundary poses' p to the ranks that hold them as ghosts
 __device__ __forceinline__ void x_w_push(const Dev& d, uint32_t gtid, uint32_t gsz) {
-    for (uint32_t l = gtid; l < d.L; l += gsz) {
+    for (uint32_t l = blockIdx.x + gridDim.x * threadIdx.x; l < d.L; l += gridDim.x * blockDim.x) {      // round-robin over blocks: see k_pcg_stream
         if (d.lm_part_ptr[l] == d.lm_part_ptr[l + 1]) continue;
         const double2 w = lm_w_sum(d, l);
         const uint32_t owner = l / d.xc.slice;
@@ -157,7 +157,7 @@ __device__ __forceinline__ void x_w_push(const Dev& d, uint32_t gtid, uint32_t g
 // the landmark (pass B gathers it from d.w_sum == the own region's u array); ghost p into the tail of d.p
 __device__ __forceinline__ void x_u_own(const Dev& d, uint32_t gtid, uint32_t gsz) {
     for (uint32_t i = threadIdx.x; i < 3 * d.nG; i += blockDim.x) d.p[3ull * d.nP + i] = x_ptr(d, d.xc.rank, d.xc.o_ghost)[i];   // same values from every block
-    for (uint32_t i = gtid; i < d.xc.slice; i += gsz) {
+    for (uint32_t i = blockIdx.x + gridDim.x * threadIdx.x; i < d.xc.slice; i += gridDim.x * blockDim.x) {
         const uint32_t l = d.xc.rank * d.xc.slice + i;
         if (l >= d.L) break;
         const uint32_t mask = d.xc.lm_mask[l];
