@@ -124,7 +124,8 @@ int upload_graph(tsb_ctx* c) {
         x.o_hll = o; o = al(o + 8ull * 3 * g.L + 64);
         x.o_hinv = o; o = al(o + 8ull * 3 * g.L + 64);
         x.o_bl = o; o = al(o + 8ull * 2 * g.L + 64);
-        x.o_w = o; o = al(o + 8ull * 2 * x.world * x.slice);
+        x.o_w = o; o = al(o + 8ull * 2 * x.world * g.L + 64);          // rx[src][landmark] of the PCG's all-gather
+        x.o_bw = o; o = al(o + 8ull * 2 * x.world * x.slice);
         x.o_u = o; o = al(o + 8ull * 2 * g.L + 64);
         x.o_dl = o; o = al(o + 8ull * 2 * g.L + 64);
         x.o_top = o; o = al(o + 8ull * (3 * 4096 + 4 * kXMaxWorld));
@@ -132,6 +133,7 @@ int upload_graph(tsb_ctx* c) {
         for (int r = 0; r < c->world; ++r) x.peer[r] = c->xpeer[r];
         x.nExp = (uint32_t)(s.x_exp.size() / 3);
         TRY(upload(c, x.exp, s.x_exp)); TRY(upload(c, x.lm_mask, s.lm_mask));
+        TRY(dalloc(c, x.done, (size_t)2)); CU(cudaMemsetAsync(x.done, 0, 8, c->stream));
     }
     const bool xp = d.xc.world > 1;
     // per-edge data gathered into assembly order
@@ -387,13 +389,8 @@ int enqueue_linearize(tsb_ctx* c) {
     else if (p2p(c)) {
         // owner-computes over NVLink: every rank pushes the sums of the landmarks it touches to their owners (+ its chi2),
         // the owner adds them in rank order, inverts and pushes Hll / Hll^-1 / b_l back to every rank
-        launch_x_lm5_push(c->d, c->stream);
-        launch_x_scal_push(c->d, 0, c->d.scal + S_CHI2, c->stream);
         mark(2);
-        x_sync(c, XP_LM5);
-        launch_x_lm5_own(c->d, c->stream);
-        launch_x_scal_sum(c->d, 0, c->d.scal + S_CHI2, c->stream);
-        x_sync(c, XP_HINV);
+        launch_x_lm5_exchange(c->d, c->xseq + 1, c->stream); c->xseq += 2;
         mark(3);
     } else {
         launch_lm_sum(c->d, false, c->stream);

@@ -29,7 +29,8 @@ struct XDev {
     uint32_t world, rank, slice, nExp;     // slice: landmarks owned per rank (owner(l) = l / slice); nExp: export entries
     uint64_t seq;                          // flag value base of this launch (the host advances it identically on all ranks)
     char* peer[kXMaxWorld];                // region of every rank as mapped here (peer[rank] = own region)
-    size_t o_flags, o_scal, o_ghost, o_lm5, o_hll, o_hinv, o_bl, o_w, o_u, o_dl, o_top;   // byte offsets inside a region
+    size_t o_flags, o_scal, o_ghost, o_lm5, o_hll, o_hinv, o_bl, o_w, o_bw, o_u, o_dl, o_top;   // byte offsets inside a region
+    uint32_t* done;                        // two "blocks finished" counters of the fused push / own kernels (local, zero between uses)
     const uint32_t* exp;                   // 3 per export entry: local pose, destination rank, ghost slot there
     const uint8_t* lm_mask;                // per landmark: bit r set = rank r has LM edges to it
     uint32_t top_off, top_total;           // this rank's first node / all nodes of the global top level
@@ -169,8 +170,7 @@ void launch_init_pose(const double* xyt, uint32_t n, double4* out, cudaStream_t 
 void launch_read_pose(const double4* pose, uint32_t n, double* xyt, cudaStream_t s);
 // peer exchange between separately launched kernels (xchg.cuh)
 void launch_x_signal_wait(const Dev& d, uint32_t point, uint64_t value, cudaStream_t s);   // publish `value`, then wait for every peer's
-void launch_x_lm5_push(const Dev& d, cudaStream_t s);          // landmark sums of this rank -> the owners' receive buffers
-void launch_x_lm5_own(const Dev& d, cudaStream_t s);           // owners: sum in rank order, finalize, push Hll / Hll^-1 / b_l to all
+void launch_x_lm5_exchange(const Dev& d, uint64_t v, cudaStream_t s);   // landmark sums -> owners (flag v), owners finalize and push Hll / Hll^-1 / b_l to all (flag v + 1), wait
 void launch_x_push_ghost(const Dev& d, const double* vec, cudaStream_t s);   // boundary-pose entries of vec -> ghost buffers of the peers
 void launch_x_w_push(const Dev& d, cudaStream_t s);            // back-substitution: this rank's Hpl^T delta_p per touched landmark -> owners
 void launch_x_backsub_own(const Dev& d, cudaStream_t s);       // owners: delta_l = Hll^-1 (b_l - sum over ranks), pushed to every rank

@@ -1127,8 +1127,11 @@ bool launch_pcg_stream(const Dev& d, cudaStream_t s) {
         cudaGetDevice(&dev);
         cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
         cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, dev);
-        if (cudaFuncSetAttribute(k_pcg_stream, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kPsSmemBytes) != cudaSuccess) cudaGetLastError();
-        else cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_pcg_stream, kPsThreads, kPsSmemBytes);
+        int per_sm_x = 0;
+        if (cudaFuncSetAttribute(k_pcg_stream<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kPsSmemBytes) != cudaSuccess ||
+            cudaFuncSetAttribute(k_pcg_stream<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kPsSmemBytes) != cudaSuccess) cudaGetLastError();
+        else { cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_pcg_stream<false>, kPsThreads, kPsSmemBytes);
+               cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm_x, k_pcg_stream<true>, kPsThreads, kPsSmemBytes); per_sm = per_sm < per_sm_x ? per_sm : per_sm_x; }
         blocks = coop ? sms * per_sm : 0;
     }
     uint32_t min_units = 4u * (uint32_t)blocks;
@@ -1138,7 +1141,8 @@ bool launch_pcg_stream(const Dev& d, cudaStream_t s) {
     Dev dd = d; void* args[] = {&dd};
     cudaMemsetAsync(dd.gbar, 0, sizeof(uint32_t), s);
     const uint32_t grid = d.nBlocks < (uint32_t)blocks ? d.nBlocks : (uint32_t)blocks;
-    if (cudaLaunchCooperativeKernel((void*)k_pcg_stream, dim3(grid), dim3(kPsThreads), args, kPsSmemBytes, s) != cudaSuccess) { cudaGetLastError(); return false; }
+    const void* fn = d.xc.world > 1 ? (const void*)k_pcg_stream<true> : (const void*)k_pcg_stream<false>;
+    if (cudaLaunchCooperativeKernel(fn, dim3(grid), dim3(kPsThreads), args, kPsSmemBytes, s) != cudaSuccess) { cudaGetLastError(); return false; }
     ++g_launches;
     return true;
 }
@@ -1302,11 +1306,15 @@ void launch_update_state(const Dev& d, double step, cudaStream_t s) {
     k_reduce_to<<<1, 1024, 0, s>>>(d.part2, nb, d.scal + S_DELTA2L); ++g_launches;
 }
 void launch_x_signal_wait(const Dev& d, uint32_t point, uint64_t value, cudaStream_t s) {
-    k_x_signal<<<1, 1, 0, s>>>(d, point, (unsigned long long)value); ++g_launches;
-    k_x_wait<<<1, 1, 0, s>>>(d, point, (unsigned long long)value); ++g_launches;
+    k_x_signal<<<1, 32, 0, s>>>(d, point, (unsigned long long)value); ++g_launches;
+    k_x_wait<<<1, 32, 0, s>>>(d, point, (unsigned long long)value); ++g_launches;
 }
-void launch_x_lm5_push(const Dev& d, cudaStream_t s) { if (d.L) { k_x_lm5_push<<<cdiv(d.L, kThreads), kThreads, 0, s>>>(d); ++g_launches; } }
-void launch_x_lm5_own(const Dev& d, cudaStream_t s) { k_x_lm5_own<<<cdiv(d.xc.slice, kThreads), kThreads, 0, s>>>(d); ++g_launches; }
+// fused landmark exchange of the linearisation: push (+ chi2, flag v at XP_LM5), own (waits v, flag v + 1 at XP_HINV), wait v + 1
+void launch_x_lm5_exchange(const Dev& d, uint64_t v, cudaStream_t s) {
+    k_x_lm5_push<<<cdiv(d.L ? d.L : 1u, kThreads), kThreads, 0, s>>>(d, (unsigned long long)v); ++g_launches;
+    k_x_lm5_own<<<cdiv(d.xc.slice, kThreads), kThreads, 0, s>>>(d, (unsigned long long)v); ++g_launches;
+    k_x_wait<<<1, 32, 0, s>>>(d, XP_HINV, (unsigned long long)(v + 1)); ++g_launches;
+}
 void launch_x_push_ghost(const Dev& d, const double* vec, cudaStream_t s) {
     if (d.xc.nExp) { k_x_push_ghost<<<cdiv(d.xc.nExp, kThreads), kThreads, 0, s>>>(d, vec); ++g_launches; }
 }

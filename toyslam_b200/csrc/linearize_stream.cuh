@@ -174,7 +174,7 @@ __global__ void __launch_bounds__(kLsThreads, 2) k_linearize_stream(const Dev d)
         // the ODOM / prior part of this unit's poses for this thread's first reduction item
         const uint32_t nitems = np * kStageRows;
         double od0 = 0;
-        if (last && tid < nitems) { const int oi = ls_od_index(tid % kStageRows); if (oi >= 0) od0 = d.pose_od[6ull * (cur.p0 + tid / kStageRows) + oi]; }
+        if (last && tid < nitems) { const int oi = ls_od_index(tid / np); if (oi >= 0) od0 = d.pose_od[6ull * (cur.p0 + tid % np) + oi]; }
 
         // ---- per-edge linearisation, products staged in `rows`, Hpl written once ------------------------------
         if (tid < n) { const uint32_t q = pk[tid];
@@ -185,7 +185,10 @@ __global__ void __launch_bounds__(kLsThreads, 2) k_linearize_stream(const Dev d)
         const bool multi = np == 1 && pptr[1] - pptr[0] > kChunkEdges;      // only a single heavy pose is ever split
 #pragma unroll 1
         for (uint32_t item = tid; item < nitems; item += kLsThreads) {
-            const uint32_t pl = item / kStageRows, row = item % kStageRows;
+            // item -> (row, pose) with the POSE varying fastest: the lanes of a warp then read one staged row at offsets that grow by
+            // the poses' edge counts (19 at C4: 3 mod 16 double-banks, conflict-free) instead of nine rows of three or four poses
+            // whose offsets collide (2.6x the conflict-free wavefronts, profiles/r1_lin_stream2_c4_ncu_summary.csv)
+            const uint32_t row = item / np, pl = item - row * np;
             const uint32_t b = max(pptr[pl], cur.e0) - cur.e0, e = min(pptr[pl + 1], cur.e1) - cur.e0;
             double sum = seg_sum_lean(rows + row * kStageStride, b, e);
             if (multi) { heavy += sum; sum = heavy; }             // np == 1: item == tid < 9; same order as acc += seg_sum

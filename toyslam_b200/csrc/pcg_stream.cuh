@@ -227,6 +227,8 @@ __device__ __forceinline__ bool ps_pose_phase(const Dev& d, double alpha, bool c
     return agg;
 }
 
+// XP: compiled with the NVLink peer exchange (world > 1); the single-GPU instance carries none of that code
+template <bool XP>
 __global__ void __launch_bounds__(kPsThreads, 2) k_pcg_stream(const Dev d) {
     extern __shared__ __align__(32) unsigned char smem_raw[];
     double* red = reinterpret_cast<double*>(smem_raw + kPsRed);
@@ -256,19 +258,39 @@ __global__ void __launch_bounds__(kPsThreads, 2) k_pcg_stream(const Dev d) {
     // world > 1 (peer exchange, xchg.cuh): the ranks' parts of every scalar are added in rank order -- every rank sees
     // the same bits and takes the same branches.  With the hierarchy the top level is GLOBAL: every rank pushes the
     // residual of its top nodes to all ranks, the dense mat-vec and its part of r'z are replicated.
-    const bool xp = d.xc.world > 1;
+    constexpr bool xp = XP;
     unsigned long long xv = d.xc.seq;
     res_gsync(grid, d.gbar, gtarget);
+    double vloc = 0;
     auto coarse_step = [&]() -> double {
         if (coarse) {
-            if (ml && xp) { ml_coarse_push(d, gtid, gsz); x_gsync(grid, d, gtarget, XP_TOP, ++xv); if (crow) ml_coarse_top(d, gtid, gsz, rc_s); }
+            if (ml && xp) {
+                // one exchange step carries the residual of this rank's top nodes AND its part of r'z (fine level + its own
+                // lower levels), which every block can form right after the grid barrier; block 0 publishes it with the flag
+                ml_coarse_push(d, gtid, gsz);
+                __threadfence_system();
+                res_gsync(grid, d.gbar, gtarget);
+                vloc = reduce_all(d.part, nb, red) + reduce_all(d.cdot + d.nc, ncdot - d.nc, red);
+                ++xv;
+                if (blockIdx.x == 0) {
+                    if (tid < d.xc.world && tid != d.xc.rank) x_ptr(d, tid, d.xc.o_scal)[3 * kXMaxWorld + d.xc.rank] = vloc;
+                    x_signal_block(d, XP_TOP, xv);
+                }
+                x_wait_block(d, XP_TOP, xv);
+                if (crow) ml_coarse_top(d, gtid, gsz, rc_s);
+            }
             else if (ml) ml_coarse_phase(d, gtid, gsz, rc_s, crow);
             else if (crow) coarse_phase(d, gtid >> 5, gsz >> 5, rc_s, rc_shared);
             res_gsync(grid, d.gbar, gtarget);
         }
+        if (ml && xp) {          // ranks' parts in rank order, then the replicated top-level part
+            double v = 0;
+            for (uint32_t r = 0; r < d.xc.world; ++r) v += r == d.xc.rank ? vloc : x_ptr(d, d.xc.rank, d.xc.o_scal)[3 * kXMaxWorld + r];
+            return v + reduce_all(d.cdot, d.nc, red);
+        }
         double v = reduce_all(d.part, nb, red);
-        if (ml && xp) { v += reduce_all(d.cdot + d.nc, ncdot - d.nc, red); v = x_scalar_sum(d, 3, XP_TOP, ++xv, v); v += reduce_all(d.cdot, d.nc, red); }
-        else { if (coarse) v += reduce_all(d.cdot, ncdot, red); if (xp) v = x_scalar_sum(d, 3, XP_TOP, ++xv, v); }
+        if (coarse) v += reduce_all(d.cdot, ncdot, red);
+        if (xp) v = x_scalar_sum(d, 3, XP_TOP, ++xv, v);
         return v;
     };
     double rz0 = coarse_step();
@@ -286,17 +308,18 @@ __global__ void __launch_bounds__(kPsThreads, 2) k_pcg_stream(const Dev d) {
             TICK(0);
             res_gsync(grid, d.gbar, gtarget);
             TICK(1);
-            if (xp) {             // landmark sums across ranks: partial w -> owner, owner adds in rank order, u = Hll^-1 w -> every toucher
-                x_w_push(d, gtid, gsz);
+            if (xp) {             // landmark sums across ranks: one all-gather step among the touchers (xchg.cuh)
+                x_w_push(d);
                 x_gsync(grid, d, gtarget, XP_W, ++xv);
-                x_u_own(d, gtid, gsz);
+                x_u_local(d);
                 for (uint32_t p = gtid; p < d.nP; p += gsz) hpp_apply(d, p, d.sp + 3ull * p);
                 TICK(2);
-                x_gsync(grid, d, gtarget, XP_U, ++xv);
+                res_gsync(grid, d.gbar, gtarget);
             } else {
-            // landmarks are dealt round-robin over the BLOCKS (landmark l -> block l mod nb): with l = gtid the 20 k landmarks of
+            // landmarks are dealt round-robin over the BLOCKS (warp-sized groups, group g -> block g mod nb): with l = gtid the 20 k landmarks of
             // C3 all sat on the first 39 blocks while the other 257 waited at the barrier (35 k + 23 k cycles per iteration)
-            for (uint32_t l = blockIdx.x + nb * tid; l < d.L; l += nb * kPsThreads) {          // u_l = Hll^-1 w_l straight away: pass B then gathers it raw
+            // (groups of 32 consecutive landmarks, one per warp, so that the per-landmark arrays are still read coalesced)
+            for (uint32_t l = 32 * (blockIdx.x + nb * (tid >> 5)) + (tid & 31); l < d.L; l += 32 * nb * (kPsThreads / 32)) {          // u_l = Hll^-1 w_l straight away: pass B then gathers it raw
                 const double2 w = lm_w_sum(d, l); const double* hi = d.hinv + 3ull * l;
                 reinterpret_cast<double2*>(d.w_sum)[l] = make_double2(hi[0] * w.x + hi[1] * w.y, hi[1] * w.x + hi[2] * w.y);
             }
