@@ -17,7 +17,9 @@ def load_golden(name):
     return np.load(os.path.join(GOLDEN, name + ".npz"))
 
 
-GOLDEN_CASES = ["g_tiny", "g_small", "g_loops", "g_outliers", "g_odom_only", "c1"]
+GOLDEN_CASES = ["g_tiny", "g_small", "g_loops", "g_outliers", "g_odom_only", "g_worse", "g_worse_lm", "g_converged", "c1"]
+# exit codes the fixtures end with (OptimizerCpu.h:140-179): 1 "Error is getting worse", 2 "Plateau", 3 "CONVERGED"
+GOLDEN_EXIT_CODES = {"g_worse": 1, "g_worse_lm": 1, "c1": 2, "g_converged": 3}
 
 
 def wrap(a):

@@ -208,6 +208,28 @@ def test_reply_matches_oracle_reply(gpu):
     assert sorted(map(key, a["edges"])) == sorted(map(key, b["edges"]))
 
 
+@pytest.mark.parametrize("name", ["c1", "g_loops"])
+def test_reply_matches_reference_decoded_fixture(gpu, name):
+    """The reply the CUDA path writes against tests/golden/*_reply.npz: an oracle reply as decoded by the REFERENCE's own
+    decoder (python/remote/bytes_to_graph.py:49-109, tests/make_reply_fixture.py).  Same vertex ids in the same order,
+    same types, every edge and fixed id echoed bit for bit, values within the fp32 wire precision."""
+    from toyslam_b200 import wire
+    f = load_golden(name + "_reply"); d = load_golden(name)
+    g = gpu(iterations=int(d["iterations"]), pcg_tol=1e-14, pcg_max_iters=5000, enable_exits=bool(d["exits"]))
+    g.load_wire(d["request"].tobytes()); g.optimize()
+    r = wire.decode_reply(g.reply())
+    assert np.array_equal(np.array(r["order"], np.uint32), f["vertex_id"]) and sorted(r["fixed"]) == list(f["fixed"])
+    for vid, vt, val in zip(f["vertex_id"], f["vertex_type"], f["vertex_value"]):
+        t, v = r["vertices"][int(vid)]
+        assert t == vt and np.allclose(v[:2], val[:2], rtol=0, atol=2e-6 * max(1.0, np.max(np.abs(val[:2]))))
+        if t == 0:
+            assert abs(np.arctan2(np.sin(v[2] - val[2]), np.cos(v[2] - val[2]))) < 2e-6
+    assert len(r["edges"]) == len(f["edge_type"])
+    for k, (et, a, b, meas, inf) in enumerate(r["edges"]):
+        assert (et, a, b) == (f["edge_type"][k], f["edge_ij"][k, 0], f["edge_ij"][k, 1])
+        assert np.array_equal(meas.ravel(), f["edge_meas"][k, :meas.size]) and np.array_equal(inf, f["edge_inf"][k, :len(inf)])
+
+
 def test_load_soa_equals_load_wire(gpu):
     from toyslam_b200 import synth
     gr = synth.make_config("c2", scale=0.03, seed=5)

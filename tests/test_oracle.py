@@ -11,6 +11,9 @@ from toyslam_b200 import synth, wire
 # atan2(R10, R00).  The two differ by ~1e-8 rad on the ODOM theta residual, hence these tolerances.
 TOL = {"c1": 1e-10}
 DEFAULT_TOL = 2e-7
+# the same ~1e-8 rad acts on the translation residual through the lever arm |x_j - x_i|: the two fixtures that start
+# several metres from the optimum see it at 1e-7 m (all others stay below 1e-12)
+EDGE_XY_TOL = {"g_worse": 5e-7, "g_worse_lm": 5e-7}
 
 
 @pytest.mark.parametrize("name", GOLDEN_CASES)
@@ -21,13 +24,13 @@ def test_linearization_matches_reference_python(name):
     assert np.array_equal(pi, d["pose_ids"]) and np.array_equal(li, d["lm_ids"])
     for k in range(o.El):
         e, A, B = o.edge_lm(k)
-        assert np.allclose(e, d["lm_e"][k], rtol=0, atol=1e-12)
-        assert np.allclose(A, d["lm_A"][k], rtol=0, atol=1e-11)
+        assert np.allclose(e, d["lm_e"][k], rtol=0, atol=EDGE_XY_TOL.get(name, 1e-12))
+        assert np.allclose(A, d["lm_A"][k], rtol=0, atol=10 * EDGE_XY_TOL.get(name, 1e-12))
         assert np.allclose(B, d["lm_B"][k], rtol=0, atol=1e-14)
     for k in range(o.Eo):
         e = o.edge_odom(k)
-        assert np.allclose(e[:2], d["od_e"][k][:2], rtol=0, atol=1e-12)
-        assert abs(e[2] - d["od_e"][k][2]) < 1e-7
+        assert np.allclose(e[:2], d["od_e"][k][:2], rtol=0, atol=EDGE_XY_TOL.get(name, 1e-12))
+        assert abs(e[2] - d["od_e"][k][2]) < (3e-7 if name in EDGE_XY_TOL else 1e-7)
     H, b, chi2 = o.assemble_dense()
     tol = TOL.get(name, DEFAULT_TOL)
     assert np.max(np.abs(H - d["H"])) <= tol * np.max(np.abs(d["H"]))
@@ -98,3 +101,40 @@ def test_synthetic_generator_shapes():
     assert (o.P, o.Eo, o.El) == (200, 199, 3000)
     traj, its, code = o.optimize_sparse(5, False, 1e-12, 2000, 1)
     assert traj[-1] < traj[0]
+
+
+def test_fixtures_cover_every_exit_code():
+    """OptimizerCpu.h:140-179 has three early exits; each is reached by a fixture, and the oracle reproduces it."""
+    from conftest import GOLDEN_EXIT_CODES
+    from oracle.oracle import OracleGraph
+    assert set(GOLDEN_EXIT_CODES.values()) == {1, 2, 3}
+    for name, code in GOLDEN_EXIT_CODES.items():
+        d = load_golden(name)
+        assert int(d["exit_code"]) == code and bool(d["exits"])
+        o = OracleGraph(d["request"].tobytes())
+        traj, got = o.optimize_dense(int(d["iterations"]), True)
+        assert got == code and len(traj) == len(d["traj"]), (name, got, len(traj))
+
+
+@pytest.mark.parametrize("name", ["c1", "g_loops"])
+def test_reply_decodes_like_the_reference_decoder(name):
+    """tests/golden/*_reply.npz hold an oracle reply and what the REFERENCE's decoder (python/remote/bytes_to_graph.py:49-109,
+    run by tests/make_reply_fixture.py) made of it: toyslam_b200/wire.py must read the same graph from the same bytes,
+    and the oracle must still produce those bytes."""
+    from oracle.oracle import OracleGraph
+    from toyslam_b200 import wire
+    f = load_golden(name + "_reply"); d = load_golden(name)
+    reply = f["reply"].tobytes()
+    o = OracleGraph(d["request"].tobytes()); o.optimize_dense(int(d["iterations"]), bool(d["exits"]))
+    assert o.reply() == reply
+    r = wire.decode_reply(reply)
+    assert np.array_equal(np.array(r["order"], np.uint32), f["vertex_id"]) and sorted(r["fixed"]) == list(f["fixed"])
+    for vid, vt, val in zip(f["vertex_id"], f["vertex_type"], f["vertex_value"]):
+        t, v = r["vertices"][int(vid)]
+        assert t == vt and np.array_equal(v[:2].astype(np.float64), val[:2])
+        if t == 0:          # the reference decoder keeps the pose as a float32 rotation matrix: theta comes back through atan2
+            assert abs(np.arctan2(np.sin(v[2] - val[2]), np.cos(v[2] - val[2]))) < 1e-6
+    assert len(r["edges"]) == len(f["edge_type"])
+    for k, (et, a, b, meas, inf) in enumerate(r["edges"]):
+        assert (et, a, b) == (f["edge_type"][k], f["edge_ij"][k, 0], f["edge_ij"][k, 1])
+        assert np.array_equal(meas.ravel(), f["edge_meas"][k, :meas.size]) and np.array_equal(inf, f["edge_inf"][k, :len(inf)])

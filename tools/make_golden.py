@@ -10,7 +10,7 @@ python/tools.py:2 imports it without using it on the math path):
   * per-edge e, A, B         python/optimizer/edges2d.py:21-53,65-78
   * H, b, chi2               python/optimizer/graph_optimizer.py:94-156  (b sign flipped and the
                              fixed-vertex b zeroing undone to match OptimizerCpu.h:109-138)
-  * reply decoding           python/remote/bytes_to_graph.py:49-109 (exercised in tests)
+  * reply decoding           python/remote/bytes_to_graph.py:49-109 -- pinned by tests/make_reply_fixture.py (*_reply.npz)
   * C1 default-sim graph     python/slam_main.py:26-187 re-stated headlessly (the script opens a
                              matplotlib window at import), calling the reference's own lidar /
                              environment / slam helpers with np.random.seed(0)
@@ -53,7 +53,8 @@ def pose_mat(x, y, th):
     return np.array([[c, -s, x], [s, c, y], [0, 0, 1.0]])
 
 
-def random_graph(seed, P, L, n_lm_edges, loop_closures=0, fix_lm=False, scrambled_ids=False, outliers=False):
+def random_graph(seed, P, L, n_lm_edges, loop_closures=0, fix_lm=False, scrambled_ids=False, outliers=False,
+                 est_noise=0.15, lm_noise=0.3, info_scale=1.0, meas_noise=1.0):
     """A random OptGraph whose every value is already fp32-representable, so the wire round trip
     is lossless and reference-Python and wire consumers see identical numbers."""
     rng = np.random.default_rng(seed)
@@ -67,10 +68,13 @@ def random_graph(seed, P, L, n_lm_edges, loop_closures=0, fix_lm=False, scramble
         gt[i] = [gt[i - 1, 0] + np.cos(th), gt[i - 1, 1] + np.sin(th), th + rng.normal(0, 0.4)]
     lm_gt = gt[rng.integers(0, P, L), :2] + rng.uniform(-4, 4, (L, 2))
     g = OptGraph()
-    est = f32(gt + rng.normal(0, 0.15, gt.shape))
+    est = gt + rng.normal(0, est_noise, gt.shape)
+    big = np.abs(est[:, 2]) > np.pi          # the client sends atan2(R10, R00): keep theta in (-pi, pi] so that fp32(theta) is what travels
+    est[big, 2] = np.arctan2(np.sin(est[big, 2]), np.cos(est[big, 2]))
+    est = f32(est)
     est[0] = f32(gt[0])
     order = rng.permutation(P + L) if scrambled_ids else np.arange(P + L)
-    lm_est = f32(lm_gt + rng.normal(0, 0.3, lm_gt.shape))
+    lm_est = f32(lm_gt + rng.normal(0, lm_noise, lm_gt.shape))
     for k in order:
         if k < P:
             g.add_vertex(int(pid[k]), VertexPose2d(pose_mat(*est[k])), k == 0)
@@ -79,18 +83,18 @@ def random_graph(seed, P, L, n_lm_edges, loop_closures=0, fix_lm=False, scramble
     pairs = [(i, i + 1) for i in range(P - 1)]
     for _ in range(loop_closures):
         a, b = sorted(rng.choice(P, 2, replace=False)); pairs.append((int(a), int(b)))
-    odom_inf = f32(np.diag([4.0, 4.0, 65.1]))
+    odom_inf = f32(np.diag([4.0, 4.0, 65.1]) * info_scale)
     for (a, b) in pairs:
         rel = np.linalg.inv(pose_mat(*gt[a])) @ pose_mat(*gt[b])
-        th = np.arctan2(rel[1, 0], rel[0, 0]) + rng.normal(0, 0.02)
-        Z = pose_mat(rel[0, 2] + rng.normal(0, 0.05), rel[1, 2] + rng.normal(0, 0.05), th)
+        th = np.arctan2(rel[1, 0], rel[0, 0]) + rng.normal(0, 0.02) * meas_noise
+        Z = pose_mat(rel[0, 2] + rng.normal(0, 0.05) * meas_noise, rel[1, 2] + rng.normal(0, 0.05) * meas_noise, th)
         if outliers and rng.random() < 0.2:
             Z[0, 2] += 3.0
         g.add_edge(EdgeOdometry2d(int(pid[a]), int(pid[b]), f32(Z), odom_inf))
-    lm_inf = f32(np.diag([44.4, 30.0]))
+    lm_inf = f32(np.diag([44.4, 30.0]) * info_scale)
     for _ in range(n_lm_edges):
         a, l = int(rng.integers(0, P)), int(rng.integers(0, L))
-        loc = (np.linalg.inv(pose_mat(*gt[a])) @ np.array([lm_gt[l, 0], lm_gt[l, 1], 1.0]))[:2] + rng.normal(0, 0.05, 2)
+        loc = (np.linalg.inv(pose_mat(*gt[a])) @ np.array([lm_gt[l, 0], lm_gt[l, 1], 1.0]))[:2] + rng.normal(0, 0.05, 2) * meas_noise
         if outliers and rng.random() < 0.2:
             loc += 2.0
         meas = f32([np.hypot(*loc), np.arctan2(loc[1], loc[0])])
@@ -273,6 +277,12 @@ def main():
     save_case("g_loops", random_graph(3, P=30, L=15, n_lm_edges=200, loop_closures=6, scrambled_ids=True), 30)
     save_case("g_outliers", random_graph(4, P=25, L=12, n_lm_edges=150, loop_closures=3, outliers=True, fix_lm=True), 25, exits=False)
     save_case("g_odom_only", random_graph(5, P=20, L=0, n_lm_edges=0, loop_closures=4), 20)
+    # the two early exits no other fixture reaches (OptimizerCpu.h:140-149 "Error is getting worse", :173-177 "CONVERGED"):
+    # a start far from the optimum with loop closures (the error rises three times in a row), once ODOM-only and once
+    # with landmarks, and a near-converged start with stiff information (|delta| < 1e-3 while the error still moves)
+    save_case("g_worse", random_graph(102, P=8, L=0, n_lm_edges=0, loop_closures=6, outliers=True, est_noise=3.0), 40)
+    save_case("g_worse_lm", random_graph(100, P=8, L=3, n_lm_edges=8, loop_closures=5, outliers=True, est_noise=3.0, lm_noise=3.0), 40)
+    save_case("g_converged", random_graph(20, P=10, L=6, n_lm_edges=40, est_noise=2e-4, lm_noise=2e-4, info_scale=1e3, meas_noise=0.02), 30)
     # C1: the reference's default simulation, as sent by its own client
     g = default_sim_graph()
     req = quiet(graph_to_bytes, g)
