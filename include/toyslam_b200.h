@@ -109,6 +109,11 @@ int tsb_get_counts(const tsb_ctx* ctx, tsb_counts* out);
  * rank-independent parts (pose cuts, boundary-pose list) and must be equal on every rank */
 int tsb_host_plan(const void* payload, uint32_t nbytes, int32_t rank, int32_t world, tsb_counts* out,
                   uint32_t* n_ghost, uint32_t* n_boundary, uint64_t* structure_hash);
+/* host-only: rank `rank`'s integer structure (same arrays as tsb_read_structure; sizes from tsb_host_plan) -- lets the
+ * "per-rank index map == the 1-rank map restricted to the rank's pose range" test run without a GPU
+ * (replaces the per-rank part of GraphGpu::ToDevice, remote/cuda/graph/GraphGpu.h:80-187) */
+int tsb_host_structure(const void* payload, uint32_t nbytes, int32_t rank, int32_t world, uint32_t* lm_perm,
+                       uint32_t* pose_ptr, uint32_t* chunk_desc, uint32_t* slot_lm, uint32_t* lm_packed);
 int tsb_reset_state(tsb_ctx* ctx);                  /* state <- the values loaded (device-to-device)  */
 int tsb_set_state(tsb_ctx* ctx, const double* pose_xytheta, const double* lm_xy);
 

@@ -262,8 +262,18 @@ def test_full_size_c2_properties(gpu, monkeypatch):
     assert np.all(np.diff(chi) < 0)
     assert all(p.pcg_rel_residual <= 1e-12 for p in per)
     o = OracleGraph(payload)
-    traj, _, _ = o.optimize_sparse(6, False, tol=1e-12, max_pcg=20000, threads=0)
+    traj, _, _ = o.optimize_sparse(6, False, tol=1e-13, max_pcg=40000, threads=0)
     assert np.max(np.abs(chi - traj) / traj) < CHI2_TOL
+    # state as well: the same request solved to 1e-13 by both sides (GPU: two-level / smoother-block PCG, oracle: block-
+    # Jacobi PCG).  Each stops on its own preconditioned norm, so at 34 000 unknowns the two states agree to ~1e-9, not to
+    # the last bit of the 1e-9 bar that the golden graphs (direct solve) are held to: asserted at 1e-8 here, and the
+    # GPU step is checked against the oracle's own full system below (no solver on the oracle side at all)
+    g13 = gpu(iterations=6, pcg_tol=1e-13, pcg_max_iters=40000, enable_exits=False); g13.load_wire(payload); g13.optimize()
+    assert state_diff(*g13.state(), *o.state()) < 10 * STATE_TOL
+    o.set_state(*g13.state())
+    g13.linearize(); g13.solve()
+    res, chi2_o = o.residual_sparse(*g13.delta())
+    assert res <= 1e-10, res
     # fine level of the resident kernel: exact 34-pose Schur blocks (the default starts a request with them and
     # falls back to the 3x3 pose blocks once a probe solve says they stopped paying) against 3x3 blocks throughout
     # (TSB_SMOOTHER=0) and smoother blocks throughout (=1): same trajectory, well under 60 % of the PCG iterations on

@@ -73,3 +73,35 @@ def test_multilevel_hierarchy_of_large_graphs():
             n = -(-n // ratio); levels += 1
         assert (c.n_ml_levels, c.n_ml_top) == (levels, n), (c.n_pose, c.n_ml_levels, c.n_ml_top, levels, n)
         assert 512 < c.n_ml_top <= 1024 or levels == 1
+
+
+def test_per_rank_structure_is_the_restriction_of_the_one_rank_structure():
+    """The edge -> block index map of rank r is the 1-rank map restricted to r's pose range, bit for bit: the same LM
+    edges in the same assembly order (sorted by pose, landmark, request index), the same row pointers up to the
+    offset, chunks that tile the rank's edges and poses, and per chunk the slots an independent numpy derivation gives."""
+    from toyslam_b200 import synth, capi
+    payload = synth.to_payload(synth.make_config("c3", scale=0.03, seed=4))
+    c1, s1 = capi.host_structure(payload, 0, 1)
+    g = synth.make_config("c3", scale=0.03, seed=4)
+    lm_i = g["lm_ij"][:, 0].astype(np.int64); lm_l = g["lm_ij"][:, 1].astype(np.int64) - c1.n_pose
+    assert np.array_equal(s1["lm_perm"], np.lexsort((np.arange(len(lm_i)), lm_l, lm_i)).astype(np.uint32))
+    for world in (2, 4, 8):
+        seen = 0
+        for rank in range(world):
+            c, s = capi.host_structure(payload, rank, world)
+            pb, pe = c.pose_begin, c.pose_end
+            e0, e1 = int(s1["pose_ptr"][pb]), int(s1["pose_ptr"][pe])
+            assert np.array_equal(s["lm_perm"], s1["lm_perm"][e0:e1])
+            assert np.array_equal(s["pose_ptr"], s1["pose_ptr"][pb:pe + 1] - e0)
+            cd = s["chunk_desc"]
+            assert cd[0, 0] == 0 and cd[-1, 1] == e1 - e0 and np.array_equal(cd[1:, 0], cd[:-1, 1])
+            assert cd[0, 2] == 0 and cd[-1, 3] == pe - pb
+            for (a, b, p0, p1, s0, sl1, blk, _) in cd[:: max(1, len(cd) // 40)]:          # a sample of chunks, slot by slot
+                lms = lm_l[s["lm_perm"][a:b]]; uniq, cnt = np.unique(lms, return_counts=True)
+                by_len = np.lexsort((uniq, -cnt))
+                assert np.array_equal(s["slot_lm"][s0:sl1], uniq[by_len])
+                rank_of = np.empty(len(uniq), np.uint32); rank_of[by_len] = np.arange(len(uniq), dtype=np.uint32)
+                packed = ((lm_i[s["lm_perm"][a:b]] - pb - p0).astype(np.uint32) << 16) | rank_of[np.searchsorted(uniq, lms)]
+                assert np.array_equal(s["lm_packed"][a:b], packed)
+            seen += e1 - e0
+        assert seen == c1.n_lmedge

@@ -17,7 +17,7 @@ import numpy as np
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libtoyslam_b200.so")
 
-SYMBOLS = ["tsb_nccl_unique_id", "tsb_create", "tsb_destroy", "tsb_last_error", "tsb_load_wire", "tsb_load_soa", "tsb_get_counts", "tsb_host_plan",
+SYMBOLS = ["tsb_nccl_unique_id", "tsb_create", "tsb_destroy", "tsb_last_error", "tsb_load_wire", "tsb_load_soa", "tsb_get_counts", "tsb_host_plan", "tsb_host_structure",
            "tsb_reset_state", "tsb_set_state", "tsb_linearize", "tsb_solve", "tsb_optimize", "tsb_read_ids",
            "tsb_read_state", "tsb_read_delta", "tsb_get_transfer_bytes", "tsb_read_system", "tsb_read_structure", "tsb_reply_size",
            "tsb_write_reply", "tsb_odom_linearize_noalloc"]
@@ -109,6 +109,20 @@ def host_plan(payload: bytes, rank: int, world: int):
 
 def _p(a):
     return None if a is None else a.ctypes.data_as(C.c_void_p)
+
+
+def host_structure(payload: bytes, rank: int, world: int):
+    """Integer structure arrays of one rank, built on the host (no GPU): dict like GraphOptimizerGpu.structure()."""
+    c, _, _, _ = host_plan(payload, rank, world)
+    nP = c.pose_end - c.pose_begin
+    out = dict(lm_perm=np.zeros(c.n_lmedge_local, np.uint32), pose_ptr=np.zeros(nP + 1, np.uint32),
+               chunk_desc=np.zeros((c.n_chunks, 8), np.uint32), slot_lm=np.zeros(c.n_slots, np.uint32),
+               lm_packed=np.zeros(c.n_lmedge_local, np.uint32))
+    rc = lib().tsb_host_structure(payload, C.c_uint32(len(payload)), C.c_int32(rank), C.c_int32(world),
+                                  *(_p(out[k]) for k in ("lm_perm", "pose_ptr", "chunk_desc", "slot_lm", "lm_packed")))
+    if rc:
+        raise TsbError(rc, lib().tsb_last_error(None).decode())
+    return c, out
 
 
 class TsbError(RuntimeError):

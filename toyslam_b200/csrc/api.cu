@@ -716,6 +716,22 @@ int tsb_host_plan(const void* payload, uint32_t nbytes, int32_t rank, int32_t wo
     return TSB_OK;
 }
 
+// Host-only: the integer structure arrays of rank `rank` (sizes from tsb_host_plan: n_lmedge_local, pose range,
+// n_chunks, n_slots).  lm_perm holds REQUEST-order LM edge indices in this rank's assembly order.
+int tsb_host_structure(const void* payload, uint32_t nbytes, int32_t rank, int32_t world, uint32_t* lm_perm, uint32_t* pose_ptr,
+                       uint32_t* chunk_desc, uint32_t* slot_lm, uint32_t* lm_packed) {
+    if (!payload || world < 1 || rank < 0 || rank >= world) return TSB_EINVAL;
+    HostGraph g; Structure st; std::string err;
+    if (!parse_wire((const uint8_t*)payload, nbytes, g, err)) { g_create_error = err; return TSB_EPARSE; }
+    build_structure(g, (uint32_t)rank, (uint32_t)world, st, 0, nullptr, 0);
+    if (lm_perm) for (size_t k = 0; k < st.lm_perm.size(); ++k) lm_perm[k] = st.le_local[st.lm_perm[k]];
+    if (pose_ptr) std::memcpy(pose_ptr, st.pose_ptr.data(), 4 * st.pose_ptr.size());
+    if (chunk_desc && !st.chunks.empty()) std::memcpy(chunk_desc, st.chunks.data(), 32 * st.chunks.size());
+    if (slot_lm && !st.slot_lm.empty()) std::memcpy(slot_lm, st.slot_lm.data(), 4 * st.slot_lm.size());
+    if (lm_packed && !st.lm_packed.empty()) std::memcpy(lm_packed, st.lm_packed.data(), 4 * st.lm_packed.size());
+    return TSB_OK;
+}
+
 int tsb_get_counts(const tsb_ctx* c, tsb_counts* o) {
     if (!c || !o || !c->loaded) return TSB_EINVAL;
     o->n_pose = c->g.P; o->n_lm = c->g.L; o->n_odom = c->g.Eo; o->n_lmedge = c->g.El; o->n_fixed = (uint32_t)c->g.fixed.size();
