@@ -70,6 +70,8 @@ typedef struct tsb_counts {
     uint32_t replicated;                                      /* 1: world > 1 but the graph is solved whole on every rank (it fits one GPU's resident kernel) */
     uint32_t n_aggregates;                                    /* coarse space of the two-level preconditioner (this rank) */
     uint32_t n_ml_levels, n_ml_top;                           /* multilevel hierarchy of the streamed PCG: levels, nodes of the dense top level */
+    uint32_t structure_reuses;                                /* loads on this context that found the previous request's topology (same integer part of the
+                                                                 payload) and kept its assembly structure and device index arrays; only values were refreshed */
 } tsb_counts;
 
 typedef struct tsb_iter_stats {

@@ -39,7 +39,7 @@ class GraphSoa(C.Structure):
 class Counts(C.Structure):
     _fields_ = [(n, C.c_uint32) for n in ("n_pose", "n_lm", "n_odom", "n_lmedge", "n_fixed", "dim", "pose_begin",
                                           "pose_end", "n_lmedge_local", "n_odom_local", "n_chunks", "n_blocks", "n_slots",
-                                          "pcg_path", "replicated", "n_aggregates", "n_ml_levels", "n_ml_top")]
+                                          "pcg_path", "replicated", "n_aggregates", "n_ml_levels", "n_ml_top", "structure_reuses")]
 
 
 class IterStats(C.Structure):

@@ -11,6 +11,7 @@
 #include <cstdlib>
 #include <cstring>
 #include <string>
+#include <type_traits>
 #include <vector>
 
 using namespace tsb;
@@ -43,6 +44,9 @@ struct tsb_ctx {
     // peer exchange over NVLink (device_graph.h XDev): this rank's region, the peers' regions opened through CUDA IPC
     char* xreg = nullptr; size_t xbytes = 0; char* xpeer[kXMaxWorld] = {}; uint64_t xseq = 0, xlaunch = 0;
     std::vector<uint32_t> gt_ecnt, gt_eoff;               // coarse edges of every rank's top level (global top lists)
+    // structure reuse: topology of the graph whose structure / index arrays are on the device
+    uint64_t topo_hash = 0; uint32_t topo_counts[6] = {0, 0, 0, 0, 0, 0}; bool topo_valid = false, reuse_ints = false;
+    int structure_reuses = 0, st_world = 1, st_rank = 0;      // st_*: effective world / rank the kept structure was built for
     bool use_p2p = true;                                  // TSB_P2P=0: NCCL collectives between phase launches (round-1 path)
     // coarse levels of the preconditioner (two-level aggregates for the resident kernel, multilevel hierarchy for the
     // streamed one): the dense top operator is inverted by k_coarse_invert
@@ -91,10 +95,13 @@ template <typename T> int dalloc(tsb_ctx* c, T*& out, size_t n) {
     { size_t used = c->arena_off; for (size_t i = 0; i < c->arena_blk; ++i) used += c->arena[i].second; c->arena_used = std::max(c->arena_used, used); }
     return TSB_OK;
 }
-template <typename T, typename U> int upload(tsb_ctx* c, const U*& out, const std::vector<T>& v) {
+template <typename T, typename U, typename A> int upload(tsb_ctx* c, const U*& out, const std::vector<T, A>& v) {
     static_assert(sizeof(T) == sizeof(U) || sizeof(U) % sizeof(T) == 0, "layout");
     T* p = nullptr;
     if (int rc = dalloc(c, p, v.size())) return rc;
+    // same topology as the previous request: the bump allocator hands out the same addresses in the same order and the
+    // integer (structure) arrays are still there -- only floating-point values travel again
+    if (c->reuse_ints && std::is_integral<T>::value) { out = reinterpret_cast<const U*>(p); return TSB_OK; }
     if (!v.empty()) CU(cudaMemcpyAsync(p, v.data(), v.size() * sizeof(T), cudaMemcpyHostToDevice, c->stream));
     c->h2d += v.size() * sizeof(T);
     out = reinterpret_cast<const U*>(p); return TSB_OK;
@@ -137,9 +144,10 @@ int upload_graph(tsb_ctx* c) {
     }
     const bool xp = d.xc.world > 1;
     // per-edge data gathered into assembly order
-    std::vector<double> z(2ull * d.nE), w(2ull * d.nE);
-    for (uint32_t k = 0; k < d.nE; ++k) {
-        const uint32_t e = s.le_local[s.lm_perm[k]];
+    pvec<double> z, w; z.resize(2ull * d.nE); w.resize(2ull * d.nE);
+#pragma omp parallel for schedule(static)
+    for (long long kk = 0; kk < (long long)d.nE; ++kk) {
+        const uint32_t k = (uint32_t)kk, e = s.le_local[s.lm_perm[k]];
         z[2ull * k] = g.le_z[2ull * e]; z[2ull * k + 1] = g.le_z[2ull * e + 1];
         w[2ull * k] = g.le_w[2ull * e]; w[2ull * k + 1] = g.le_w[2ull * e + 1];
     }
@@ -642,7 +650,27 @@ int tsb_load_wire(tsb_ctx* c, const void* payload, uint32_t nbytes) {
     if (!c || (!payload && nbytes)) return TSB_EINVAL;
     CU(cudaSetDevice(c->cfg.device));
     free_graph(c); c->h2d = c->d2h = 0;
-    if (!parse_wire((const uint8_t*)payload, nbytes, c->g, c->err)) return TSB_EPARSE;
+    if (!parse_wire((const uint8_t*)payload, nbytes, c->g, c->err)) { c->topo_valid = false; return TSB_EPARSE; }
+    // Structure reuse: a request whose INTEGER part (ids, types, edge lists, fixed ids) hashes like the previous one on
+    // this context keeps the assembly structure and every index array already on the device; only values are refreshed.
+    // (The reference rebuilds graph, index map and device buffers per request: ConnectionHandler.h:18-20, GraphGpu.h:80-187.)
+    {
+        // the switches that decide which structure is built are part of the key
+        auto on = [](const char* n) { const char* e = std::getenv(n); return (e && e[0] == '1') ? 1u : 0u; };
+        const uint32_t mode = on("TSB_FORCE_SHARD") | on("TSB_NO_RESIDENT") << 1 | on("TSB_NO_STREAM") << 2 | (c->force_phased ? 8u : 0u) | c->ml_top << 4;
+        const uint32_t cnt[6] = {c->g.P, c->g.L, c->g.Eo, c->g.El, (uint32_t)c->g.fixed.size() ^ (mode << 8), nbytes};
+        const char* nr = std::getenv("TSB_NO_REUSE");
+        c->reuse_ints = c->topo_valid && c->topo_hash == c->g.topo_hash && std::memcmp(cnt, c->topo_counts, sizeof(cnt)) == 0 &&
+                        c->arena.size() == 1 && !(nr && nr[0] == '1');
+        c->topo_hash = c->g.topo_hash; std::memcpy(c->topo_counts, cnt, sizeof(cnt)); c->topo_valid = false;
+        if (c->reuse_ints) {
+            ++c->structure_reuses;
+            c->world = c->st_world; c->rank = c->st_rank;
+            const int rc = upload_graph(c);
+            c->reuse_ints = false; c->topo_valid = rc == TSB_OK;
+            return rc;
+        }
+    }
     // Sharding decision.  A graph that fits the shared-memory-resident kernel of ONE GPU is latency-bound, not
     // bandwidth-bound: splitting it over NVLink only adds collective latency to every PCG phase, so with world > 1
     // every rank solves it whole (replicated, no collective; results are bit-identical on all ranks).  Larger
@@ -654,14 +682,15 @@ int tsb_load_wire(tsb_ctx* c, const void* payload, uint32_t nbytes) {
     c->world = c->cfg.world; c->rank = c->cfg.rank;
     if (c->cfg.world > 1 && res_nb > 0 && !(fs && fs[0] == '1')) {
         build_structure(c->g, 0, 1, c->st, res_nb, &c->rp);
-        if (c->rp.nb > 0) { c->world = 1; c->rank = 0; return upload_graph(c); }
+        if (c->rp.nb > 0) { c->world = 1; c->rank = 0; c->st_world = 1; c->st_rank = 0; const int rc = upload_graph(c); c->topo_valid = rc == TSB_OK; return rc; }
     }
     // graphs beyond the resident kernel run the streamed PCG with the multilevel hierarchy (one GPU; the sharded path
     // and TSB_PCG_PHASED=1 / TSB_ML=0 keep the two-level aggregates)
     const char* ns = std::getenv("TSB_NO_STREAM");
     const uint32_t ml_top = ((c->world <= 1 || c->use_p2p) && c->use_coarse && !c->force_phased && !(ns && ns[0] == '1')) ? c->ml_top : 0;
     build_structure(c->g, (uint32_t)c->rank, (uint32_t)c->world, c->st, c->world <= 1 ? res_nb : 0, &c->rp, ml_top);
-    return upload_graph(c);
+    c->st_world = c->world; c->st_rank = c->rank;
+    { const int rc = upload_graph(c); c->topo_valid = rc == TSB_OK; return rc; }
 }
 
 int tsb_load_soa(tsb_ctx* c, const tsb_graph_soa* s) {
@@ -741,6 +770,7 @@ int tsb_get_counts(const tsb_ctx* c, tsb_counts* o) {
     o->pcg_path = c->d.res_nb ? 1u : (c->pcg_streamed || c->d.mlLv || c->d.xc.world > 1) ? 3u : (c->world <= 1 && !c->force_phased ? 0u : 2u);
     o->replicated = (c->cfg.world > 1 && c->world == 1) ? 1u : 0u; o->n_aggregates = c->d.nA;
     o->n_ml_levels = c->d.mlLv; o->n_ml_top = c->d.mlLv ? c->d.ml[c->d.mlLv - 1].n : 0;
+    o->structure_reuses = (uint32_t)c->structure_reuses;
     return TSB_OK;
 }
 

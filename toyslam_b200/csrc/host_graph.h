@@ -6,7 +6,22 @@
 #include <string>
 #include <vector>
 
+#include <memory>
+#include <utility>
+
 namespace tsb {
+
+// vector whose resize() leaves new elements uninitialised: the big per-edge arrays are filled by a parallel loop, which
+// then also takes the first-touch page faults in parallel (zero-filling ~2 GB from one thread cost more than the parse)
+template <class T> struct NoInitAlloc : std::allocator<T> {
+    template <class U> struct rebind { using other = NoInitAlloc<U>; };
+    NoInitAlloc() = default;
+    template <class U> NoInitAlloc(const NoInitAlloc<U>&) {}
+    template <class U, class... A> void construct(U* p, A&&... a) {
+        if constexpr (sizeof...(A) == 0) ::new ((void*)p) U; else ::new ((void*)p) U(std::forward<A>(a)...);
+    }
+};
+template <class T> using pvec = std::vector<T, NoInitAlloc<T>>;
 
 struct HostGraph {
     uint32_t P = 0, L = 0, Eo = 0, El = 0;
@@ -15,18 +30,31 @@ struct HostGraph {
     std::vector<double> pose_xyt;     // 3 per pose (x, y, theta) widened from fp32
     std::vector<double> lm_xy;        // 2 per landmark
     // edges in request order, split by type
-    std::vector<uint32_t> od_i, od_j; // canonical pose indices
-    std::vector<double> od_zinv;      // 6 per edge: top two rows of inverse(Z) (EdgeSe2.h:32), fp64
-    std::vector<double> od_w;         // 3 per edge: information diagonal
-    std::vector<uint32_t> le_i, le_l; // pose index, landmark index
-    std::vector<double> le_z;         // 2 per edge: (r cos b, r sin b)  (EdgeSe2Point2d.h:34-35)
-    std::vector<double> le_w;         // 2 per edge
+    pvec<uint32_t> od_i, od_j;        // canonical pose indices
+    pvec<double> od_zinv;             // 6 per edge: top two rows of inverse(Z) (EdgeSe2.h:32), fp64
+    pvec<double> od_w;                // 3 per edge: information diagonal
+    pvec<uint32_t> le_i, le_l;        // pose index, landmark index
+    pvec<double> le_z;                // 2 per edge: (r cos b, r sin b)  (EdgeSe2Point2d.h:34-35)
+    pvec<double> le_w;                // 2 per edge
     std::vector<uint32_t> fixed;      // canonical vertex index (pose k -> k, landmark k -> P + k), repeats kept
     // reply echo
-    std::vector<uint8_t> request;     // copy of the payload
+    pvec<uint8_t> request;            // copy of the payload
     std::vector<uint32_t> req_vertex; // per request vertex: canonical index | type << 31; 0xFFFFFFFF = dropped duplicate
     uint32_t edges_offset = 0;        // byte offset of the edge count in `request`
     uint32_t reply_bytes = 0;
+    // per request edge: byte offset of its record and its index among the edges of its type (ODOM / LM): what lets the
+    // value decode and the reply encode run in parallel over edges (records have no fixed stride in general)
+    pvec<uint32_t> edge_off, edge_slot;
+    uint32_t fixed_offset = 0;        // byte offset of the fixed-id count
+    // 64-bit hash of the INTEGER part of the payload (ids, types, shapes, fixed ids -- everything but the float values):
+    // two requests with the same hash and counts have the same assembly structure (tsb_load_wire reuses it)
+    uint64_t topo_hash = 0;
+    // empties the graph but keeps every buffer: the next request of a persistent context does not page-fault them in again
+    void reset() {
+        P = L = Eo = El = 0; pose_id.clear(); lm_id.clear(); pose_xyt.clear(); lm_xy.clear(); od_i.clear(); od_j.clear(); od_zinv.clear();
+        od_w.clear(); le_i.clear(); le_l.clear(); le_z.clear(); le_w.clear(); fixed.clear(); request.clear(); req_vertex.clear();
+        edges_offset = reply_bytes = fixed_offset = 0; edge_off.clear(); edge_slot.clear(); topo_hash = 0;
+    }
 };
 
 // DeserializeGraph.h:9-174, bounds-checked.  Returns false and sets `err` on malformed input.

@@ -48,7 +48,7 @@ struct IdMap {
 }  // namespace
 
 bool parse_wire(const uint8_t* buf, uint32_t nbytes, HostGraph& g, std::string& err) {
-    g = HostGraph();
+    g.reset();
     Reader r{buf, buf + nbytes};
     auto fail = [&](const char* m) { err = m; return false; };
     if (!r.have(4)) return fail("truncated payload: vertex count");
@@ -106,66 +106,97 @@ bool parse_wire(const uint8_t* buf, uint32_t nbytes, HostGraph& g, std::string& 
     g.edges_offset = (uint32_t)(r.p - buf);
     if (!r.have(4)) return fail("truncated payload: edge count");
     const uint32_t E = r.u32();
-    if ((uint64_t)E * 44 > nbytes) return fail("edge count exceeds payload size");
-    {   // no reallocation while the edges stream in (E bounds both kinds)
-        const size_t cap = E;
-        g.le_i.reserve(cap); g.le_l.reserve(cap); g.le_z.reserve(2 * cap); g.le_w.reserve(2 * cap);
-        const size_t ocap = std::min<size_t>(cap, (size_t)g.P * 4 + 1024);
-        g.od_i.reserve(ocap); g.od_j.reserve(ocap); g.od_zinv.reserve(6 * ocap); g.od_w.reserve(3 * ocap);
-    }
-    uint32_t reply = g.edges_offset + 4;     // bytes of the reply so far (vertex section is the same size
-                                             // unless duplicates were dropped; fixed below)
+    if ((uint64_t)E * 36 > nbytes) return fail("edge count exceeds payload size");
+    // ---- pass 1 over edges (sequential, headers only): record offsets, per-type indices, shape checks --------------------
+    // Records have no fixed stride in general (ODOM as (x, y, theta) or as a matrix, information diagonals of any length
+    // up to the edge dimension), so the offsets come from one cheap scan; the values are then decoded in parallel.
+    g.edge_off.resize(E); g.edge_slot.resize(E);
+    uint32_t nO = 0, nL = 0;
     for (uint32_t i = 0; i < E; ++i) {
         if (!r.have(20)) return fail("truncated payload: edge header");
-        const uint32_t type = r.u32(), id1 = r.u32(), id2 = r.u32(), rows = r.u32(), cols = r.u32();
+        g.edge_off[i] = (uint32_t)(r.p - buf);
+        const uint32_t type = r.u32(); r.p += 8; const uint32_t rows = r.u32(), cols = r.u32();
         if (type > 1) return fail("NOT IMPLE INF edge type");
-        double Z[9] = {1, 0, 0, 0, 1, 0, 0, 0, 1}; double rb[2] = {0, 0};
-        if (rows == 0) {                                   // DeserializeGraph.h:74-95
-            if (type == 0) { if (!r.have(12)) return fail("truncated payload: measurement");
-                const float x = r.f32(), y = r.f32(), t = r.f32(); transform2d(x, y, t, Z); }
-            else { if (!r.have(8)) return fail("truncated payload: measurement"); rb[0] = r.f32(); rb[1] = r.f32(); }
-        } else {                                           // DeserializeGraph.h:97-116: cols x cols values
+        uint32_t mbytes;
+        if (rows == 0) mbytes = type == 0 ? 12u : 8u;      // DeserializeGraph.h:74-95
+        else {                                             // DeserializeGraph.h:97-116: cols x cols values
             if (type != 0) return fail("NOT IMPLE INF edge type");
             if (cols > 3) return fail("ODOM measurement larger than 3x3");
-            if (!r.have(4ull * cols * cols)) return fail("truncated payload: measurement");
-            for (uint32_t a = 0; a < cols; ++a) for (uint32_t b = 0; b < cols; ++b) Z[3 * a + b] = (double)r.f32();
+            mbytes = 4u * cols * cols;
         }
-        if (!r.have(8)) return fail("truncated payload: information header");
+        if (!r.have((size_t)mbytes + 8)) return fail("truncated payload: measurement");
+        r.p += mbytes;
         const uint32_t ri = r.u32(), ci = r.u32();
         if (ri != 0) return fail("NOT IMPLE INF NxN");
-        const uint32_t nd = type == 0 ? 3u : 2u;
-        if (ci > nd) return fail("information diagonal longer than the edge dimension");
+        if (ci > (type == 0 ? 3u : 2u)) return fail("information diagonal longer than the edge dimension");
         if (!r.have(4ull * ci)) return fail("truncated payload: information");
+        r.p += 4ull * ci;
+        g.edge_slot[i] = type == 0 ? nO++ : nL++;
+    }
+    g.Eo = nO; g.El = nL;
+    g.od_i.resize(nO); g.od_j.resize(nO); g.od_zinv.resize(6ull * nO); g.od_w.resize(3ull * nO);
+    g.le_i.resize(nL); g.le_l.resize(nL); g.le_z.resize(2ull * nL); g.le_w.resize(2ull * nL);
+    // ---- pass 2 (parallel over edges): ids -> canonical indices, values, topology hash ------------------------------------
+    uint32_t bad = 0xFFFFFFFFu; int bad_kind = 0;           // lowest failing edge and why (same message as a sequential parse)
+    uint64_t hsum = 0;
+    auto mix = [](uint64_t x) { x += 0x9E3779B97F4A7C15ull; x = (x ^ (x >> 30)) * 0xBF58476D1CE4E5B9ull; x = (x ^ (x >> 27)) * 0x94D049BB133111EBull; return x ^ (x >> 31); };
+#pragma omp parallel for schedule(static) reduction(+ : hsum)
+    for (long long ii = 0; ii < (long long)E; ++ii) {
+        const uint32_t i = (uint32_t)ii;
+        Reader q{buf + g.edge_off[i], buf + nbytes};
+        const uint32_t type = q.u32(), id1 = q.u32(), id2 = q.u32(), rows = q.u32(), cols = q.u32();
+        double Z[9] = {1, 0, 0, 0, 1, 0, 0, 0, 1}; double rb[2] = {0, 0};
+        if (rows == 0) {
+            if (type == 0) { const float x = q.f32(), y = q.f32(), t = q.f32(); transform2d(x, y, t, Z); }
+            else { rb[0] = q.f32(); rb[1] = q.f32(); }
+        } else for (uint32_t a = 0; a < cols; ++a) for (uint32_t b = 0; b < cols; ++b) Z[3 * a + b] = (double)q.f32();
+        q.u32(); const uint32_t ci = q.u32();
         double w[3] = {1, 1, 1};                           // identity, diagonal overwritten (:124-142)
-        for (uint32_t j = 0; j < ci; ++j) w[j] = (double)r.f32();
+        for (uint32_t j = 0; j < ci; ++j) w[j] = (double)q.f32();
+        hsum += mix(mix(mix((uint64_t)i << 32 | type << 16 | rows << 12 | cols << 8 | ci) ^ id1) ^ ((uint64_t)id2 << 1));
         const uint32_t a = m.find(id1), b = m.find(id2);
-        if (a == 0xFFFFFFFFu || b == 0xFFFFFFFFu) return fail("edge references an unknown vertex id");
+        int kind = 0;
+        if (a == 0xFFFFFFFFu || b == 0xFFFFFFFFu) kind = 1;
+        else if (type == 0 && ((a | b) & 0x80000000u)) kind = 2;
+        else if (type == 1 && ((a & 0x80000000u) || !(b & 0x80000000u))) kind = 3;
+        if (kind) {
+#pragma omp critical(tsb_parse_error)
+            if (i < bad) { bad = i; bad_kind = kind; }
+            continue;
+        }
+        const size_t k = g.edge_slot[i];
         if (type == 0) {
-            if ((a | b) & 0x80000000u) return fail("ODOM edge must connect two Se2 vertices");
-            g.od_i.push_back(a); g.od_j.push_back(b);
-            double zi[6]; zinv6(Z, zi);
-            g.od_zinv.insert(g.od_zinv.end(), zi, zi + 6); g.od_w.insert(g.od_w.end(), w, w + 3);
-            reply += 12 + 8 + 36 + 8 + 12;
+            g.od_i[k] = a; g.od_j[k] = b;
+            zinv6(Z, &g.od_zinv[6 * k]); g.od_w[3 * k] = w[0]; g.od_w[3 * k + 1] = w[1]; g.od_w[3 * k + 2] = w[2];
         } else {
-            if ((a & 0x80000000u) || !(b & 0x80000000u)) return fail("LM edge must be (Se2, Point2)");
-            g.le_i.push_back(a); g.le_l.push_back(b & 0x7FFFFFFFu);
+            g.le_i[k] = a; g.le_l[k] = b & 0x7FFFFFFFu;
             double sb, cb; sincos(rb[1], &sb, &cb);          // same values as separate cos / sin calls (glibc)
-            g.le_z.push_back(rb[0] * cb); g.le_z.push_back(rb[0] * sb);
-            g.le_w.push_back(w[0]); g.le_w.push_back(w[1]);
-            reply += 12 + 8 + 8 + 8 + 8;
+            g.le_z[2 * k] = rb[0] * cb; g.le_z[2 * k + 1] = rb[0] * sb;
+            g.le_w[2 * k] = w[0]; g.le_w[2 * k + 1] = w[1];
         }
     }
-    g.Eo = (uint32_t)g.od_i.size(); g.El = (uint32_t)g.le_i.size();
+    if (bad != 0xFFFFFFFFu)
+        return fail(bad_kind == 1 ? "edge references an unknown vertex id" : bad_kind == 2 ? "ODOM edge must connect two Se2 vertices" : "LM edge must be (Se2, Point2)");
+    g.fixed_offset = (uint32_t)(r.p - buf);
     if (!r.have(4)) return fail("truncated payload: fixed count");
     const uint32_t F = r.u32();
     if (!r.have(4ull * F)) return fail("truncated payload: fixed ids");
+    uint64_t h = mix(((uint64_t)V << 32) | E) ^ mix(F);
     for (uint32_t i = 0; i < F; ++i) {
-        const uint32_t c = m.find(r.u32());
+        const uint32_t id = r.u32(), c = m.find(id);
         if (c == 0xFFFFFFFFu) return fail("fixed id is not a vertex");
         g.fixed.push_back((c & 0x80000000u) ? g.P + (c & 0x7FFFFFFFu) : c);   // FixVertex: push_back, repeats kept
+        h = mix(h ^ id);
     }
-    g.request.assign(buf, buf + nbytes);
-    g.reply_bytes = 4 + 20 * g.P + 16 * g.L + (reply - g.edges_offset) + 4 + 4 * F;
+    for (uint32_t i = 0; i < V; ++i) h += mix(((uint64_t)i << 33) ^ ((uint64_t)vtype[i] << 32) ^ vid[i]);
+    g.topo_hash = h + hsum;
+    g.request.resize(nbytes);
+    {   // copy of the payload for the reply echo, in parallel slices
+        const long long nsl = (long long)((nbytes + (8u << 20) - 1) / (8u << 20));
+#pragma omp parallel for schedule(static)
+        for (long long sl = 0; sl < nsl; ++sl) { const size_t o = (size_t)sl * (8u << 20); std::memcpy(&g.request[o], buf + o, std::min<size_t>(8u << 20, nbytes - o)); }
+    }
+    g.reply_bytes = 4 + 20 * g.P + 16 * g.L + 4 + 76 * nO + 44 * nL + 4 + 4 * F;
     return true;
 }
 
@@ -190,22 +221,33 @@ void encode_reply(const HostGraph& g, const double* pose_xyt, const double* lm_x
         }
     }
     const uint32_t E = r.u32(); pu(E);
-    for (uint32_t i = 0; i < E; ++i) {
-        const uint32_t type = r.u32(), id1 = r.u32(), id2 = r.u32(), rows = r.u32(), cols = r.u32();
-        pu(type); pu(id1); pu(id2);
+    // edges are echoed in the reply shape (ODOM 76 B, LM 44 B): output offsets follow from the per-type indices
+    uint8_t* const ebase = o;
+#pragma omp parallel for schedule(static)
+    for (long long ii = 0; ii < (long long)E; ++ii) {
+        const uint32_t i = (uint32_t)ii;
+        Reader q{in + g.edge_off[i], in + g.request.size()};
+        const uint32_t type = q.u32(), id1 = q.u32(), id2 = q.u32(), rows = q.u32(), cols = q.u32();
+        const size_t nod = type == 0 ? g.edge_slot[i] : i - g.edge_slot[i], nlm = i - nod;      // edges of each type before this one
+        uint8_t* w = ebase + 76 * nod + 44 * nlm;
+        auto wu = [&](uint32_t v) { std::memcpy(w, &v, 4); w += 4; };
+        auto wf = [&](float v) { std::memcpy(w, &v, 4); w += 4; };
+        wu(type); wu(id1); wu(id2);
         if (type == 0) {
-            pu(3u); pu(3u);
-            if (rows == 0) { const float x = r.f32(), y = r.f32(), t = r.f32(); double Z[9]; transform2d(x, y, t, Z);
-                for (int q = 0; q < 9; ++q) pf((float)Z[q]); }
+            wu(3u); wu(3u);
+            if (rows == 0) { const float x = q.f32(), y = q.f32(), t = q.f32(); double Z[9]; transform2d(x, y, t, Z);
+                for (int k = 0; k < 9; ++k) wf((float)Z[k]); }
             else { float Z[9] = {1, 0, 0, 0, 1, 0, 0, 0, 1};
-                for (uint32_t a = 0; a < cols; ++a) for (uint32_t b = 0; b < cols; ++b) Z[3 * a + b] = r.f32();
-                for (int q = 0; q < 9; ++q) pf(Z[q]); }
-        } else { pu(2u); pu(1u); pf(r.f32()); pf(r.f32()); }   // Vector2 held as a 2 x 1 dynamic matrix
-        r.u32(); const uint32_t ci = r.u32();
+                for (uint32_t a = 0; a < cols; ++a) for (uint32_t b = 0; b < cols; ++b) Z[3 * a + b] = q.f32();
+                for (int k = 0; k < 9; ++k) wf(Z[k]); }
+        } else { wu(2u); wu(1u); wf(q.f32()); wf(q.f32()); }   // Vector2 held as a 2 x 1 dynamic matrix
+        q.u32(); const uint32_t ci = q.u32();
         const uint32_t nd = type == 0 ? 3u : 2u;
-        pu(0u); pu(nd);
-        for (uint32_t j = 0; j < nd; ++j) pf(j < ci ? r.f32() : 1.0f);
+        wu(0u); wu(nd);
+        for (uint32_t j = 0; j < nd; ++j) wf(j < ci ? q.f32() : 1.0f);
     }
+    o = ebase + 76ull * g.Eo + 44ull * g.El;
+    r.p = in + g.fixed_offset;
     const uint32_t F = r.u32(); pu(F);
     for (uint32_t i = 0; i < F; ++i) pu(r.u32());
 }
