@@ -555,3 +555,14 @@ def test_graph_optimizer_server_end_to_end(gpu):
     assert set(a["vertices"]) == set(b["vertices"]) and len(a["edges"]) == len(b["edges"])
     for vid, (t, v) in a["vertices"].items():
         assert np.allclose(v, b["vertices"][vid][1], rtol=0, atol=2e-6)
+
+
+def test_graph_optimizer_server_drives_two_gpus(gpu):
+    """TSB_GPUS=2: the one server process creates a context per GPU and shards a 10 k-pose request over them; the reply
+    equals the single-GPU result (tools/server_check.py).  Skipped on a 1-GPU box."""
+    import os, subprocess, sys, torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    from conftest import ROOT
+    r = subprocess.run([sys.executable, os.path.join(ROOT, "tools", "server_check.py"), "--gpus", "2"], capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0 and "SERVER MGPU OK" in r.stdout, r.stdout[-3000:] + r.stderr[-3000:]

@@ -6,6 +6,8 @@
 
 #include <nccl.h>
 
+#include <unistd.h>
+
 #include <cmath>
 #include <cstdio>
 #include <cstdlib>
@@ -42,7 +44,7 @@ struct tsb_ctx {
     uint64_t h2d = 0, d2h = 0;                            // bytes copied since the last tsb_load_*
     ncclComm_t comm = nullptr;                            // world > 1: one communicator, collectives on `stream`
     // peer exchange over NVLink (device_graph.h XDev): this rank's region, the peers' regions opened through CUDA IPC
-    char* xreg = nullptr; size_t xbytes = 0; char* xpeer[kXMaxWorld] = {}; uint64_t xseq = 0, xlaunch = 0;
+    char* xreg = nullptr; size_t xbytes = 0; char* xpeer[kXMaxWorld] = {}; bool xpeer_ipc[kXMaxWorld] = {}; uint64_t xseq = 0, xlaunch = 0;
     std::vector<uint32_t> gt_ecnt, gt_eoff;               // coarse edges of every rank's top level (global top lists)
     // structure reuse: topology of the graph whose structure / index arrays are on the device
     uint64_t topo_hash = 0; uint32_t topo_counts[6] = {0, 0, 0, 0, 0, 0}; bool topo_valid = false, reuse_ints = false;
@@ -317,27 +319,44 @@ int allreduce(tsb_ctx* c, double* buf, size_t n) {
 int x_ensure(tsb_ctx* c, size_t bytes) {
     if (bytes <= c->xbytes) return TSB_OK;
     CU(cudaStreamSynchronize(c->stream));
-    for (int r = 0; r < c->cfg.world; ++r) if (r != c->cfg.rank && c->xpeer[r]) { cudaIpcCloseMemHandle(c->xpeer[r]); c->xpeer[r] = nullptr; }
-    if (c->xreg) { cudaFree(c->xreg); c->xreg = nullptr; c->xbytes = 0; }
+    for (int r = 0; r < c->cfg.world; ++r) { if (r != c->cfg.rank && c->xpeer[r] && c->xpeer_ipc[r]) cudaIpcCloseMemHandle(c->xpeer[r]); c->xpeer[r] = nullptr; }
+    if (c->xreg) {      // peers may still be reading the old region: everybody reaches this point before anybody frees
+        int* dz = nullptr; CU(cudaMalloc((void**)&dz, 4)); CU(cudaMemsetAsync(dz, 0, 4, c->stream));
+        ncclAllReduce(dz, dz, 1, ncclInt, ncclSum, c->comm, c->stream); CU(cudaStreamSynchronize(c->stream)); cudaFree(dz);
+        cudaFree(c->xreg); c->xreg = nullptr; c->xbytes = 0;
+    }
     bytes = std::max(bytes + bytes / 4, size_t(32) << 20);
     CU(cudaMalloc((void**)&c->xreg, bytes));
     CU(cudaMemsetAsync(c->xreg, 0, bytes, c->stream));
-    cudaIpcMemHandle_t h;
-    CU(cudaIpcGetMemHandle(&h, c->xreg));
-    static_assert(sizeof(cudaIpcMemHandle_t) == 64, "ipc handle size");
+    // what every rank tells the others about its region: the CUDA-IPC handle (ranks in other processes open it), and
+    // process id + device + raw address (ranks that are threads of THIS process -- graph_optimizer driving several GPUs --
+    // enable peer access and use the address directly: cudaIpcOpenMemHandle refuses handles of its own process)
+    struct XInfo { cudaIpcMemHandle_t h; long long pid; unsigned long long addr; int device; int pad; };
+    static_assert(sizeof(cudaIpcMemHandle_t) == 64 && sizeof(XInfo) == 88, "exchange record");
+    XInfo mine{}; mine.pid = (long long)getpid(); mine.addr = (unsigned long long)(uintptr_t)c->xreg; mine.device = c->cfg.device;
+    CU(cudaIpcGetMemHandle(&mine.h, c->xreg));
     char* hb = nullptr;
-    CU(cudaMalloc((void**)&hb, 64 * (size_t)c->cfg.world));
-    CU(cudaMemcpyAsync(hb + 64 * (size_t)c->cfg.rank, &h, 64, cudaMemcpyHostToDevice, c->stream));
-    const ncclResult_t r = ncclAllGather(hb + 64 * (size_t)c->cfg.rank, hb, 64, ncclChar, c->comm, c->stream);
+    CU(cudaMalloc((void**)&hb, sizeof(XInfo) * (size_t)c->cfg.world));
+    CU(cudaMemcpyAsync(hb + sizeof(XInfo) * (size_t)c->cfg.rank, &mine, sizeof(XInfo), cudaMemcpyHostToDevice, c->stream));
+    const ncclResult_t r = ncclAllGather(hb + sizeof(XInfo) * (size_t)c->cfg.rank, hb, sizeof(XInfo), ncclChar, c->comm, c->stream);
     if (r != ncclSuccess) { cudaFree(hb); c->err = std::string("ncclAllGather: ") + ncclGetErrorString(r); return TSB_ENCCL; }
-    std::vector<cudaIpcMemHandle_t> all(c->cfg.world);
-    CU(cudaMemcpyAsync(all.data(), hb, 64 * (size_t)c->cfg.world, cudaMemcpyDeviceToHost, c->stream));
+    std::vector<XInfo> all(c->cfg.world);
+    CU(cudaMemcpyAsync(all.data(), hb, sizeof(XInfo) * (size_t)c->cfg.world, cudaMemcpyDeviceToHost, c->stream));
     CU(cudaStreamSynchronize(c->stream));
     cudaFree(hb);
     for (int q = 0; q < c->cfg.world; ++q) {
+        c->xpeer_ipc[q] = false;
         if (q == c->cfg.rank) { c->xpeer[q] = c->xreg; continue; }
-        const cudaError_t e = cudaIpcOpenMemHandle((void**)&c->xpeer[q], all[q], cudaIpcMemLazyEnablePeerAccess);
-        if (e != cudaSuccess) { c->err = std::string("cudaIpcOpenMemHandle (peer exchange needs one process per GPU with peer access): ") + cudaGetErrorString(e); return TSB_ECUDA; }
+        if (all[q].pid == mine.pid) {
+            const cudaError_t e = cudaDeviceEnablePeerAccess(all[q].device, 0);
+            if (e != cudaSuccess && e != cudaErrorPeerAccessAlreadyEnabled) { c->err = std::string("cudaDeviceEnablePeerAccess: ") + cudaGetErrorString(e); return TSB_ECUDA; }
+            cudaGetLastError();
+            c->xpeer[q] = (char*)(uintptr_t)all[q].addr;
+            continue;
+        }
+        const cudaError_t e = cudaIpcOpenMemHandle((void**)&c->xpeer[q], all[q].h, cudaIpcMemLazyEnablePeerAccess);
+        if (e != cudaSuccess) { c->err = std::string("cudaIpcOpenMemHandle (the peer exchange needs GPUs with peer access): ") + cudaGetErrorString(e); return TSB_ECUDA; }
+        c->xpeer_ipc[q] = true;
     }
     c->xbytes = bytes; c->xseq = 0; c->xlaunch = 0;           // flags are zero everywhere: every rank memset before it entered the all-gather
     return TSB_OK;
@@ -636,7 +655,7 @@ void tsb_destroy(tsb_ctx* c) {
     if (!c) return;
     cudaSetDevice(c->cfg.device);
     free_graph(c); release_arena(c);
-    for (int r = 0; r < c->cfg.world; ++r) if (r != c->cfg.rank && c->xpeer[r]) cudaIpcCloseMemHandle(c->xpeer[r]);
+    for (int r = 0; r < c->cfg.world; ++r) if (r != c->cfg.rank && c->xpeer[r] && c->xpeer_ipc[r]) cudaIpcCloseMemHandle(c->xpeer[r]);
     if (c->xreg) cudaFree(c->xreg);
     if (c->comm) ncclCommDestroy(c->comm);
     if (c->h_scal) cudaFreeHost(c->h_scal);

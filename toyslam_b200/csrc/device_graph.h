@@ -1,6 +1,7 @@
 // device_graph.h -- device-resident graph, assembly structure and linear system (fp64 SoA in HBM).
 #pragma once
 #include <cuda_runtime.h>
+#include <atomic>
 #include <cstdint>
 #include "host_graph.h"
 
@@ -177,6 +178,6 @@ void launch_x_backsub_own(const Dev& d, cudaStream_t s);       // owners: delta_
 void launch_x_scal_push(const Dev& d, uint32_t slot, const double* src, cudaStream_t s);
 void launch_x_scal_sum(const Dev& d, uint32_t slot, double* dst, cudaStream_t s);
 size_t linearize_smem_bytes();
-extern uint64_t g_launches;   // kernels launched by this library since load
+extern std::atomic<uint64_t> g_launches;   // kernels launched by this library since load (all contexts, all threads)
 
 }  // namespace tsb

@@ -21,8 +21,10 @@
 #include "../../include/toyslam_b200.h"
 
 #include <cooperative_groups.h>
+#include <atomic>
 #include <cstdio>
 #include <cstdlib>
+#include <mutex>
 namespace cg = cooperative_groups;
 
 namespace tsb {
@@ -1047,35 +1049,62 @@ __global__ void k_read_pose(const double4* pose, uint32_t n, double* xyt) {
 // ------------------------------------------------------------------------------------------------
 // launchers
 // ------------------------------------------------------------------------------------------------
-uint64_t g_launches = 0;
+std::atomic<uint64_t> g_launches{0};
 static inline uint32_t cdiv(uint32_t a, uint32_t b) { return (a + b - 1) / b; }
 size_t linearize_smem_bytes() { return LayLin::bytes; }
 
-static bool g_attr_set = false;
-static int g_coop_blocks = 0;      // co-resident blocks of the persistent PCG kernel on this device
-static int g_stream_blocks = 0;    // grid of the streaming kernels: resident blocks per SM x SMs
-static void set_attrs() {
-    if (g_attr_set) return;
-    cudaFuncSetAttribute(k_linearize, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)LayLin::bytes);
-    cudaFuncSetAttribute(k_schur_prep, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)LaySchur::bytes);
-    cudaFuncSetAttribute(k_pcg_pass_a<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)LayA::bytes);
-    cudaFuncSetAttribute(k_pcg_pass_a<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)LayA::bytes);
-    cudaFuncSetAttribute(k_pcg_pass_b, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)LayB::bytes);
-    cudaFuncSetAttribute(k_pcg_persistent, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)LayPcg::bytes);
-    int dev = 0, sms = 0, per_sm = 0;
+// Per-DEVICE launch parameters.  cudaFuncSetAttribute (the > 48 KB shared-memory opt-in) and the occupancy-derived grid
+// sizes belong to a device, not to the process: one server process may drive several GPUs (one context per GPU, one
+// host thread each), and a context on device 1 must not find the kernels configured for device 0 only.
+struct DevInfo {
+    bool init = false;
+    int coop_blocks = 0;       // co-resident blocks of k_pcg_persistent
+    int stream_blocks = 0;     // grid of k_linearize_stream: resident blocks per SM x SMs
+    int pcg_stream_blocks = 0; // grid of k_pcg_stream (0: no cooperative launch)
+    int ci_blocks = 0;         // grid of k_coarse_invert (SM count, 0: unavailable)
+    int res_blocks = 0;        // SM count if k_pcg_resident can be co-scheduled with one block per SM
+    int sb_ok = 0;             // k_sb_build configured
+    int ps_b_blocks = 0;       // grid of the stand-alone streamed pass B
+    size_t top_smem = 0;       // dynamic shared memory k_ml_top may use
+};
+constexpr int kMaxDevices = 64;
+constexpr size_t kMlTopSmemMax = 150 * 1024;      // + ~41 KB static < 227 KB: nc up to 6 400
+static DevInfo g_dev[kMaxDevices];
+static std::mutex g_dev_mu;
+static DevInfo& set_attrs() {
+    int dev = 0;
     cudaGetDevice(&dev);
+    DevInfo& di = g_dev[dev < 0 || dev >= kMaxDevices ? 0 : dev];
+    if (di.init) return di;
+    std::lock_guard<std::mutex> lock(g_dev_mu);
+    if (di.init) return di;
+    int sms = 0, per_sm = 0, coop = 0;
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, dev);
+    auto opt_in = [](const void* fn, size_t bytes) { if (cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes) != cudaSuccess) { cudaGetLastError(); return false; } return true; };
+    opt_in((const void*)k_linearize, LayLin::bytes); opt_in((const void*)k_schur_prep, LaySchur::bytes);
+    opt_in((const void*)k_pcg_pass_a<0>, LayA::bytes); opt_in((const void*)k_pcg_pass_a<1>, LayA::bytes);
+    opt_in((const void*)k_pcg_pass_b, LayB::bytes); opt_in((const void*)k_pcg_persistent, LayPcg::bytes);
     cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_pcg_persistent, kThreads, LayPcg::bytes);
-    g_coop_blocks = sms * per_sm;
-    cudaFuncSetAttribute(k_linearize_stream, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kLsSmemBytes);
-    int ls_per_sm = 0;
-    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&ls_per_sm, k_linearize_stream, kLsThreads, kLsSmemBytes);
-    g_stream_blocks = sms * ls_per_sm;
-    g_attr_set = true;
+    di.coop_blocks = coop ? sms * per_sm : 0;
+    if (opt_in((const void*)k_linearize_stream, kLsSmemBytes)) { per_sm = 0; cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_linearize_stream, kLsThreads, kLsSmemBytes); di.stream_blocks = sms * per_sm; }
+    if (opt_in((const void*)k_pcg_stream<false>, kPsSmemBytes) && opt_in((const void*)k_pcg_stream<true>, kPsSmemBytes)) {
+        int a = 0, b = 0;
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&a, k_pcg_stream<false>, kPsThreads, kPsSmemBytes);
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b, k_pcg_stream<true>, kPsThreads, kPsSmemBytes);
+        di.pcg_stream_blocks = coop ? sms * (a < b ? a : b) : 0;
+    }
+    if (opt_in((const void*)k_coarse_invert, kCiSmemBytes)) { per_sm = 0; cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_coarse_invert, kCiThreads, kCiSmemBytes); di.ci_blocks = (coop && per_sm >= 1) ? sms : 0; }
+    if (opt_in((const void*)k_pcg_resident, kResSmemBytes)) { per_sm = 0; cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_pcg_resident, kResThreads, kResSmemBytes); di.res_blocks = (coop && per_sm >= 1) ? sms : 0; }
+    di.sb_ok = opt_in((const void*)k_sb_build, kSbSmemBytes) ? 1 : 0;
+    if (opt_in((const void*)k_ps_pass_b, kPsSmemBytes)) { per_sm = 0; cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_ps_pass_b, kPsThreads, kPsSmemBytes); di.ps_b_blocks = sms * per_sm; }
+    di.top_smem = opt_in((const void*)k_ml_top, kMlTopSmemMax) ? kMlTopSmemMax : 48 * 1024;
+    di.init = true;
+    return di;
 }
 
 void launch_linearize(const Dev& d, cudaStream_t s) {
-    set_attrs();
+    const int g_stream_blocks = set_attrs().stream_blocks;
     const uint32_t nob = cdiv(d.nP, kThreads);
     if (nob) { k_odom<<<nob, kThreads, 0, s>>>(d); ++g_launches; }
     // HBM-sized graphs stream their chunks through persistent blocks (2 per SM); small ones take one unit per block
@@ -1106,7 +1135,7 @@ void launch_schur_prep(const Dev& d, cudaStream_t s) {
 }
 // whole PCG + back-substitution in one cooperative launch; returns false if the device cannot co-schedule it
 bool launch_pcg_persistent(const Dev& d, cudaStream_t s) {
-    set_attrs();
+    const int g_coop_blocks = set_attrs().coop_blocks;
     if (g_coop_blocks <= 0) return false;
     uint32_t want = d.nBlocks > cdiv(d.nP, kThreads) ? d.nBlocks : cdiv(d.nP, kThreads);
     if (cdiv(d.L, kThreads) > want) want = cdiv(d.L, kThreads);
@@ -1121,19 +1150,7 @@ bool launch_pcg_persistent(const Dev& d, cudaStream_t s) {
 // HBM-sized graphs on one GPU: the streamed variant of the persistent kernel (>= 4 units per resident block);
 // leaves the landmark back-substitution to the caller (launch_pcg_pass_a<1>, launch_pcg_mid, launch_backsub)
 bool launch_pcg_stream(const Dev& d, cudaStream_t s) {
-    static int blocks = -1;
-    if (blocks < 0) {
-        int dev = 0, sms = 0, per_sm = 0, coop = 0;
-        cudaGetDevice(&dev);
-        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-        cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, dev);
-        int per_sm_x = 0;
-        if (cudaFuncSetAttribute(k_pcg_stream<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kPsSmemBytes) != cudaSuccess ||
-            cudaFuncSetAttribute(k_pcg_stream<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kPsSmemBytes) != cudaSuccess) cudaGetLastError();
-        else { cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_pcg_stream<false>, kPsThreads, kPsSmemBytes);
-               cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm_x, k_pcg_stream<true>, kPsThreads, kPsSmemBytes); per_sm = per_sm < per_sm_x ? per_sm : per_sm_x; }
-        blocks = coop ? sms * per_sm : 0;
-    }
+    const int blocks = set_attrs().pcg_stream_blocks;
     uint32_t min_units = 4u * (uint32_t)blocks;
     { const char* e = getenv("TSB_STREAM_MIN_UNITS"); if (e) min_units = (uint32_t)atoi(e);
       e = getenv("TSB_NO_STREAM"); if (e && e[0] == '1' && !d.mlLv && d.xc.world <= 1) return false; }
@@ -1165,23 +1182,13 @@ void launch_ml_levels(const Dev& d, cudaStream_t s) {
 }
 void launch_ml_top(const Dev& d, cudaStream_t s) {
     if (!d.mlLv) return;
-    static size_t top_smem = 0;
     const size_t smem = sizeof(double) * 3 * d.nc;
-    if (smem > top_smem) { cudaFuncSetAttribute(k_ml_top, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); top_smem = smem; }
+    if (smem > set_attrs().top_smem) return;              // cannot happen for nc <= 32 x 148 (k_coarse_invert's own limit)
     k_ml_top<<<d.ml[d.mlLv - 1].n, kMlTopThreads, smem, s>>>(d, d.tl_ptr, d.tl_edge, d.tl_node); ++g_launches;
 }
 // Ai = Ac^-1 and F_COARSE in one cooperative launch; false: not launchable here
 bool launch_coarse_invert(const Dev& d, cudaStream_t s) {
-    static int blocks = -1;
-    if (blocks < 0) {
-        int dev = 0, sms = 0, per_sm = 0, coop = 0;
-        cudaGetDevice(&dev);
-        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-        cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, dev);
-        if (cudaFuncSetAttribute(k_coarse_invert, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kCiSmemBytes) != cudaSuccess) cudaGetLastError();
-        else cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_coarse_invert, kCiThreads, kCiSmemBytes);
-        blocks = (coop && per_sm >= 1) ? sms : 0;
-    }
+    const int blocks = set_attrs().ci_blocks;
     const uint32_t nb = (d.nc + 31) / 32;
     if (!blocks || !d.cbar || !nb || nb > (uint32_t)blocks) return false;
     Dev dd = d; void* args[] = {&dd};
@@ -1199,22 +1206,9 @@ void launch_pcg_coarse(const Dev& d, int init, cudaStream_t s) {
     }
     k_pcg_coarse<<<cdiv(d.nc, kThreads / 32), kThreads, 0, s>>>(d, init); ++g_launches;
 }
-static int g_res_blocks = -1;      // SM count if k_pcg_resident can be co-scheduled with one block per SM, else 0
-int resident_blocks_available() {
-    if (g_res_blocks >= 0) return g_res_blocks;
-    int dev = 0, sms = 0, per_sm = 0, coop = 0;
-    cudaGetDevice(&dev);
-    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-    cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, dev);
-    if (cudaFuncSetAttribute(k_pcg_resident, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kResSmemBytes) != cudaSuccess) { cudaGetLastError(); per_sm = 0; }
-    else cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_pcg_resident, kResThreads, kResSmemBytes);
-    g_res_blocks = (coop && per_sm >= 1) ? sms : 0;
-    return g_res_blocks;
-}
+int resident_blocks_available() { return set_attrs().res_blocks; }
 bool launch_sb_build(const Dev& d, cudaStream_t s) {
-    static int ok = -1;
-    if (ok < 0) ok = cudaFuncSetAttribute(k_sb_build, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSbSmemBytes) == cudaSuccess ? 1 : 0;
-    if (!ok) { cudaGetLastError(); return false; }
+    if (!set_attrs().sb_ok) return false;
     if (!d.res_nb || !d.sbinv) return false;
     k_sb_build<<<d.res_nb * kSbPerBlock, kSbThreads, kSbSmemBytes, s>>>(d); ++g_launches;
     return true;
@@ -1236,15 +1230,7 @@ void launch_pcg_init(const Dev& d, cudaStream_t s) {
 }
 // grid of the stand-alone streamed pass B (2 blocks per SM) when this graph is large enough for it, else 0
 static uint32_t ps_phase_grid(const Dev& d) {
-    static int blocks = -1;
-    if (blocks < 0) {
-        int dev = 0, sms = 0, pb = 0;
-        cudaGetDevice(&dev);
-        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-        if (cudaFuncSetAttribute(k_ps_pass_b, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kPsSmemBytes) != cudaSuccess) cudaGetLastError();
-        else cudaOccupancyMaxActiveBlocksPerMultiprocessor(&pb, k_ps_pass_b, kPsThreads, kPsSmemBytes);
-        blocks = sms * pb;
-    }
+    const int blocks = set_attrs().ps_b_blocks;
     uint32_t min_units = 4u * (uint32_t)(blocks > 0 ? blocks : 0);
     { const char* e = getenv("TSB_STREAM_MIN_UNITS"); if (e) min_units = (uint32_t)atoi(e);
       e = getenv("TSB_NO_STREAM"); if (e && e[0] == '1') return 0; }

@@ -9,9 +9,12 @@
 #pragma once
 #include <cstdint>
 #include <cstdio>
+#include <algorithm>
+#include <cstdlib>
 #include <cstring>
 #include <stdexcept>
 #include <string>
+#include <thread>
 #include <vector>
 
 #include "../../include/toyslam_b200.h"
@@ -20,22 +23,48 @@
 enum class VertexType : unsigned { Se2 = 0, Point2 = 1 };       // remote/graph/vertex/VertexType.h:3-7
 enum class EdgeType : unsigned { Se2 = 0, Se2Point2 = 1 };      // remote/graph/edge/EdgeType.h:3-7
 
-// One process-wide context: the reference rebuilds solver/optimizer/graph per request
+// One process-wide set of contexts: the reference rebuilds solver/optimizer/graph per request
 // (ConnectionHandler.h:18-20); device buffers, streams and the NCCL communicator persist here.
+// TSB_GPUS=N (default 1) makes the ONE server process drive N GPUs (devices 0 .. N-1): one context per GPU, rank r on
+// device r, a request is edge-sharded over them (contiguous pose ranges, NVLink peer exchange inside the kernels).  The
+// library's calls are collective over the ranks, so every call runs on all contexts at once from N short-lived host
+// threads (remote/app/main.cpp:42 has one thread for everything; the GPU work is what runs in parallel here).
 class GpuContext {
 public:
-    static tsb_ctx* Get(int enable_exits = 1, int verbose = 1) {
-        static GpuContext inst(enable_exits, verbose);
-        return inst.ctx;
+    static GpuContext& Instance(int enable_exits = 1, int verbose = 1) { static GpuContext inst(enable_exits, verbose); return inst; }
+    static tsb_ctx* Get(int enable_exits = 1, int verbose = 1) { return Instance(enable_exits, verbose).ctx[0]; }
+    int world() const { return (int)ctx.size(); }
+    // fn(rank, ctx) on every rank concurrently; the first non-zero status wins (rank order)
+    template <class F> int Each(F fn) {
+        if (ctx.size() == 1) return fn(0, ctx[0]);
+        std::vector<int> rc(ctx.size(), 0);
+        std::vector<std::thread> th;
+        for (size_t r = 0; r < ctx.size(); ++r) th.emplace_back([&, r] { rc[r] = fn((int)r, ctx[r]); });
+        for (auto& t : th) t.join();
+        for (int v : rc) if (v) return v;
+        return 0;
     }
 private:
     GpuContext(int enable_exits, int verbose) {
-        tsb_config cfg{}; cfg.device = 0; cfg.rank = 0; cfg.world = 1; cfg.pcg_tol = 1e-12; cfg.pcg_max_iters = 20000;
-        cfg.enable_exits = enable_exits; cfg.verbose = verbose;
-        if (tsb_create(&cfg, &ctx) != TSB_OK) throw std::runtime_error(std::string("tsb_create: ") + tsb_last_error(nullptr));
+        int n = 1;
+        if (const char* e = std::getenv("TSB_GPUS")) n = std::max(1, std::atoi(e));
+        if (n > 8) throw std::runtime_error("TSB_GPUS: at most 8 GPUs");
+        unsigned char id[128] = {};
+        if (n > 1 && tsb_nccl_unique_id(id) != TSB_OK) throw std::runtime_error(std::string("tsb_nccl_unique_id: ") + tsb_last_error(nullptr));
+        ctx.assign((size_t)n, nullptr);
+        std::vector<int> rc((size_t)n, 0);
+        std::vector<std::thread> th;
+        for (int r = 0; r < n; ++r)            // ncclCommInitRank blocks until every rank has joined: create the contexts in parallel
+            th.emplace_back([&, r] {
+                tsb_config cfg{}; cfg.device = r; cfg.rank = r; cfg.world = n; cfg.nccl_id = n > 1 ? id : nullptr; cfg.pcg_tol = 1e-12;
+                cfg.pcg_max_iters = 20000; cfg.enable_exits = enable_exits; cfg.verbose = r == 0 ? verbose : 0;
+                rc[(size_t)r] = tsb_create(&cfg, &ctx[(size_t)r]);
+            });
+        for (auto& t : th) t.join();
+        for (int v : rc) if (v != TSB_OK) throw std::runtime_error(std::string("tsb_create: ") + tsb_last_error(nullptr));
     }
-    ~GpuContext() { tsb_destroy(ctx); }
-    tsb_ctx* ctx = nullptr;
+    ~GpuContext() { for (tsb_ctx* c : ctx) tsb_destroy(c); }
+    std::vector<tsb_ctx*> ctx;
 };
 
 template <typename T>
@@ -57,31 +86,41 @@ public:
     // --- bulk path: the request payload as received (DeserializeGraphStart, GraphManager.h:35-54) ---
     void LoadFromWire(const char* bytes, uint32_t nbytes) { wire.assign(bytes, bytes + nbytes); use_wire = true; }
 
-    // ToDevice (GraphGpu.h:80-187): parse / upload; throws with the library's message on a malformed payload
-    void ToDevice(tsb_ctx* ctx) {
-        int rc;
-        if (use_wire) rc = tsb_load_wire(ctx, wire.data(), (uint32_t)wire.size());
-        else {
-            tsb_graph_soa s{};
+    // ToDevice (GraphGpu.h:80-187): parse / upload on every rank; throws with the library's message on a malformed payload
+    void ToDevice(GpuContext& gc) {
+        tsb_graph_soa s{};
+        if (!use_wire) {
             s.n_pose = (uint32_t)pose_id.size(); s.n_lm = (uint32_t)lm_id.size(); s.n_odom = (uint32_t)od_ij.size() / 2;
             s.n_lmedge = (uint32_t)le_ij.size() / 2; s.n_fixed = (uint32_t)fixed.size();
             s.pose_id = pose_id.data(); s.pose_xyt = pose_xyt.data(); s.lm_id = lm_id.data(); s.lm_xy = lm_xy.data();
             s.odom_ij = od_ij.data(); s.odom_Z = od_Z.data(); s.odom_w = od_w.data();
             s.lmedge_ij = le_ij.data(); s.lmedge_meas = le_meas.data(); s.lmedge_w = le_w.data(); s.fixed_id = fixed.data();
-            rc = tsb_load_soa(ctx, &s);
         }
-        if (rc != TSB_OK) throw std::runtime_error(tsb_last_error(ctx));
+        std::string msg;
+        const int rc = gc.Each([&](int r, tsb_ctx* ctx) {
+            const int v = use_wire ? tsb_load_wire(ctx, wire.data(), (uint32_t)wire.size()) : tsb_load_soa(ctx, &s);
+            if (v != TSB_OK && r == 0) msg = tsb_last_error(ctx);
+            return v;
+        });
+        if (rc != TSB_OK) throw std::runtime_error(msg.empty() ? "tsb_load failed on a rank" : msg);
         on_device = true;
     }
+    void ToDevice(tsb_ctx*) { ToDevice(GpuContext::Instance()); }
     // SerializeGraph (SerializeGraph.h:8-72): reply payload with the 4-byte size prefix, as the reference returns it
-    std::vector<uint8_t> Serialize(tsb_ctx* ctx) const {
+    // (every rank takes part in the state gather; rank 0's bytes are the reply)
+    std::vector<uint8_t> Serialize(GpuContext& gc) const {
         uint32_t n = 0;
-        if (!on_device || tsb_reply_size(ctx, &n) != TSB_OK) return {};
-        std::vector<uint8_t> out(4 + (size_t)n);
-        std::memcpy(out.data(), &n, 4);
-        if (tsb_write_reply(ctx, out.data() + 4, n) != TSB_OK) return {};
-        return out;
+        if (!on_device || tsb_reply_size(GpuContext::Get(), &n) != TSB_OK) return {};
+        std::vector<std::vector<uint8_t>> out((size_t)gc.world());
+        const int rc = gc.Each([&](int r, tsb_ctx* ctx) {
+            out[(size_t)r].resize(4 + (size_t)n);
+            std::memcpy(out[(size_t)r].data(), &n, 4);
+            return tsb_write_reply(ctx, out[(size_t)r].data() + 4, n);
+        });
+        if (rc != TSB_OK) return {};
+        return std::move(out[0]);
     }
+    std::vector<uint8_t> Serialize(tsb_ctx*) const { return Serialize(GpuContext::Instance()); }
     bool on_device = false;
 private:
     bool use_wire = false;
@@ -99,9 +138,17 @@ public:
         if (graphIn == nullptr) return;                                    // OptimizerCpu.h:27-30
         auto* graph = dynamic_cast<GraphGpu<T>*>(graphIn);
         if (graph == nullptr) { std::printf("OptimizerGpu: not a GraphGpu\n"); return; }   // OptimizerGpu.cu:22-27
-        tsb_ctx* ctx = GpuContext::Get();
-        if (!graph->on_device) graph->ToDevice(ctx);
-        if (tsb_optimize(ctx, this->iterations, &report, nullptr) != TSB_OK) throw std::runtime_error(tsb_last_error(ctx));
+        GpuContext& gc = GpuContext::Instance();
+        if (!graph->on_device) graph->ToDevice(gc);
+        std::vector<tsb_report> rep((size_t)gc.world());
+        std::string msg;
+        const int rc = gc.Each([&](int r, tsb_ctx* ctx) {
+            const int v = tsb_optimize(ctx, this->iterations, &rep[(size_t)r], nullptr);
+            if (v != TSB_OK && r == 0) msg = tsb_last_error(ctx);
+            return v;
+        });
+        if (rc != TSB_OK) throw std::runtime_error(msg.empty() ? "tsb_optimize failed on a rank" : msg);
+        report = rep[0];
     }
     tsb_report report{};
 };

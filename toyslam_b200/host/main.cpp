@@ -55,10 +55,10 @@ void serve(int fd, int iters) {
         try {
             OptimizerGpu<float> optimizer((unsigned)iters, nullptr);
             GraphGpu<float> graph;
-            { Timer t("DeserializeGraph"); graph.LoadFromWire(bytes.data(), (uint32_t)bytes.size()); graph.ToDevice(GpuContext::Get()); }
+            { Timer t("DeserializeGraph"); graph.LoadFromWire(bytes.data(), (uint32_t)bytes.size()); graph.ToDevice(GpuContext::Instance()); }
             { Timer t("OptimizeGPU"); optimizer.Optimize(&graph); }
             std::vector<uint8_t> data;
-            { Timer t("SerializeGraph"); data = graph.Serialize(GpuContext::Get()); }
+            { Timer t("SerializeGraph"); data = graph.Serialize(GpuContext::Instance()); }
             std::cout << "SendSync() data size: " << data.size() << std::endl;
             Timer t("Sending");
             if (!write_all(fd, data.data(), data.size())) return;
@@ -88,7 +88,7 @@ int main(int argc, char* argv[]) {
         std::cerr << "this build ships the PIPELINE=gpu path only; `cpu eigen` is the reference's own pipeline\n";
         return 2;
     }
-    try { GpuContext::Get(); } catch (const std::exception& e) { std::cerr << "ConnectionManager error: " << e.what() << std::endl; return 1; }
+    try { const int n = GpuContext::Instance().world(); std::cout << "GPUs: " + std::to_string(n) << std::endl; } catch (const std::exception& e) { std::cerr << "ConnectionManager error: " << e.what() << std::endl; return 1; }
 
     addrinfo hints{}; hints.ai_family = AF_INET; hints.ai_socktype = SOCK_STREAM; hints.ai_flags = AI_PASSIVE;
     addrinfo* res = nullptr;
