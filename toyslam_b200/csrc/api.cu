@@ -670,6 +670,7 @@ int tsb_load_wire(tsb_ctx* c, const void* payload, uint32_t nbytes) {
     CU(cudaSetDevice(c->cfg.device));
     free_graph(c); c->h2d = c->d2h = 0;
     if (!parse_wire((const uint8_t*)payload, nbytes, c->g, c->err)) { c->topo_valid = false; return TSB_EPARSE; }
+    if (c->g.reply_bytes > 0x7FFFFFFFu) { c->topo_valid = false; c->err = "reply would exceed the signed 32-bit frame size of the wire protocol"; return TSB_EPARSE; }
     // Structure reuse: a request whose INTEGER part (ids, types, edge lists, fixed ids) hashes like the previous one on
     // this context keeps the assembly structure and every index array already on the device; only values are refreshed.
     // (The reference rebuilds graph, index map and device buffers per request: ConnectionHandler.h:18-20, GraphGpu.h:80-187.)
@@ -706,7 +707,10 @@ int tsb_load_wire(tsb_ctx* c, const void* payload, uint32_t nbytes) {
     // graphs beyond the resident kernel run the streamed PCG with the multilevel hierarchy (one GPU; the sharded path
     // and TSB_PCG_PHASED=1 / TSB_ML=0 keep the two-level aggregates)
     const char* ns = std::getenv("TSB_NO_STREAM");
-    const uint32_t ml_top = ((c->world <= 1 || c->use_p2p) && c->use_coarse && !c->force_phased && !(ns && ns[0] == '1')) ? c->ml_top : 0;
+    // top level: 1024 nodes, 1536 for the million-pose graphs (their PCG iteration moves 2.5 GB, the 170 MB dense inverse is
+    // cheap beside it and every halving of the top spacing saves ~30 % of the iterations); TSB_ML_TOP overrides
+    const uint32_t top_default = (c->ml_top == kMlTopDefault && c->g.P >= 500000u) ? kMlTopMax : c->ml_top;
+    const uint32_t ml_top = ((c->world <= 1 || c->use_p2p) && c->use_coarse && !c->force_phased && !(ns && ns[0] == '1')) ? top_default : 0;
     build_structure(c->g, (uint32_t)c->rank, (uint32_t)c->world, c->st, c->world <= 1 ? res_nb : 0, &c->rp, ml_top);
     c->st_world = c->world; c->st_rank = c->rank;
     { const int rc = upload_graph(c); c->topo_valid = rc == TSB_OK; return rc; }

@@ -78,7 +78,8 @@ uint32_t ml_plan(uint32_t nP, uint32_t top_max, std::vector<std::pair<uint32_t, 
     uint32_t n = nP, spacing = 1, cnt = 0;
     bool first = true;
     while ((first || n > top_max) && cnt < kMlMaxLevels) {
-        const uint32_t ratio = (!first && (n + 1) / 2 <= top_max) ? 2u : 4u;
+        uint32_t ratio = 4;                       // the last step takes the smallest ratio that fits the top level: the finer it is, the fewer PCG iterations
+        if (!first) { if ((n + 1) / 2 <= top_max) ratio = 2; else if ((n + 2) / 3 <= top_max) ratio = 3; }
         spacing *= ratio; n = (n + ratio - 1) / ratio; ++cnt; first = false;
         if (levels) levels->emplace_back(ratio, spacing);
     }

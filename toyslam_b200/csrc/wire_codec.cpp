@@ -196,7 +196,10 @@ bool parse_wire(const uint8_t* buf, uint32_t nbytes, HostGraph& g, std::string& 
 #pragma omp parallel for schedule(static)
         for (long long sl = 0; sl < nsl; ++sl) { const size_t o = (size_t)sl * (8u << 20); std::memcpy(&g.request[o], buf + o, std::min<size_t>(8u << 20, nbytes - o)); }
     }
-    g.reply_bytes = 4 + 20 * g.P + 16 * g.L + 4 + 76 * nO + 44 * nL + 4 + 4 * F;
+    {   // the reply frame carries a signed 32-bit size: computed in 64 bits, saturated (tsb_load_wire rejects > INT32_MAX)
+        const uint64_t rb = 4 + 20ull * g.P + 16ull * g.L + 4 + 76ull * nO + 44ull * nL + 4 + 4ull * F;
+        g.reply_bytes = rb > 0xFFFFFFFFull ? 0xFFFFFFFFu : (uint32_t)rb;
+    }
     return true;
 }
 
