@@ -78,8 +78,8 @@ struct MlLevel {
     uint32_t n = 0, ratio = 4, spacing = 4;      // nodes, nodes of the level below per node interval, poses per node interval
     std::vector<uint32_t> node_ptr;              // n + 1 offsets into edge_lm: coarse edges of a node, landmark ascending
     std::vector<uint32_t> edge_lm;               // landmark of each coarse edge
-    std::vector<uint32_t> ref_ptr;               // nnz + 1 offsets into ref
-    std::vector<uint32_t> ref;                   // child edge index (level below; level 1: LM edge in assembly order) << 4 | (child - ratio * K + 7)
+    pvec<uint32_t> ref_ptr;                      // nnz + 1 offsets into ref
+    pvec<uint32_t> ref;                          // child edge index (level below; level 1: LM edge in assembly order) << 4 | (child - ratio * K + 7)
 };
 
 // Assembly structure of one rank (all integer; compared bit-exactly in tests).

@@ -8,6 +8,9 @@
 #include "host_graph.h"
 
 #include <algorithm>
+#include <chrono>
+#include <cstdio>
+#include <cstdlib>
 #include <numeric>
 #ifdef _OPENMP
 #include <omp.h>
@@ -16,6 +19,18 @@
 namespace tsb {
 
 namespace {
+
+// TSB_HOST_TIMING=1: wall time of each section of build_structure on stderr
+struct SectionTimer {
+    bool on = std::getenv("TSB_HOST_TIMING") != nullptr;
+    std::chrono::steady_clock::time_point t = std::chrono::steady_clock::now();
+    void lap(const char* what) {
+        if (!on) return;
+        const auto n = std::chrono::steady_clock::now();
+        std::fprintf(stderr, "[tsb] build_structure %-28s %8.1f ms\n", what, std::chrono::duration<double, std::milli>(n - t).count());
+        t = n;
+    }
+};
 
 // One level of the hierarchy from the level below (child nodes with their landmark-sorted edge lists).
 // Parent K interpolates to the children ratio*K - (ratio-1) .. ratio*K + (ratio-1); its coarse edges are the distinct
@@ -29,42 +44,69 @@ void build_ml_level(const std::vector<uint32_t>& cptr, const std::vector<uint32_
     nt = omp_get_max_threads();
 #endif
     nt = std::max(1, std::min<int>(nt, (int)(n / 64 + 1)));
-    std::vector<std::vector<uint32_t>> t_lm(nt), t_cnt(nt), t_ref(nt);
+    auto k_lo_of = [&](uint32_t K) { return ratio * K >= ratio - 1 ? ratio * K - (ratio - 1) : 0u; };
+    auto k_hi_of = [&](uint32_t K) { return (uint32_t)std::min<uint64_t>(nc - 1, (uint64_t)ratio * K + ratio - 1); };
+    // every child edge of a node's children is one entry of `ref`: the node's offset into it is known up front, so the
+    // threads write their part of `ref` in place; the thread ranges are balanced by that count
+    std::vector<uint64_t> roff(n + 1, 0);
+    for (uint32_t K = 0; K < n; ++K) roff[K + 1] = roff[K] + (cptr[k_hi_of(K) + 1] - cptr[k_lo_of(K)]);
+    lv.ref.resize(roff[n]);
+    std::vector<std::vector<uint32_t>> t_lm(nt), t_cnt(nt);
     std::vector<uint32_t> t_lo(nt + 1);
-    for (int t = 0; t <= nt; ++t) t_lo[t] = (uint32_t)((uint64_t)n * t / nt);
+    for (int t = 0; t <= nt; ++t) t_lo[t] = t == nt ? n : (uint32_t)(std::lower_bound(roff.begin(), roff.end(), roff[n] * (uint64_t)t / nt) - roff.begin());
 #pragma omp parallel for num_threads(nt) schedule(static, 1)
     for (int t = 0; t < nt; ++t) {
-        std::vector<uint64_t> tmp;
-        auto& olm = t_lm[t]; auto& ocnt = t_cnt[t]; auto& oref = t_ref[t];
+        std::vector<uint64_t> tmp, tmp2;
+        uint32_t run[2 * 8 + 2];
+        auto& olm = t_lm[t]; auto& ocnt = t_cnt[t];
+        const size_t guess = (size_t)((roff[t_lo[t + 1]] - roff[t_lo[t]]) / 2 + 64);
+        olm.reserve(guess); ocnt.reserve(guess);
         for (uint32_t K = t_lo[t]; K < t_lo[t + 1]; ++K) {
-            const uint32_t k_lo = ratio * K >= ratio - 1 ? ratio * K - (ratio - 1) : 0;
-            const uint32_t k_hi = std::min<uint64_t>(nc - 1, (uint64_t)ratio * K + ratio - 1);
+            const uint32_t k_lo = k_lo_of(K), k_hi = k_hi_of(K);
+            // keys (landmark, child edge, child offset); every child's list is landmark-sorted and the child edge indices
+            // ascend from child to child, so the sorted order is a merge of <= 7 sorted runs (a third of std::sort's time)
             tmp.clear();
-            for (uint32_t k = k_lo; k <= k_hi; ++k)
+            uint32_t nrun = 0;
+            for (uint32_t k = k_lo; k <= k_hi; ++k) {
+                run[nrun++] = (uint32_t)tmp.size();
                 for (uint32_t e = cptr[k]; e < cptr[k + 1]; ++e)
                     tmp.push_back(((uint64_t)clm[e] << 32) | ((uint64_t)e << 4) | (uint64_t)(k + 7 - ratio * K));
-            std::sort(tmp.begin(), tmp.end());
+            }
+            run[nrun] = (uint32_t)tmp.size();
+            tmp2.resize(tmp.size());
+            while (nrun > 1) {
+                uint32_t nout = 0;
+                for (uint32_t q = 0; q < nrun; q += 2) {
+                    const uint32_t lo = run[q], mid = run[q + 1], hi = q + 2 <= nrun ? run[std::min(q + 2, nrun)] : mid;
+                    const uint64_t *a = tmp.data() + lo, *ae = tmp.data() + mid, *b = ae, *be = tmp.data() + (q + 1 < nrun ? hi : mid);
+                    uint64_t* o = tmp2.data() + lo;
+                    while (a < ae && b < be) { const bool tb = *b < *a; *o++ = tb ? *b : *a; a += !tb; b += tb; }
+                    while (a < ae) *o++ = *a++;
+                    while (b < be) *o++ = *b++;
+                    run[nout++] = lo;
+                }
+                run[nout] = (uint32_t)tmp.size();
+                nrun = nout; tmp.swap(tmp2);
+            }
             uint32_t ne = 0;
+            uint32_t* oref = lv.ref.data() + roff[K];
             for (size_t q = 0; q < tmp.size(); ++q) {
                 const uint32_t l = (uint32_t)(tmp[q] >> 32);
                 if (q == 0 || l != (uint32_t)(tmp[q - 1] >> 32)) { olm.push_back(l); ocnt.push_back(0); ++ne; }
-                ocnt.back()++; oref.push_back((uint32_t)tmp[q]);
+                ocnt.back()++; oref[q] = (uint32_t)tmp[q];
             }
             lv.node_ptr[K + 1] = ne;
         }
     }
     for (uint32_t K = 0; K < n; ++K) lv.node_ptr[K + 1] += lv.node_ptr[K];
     const uint32_t nnz = lv.node_ptr[n];
-    lv.edge_lm.resize(nnz); lv.ref_ptr.assign(nnz + 1, 0);
-    size_t nref = 0; for (int t = 0; t < nt; ++t) nref += t_ref[t].size();
-    lv.ref.resize(nref);
-    std::vector<size_t> e_off(nt + 1, 0), r_off(nt + 1, 0);
-    for (int t = 0; t < nt; ++t) { e_off[t + 1] = e_off[t] + t_lm[t].size(); r_off[t + 1] = r_off[t] + t_ref[t].size(); }
+    lv.edge_lm.resize(nnz); lv.ref_ptr.resize((size_t)nnz + 1); lv.ref_ptr[0] = 0;
+    std::vector<size_t> e_off(nt + 1, 0);
+    for (int t = 0; t < nt; ++t) e_off[t + 1] = e_off[t] + t_lm[t].size();
 #pragma omp parallel for num_threads(nt) schedule(static, 1)
     for (int t = 0; t < nt; ++t) {
         std::copy(t_lm[t].begin(), t_lm[t].end(), lv.edge_lm.begin() + e_off[t]);
-        std::copy(t_ref[t].begin(), t_ref[t].end(), lv.ref.begin() + r_off[t]);
-        size_t r = r_off[t];
+        size_t r = roff[t_lo[t]];
         for (size_t q = 0; q < t_cnt[t].size(); ++q) { r += t_cnt[t][q]; lv.ref_ptr[e_off[t] + q + 1] = (uint32_t)r; }
     }
 }
@@ -87,6 +129,7 @@ uint32_t ml_plan(uint32_t nP, uint32_t top_max, std::vector<std::pair<uint32_t, 
 }
 void build_hierarchy(Structure& s, const std::vector<uint32_t>& elm, uint32_t top_max) {
     s.ml.clear(); s.ml_local = 0;
+    SectionTimer tm;
     s.ml.reserve(kMlMaxLevels);                  // the loop keeps pointers into the previous level
     std::vector<std::pair<uint32_t, uint32_t>> plan;
     if (!ml_plan(s.nP, top_max, &plan)) return;
@@ -94,8 +137,10 @@ void build_hierarchy(Structure& s, const std::vector<uint32_t>& elm, uint32_t to
     for (const auto& lv : plan) {
         s.ml.emplace_back();
         build_ml_level(*cptr, *clm, lv.first, lv.second, s.ml.back());
+        if (std::getenv("TSB_HOST_TIMING")) std::fprintf(stderr, "[tsb]   level spacing %u: n %u nnz %zu refs %zu\n", lv.second, s.ml.back().n, s.ml.back().edge_lm.size(), s.ml.back().ref.size());
         if (lv.first == 4 && lv.second <= kMlHalo && s.ml_local + 1 == s.ml.size()) s.ml_local = (uint32_t)s.ml.size();
         cptr = &s.ml.back().node_ptr; clm = &s.ml.back().edge_lm;
+        tm.lap("  hierarchy level");
     }
 }
 
@@ -104,6 +149,7 @@ void build_hierarchy(Structure& s, const std::vector<uint32_t>& elm, uint32_t to
 void build_structure(const HostGraph& g, uint32_t rank, uint32_t world, Structure& s, uint32_t resident_blocks, ResidentPlan* rp,
                      uint32_t ml_top) {
     s = Structure();
+    SectionTimer tm;
     const uint32_t P = g.P, L = g.L;
     // ---- pose partition: contiguous ranges balanced by edge work --------------------------------
     std::vector<uint32_t> deg(P + 1, 0);
@@ -128,21 +174,36 @@ void build_structure(const HostGraph& g, uint32_t rank, uint32_t world, Structur
     s.pose_ptr.assign(nP + 1, 0);
     for (uint32_t p = 0; p < nP; ++p) s.pose_ptr[p + 1] = s.pose_ptr[p] + deg[pb + p];
     const uint32_t nE = s.pose_ptr[nP];
-    s.le_local.reserve(nE);
-    std::vector<uint32_t> cur(s.pose_ptr.begin(), s.pose_ptr.end() - 1);
-    s.lm_perm.resize(nE);
-    for (uint32_t e = 0; e < g.El; ++e) {
-        const uint32_t p = g.le_i[e];
-        if (p < pb || p >= pe) continue;
-        s.lm_perm[cur[p - pb]++] = (uint32_t)s.le_local.size();     // stable: request order inside a pose
-        s.le_local.push_back(e);
+    // request edges of this rank's poses, in request order.  Requests usually list the LM edges pose by pose (the reference's
+    // simulator does): then the local edges are one contiguous request range already grouped by pose and the scatter
+    // below is the identity
+    bool grouped = true;
+#pragma omp parallel for schedule(static) reduction(&& : grouped)
+    for (long long e = 1; e < (long long)g.El; ++e) grouped = grouped && g.le_i[e - 1] <= g.le_i[e];
+    s.le_local.resize(nE); s.lm_perm.resize(nE);
+    if (grouped) {
+        const uint32_t first = (uint32_t)(std::lower_bound(g.le_i.begin(), g.le_i.end(), pb) - g.le_i.begin());
+#pragma omp parallel for schedule(static)
+        for (long long k = 0; k < (long long)nE; ++k) { s.le_local[k] = first + (uint32_t)k; s.lm_perm[k] = (uint32_t)k; }
+    } else {
+        std::vector<uint32_t> cur(s.pose_ptr.begin(), s.pose_ptr.end() - 1);
+        uint32_t nl = 0;
+        for (uint32_t e = 0; e < g.El; ++e) {
+            const uint32_t p = g.le_i[e];
+            if (p < pb || p >= pe) continue;
+            s.lm_perm[cur[p - pb]++] = nl;                               // stable: request order inside a pose
+            s.le_local[nl++] = e;
+        }
     }
-    for (uint32_t p = 0; p < nP; ++p) {                              // then by landmark inside a pose
+#pragma omp parallel for schedule(dynamic, 1024)
+    for (long long pp = 0; pp < (long long)nP; ++pp) {                   // then by landmark inside a pose
+        const uint32_t p = (uint32_t)pp;
         auto b = s.lm_perm.begin() + s.pose_ptr[p], e = s.lm_perm.begin() + s.pose_ptr[p + 1];
         std::sort(b, e, [&](uint32_t x, uint32_t y) {
             const uint32_t lx = g.le_l[s.le_local[x]], ly = g.le_l[s.le_local[y]];
             return lx != ly ? lx < ly : x < y; });
     }
+    tm.lap("partition + edge order");
     // ---- blocks and chunks ------------------------------------------------------------------------
     s.blk_chunk_ptr.push_back(0);
     for (uint32_t p = 0; p < nP;) {
@@ -164,42 +225,72 @@ void build_structure(const HostGraph& g, uint32_t rank, uint32_t world, Structur
         }
         s.blk_chunk_ptr.push_back((uint32_t)s.chunks.size());
     }
+    tm.lap("chunks");
     // ---- slots: distinct landmarks per chunk ---------------------------------------------------------
     s.lm_packed.resize(nE); s.slot_edge.resize(nE);
-    s.slot_ptr.push_back(0);
     std::vector<uint32_t> elm(nE);                       // landmark of each LM edge in assembly order
-    for (uint32_t k = 0; k < nE; ++k) elm[k] = g.le_l[s.le_local[s.lm_perm[k]]];
-    std::vector<uint32_t> stamp(L, 0xFFFFFFFFu), lslot(L, 0), uniq, ucnt, order, srank, cnt;
-    for (uint32_t ci = 0; ci < s.chunks.size(); ++ci) {
-        ChunkDesc& c = s.chunks[ci];
-        const uint32_t n = c.e1 - c.e0;
-        // distinct landmarks of the chunk (stamp table: O(n)), then sorted by landmark
-        uniq.clear();
-        for (uint32_t k = 0; k < n; ++k) { const uint32_t l = elm[c.e0 + k]; if (stamp[l] != ci) { stamp[l] = ci; uniq.push_back(l); } }
-        std::sort(uniq.begin(), uniq.end());
-        const uint32_t nu = (uint32_t)uniq.size();
-        for (uint32_t q = 0; q < nu; ++q) lslot[uniq[q]] = q;          // landmark-sorted index
-        // slots are numbered by descending edge count (ties: ascending landmark): the 32 lanes of a warp that sum
-        // neighbouring slots then run the same number of iterations
-        ucnt.assign(nu, 0); srank.resize(nu); order.resize(nu);
-        for (uint32_t k = 0; k < n; ++k) ucnt[lslot[elm[c.e0 + k]]]++;
-        std::iota(order.begin(), order.end(), 0u);
-        std::stable_sort(order.begin(), order.end(), [&](uint32_t x, uint32_t y) { return ucnt[x] > ucnt[y]; });
-        for (uint32_t q = 0; q < nu; ++q) srank[order[q]] = q;
-        c.s0 = (uint32_t)s.slot_lm.size(); c.s1 = c.s0 + nu;
-        for (uint32_t q = 0; q < nu; ++q) s.slot_lm.push_back(uniq[order[q]]);
-        cnt.assign(nu + 1, 0);
-        uint32_t pose = c.p0;
-        for (uint32_t k = 0; k < n; ++k) {
-            const uint32_t slot = srank[lslot[elm[c.e0 + k]]];
-            while (c.e0 + k >= s.pose_ptr[pose + 1]) ++pose;
-            s.lm_packed[c.e0 + k] = ((pose - c.p0) << 16) | slot;
-            cnt[slot + 1]++;
+#pragma omp parallel for schedule(static)
+    for (long long k = 0; k < (long long)nE; ++k) elm[k] = g.le_l[s.le_local[s.lm_perm[k]]];
+    std::vector<uint32_t> stamp(L, 0xFFFFFFFFu), lslot(L, 0), uniq, cnt;      // also used by the aggregate path below
+    {
+        // every thread takes a contiguous range of chunks (<= kChunkEdges edges each: balanced) and numbers its slots from
+        // 0; the ranges are concatenated afterwards.  lm_packed / slot_edge / slot_ptr hold chunk-relative or edge-absolute
+        // values, so only ChunkDesc::s0 / s1 need the thread's slot offset
+        const uint32_t nCh = (uint32_t)s.chunks.size();
+        int nt = 1;
+#ifdef _OPENMP
+        nt = omp_get_max_threads();
+#endif
+        nt = std::max(1, std::min<int>(nt, (int)(nCh / 256 + 1)));
+        std::vector<std::vector<uint32_t>> t_slm(nt), t_sptr(nt);
+#pragma omp parallel for num_threads(nt) schedule(static, 1)
+        for (int t = 0; t < nt; ++t) {
+            const uint32_t c_lo = (uint32_t)((uint64_t)nCh * t / nt), c_hi = (uint32_t)((uint64_t)nCh * (t + 1) / nt);
+            std::vector<uint32_t> st_(L, 0xFFFFFFFFu), ls_(L, 0), uq, ucnt, order, srank, ct;
+            auto& oslm = t_slm[t]; auto& osptr = t_sptr[t];
+            for (uint32_t ci = c_lo; ci < c_hi; ++ci) {
+                ChunkDesc& c = s.chunks[ci];
+                const uint32_t n = c.e1 - c.e0;
+                // distinct landmarks of the chunk (stamp table: O(n)), then sorted by landmark
+                uq.clear();
+                for (uint32_t k = 0; k < n; ++k) { const uint32_t l = elm[c.e0 + k]; if (st_[l] != ci) { st_[l] = ci; uq.push_back(l); } }
+                std::sort(uq.begin(), uq.end());
+                const uint32_t nu = (uint32_t)uq.size();
+                for (uint32_t q = 0; q < nu; ++q) ls_[uq[q]] = q;          // landmark-sorted index
+                // slots are numbered by descending edge count (ties: ascending landmark): the 32 lanes of a warp that sum
+                // neighbouring slots then run the same number of iterations
+                ucnt.assign(nu, 0); srank.resize(nu); order.resize(nu);
+                for (uint32_t k = 0; k < n; ++k) ucnt[ls_[elm[c.e0 + k]]]++;
+                std::iota(order.begin(), order.end(), 0u);
+                std::stable_sort(order.begin(), order.end(), [&](uint32_t x, uint32_t y) { return ucnt[x] > ucnt[y]; });
+                for (uint32_t q = 0; q < nu; ++q) srank[order[q]] = q;
+                c.s0 = (uint32_t)oslm.size(); c.s1 = c.s0 + nu;            // thread-relative until the ranges are joined
+                for (uint32_t q = 0; q < nu; ++q) oslm.push_back(uq[order[q]]);
+                ct.assign(nu + 1, 0);
+                uint32_t pose = c.p0;
+                for (uint32_t k = 0; k < n; ++k) {
+                    const uint32_t slot = srank[ls_[elm[c.e0 + k]]];
+                    while (c.e0 + k >= s.pose_ptr[pose + 1]) ++pose;
+                    s.lm_packed[c.e0 + k] = ((pose - c.p0) << 16) | slot;
+                    ct[slot + 1]++;
+                }
+                for (size_t q = 0; q < nu; ++q) ct[q + 1] += ct[q];
+                for (size_t q = 0; q < nu; ++q) osptr.push_back(c.e0 + ct[q + 1]);
+                for (uint32_t k = 0; k < n; ++k) s.slot_edge[c.e0 + ct[s.lm_packed[c.e0 + k] & 0xffffu]++] = (uint16_t)k;
+            }
         }
-        for (size_t q = 0; q < nu; ++q) cnt[q + 1] += cnt[q];
-        for (size_t q = 0; q < nu; ++q) s.slot_ptr.push_back(c.e0 + cnt[q + 1]);
-        for (uint32_t k = 0; k < n; ++k) s.slot_edge[c.e0 + cnt[s.lm_packed[c.e0 + k] & 0xffffu]++] = (uint16_t)k;
+        std::vector<uint32_t> s_off(nt + 1, 0);
+        for (int t = 0; t < nt; ++t) s_off[t + 1] = s_off[t] + (uint32_t)t_slm[t].size();
+        s.slot_lm.resize(s_off[nt]); s.slot_ptr.resize((size_t)s_off[nt] + 1); s.slot_ptr[0] = 0;
+#pragma omp parallel for num_threads(nt) schedule(static, 1)
+        for (int t = 0; t < nt; ++t) {
+            std::copy(t_slm[t].begin(), t_slm[t].end(), s.slot_lm.begin() + s_off[t]);
+            std::copy(t_sptr[t].begin(), t_sptr[t].end(), s.slot_ptr.begin() + 1 + s_off[t]);
+            const uint32_t c_lo = (uint32_t)((uint64_t)nCh * t / nt), c_hi = (uint32_t)((uint64_t)nCh * (t + 1) / nt);
+            for (uint32_t ci = c_lo; ci < c_hi; ++ci) { s.chunks[ci].s0 += s_off[t]; s.chunks[ci].s1 += s_off[t]; }
+        }
     }
+    tm.lap("slots");
     // ---- landmark-major CSR over slots ---------------------------------------------------------------
     const uint32_t nS = (uint32_t)s.slot_lm.size();
     s.lm_part_ptr.assign(L + 1, 0);
@@ -208,6 +299,7 @@ void build_structure(const HostGraph& g, uint32_t rank, uint32_t world, Structur
     s.lm_part_idx.resize(nS);
     { std::vector<uint32_t> c2(s.lm_part_ptr.begin(), s.lm_part_ptr.end() - 1);
       for (uint32_t q = 0; q < nS; ++q) s.lm_part_idx[c2[s.slot_lm[q]]++] = q; }
+    tm.lap("landmark CSR over slots");
     // ---- ODOM edges touching a local pose -----------------------------------------------------------
     auto local = [&](uint32_t p) { return p >= pb && p < pe; };
     std::vector<uint32_t> ghosts;
@@ -239,6 +331,7 @@ void build_structure(const HostGraph& g, uint32_t rank, uint32_t world, Structur
     s.od_in_edge.resize(s.od_in_ptr[nP]);
     { std::vector<uint32_t> c2(s.od_in_ptr.begin(), s.od_in_ptr.end() - 1);
       for (uint32_t k = 0; k < nO; ++k) if (s.od_b[k] < nP) s.od_in_edge[c2[s.od_b[k]]++] = k; }
+    tm.lap("odom lists");
     // ---- boundary poses (same list on every rank) ---------------------------------------------------
     if (world > 1) {
         auto owner = [&](uint32_t p) { return (uint32_t)(std::upper_bound(s.cuts.begin(), s.cuts.end(), p) - s.cuts.begin()) - 1; };
@@ -265,6 +358,7 @@ void build_structure(const HostGraph& g, uint32_t rank, uint32_t world, Structur
         s.lm_mask.assign(L, 0);
         for (uint32_t e = 0; e < g.El; ++e) s.lm_mask[g.le_l[e]] |= (uint8_t)(1u << owner(g.le_i[e]));
     }
+    tm.lap("boundary / exchange lists");
     // ---- coarse space: aggregates of agg_K consecutive local poses ------------------------------------
     {
         // ---- resident plan: pose / landmark ranges per block, balanced by LM edges ----------------------------
@@ -332,7 +426,8 @@ void build_structure(const HostGraph& g, uint32_t rank, uint32_t world, Structur
             s.agg_K = 32; s.nA = 0; s.agg_ptr.assign(1, 0);
             s.aslot_ptr.push_back(0); s.cpair_ptr.push_back(0);
             s.edge_pose.resize(nE);
-            for (uint32_t p = 0; p < nP; ++p) for (uint32_t k = s.pose_ptr[p]; k < s.pose_ptr[p + 1]; ++k) s.edge_pose[k] = p;
+#pragma omp parallel for schedule(static)
+            for (long long p = 0; p < (long long)nP; ++p) for (uint32_t k = s.pose_ptr[p]; k < s.pose_ptr[p + 1]; ++k) s.edge_pose[k] = (uint32_t)p;
         }
         const bool use_ml = !resident && top_rank > 0;
         if (!resident && !use_ml) {
@@ -400,6 +495,7 @@ void build_structure(const HostGraph& g, uint32_t rank, uint32_t world, Structur
         }
         }
     }
+    tm.lap("coarse space / hierarchy");
     // ---- fixed vertices ---------------------------------------------------------------------------
     s.fixed_pose_count.assign(nP, 0); s.fixed_lm_count.assign(L, 0);
     for (uint32_t v : g.fixed) {
