@@ -48,6 +48,7 @@ struct tsb_ctx {
     std::vector<uint32_t> gt_ecnt, gt_eoff;               // coarse edges of every rank's top level (global top lists)
     // structure reuse: topology of the graph whose structure / index arrays are on the device
     uint64_t topo_hash = 0; uint32_t topo_counts[6] = {0, 0, 0, 0, 0, 0}; bool topo_valid = false, reuse_ints = false;
+    pvec<uint8_t> soa_wire;                                   // tsb_load_soa: the request bytes laid out from the SoA arrays (kept across requests)
     int structure_reuses = 0, st_world = 1, st_rank = 0;      // st_*: effective world / rank the kept structure was built for
     bool use_p2p = true;                                  // TSB_P2P=0: NCCL collectives between phase launches (round-1 path)
     // coarse levels of the preconditioner (two-level aggregates for the resident kernel, multilevel hierarchy for the
@@ -718,27 +719,40 @@ int tsb_load_wire(tsb_ctx* c, const void* payload, uint32_t nbytes) {
 
 int tsb_load_soa(tsb_ctx* c, const tsb_graph_soa* s) {
     if (!c || !s) return TSB_EINVAL;
-    // encode exactly what the reference client would send (graph_to_bytes.py:32-67), then take the wire path
-    std::vector<uint8_t> buf;
-    auto pu = [&](uint32_t v) { const uint8_t* p = (const uint8_t*)&v; buf.insert(buf.end(), p, p + 4); };
-    auto pf = [&](float v) { const uint8_t* p = (const uint8_t*)&v; buf.insert(buf.end(), p, p + 4); };
-    buf.reserve(16 + 20ull * s->n_pose + 16ull * s->n_lm + 76ull * s->n_odom + 44ull * s->n_lmedge + 4ull * s->n_fixed);
-    pu(s->n_pose + s->n_lm);
-    for (uint32_t i = 0; i < s->n_pose; ++i) { pu(s->pose_id[i]); pu(0); for (int q = 0; q < 3; ++q) pf(s->pose_xyt[3ull * i + q]); }
-    for (uint32_t i = 0; i < s->n_lm; ++i) { pu(s->lm_id[i]); pu(1); pf(s->lm_xy[2ull * i]); pf(s->lm_xy[2ull * i + 1]); }
-    pu(s->n_odom + s->n_lmedge);
-    for (uint32_t i = 0; i < s->n_odom; ++i) {
-        pu(0); pu(s->odom_ij[2ull * i]); pu(s->odom_ij[2ull * i + 1]); pu(3); pu(3);
-        for (int q = 0; q < 9; ++q) pf(s->odom_Z[9ull * i + q]);
-        pu(0); pu(3); for (int q = 0; q < 3; ++q) pf(s->odom_w[3ull * i + q]);
+    // The request bytes are needed in any case (the reply echoes the edges from them, SerializeGraph.h:30-63), so the SoA
+    // arrays are laid out as exactly what the reference client would send (graph_to_bytes.py:32-67) -- fixed-size records
+    // at known offsets, written by a parallel loop into a buffer the context keeps -- and take the wire path, whose decode
+    // is parallel as well
+    const uint64_t oV = 4, oL = oV + 20ull * s->n_pose, oE = oL + 16ull * s->n_lm, oO = oE + 4, oM = oO + 76ull * s->n_odom,
+                   oF = oM + 44ull * s->n_lmedge, total = oF + 4 + 4ull * s->n_fixed;
+    if (total > 0xFFFFFFFFull) { c->err = "graph too large for the 32-bit wire size prefix"; return TSB_EINVAL; }
+    if ((s->n_pose && (!s->pose_id || !s->pose_xyt)) || (s->n_lm && (!s->lm_id || !s->lm_xy)) || (s->n_odom && (!s->odom_ij || !s->odom_Z || !s->odom_w)) ||
+        (s->n_lmedge && (!s->lmedge_ij || !s->lmedge_meas || !s->lmedge_w)) || (s->n_fixed && !s->fixed_id)) { c->err = "tsb_load_soa: null array"; return TSB_EINVAL; }
+    pvec<uint8_t>& buf = c->soa_wire; buf.resize(total);
+    uint8_t* o = buf.data();
+    auto pu = [](uint8_t* p, uint32_t v) { std::memcpy(p, &v, 4); };
+    pu(o, s->n_pose + s->n_lm); pu(o + oE, s->n_odom + s->n_lmedge); pu(o + oF, s->n_fixed);
+#pragma omp parallel
+    {
+#pragma omp for schedule(static) nowait
+        for (long long i = 0; i < (long long)s->n_pose; ++i) { uint8_t* p = o + oV + 20ull * i; pu(p, s->pose_id[i]); pu(p + 4, 0); std::memcpy(p + 8, s->pose_xyt + 3ull * i, 12); }
+#pragma omp for schedule(static) nowait
+        for (long long i = 0; i < (long long)s->n_lm; ++i) { uint8_t* p = o + oL + 16ull * i; pu(p, s->lm_id[i]); pu(p + 4, 1); std::memcpy(p + 8, s->lm_xy + 2ull * i, 8); }
+#pragma omp for schedule(static) nowait
+        for (long long i = 0; i < (long long)s->n_odom; ++i) {
+            uint8_t* p = o + oO + 76ull * i;
+            pu(p, 0); std::memcpy(p + 4, s->odom_ij + 2ull * i, 8); pu(p + 12, 3); pu(p + 16, 3); std::memcpy(p + 20, s->odom_Z + 9ull * i, 36);
+            pu(p + 56, 0); pu(p + 60, 3); std::memcpy(p + 64, s->odom_w + 3ull * i, 12);
+        }
+#pragma omp for schedule(static) nowait
+        for (long long i = 0; i < (long long)s->n_lmedge; ++i) {
+            uint8_t* p = o + oM + 44ull * i;
+            pu(p, 1); std::memcpy(p + 4, s->lmedge_ij + 2ull * i, 8); pu(p + 12, 0); pu(p + 16, 2); std::memcpy(p + 20, s->lmedge_meas + 2ull * i, 8);
+            pu(p + 28, 0); pu(p + 32, 2); std::memcpy(p + 36, s->lmedge_w + 2ull * i, 8);
+        }
+#pragma omp for schedule(static)
+        for (long long i = 0; i < (long long)s->n_fixed; ++i) pu(o + oF + 4 + 4ull * i, s->fixed_id[i]);
     }
-    for (uint32_t i = 0; i < s->n_lmedge; ++i) {
-        pu(1); pu(s->lmedge_ij[2ull * i]); pu(s->lmedge_ij[2ull * i + 1]); pu(0); pu(2);
-        pf(s->lmedge_meas[2ull * i]); pf(s->lmedge_meas[2ull * i + 1]);
-        pu(0); pu(2); pf(s->lmedge_w[2ull * i]); pf(s->lmedge_w[2ull * i + 1]);
-    }
-    pu(s->n_fixed);
-    for (uint32_t i = 0; i < s->n_fixed; ++i) pu(s->fixed_id[i]);
     return tsb_load_wire(c, buf.data(), (uint32_t)buf.size());
 }
 
