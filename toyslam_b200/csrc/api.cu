@@ -8,6 +8,7 @@
 
 #include <unistd.h>
 
+#include <algorithm>
 #include <cmath>
 #include <cstdio>
 #include <cstdlib>
@@ -290,7 +291,7 @@ int upload_graph(tsb_ctx* c) {
     c->part_cap = std::max<uint32_t>(std::max<uint32_t>(d.nBlocks, (std::max(d.nP, g.L) + kThreads - 1) / kThreads) + 1, 4096);
     TRY(dalloc(c, d.part, c->part_cap)); TRY(dalloc(c, d.part2, c->part_cap));
     TRY(dalloc(c, d.scal, (size_t)S_COUNT)); TRY(dalloc(c, d.flags, (size_t)F_COUNT));
-    { const char* e = std::getenv("TSB_PCG_TIMING"); if (e && e[0] == '1') { TRY(dalloc(c, d.dbg, (size_t)16)); CU(cudaMemsetAsync(d.dbg, 0, 128, c->stream)); } }
+    { const char* e = std::getenv("TSB_PCG_TIMING"); if (e && e[0] == '1') { TRY(dalloc(c, d.dbg, (size_t)16 + 9 * 1024)); CU(cudaMemsetAsync(d.dbg, 0, 8 * (16 + 9 * 1024), c->stream)); } }
     CU(cudaMemsetAsync(d.scal, 0, sizeof(double) * S_COUNT, c->stream));
     CU(cudaMemsetAsync(d.flags, 0, sizeof(int) * F_COUNT, c->stream));
     CU(cudaMemsetAsync(d.p, 0, 24ull * nPG, c->stream));
@@ -517,6 +518,21 @@ int run_solve(tsb_ctx* c, bool refresh_coarse = true, bool smoother = true) {
             std::fprintf(stderr, "[tsb] streamed PCG, %d iterations, SM cycles per iteration (block 0):", its);
             for (int q = 0; q < 8; ++q) std::fprintf(stderr, " %s=%lld", nm[q], its ? t[q] / its : 0);
             std::fprintf(stderr, "\n");
+            if (std::getenv("TSB_PCG_TIMING_BLOCKS") && its) {       // spread over the blocks: which phase waits for whom
+                std::vector<long long> all(9 * 1024);
+                CU(cudaMemcpy(all.data(), d.dbg + 16, 8 * all.size(), cudaMemcpyDeviceToHost));
+                uint32_t nb = 0; while (nb < 1024 && all[9 * nb + 8]) ++nb;
+                for (int q : {0, 2, 4, 6}) {
+                    std::vector<std::pair<long long, uint32_t>> v;
+                    for (uint32_t b = 0; b < nb; ++b) v.emplace_back(all[9 * b + q] / its, b);
+                    std::sort(v.begin(), v.end());
+                    std::fprintf(stderr, "[tsb]   %-7s over %u blocks: min %lld  p10 %lld  median %lld  p90 %lld  max %lld | slowest:", nm[q], nb, v[0].first, v[nb / 10].first,
+                                 v[nb / 2].first, v[nb * 9 / 10].first, v[nb - 1].first);
+                    for (uint32_t k = 0; k < 4 && k < nb; ++k) { const uint32_t b = v[nb - 1 - k].second;
+                        std::fprintf(stderr, " b%u/sm%lld/%lldch=%lld", b, all[9 * b + 8] & 0xffffffff, all[9 * b + 8] >> 32, v[nb - 1 - k].first); }
+                    std::fprintf(stderr, "\n");
+                }
+            }
         }
         launch_pcg_pass_a(d, 1, c->stream);
         if (p2p(c)) {          // Hpl^T delta_p summed over ranks by the landmark's owner, delta_l pushed back to every rank

@@ -298,7 +298,7 @@ __global__ void __launch_bounds__(kPsThreads, 2) k_pcg_stream(const Dev d) {
     const double tol2 = d.scal[S_TOL2]; const int maxit = d.flags[F_MAXIT];
     int it = 0;
     // optional phase timing (TSB_PCG_TIMING=1): SM cycles of block 0 per phase, barrier waits separate
-    const bool timing = d.dbg != nullptr && blockIdx.x == 0 && tid == 0;
+    const bool timing = d.dbg != nullptr && tid == 0;                 // every block: d.dbg[16 + 9 b ..] = its eight counters + SM id
     long long tk = 0; long long tacc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
 #define TICK(slot) do { if (timing) { const long long now_ = clock64(); tacc[slot] += now_ - tk; tk = now_; } } while (0)
     if (rz0 > 0) {
@@ -351,6 +351,11 @@ __global__ void __launch_bounds__(kPsThreads, 2) k_pcg_stream(const Dev d) {
     if (blockIdx.x == 0 && tid == 0) {
         d.scal[S_RZ0] = rz0; d.scal[S_RZ] = rz; d.scal[S_BETA] = beta; d.flags[F_ITERS] = it; d.flags[F_DONE] = 1;
         if (timing) for (int q = 0; q < 8; ++q) d.dbg[q] = tacc[q];
+    }
+    if (timing) {
+        uint32_t smid; asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
+        for (int q = 0; q < 8; ++q) d.dbg[16 + 9 * blockIdx.x + q] = tacc[q];
+        d.dbg[16 + 9 * blockIdx.x + 8] = (long long)smid | ((long long)(ce - cb) << 32);
     }
 #undef TICK
 }
