@@ -66,10 +66,9 @@ __device__ __forceinline__ void ps_pass_a(const Dev& d, unsigned char* smem, uin
     double* pvec = reinterpret_cast<double*>(smem + kPsAux);
     unsigned char* ring = smem + kPsRing;
     const uint32_t bar0 = smem_u32(smem + kPsBar), tid = threadIdx.x;
-    const ChunkDesc zero = {0, 0, 0, 0, 0, 0, 0xFFFFFFFFu, 0};
-    ChunkDesc cur = d.chunks[cb];
-    ChunkDesc nx1 = cb + 1 < ce ? d.chunks[cb + 1] : zero;
-    ChunkDesc nx2 = cb + 2 < ce ? d.chunks[cb + 2] : zero;
+    ChunkDesc cur = d.chunks[cb];                       // clamped, not selected against a dummy: see k_linearize_stream
+    ChunkDesc nx1 = d.chunks[min(cb + 1, ce - 1)];
+    ChunkDesc nx2 = d.chunks[min(cb + 2, ce - 1)];
     if (tid == 0) {
         ps_issue<0>(d, cur, ring + (kbase % kLsStages) * kPsStageBytes, bar0 + 8 * (kbase % kLsStages));
         if (cb + 1 < ce) ps_issue<0>(d, nx1, ring + ((kbase + 1) % kLsStages) * kPsStageBytes, bar0 + 8 * ((kbase + 1) % kLsStages));
@@ -98,7 +97,7 @@ __device__ __forceinline__ void ps_pass_a(const Dev& d, unsigned char* smem, uin
         unsigned char* st = ring + sidx * kPsStageBytes;
         const uint32_t n = cur.e1 - cur.e0, ns = cur.s1 - cur.s0;
         const bool newunit = c + 1 < ce && nx1.block != cur.block;
-        const ChunkDesc nx3 = c + 3 < ce ? d.chunks[c + 3] : zero;
+        const ChunkDesc nx3 = d.chunks[min(c + 3, ce - 1)];
         // p of the next chunk's poses when it starts a new unit: a raw load, in flight during this chunk
         const uint32_t tn = newunit ? 3 * (nx1.p1 - nx1.p0) : 0;
         double pn = 0;
@@ -137,10 +136,9 @@ __device__ __forceinline__ double ps_pass_b(const Dev& d, unsigned char* smem, u
     unsigned char* ring = smem + kPsRing;
     const uint32_t bar0 = smem_u32(smem + kPsBar), tid = threadIdx.x;
     const double2* usum = reinterpret_cast<const double2*>(d.w_sum);        // u_l = Hll^-1 w_l, written by the middle phase
-    const ChunkDesc zero = {0, 0, 0, 0, 0, 0, 0xFFFFFFFFu, 0};
     ChunkDesc cur = d.chunks[cb];
-    ChunkDesc nx1 = cb + 1 < ce ? d.chunks[cb + 1] : zero;
-    ChunkDesc nx2 = cb + 2 < ce ? d.chunks[cb + 2] : zero;
+    ChunkDesc nx1 = d.chunks[min(cb + 1, ce - 1)];
+    ChunkDesc nx2 = d.chunks[min(cb + 2, ce - 1)];
     if (tid == 0) {
         ps_issue<1>(d, cur, ring + (kbase % kLsStages) * kPsStageBytes, bar0 + 8 * (kbase % kLsStages));
         if (cb + 1 < ce) ps_issue<1>(d, nx1, ring + ((kbase + 1) % kLsStages) * kPsStageBytes, bar0 + 8 * ((kbase + 1) % kLsStages));
@@ -157,11 +155,11 @@ __device__ __forceinline__ double ps_pass_b(const Dev& d, unsigned char* smem, u
         const uint32_t k = kbase + (c - cb), sidx = k % kLsStages;
         unsigned char* st = ring + sidx * kPsStageBytes;
         const uint32_t n = cur.e1 - cur.e0, np = cur.p1 - cur.p0;
-        const bool last = nx1.block != cur.block;                    // `zero` ends the block's final unit
-        const ChunkDesc nx3 = c + 3 < ce ? d.chunks[c + 3] : zero;
+        const bool last = c + 1 >= ce || nx1.block != cur.block;      // the block's final chunk ends its unit
+        const ChunkDesc nx3 = d.chunks[min(c + 3, ce - 1)];
         // next chunk: u of its slots; this unit's sp and p if it ends here (global loads in flight during this chunk)
         double2 un = {};
-        const uint32_t ns_next = nx1.s1 - nx1.s0;
+        const uint32_t ns_next = c + 1 < ce ? nx1.s1 - nx1.s0 : 0u;
         if (c + 1 < ce) {
             const uint32_t s2 = (k + 1) % kLsStages;
             mbar_wait(bar0 + 8 * s2, ((k + 1) / kLsStages) & 1u);
