@@ -127,12 +127,10 @@ __global__ void __launch_bounds__(kLsThreads, 2) k_linearize_stream(const Dev d)
     if (cb >= ce) { if (tid == 0) d.part[blockIdx.x] = 0; return; }
 
     // chunk descriptors, read by every thread (uniform loads) up to three chunks ahead
-    // descriptors beyond the block's range are never used: the loads are clamped instead of selected against a dummy, because a
-    // select right behind the load made every warp sit out the load's full latency at the top of each chunk (ncu r2a: 8.6 % of the
-    // kernel's stall samples, long scoreboard, at that line)
+    const ChunkDesc zero = {0, 0, 0, 0, 0, 0, 0xFFFFFFFFu, 0};
     ChunkDesc cur = d.chunks[cb];
-    ChunkDesc nx1 = d.chunks[min(cb + 1, ce - 1)];
-    ChunkDesc nx2 = d.chunks[min(cb + 2, ce - 1)];
+    ChunkDesc nx1 = cb + 1 < ce ? d.chunks[cb + 1] : zero;
+    ChunkDesc nx2 = cb + 2 < ce ? d.chunks[cb + 2] : zero;
     if (tid == 0) {
         ls_issue(d, cur, ring, bar0);
         if (cb + 1 < ce) ls_issue(d, nx1, ring + kLsStageBytes, bar0 + 8);
@@ -149,9 +147,8 @@ __global__ void __launch_bounds__(kLsThreads, 2) k_linearize_stream(const Dev d)
         const uint32_t k = c - cb, sidx = k % kLsStages;
         unsigned char* st = ring + sidx * kLsStageBytes;
         const uint32_t n = cur.e1 - cur.e0, ns = cur.s1 - cur.s0, np = cur.p1 - cur.p0;
-        const bool has1 = c + 1 < ce;
-        const bool last = !has1 || nx1.block != cur.block;        // the block's final chunk ends its unit
-        const ChunkDesc nx3 = d.chunks[min(c + 3, ce - 1)];       // consumed at the end of this iteration
+        const bool last = nx1.block != cur.block;                 // `zero` has block 0xFFFFFFFF: the block's final chunk ends its unit
+        const ChunkDesc nx3 = c + 3 < ce ? d.chunks[c + 3] : zero;  // consumed at the end of this iteration
         mbar_wait(bar0 + 8 * sidx, (k / kLsStages) & 1u);
         const uint32_t* pk = reinterpret_cast<const uint32_t*>(st + kLsPk) + (cur.e0 & 3u);
         const uint16_t* sedge = reinterpret_cast<const uint16_t*>(st + kLsSe) + (cur.e0 & 7u);
@@ -166,8 +163,8 @@ __global__ void __launch_bounds__(kLsThreads, 2) k_linearize_stream(const Dev d)
         }
         // ---- prefetch for the next chunk: per-edge values and slot landmarks into registers -------------------
         double2 nz0 = {}, nw0 = {}, lmv0 = {};
-        const uint32_t ns_next = has1 ? nx1.s1 - nx1.s0 : 0u;
-        if (has1 && tid < nx1.e1 - nx1.e0) { nz0 = d.le_z[nx1.e0 + tid]; nw0 = d.le_w[nx1.e0 + tid]; }
+        const uint32_t ns_next = nx1.s1 - nx1.s0;
+        if (tid < nx1.e1 - nx1.e0) { nz0 = d.le_z[nx1.e0 + tid]; nw0 = d.le_w[nx1.e0 + tid]; }
         if (c + 1 < ce) {
             const uint32_t s2 = (k + 1) % kLsStages;
             mbar_wait(bar0 + 8 * s2, ((k + 1) / kLsStages) & 1u);          // issued two iterations ago

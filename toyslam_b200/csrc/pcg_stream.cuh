@@ -66,7 +66,9 @@ __device__ __forceinline__ void ps_pass_a(const Dev& d, unsigned char* smem, uin
     double* pvec = reinterpret_cast<double*>(smem + kPsAux);
     unsigned char* ring = smem + kPsRing;
     const uint32_t bar0 = smem_u32(smem + kPsBar), tid = threadIdx.x;
-    ChunkDesc cur = d.chunks[cb];                       // clamped, not selected against a dummy: see k_linearize_stream
+    // descriptors beyond the block's range are never used: the loads are clamped rather than selected against a dummy (a select
+    // right behind the load makes every warp wait out the load at the top of each chunk)
+    ChunkDesc cur = d.chunks[cb];
     ChunkDesc nx1 = d.chunks[min(cb + 1, ce - 1)];
     ChunkDesc nx2 = d.chunks[min(cb + 2, ce - 1)];
     if (tid == 0) {
