@@ -510,7 +510,7 @@ __device__ __forceinline__ void ml_coarse_phase(const Dev& d, uint32_t gtid, uin
 
 // Sharded (peer exchange): the same in two steps with the exchange between them.  Step 1: the upper levels of this rank
 // and the corrected top-level residual of this rank's top nodes, pushed into every rank's copy of the global top residual.
-__device__ __forceinline__ void ml_coarse_push(const Dev& d, uint32_t gtid, uint32_t gsz) {
+__device__ __noinline__ void ml_coarse_push(const Dev& d, uint32_t gtid, uint32_t gsz) {
     const uint32_t Lv = d.mlLv, top = Lv - 1, nloc = d.mlLocal;
     for (uint32_t l = nloc; l < top; ++l) {
         const MlDev& lv = d.ml[l];

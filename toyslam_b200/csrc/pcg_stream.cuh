@@ -28,9 +28,30 @@ static_assert(sizeof(double) * 3 * kStageStride >= sizeof(double) * 3 * kCoarseM
 static_assert(2 * kPsVecLen * 8 <= 16 * kChunkEdges && kPsStageBytes % 32 == 0 && kPsH % 32 == 0, "layout");
 static_assert(2 * (kPsSmemBytes + 1024) <= 227 * 1024, "two blocks per SM");
 
+// A chunk descriptor packed into four words for the chunk loops: they carry the descriptors of four chunks at a time, and at the
+// 64-register cap (2 x 512 threads per SM) the 32 registers of four plain ChunkDesc left k_pcg_stream<true> -- which keeps a few
+// more values alive across the passes -- with a dozen spill reloads inside pass A's loop (pass A then took as long for half the
+// chunks at 2 GPUs as for all of them at 1: profiles/r2c_pcg_phase_spread_n2.txt).  w = n | np << 10 | ns << 18 | (unit & 1) << 28:
+// n, ns <= 512, np <= 128; consecutive chunks belong to the same or to consecutive units, so one bit of the unit tells them apart.
+struct PDesc {
+    uint32_t e0, p0, s0, w;
+    __device__ __forceinline__ uint32_t n() const { return w & 1023u; }
+    __device__ __forceinline__ uint32_t np() const { return (w >> 10) & 255u; }
+    __device__ __forceinline__ uint32_t ns() const { return (w >> 18) & 1023u; }
+    __device__ __forceinline__ uint32_t ub() const { return w >> 28; }
+    __device__ __forceinline__ uint32_t e1() const { return e0 + n(); }
+    __device__ __forceinline__ uint32_t p1() const { return p0 + np(); }
+    __device__ __forceinline__ uint32_t s1() const { return s0 + ns(); }
+};
+__device__ __forceinline__ PDesc pd_pack(const ChunkDesc& ch) {
+    return PDesc{ch.e0, ch.p0, ch.s0, (ch.e1 - ch.e0) | ((ch.p1 - ch.p0) << 10) | ((ch.s1 - ch.s0) << 18) | ((ch.block & 1u) << 28)};
+}
+__device__ __forceinline__ PDesc pd_load(const Dev& d, uint32_t c) { return pd_pack(d.chunks[c]); }
+
 // Producer (one thread): arm the stage's barrier and start the bulk copies of chunk `ch` for pass A (PASS 0) or B
 template <int PASS>
-__device__ __forceinline__ void ps_issue(const Dev& d, const ChunkDesc& ch, unsigned char* stage, uint32_t bar) {
+__device__ __forceinline__ void ps_issue(const Dev& d, const PDesc& pd, unsigned char* stage, uint32_t bar) {
+    const struct { uint32_t e0, e1, p0, p1, s0, s1; } ch = {pd.e0, pd.e1(), pd.p0, pd.p1(), pd.s0, pd.s1()};
     const uint32_t n = ch.e1 - ch.e0, ns = ch.s1 - ch.s0;
     const uint32_t e4 = ch.e0 & ~3u, e8 = ch.e0 & ~7u, s4 = ch.s0 & ~3u, p4 = ch.p0 & ~3u;
     const uint32_t bPk = n ? (((ch.e1 - e4) + 3u) & ~3u) * 4u : 0u;
@@ -51,6 +72,9 @@ __device__ __forceinline__ void ps_issue(const Dev& d, const ChunkDesc& ch, unsi
     if (bSl) bulk_g2s(s + kPsIx2, d.slot_lm + s4, bSl, bar);
 }
 
+template <int PASS>
+__device__ __forceinline__ void ps_issue(const Dev& d, const ChunkDesc& ch, unsigned char* stage, uint32_t bar) { ps_issue<PASS>(d, pd_pack(ch), stage, bar); }
+
 // p_i = z_i (+ coarse correction) + beta p_i for component t of the poses starting at p0
 __device__ __forceinline__ double ps_pnew(const Dev& d, uint32_t p0, uint32_t t, double beta, bool coarse) {
     const size_t i = 3ull * p0 + t;
@@ -68,9 +92,9 @@ __device__ __forceinline__ void ps_pass_a(const Dev& d, unsigned char* smem, uin
     const uint32_t bar0 = smem_u32(smem + kPsBar), tid = threadIdx.x;
     // descriptors beyond the block's range are never used: the loads are clamped rather than selected against a dummy (a select
     // right behind the load makes every warp wait out the load at the top of each chunk)
-    ChunkDesc cur = d.chunks[cb];
-    ChunkDesc nx1 = d.chunks[min(cb + 1, ce - 1)];
-    ChunkDesc nx2 = d.chunks[min(cb + 2, ce - 1)];
+    PDesc cur = pd_load(d, cb);
+    PDesc nx1 = pd_load(d, min(cb + 1, ce - 1));
+    PDesc nx2 = pd_load(d, min(cb + 2, ce - 1));
     if (tid == 0) {
         ps_issue<0>(d, cur, ring + (kbase % kLsStages) * kPsStageBytes, bar0 + 8 * (kbase % kLsStages));
         if (cb + 1 < ce) ps_issue<0>(d, nx1, ring + ((kbase + 1) % kLsStages) * kPsStageBytes, bar0 + 8 * ((kbase + 1) % kLsStages));
@@ -92,16 +116,16 @@ __device__ __forceinline__ void ps_pass_a(const Dev& d, unsigned char* smem, uin
     }
     __syncthreads();
     uint32_t vb = 0;
-    if (tid < 3 * (cur.p1 - cur.p0)) pvec[tid] = d.p[3ull * cur.p0 + tid];
+    if (tid < 3 * cur.np()) pvec[tid] = d.p[3ull * cur.p0 + tid];
     __syncthreads();
     for (uint32_t c = cb; c < ce; ++c) {
         const uint32_t k = kbase + (c - cb), sidx = k % kLsStages;
         unsigned char* st = ring + sidx * kPsStageBytes;
-        const uint32_t n = cur.e1 - cur.e0, ns = cur.s1 - cur.s0;
-        const bool newunit = c + 1 < ce && nx1.block != cur.block;
-        const ChunkDesc nx3 = d.chunks[min(c + 3, ce - 1)];
+        const uint32_t n = cur.n(), ns = cur.ns();
+        const bool newunit = c + 1 < ce && nx1.ub() != cur.ub();
+        const PDesc nx3 = pd_load(d, min(c + 3, ce - 1));
         // p of the next chunk's poses when it starts a new unit: a raw load, in flight during this chunk
-        const uint32_t tn = newunit ? 3 * (nx1.p1 - nx1.p0) : 0;
+        const uint32_t tn = newunit ? 3 * nx1.np() : 0;
         double pn = 0;
         if (tid < tn) pn = d.p[3ull * nx1.p0 + tid];
         mbar_wait(bar0 + 8 * sidx, (k / kLsStages) & 1u);
@@ -229,7 +253,7 @@ __device__ __forceinline__ bool ps_pose_phase(const Dev& d, double alpha, bool c
 
 // XP: compiled with the NVLink peer exchange (world > 1); the single-GPU instance carries none of that code
 template <bool XP>
-__global__ void __launch_bounds__(kPsThreads, 2) k_pcg_stream(const Dev d) {
+__global__ void __launch_bounds__(kPsThreads, 2) k_pcg_stream(const __grid_constant__ Dev d) {
     extern __shared__ __align__(32) unsigned char smem_raw[];
     double* red = reinterpret_cast<double*>(smem_raw + kPsRed);
     double* rc_s = reinterpret_cast<double*>(smem_raw + kPsRows);

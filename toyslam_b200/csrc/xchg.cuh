@@ -155,7 +155,11 @@ __device__ __forceinline__ void x_gsync(cg::grid_group& grid, const Dev& d, uint
     x_wait_block(d, point, v);
 }
 // sum of one scalar per rank in rank order (every block computes the same `local`; block 0 publishes it): no grid barrier
-__device__ __forceinline__ double x_scalar_sum(const Dev& d, uint32_t slot, uint32_t point, unsigned long long v, double local) {
+// The exchange steps the persistent PCG kernel runs once per iteration are NOT inlined: inlined, their peer pointers and layout
+// words were hoisted out of the iteration loop and stayed alive across the edge passes, and ptxas then put a dozen spill reloads
+// into pass A's chunk loop (64-register cap) -- pass A took as long for half the chunks at 2 GPUs as for all of them at 1
+// (profiles/r2c_pcg_phase_spread_n2.txt).  `d` is the kernel's __grid_constant__ parameter: the reference costs no copy.
+__device__ __noinline__ double x_scalar_sum(const Dev& d, uint32_t slot, uint32_t point, unsigned long long v, double local) {
     if (blockIdx.x == 0) {
         const uint32_t r = threadIdx.x;
         if (r < d.xc.world && r != d.xc.rank) x_ptr(d, r, d.xc.o_scal)[(size_t)slot * kXMaxWorld + d.xc.rank] = local;
@@ -172,7 +176,7 @@ __device__ __forceinline__ double x_scalar_sum(const Dev& d, uint32_t slot, uint
 // u = Hll^-1 w (it holds Hll^-1 of every landmark it touches).  Same bits on every rank.  (Owner-computes -- partials to
 // the owner, u back to the touchers -- needed two exchange steps per PCG iteration.)  Block 0 also sends the boundary
 // poses' p to the ranks that hold them as ghosts.
-__device__ __forceinline__ void x_w_push(const Dev& d) {
+__device__ __noinline__ void x_w_push(const Dev& d) {
     double2* mine = reinterpret_cast<double2*>(x_ptr(d, d.xc.rank, d.xc.o_w)) + (size_t)d.xc.rank * d.L;
     for (uint32_t l = 32 * (blockIdx.x + gridDim.x * (threadIdx.x >> 5)) + (threadIdx.x & 31); l < d.L; l += 32 * gridDim.x * (blockDim.x >> 5)) {      // warp-sized groups round-robin over blocks: see k_pcg_stream
         if (d.lm_part_ptr[l] == d.lm_part_ptr[l + 1]) continue;
@@ -192,7 +196,7 @@ __device__ __forceinline__ void x_w_push(const Dev& d) {
         }
 }
 // after the exchange: u of every touched landmark into d.w_sum (pass B gathers it), ghost p into the tail of d.p
-__device__ __forceinline__ void x_u_local(const Dev& d) {
+__device__ __noinline__ void x_u_local(const Dev& d) {
     for (uint32_t i = threadIdx.x; i < 3 * d.nG; i += blockDim.x) d.p[3ull * d.nP + i] = x_ptr(d, d.xc.rank, d.xc.o_ghost)[i];   // same values from every block
     const double2* rx = reinterpret_cast<const double2*>(x_ptr(d, d.xc.rank, d.xc.o_w));
     for (uint32_t l = 32 * (blockIdx.x + gridDim.x * (threadIdx.x >> 5)) + (threadIdx.x & 31); l < d.L; l += 32 * gridDim.x * (blockDim.x >> 5)) {
