@@ -51,9 +51,30 @@ __device__ __forceinline__ void bulk_g2s(uint32_t dst, const void* src, uint32_t
                  ::"r"(dst), "l"(src), "r"(bytes), "r"(bar) : "memory");
 }
 
+// A chunk descriptor packed into four words for the chunk loops: they carry the descriptors of four chunks at a time, and at the
+// 64-register cap (2 x 512 threads per SM) the 32 registers of four plain ChunkDesc left k_pcg_stream<true> -- which keeps a few
+// more values alive across the passes -- with a dozen spill reloads inside pass A's loop (pass A then took as long for half the
+// chunks at 2 GPUs as for all of them at 1: profiles/r2c_pcg_phase_spread_n2.txt).  w = n | np << 10 | ns << 18 | (unit & 1) << 28:
+// n, ns <= 512, np <= 128; consecutive chunks belong to the same or to consecutive units, so one bit of the unit tells them apart.
+struct PDesc {
+    uint32_t e0, p0, s0, w;
+    __device__ __forceinline__ uint32_t n() const { return w & 1023u; }
+    __device__ __forceinline__ uint32_t np() const { return (w >> 10) & 255u; }
+    __device__ __forceinline__ uint32_t ns() const { return (w >> 18) & 1023u; }
+    __device__ __forceinline__ uint32_t ub() const { return w >> 28; }
+    __device__ __forceinline__ uint32_t e1() const { return e0 + n(); }
+    __device__ __forceinline__ uint32_t p1() const { return p0 + np(); }
+    __device__ __forceinline__ uint32_t s1() const { return s0 + ns(); }
+};
+__device__ __forceinline__ PDesc pd_pack(const ChunkDesc& ch) {
+    return PDesc{ch.e0, ch.p0, ch.s0, (ch.e1 - ch.e0) | ((ch.p1 - ch.p0) << 10) | ((ch.s1 - ch.s0) << 18) | ((ch.block & 1u) << 28)};
+}
+__device__ __forceinline__ PDesc pd_load(const Dev& d, uint32_t c) { return pd_pack(d.chunks[c]); }
+
 // Producer (one thread): arm the stage's barrier and start the bulk copies of chunk `ch`.
 // Sources are aligned down / sizes rounded up to 16 B (every device array carries 64 B of slack).
-__device__ __forceinline__ void ls_issue(const Dev& d, const ChunkDesc& ch, unsigned char* stage, uint32_t bar, bool with_pose = true) {
+__device__ __forceinline__ void ls_issue(const Dev& d, const PDesc& pd, unsigned char* stage, uint32_t bar, bool with_pose = true) {
+    const struct { uint32_t e0, e1, p0, p1, s0, s1; } ch = {pd.e0, pd.e1(), pd.p0, pd.p1(), pd.s0, pd.s1()};
     const uint32_t n = ch.e1 - ch.e0, ns = ch.s1 - ch.s0, np = ch.p1 - ch.p0;
     const uint32_t e4 = ch.e0 & ~3u, e8 = ch.e0 & ~7u, s4 = ch.s0 & ~3u, p4 = ch.p0 & ~3u;
     const uint32_t bPk = n ? (((ch.e1 - e4) + 3u) & ~3u) * 4u : 0u;
@@ -127,10 +148,10 @@ __global__ void __launch_bounds__(kLsThreads, 2) k_linearize_stream(const Dev d)
     if (cb >= ce) { if (tid == 0) d.part[blockIdx.x] = 0; return; }
 
     // chunk descriptors, read by every thread (uniform loads) up to three chunks ahead
-    const ChunkDesc zero = {0, 0, 0, 0, 0, 0, 0xFFFFFFFFu, 0};
-    ChunkDesc cur = d.chunks[cb];
-    ChunkDesc nx1 = cb + 1 < ce ? d.chunks[cb + 1] : zero;
-    ChunkDesc nx2 = cb + 2 < ce ? d.chunks[cb + 2] : zero;
+    // (descriptors beyond the block's range are never used: loads clamped, uses guarded by the chunk index)
+    PDesc cur = pd_load(d, cb);
+    PDesc nx1 = pd_load(d, min(cb + 1, ce - 1));
+    PDesc nx2 = pd_load(d, min(cb + 2, ce - 1));
     if (tid == 0) {
         ls_issue(d, cur, ring, bar0);
         if (cb + 1 < ce) ls_issue(d, nx1, ring + kLsStageBytes, bar0 + 8);
@@ -138,7 +159,7 @@ __global__ void __launch_bounds__(kLsThreads, 2) k_linearize_stream(const Dev d)
     }
     // per-edge values of the first chunk (afterwards prefetched one chunk ahead)
     double2 z0 = {}, w0 = {};
-    if (tid < cur.e1 - cur.e0) { z0 = d.le_z[cur.e0 + tid]; w0 = d.le_w[cur.e0 + tid]; }
+    if (tid < cur.n()) { z0 = d.le_z[cur.e0 + tid]; w0 = d.le_w[cur.e0 + tid]; }
 
     double heavy = 0;            // a pose with > kChunkEdges edges spans several chunks: its nine sums live in threads 0..8
     double rho_sum = 0;
@@ -146,9 +167,10 @@ __global__ void __launch_bounds__(kLsThreads, 2) k_linearize_stream(const Dev d)
     for (uint32_t c = cb; c < ce; ++c) {
         const uint32_t k = c - cb, sidx = k % kLsStages;
         unsigned char* st = ring + sidx * kLsStageBytes;
-        const uint32_t n = cur.e1 - cur.e0, ns = cur.s1 - cur.s0, np = cur.p1 - cur.p0;
-        const bool last = nx1.block != cur.block;                 // `zero` has block 0xFFFFFFFF: the block's final chunk ends its unit
-        const ChunkDesc nx3 = c + 3 < ce ? d.chunks[c + 3] : zero;  // consumed at the end of this iteration
+        const uint32_t n = cur.n(), ns = cur.ns(), np = cur.np(), e1 = cur.e0 + n;
+        const bool has1 = c + 1 < ce;
+        const bool last = !has1 || nx1.ub() != cur.ub();          // the block's final chunk ends its unit
+        const PDesc nx3 = pd_load(d, min(c + 3, ce - 1));         // consumed at the end of this iteration
         mbar_wait(bar0 + 8 * sidx, (k / kLsStages) & 1u);
         const uint32_t* pk = reinterpret_cast<const uint32_t*>(st + kLsPk) + (cur.e0 & 3u);
         const uint16_t* sedge = reinterpret_cast<const uint16_t*>(st + kLsSe) + (cur.e0 & 7u);
@@ -163,8 +185,8 @@ __global__ void __launch_bounds__(kLsThreads, 2) k_linearize_stream(const Dev d)
         }
         // ---- prefetch for the next chunk: per-edge values and slot landmarks into registers -------------------
         double2 nz0 = {}, nw0 = {}, lmv0 = {};
-        const uint32_t ns_next = nx1.s1 - nx1.s0;
-        if (tid < nx1.e1 - nx1.e0) { nz0 = d.le_z[nx1.e0 + tid]; nw0 = d.le_w[nx1.e0 + tid]; }
+        const uint32_t ns_next = has1 ? nx1.ns() : 0u;
+        if (has1 && tid < nx1.n()) { nz0 = d.le_z[nx1.e0 + tid]; nw0 = d.le_w[nx1.e0 + tid]; }
         if (c + 1 < ce) {
             const uint32_t s2 = (k + 1) % kLsStages;
             mbar_wait(bar0 + 8 * s2, ((k + 1) / kLsStages) & 1u);          // issued two iterations ago
@@ -189,7 +211,7 @@ __global__ void __launch_bounds__(kLsThreads, 2) k_linearize_stream(const Dev d)
             // the poses' edge counts (19 at C4: 3 mod 16 double-banks, conflict-free) instead of nine rows of three or four poses
             // whose offsets collide (2.6x the conflict-free wavefronts, profiles/r1_lin_stream2_c4_ncu_summary.csv)
             const uint32_t row = item / np, pl = item - row * np;
-            const uint32_t b = max(pptr[pl], cur.e0) - cur.e0, e = min(pptr[pl + 1], cur.e1) - cur.e0;
+            const uint32_t b = max(pptr[pl], cur.e0) - cur.e0, e = min(pptr[pl + 1], e1) - cur.e0;
             double sum = seg_sum_lean(rows + row * kStageStride, b, e);
             if (multi) { heavy += sum; sum = heavy; }             // np == 1: item == tid < 9; same order as acc += seg_sum
             if (last) {

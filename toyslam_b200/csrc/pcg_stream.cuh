@@ -28,26 +28,6 @@ static_assert(sizeof(double) * 3 * kStageStride >= sizeof(double) * 3 * kCoarseM
 static_assert(2 * kPsVecLen * 8 <= 16 * kChunkEdges && kPsStageBytes % 32 == 0 && kPsH % 32 == 0, "layout");
 static_assert(2 * (kPsSmemBytes + 1024) <= 227 * 1024, "two blocks per SM");
 
-// A chunk descriptor packed into four words for the chunk loops: they carry the descriptors of four chunks at a time, and at the
-// 64-register cap (2 x 512 threads per SM) the 32 registers of four plain ChunkDesc left k_pcg_stream<true> -- which keeps a few
-// more values alive across the passes -- with a dozen spill reloads inside pass A's loop (pass A then took as long for half the
-// chunks at 2 GPUs as for all of them at 1: profiles/r2c_pcg_phase_spread_n2.txt).  w = n | np << 10 | ns << 18 | (unit & 1) << 28:
-// n, ns <= 512, np <= 128; consecutive chunks belong to the same or to consecutive units, so one bit of the unit tells them apart.
-struct PDesc {
-    uint32_t e0, p0, s0, w;
-    __device__ __forceinline__ uint32_t n() const { return w & 1023u; }
-    __device__ __forceinline__ uint32_t np() const { return (w >> 10) & 255u; }
-    __device__ __forceinline__ uint32_t ns() const { return (w >> 18) & 1023u; }
-    __device__ __forceinline__ uint32_t ub() const { return w >> 28; }
-    __device__ __forceinline__ uint32_t e1() const { return e0 + n(); }
-    __device__ __forceinline__ uint32_t p1() const { return p0 + np(); }
-    __device__ __forceinline__ uint32_t s1() const { return s0 + ns(); }
-};
-__device__ __forceinline__ PDesc pd_pack(const ChunkDesc& ch) {
-    return PDesc{ch.e0, ch.p0, ch.s0, (ch.e1 - ch.e0) | ((ch.p1 - ch.p0) << 10) | ((ch.s1 - ch.s0) << 18) | ((ch.block & 1u) << 28)};
-}
-__device__ __forceinline__ PDesc pd_load(const Dev& d, uint32_t c) { return pd_pack(d.chunks[c]); }
-
 // Producer (one thread): arm the stage's barrier and start the bulk copies of chunk `ch` for pass A (PASS 0) or B
 template <int PASS>
 __device__ __forceinline__ void ps_issue(const Dev& d, const PDesc& pd, unsigned char* stage, uint32_t bar) {
