@@ -280,6 +280,22 @@ int upload_graph(tsb_ctx* c) {
           for (uint32_t K = 0; K < top_total; ++K) for (uint32_t e = gptr[K]; e < gptr[K + 1]; ++e) { const uint32_t at = c2[glm[e]]++; te[at] = e; tn[at] = K; } }
         TRY(upload(c, d.tl_ptr, tp)); TRY(upload(c, d.tl_edge, te)); TRY(upload(c, d.tl_node, tn));
         if (xp) { TRY(upload(c, d.gt_node_ptr, gptr)); TRY(upload(c, d.gt_edge_lm, glm)); TRY(dalloc(c, d.gtC, 6ull * d.gt_nnz)); }
+        d.xc.nCut = 0; d.xc.cut = nullptr; d.xc.cutrec = nullptr;
+        if (xp) {     // owned ODOM edges whose far end is the first pose of a higher rank: they join the top operator (mlevel.cuh)
+            std::vector<uint32_t> cut;
+            std::vector<uint32_t> toff(c->world + 1, 0);
+            for (int r = 0; r < c->world; ++r) toff[r + 1] = toff[r] + s.top_nodes[r];
+            for (uint32_t k = 0; k < s.n_od_owned && cut.size() < 3 * kXMaxCut; ++k) {
+                if (s.od_a[k] >= d.nP || s.od_b[k] < d.nP) continue;
+                const uint32_t gp = s.ghost_pose[s.od_b[k] - d.nP];
+                const uint32_t ro = (uint32_t)(std::upper_bound(s.cuts.begin(), s.cuts.end(), gp) - s.cuts.begin()) - 1;
+                if ((int)ro > c->rank && gp == s.cuts[ro]) { cut.push_back(k); cut.push_back(s.od_a[k]); cut.push_back(toff[ro]); }
+            }
+            d.xc.nCut = (uint32_t)(cut.size() / 3);
+            cut.resize(3 * kXMaxCut, 0);
+            TRY(upload(c, d.xc.cut, cut));
+            TRY(dalloc(c, d.xc.cutrec, (size_t)c->world * kXMaxCut * kXCutRec));
+        }
         else { d.gt_node_ptr = d.ml[d.mlLv - 1].node_ptr; d.gt_edge_lm = d.ml[d.mlLv - 1].edge_lm; d.gtC = d.ml[d.mlLv - 1].C; }
         TRY(dalloc(c, d.r2, 3ull * d.nP));
     }
@@ -475,6 +491,13 @@ int run_solve(tsb_ctx* c, bool refresh_coarse = true, bool smoother = true) {
                     if (cnt && ncclBroadcast(d.Ac + row, d.Ac + row, cnt, ncclDouble, r, c->comm, c->stream) != ncclSuccess) { c->err = "ncclBroadcast failed"; return TSB_ENCCL; }
                     row += cnt;
                 }
+                // ODOM edges across the cuts: every rank's records to every rank, then added to the replicated operator
+                launch_ml_cut_record(d, c->stream);
+                for (int r = 0; r < c->world; ++r) {
+                    double* seg = d.xc.cutrec + (size_t)r * kXMaxCut * kXCutRec;
+                    if (ncclBroadcast(seg, seg, (size_t)kXMaxCut * kXCutRec, ncclDouble, r, c->comm, c->stream) != ncclSuccess) { c->err = "ncclBroadcast failed"; return TSB_ENCCL; }
+                }
+                launch_ml_cut_apply(d, c->stream);
             }
         } else launch_coarse_assemble(d, c->stream);
         if (timing) cudaEventRecord(te[1], c->stream);

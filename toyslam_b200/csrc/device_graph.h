@@ -35,9 +35,16 @@ struct XDev {
     const uint32_t* exp;                   // 3 per export entry: local pose, destination rank, ghost slot there
     const uint8_t* lm_mask;                // per landmark: bit r set = rank r has LM edges to it
     uint32_t top_off, top_total;           // this rank's first node / all nodes of the global top level
+    // ODOM edges that cross a rank cut and end on the FIRST pose of a higher rank (node 0 of that rank's top level, weight 1):
+    // their off-diagonal blocks join the replicated top operator (k_ml_cut_record / k_ml_cut_apply).  3 words per edge:
+    // local ODOM edge, local pose of the near end, global top node of the far end; records of kXCutRec doubles per edge.
+    uint32_t nCut; const uint32_t* cut; double* cutrec;
 };
 
 // one level of the multilevel hierarchy (host_graph.h MlLevel) on the device
+constexpr uint32_t kXMaxCut = 8;        // cut edges per rank that enter the top operator
+constexpr uint32_t kXCutRec = 24;       // doubles per record: valid, B, nA, A0, A1, pad, X0[9], X1[9]
+
 struct MlDev {
     uint32_t n, ratio, spacing, nnz;
     uint32_t slots, cdot_off;                 // upper levels: partial sums per window; first entry of the level in Dev::cdot
@@ -145,6 +152,8 @@ void launch_schur_prep(const Dev& d, cudaStream_t s);           // K3: diag(S)^-
 void launch_coarse_assemble(const Dev& d, cudaStream_t s);      // zoff, C, Ac = Z^T S Z (dense, deterministic)
 void launch_ml_levels(const Dev& d, cudaStream_t s);            // multilevel: C_l and blockdiag(S_l)^-1 level by level
 void launch_ml_top(const Dev& d, cudaStream_t s);               // this rank's block rows of the dense top operator into Ac
+void launch_ml_cut_record(const Dev& d, cudaStream_t s);        // sharded: records of this rank's ODOM edges across a cut (xc.cutrec)
+void launch_ml_cut_apply(const Dev& d, cudaStream_t s);         // sharded: all ranks' records added to the replicated top operator
 bool launch_pcg_stream(const Dev& d, cudaStream_t s);           // streamed persistent PCG (no back-substitution)
 bool launch_coarse_invert(const Dev& d, cudaStream_t s);        // Ai = Ac^-1 + F_COARSE, one cooperative launch (blocked Gauss-Jordan)
 void launch_pcg_coarse(const Dev& d, int init, cudaStream_t s);           // yc = Ac^-1 Z^T r, cdot (phased path)

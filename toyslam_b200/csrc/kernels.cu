@@ -1180,6 +1180,8 @@ void launch_ml_levels(const Dev& d, cudaStream_t s) {
         if (l + 1 < d.mlLv) { k_ml_D<<<nb, 256, 0, s>>>(d, (int)l); ++g_launches; }
     }
 }
+void launch_ml_cut_record(const Dev& d, cudaStream_t s) { k_ml_cut_record<<<1, 32, 0, s>>>(d); ++g_launches; }
+void launch_ml_cut_apply(const Dev& d, cudaStream_t s) { k_ml_cut_apply<<<1, 32, 0, s>>>(d); ++g_launches; }
 void launch_ml_top(const Dev& d, cudaStream_t s) {
     if (!d.mlLv) return;
     const size_t smem = sizeof(double) * 3 * d.nc;

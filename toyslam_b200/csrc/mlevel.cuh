@@ -327,6 +327,52 @@ __global__ void __launch_bounds__(kMlTopThreads) k_ml_top(const Dev d, const uin
     if (timing) d.dbg[10] = clock64() - tk0;
 }
 
+// ---- setup, sharded: ODOM edges across a rank cut in the replicated top operator -------------------------------------
+// An ODOM edge (i on this rank, j = first pose of a higher rank) couples this rank's top nodes A that interpolate pose i with
+// node B = node 0 of that rank (it sits AT pose j, weight 1, zero lever arm): (A, B) += w_A(i) R(z_iA)^T diag(hoo) and its
+// transpose.  Without it the top operator is block-diagonal over the ranks on the odometry side and the PCG of a chain needs
+// 1.3x (2 ranks) to 1.8x (4 ranks) the iterations.  The owner of the edge writes one record per edge; the records of all ranks
+// are broadcast and every rank adds them to its copy of the operator in the same order (bit-identical copies).
+__global__ void k_ml_cut_record(const Dev d) {
+    const uint32_t q = threadIdx.x;
+    if (q >= kXMaxCut) return;
+    double* rec = d.xc.cutrec + (size_t)(d.xc.rank * kXMaxCut + q) * kXCutRec;
+    if (q >= d.xc.nCut) { rec[0] = 0; return; }
+    const MlDev& lv = d.ml[d.mlLv - 1];
+    const uint32_t k = d.xc.cut[3 * q], i = d.xc.cut[3 * q + 1], B = d.xc.cut[3 * q + 2], s = lv.spacing, n = lv.n;
+    const double* h = d.hoo + 3ull * k;
+    const double4 pi = d.pose[i];
+    const uint32_t qi = i / s, rem = i - qi * s;
+    const bool two = !(qi + 1 >= n || rem == 0);
+    rec[0] = 1; rec[1] = (double)B; rec[2] = two ? 2 : 1; rec[3] = (double)(d.xc.top_off + qi); rec[4] = (double)(d.xc.top_off + qi + 1); rec[5] = 0;
+    for (int side = 0; side < (two ? 2 : 1); ++side) {
+        const double w = two ? (side == 0 ? 1.0 - (double)rem / (double)s : (double)rem / (double)s) : 1.0;
+        const double4 pc = d.pose[(size_t)(qi + side) * s];
+        const double zx = -(pi.y - pc.y), zy = pi.x - pc.x;
+        double* X = rec + 6 + 9 * side;
+        X[0] = w * h[0]; X[1] = 0; X[2] = 0; X[3] = 0; X[4] = w * h[1]; X[5] = 0; X[6] = w * zx * h[0]; X[7] = w * zy * h[1]; X[8] = w * h[2];
+    }
+}
+__global__ void k_ml_cut_apply(const Dev d) {
+    if (threadIdx.x || blockIdx.x) return;
+    const uint32_t nc = d.nc;
+    for (uint32_t r = 0; r < d.xc.world; ++r)
+        for (uint32_t q = 0; q < kXMaxCut; ++q) {
+            const double* rec = d.xc.cutrec + (size_t)(r * kXMaxCut + q) * kXCutRec;
+            if (rec[0] == 0) continue;
+            const uint32_t B = (uint32_t)rec[1], nA = (uint32_t)rec[2];
+            for (uint32_t a = 0; a < nA; ++a) {
+                const uint32_t A = (uint32_t)rec[3 + a];
+                const double* X = rec + 6 + 9 * a;
+                for (uint32_t rr = 0; rr < 3; ++rr)
+                    for (uint32_t cc = 0; cc < 3; ++cc) {
+                        d.Ac[(size_t)(3 * A + rr) * nc + 3 * B + cc] += X[3 * rr + cc];
+                        d.Ac[(size_t)(3 * B + cc) * nc + 3 * A + rr] += X[3 * rr + cc];
+                    }
+            }
+        }
+}
+
 // ---- PCG phases -------------------------------------------------------------------------------------------------------
 // correction of pose i (position x, y) from all levels: sum over levels of the hat-weighted node corrections g
 __device__ __forceinline__ void ml_prolong(const Dev& d, uint32_t i, double px, double py, double& o0, double& o1, double& o2) {
