@@ -514,6 +514,12 @@ def test_two_ranks_match_one_rank(gpu):
                         "127.0.0.1", "--master-port", "29741", os.path.join(ROOT, "tools", "mgpu_check.py")],
                        capture_output=True, text=True, timeout=600)
     assert r.returncode == 0 and "MGPU OK" in r.stdout, r.stdout[-3000:] + r.stderr[-3000:]
+    # the ODOM-dominated chain: the two ranks' hierarchies are joined by the cut edge in the replicated top operator, so the sharded
+    # solve needs (nearly) the iterations of one GPU -- 1.3x without it.  Ill-conditioned: state to 1e-7 (two solves at 1e-13)
+    r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2", "--master-addr",
+                        "127.0.0.1", "--master-port", "29742", os.path.join(ROOT, "tools", "mgpu_check.py"), "--workload", "c5", "--scale", "0.02",
+                        "--iters", "3", "--state-tol", "1e-7", "--oracle", "0", "--max-iter-ratio", "1.1"], capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0 and "MGPU OK" in r.stdout, r.stdout[-3000:] + r.stderr[-3000:]
 
 
 def test_graph_optimizer_server_end_to_end(gpu):

@@ -12,6 +12,7 @@ from toyslam_b200.capi import GraphOptimizerGpu
 ap = argparse.ArgumentParser()
 ap.add_argument("--workload", default="c2"); ap.add_argument("--scale", type=float, default=0.2)
 ap.add_argument("--iters", type=int, default=6); ap.add_argument("--oracle", type=int, default=1)
+ap.add_argument("--max-iter-ratio", type=float, default=0.0, help="> 0: the sharded run may need at most this many times the PCG iterations of the 1-rank run (same preconditioner: the cut ODOM edges are in the top operator)")
 ap.add_argument("--state-tol", type=float, default=1e-8, help="N-vs-1 state tolerance (two PCG solves at 1e-13 differ by cond(S) x tol: the ill-conditioned chain c5 needs 1e-7)")
 a = ap.parse_args()
 rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
@@ -38,6 +39,7 @@ if rank == 0:
           f"pcg {rep.pcg_iters_total} vs {rep1.pcg_iters_total}; N-vs-1 chi2 rel {e_chi:.2e} state rel {e_st:.2e}; "
           f"ms {rep.ms_total:.1f} vs {rep1.ms_total:.1f}")
     ok = e_chi < 1e-8 and e_st < a.state_tol
+    if a.max_iter_ratio > 0: ok = ok and rep.pcg_iters_total <= a.max_iter_ratio * rep1.pcg_iters_total
     if a.oracle:
         from oracle.oracle import OracleGraph
         o = OracleGraph(payload); traj, _, _ = o.optimize_sparse(a.iters, False, 1e-13, 20000, 0)
