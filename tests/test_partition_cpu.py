@@ -132,3 +132,22 @@ def test_bulk_copies_of_the_streamed_kernels_stay_inside_their_arrays():
             assert off % 16 == 0 and nbytes % 16 == 0, (name, off, nbytes)
             assert 0 <= off < size + 16 and off + nbytes <= size + 64, (name, off, nbytes, size)
             assert nbytes <= slots[name], (name, nbytes)
+
+def test_chunk_descriptors_fit_the_packed_form_of_the_chunk_loops():
+    """The streamed kernels carry chunk descriptors packed into four words (PDesc, linearize_stream.cuh): n and ns in 10 bits, np
+    in 8, and ONE bit of the unit index to tell consecutive chunks of different units apart.  That needs n, ns <= 512, np <= 128,
+    and consecutive chunks in the same or in consecutive units -- checked here on graphs with ordinary, sparse and heavy poses."""
+    from toyslam_b200 import synth, capi
+    cases = [synth.make_graph(1301, 300, 19, "manhattan", seed=3), synth.make_graph(4000, 40, 1, "chain", seed=4),
+             synth.make_graph(60, 700, 650, "manhattan", seed=5)]            # the last one: poses with more LM edges than a chunk holds
+    for g in cases:
+        for world, rank in ((1, 0), (3, 1)):
+            c, s = capi.host_structure(synth.to_payload(g), rank, world)
+            d = s["chunk_desc"].astype(np.int64)
+            if not len(d):
+                continue
+            n, npz, ns, unit = d[:, 1] - d[:, 0], d[:, 3] - d[:, 2], d[:, 5] - d[:, 4], d[:, 6]
+            assert n.min() >= 0 and n.max() <= 512 and npz.min() >= 1 and npz.max() <= 128 and ns.max() <= 512 and (ns <= np.maximum(n, 0)).all()
+            step = np.diff(unit)
+            assert ((step == 0) | (step == 1)).all() and unit[0] == 0
+            assert (d[1:, 0] == d[:-1, 1]).all() and (d[1:, 4] == d[:-1, 5]).all()      # edges and slots of consecutive chunks are contiguous
