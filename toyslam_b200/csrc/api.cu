@@ -545,6 +545,8 @@ int run_solve(tsb_ctx* c, bool refresh_coarse = true, bool smoother = true) {
                 std::vector<long long> all(9 * 1024);
                 CU(cudaMemcpy(all.data(), d.dbg + 16, 8 * all.size(), cudaMemcpyDeviceToHost));
                 uint32_t nb = 0; while (nb < 1024 && all[9 * nb + 8]) ++nb;
+                if (!nb) std::fprintf(stderr, "[tsb]   (per-block counters are kept by the sharded instance of the kernel only)\n");
+                if (nb)
                 for (int q : {0, 2, 4, 6}) {
                     std::vector<std::pair<long long, uint32_t>> v;
                     for (uint32_t b = 0; b < nb; ++b) v.emplace_back(all[9 * b + q] / its, b);

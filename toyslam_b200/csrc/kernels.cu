@@ -983,6 +983,7 @@ __global__ void __launch_bounds__(kThreads, 3) k_pcg_persistent(const Dev d) {
 #include "xchg.cuh"
 #include "mlevel.cuh"
 #include "pcg_stream.cuh"
+#include "pcg_stream_single.cuh"
 
 // delta_l = Hll^-1 (b_l - Hpl^T delta_p); w_sum holds Hpl^T delta_p
 __global__ void k_backsub(const Dev d) {
@@ -1088,9 +1089,9 @@ static DevInfo& set_attrs() {
     cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_pcg_persistent, kThreads, LayPcg::bytes);
     di.coop_blocks = coop ? sms * per_sm : 0;
     if (opt_in((const void*)k_linearize_stream, kLsSmemBytes)) { per_sm = 0; cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_linearize_stream, kLsThreads, kLsSmemBytes); di.stream_blocks = sms * per_sm; }
-    if (opt_in((const void*)k_pcg_stream<false>, kPsSmemBytes) && opt_in((const void*)k_pcg_stream<true>, kPsSmemBytes)) {
+    if (opt_in((const void*)k_pcg_stream1<false>, kPsSmemBytes) && opt_in((const void*)k_pcg_stream<true>, kPsSmemBytes)) {
         int a = 0, b = 0;
-        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&a, k_pcg_stream<false>, kPsThreads, kPsSmemBytes);
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&a, k_pcg_stream1<false>, kPsThreads, kPsSmemBytes);
         cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b, k_pcg_stream<true>, kPsThreads, kPsSmemBytes);
         di.pcg_stream_blocks = coop ? sms * (a < b ? a : b) : 0;
     }
@@ -1158,7 +1159,8 @@ bool launch_pcg_stream(const Dev& d, cudaStream_t s) {
     Dev dd = d; void* args[] = {&dd};
     cudaMemsetAsync(dd.gbar, 0, sizeof(uint32_t), s);
     const uint32_t grid = d.nBlocks < (uint32_t)blocks ? d.nBlocks : (uint32_t)blocks;
-    const void* fn = d.xc.world > 1 ? (const void*)k_pcg_stream<true> : (const void*)k_pcg_stream<false>;
+    // one source per instance: see pcg_stream_single.cuh
+    const void* fn = d.xc.world > 1 ? (const void*)k_pcg_stream<true> : (const void*)k_pcg_stream1<false>;
     if (cudaLaunchCooperativeKernel(fn, dim3(grid), dim3(kPsThreads), args, kPsSmemBytes, s) != cudaSuccess) { cudaGetLastError(); return false; }
     ++g_launches;
     return true;
