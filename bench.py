@@ -330,7 +330,7 @@ def main():
     e2e_s = float(te.item())
 
     path = {0: "k_pcg_persistent (whole PCG solve in one cooperative launch)", 1: "k_pcg_resident (whole solve in one cooperative launch, Hpl resident in shared memory)",
-            2: "k_pcg_* phases + NCCL all-reduces", 3: "k_pcg_stream (whole PCG solve in one persistent cooperative launch: edge passes through a 3-stage TMA ring, "
+            2: "k_pcg_* phases + NCCL all-reduces", 3: ("k_pcg_stream<true>" if world > 1 else "k_pcg_stream1<false>") + " (whole PCG solve in one persistent cooperative launch: edge passes through a 3-stage TMA ring, "
             "multilevel preconditioner" + (", landmark sums / top-level residual / dot products exchanged over NVLink peer memory" if world > 1 else "") + ")"}[counts.pcg_path]
     line = {
         "metric": "gn_iterations_per_s", "value": value, "unit": "iter/s", "n_gpus": world, "steps": args.steps,
