@@ -151,3 +151,46 @@ def test_chunk_descriptors_fit_the_packed_form_of_the_chunk_loops():
             step = np.diff(unit)
             assert ((step == 0) | (step == 1)).all() and unit[0] == 0
             assert (d[1:, 0] == d[:-1, 1]).all() and (d[1:, 4] == d[:-1, 5]).all()      # edges and slots of consecutive chunks are contiguous
+
+def test_parse_of_interleaved_record_layouts_matches_the_standard_layout():
+    """parse_wire recognises runs of records in the reference client's layout (ODOM 76 B, LM 44 B) at a fixed stride and checks
+    them in parallel; everything else goes record by record.  A payload that interleaves blocks of LM records with ODOM records
+    in three layouts (3x3 matrix, (x, y, theta) with rows = 0, a short information diagonal) must give the same LM-side structure
+    as the plain payload of the same graph (same LM edges in the same relative order), and a payload cut in the middle of a run
+    must be rejected with the scan's message."""
+    import struct
+    from toyslam_b200 import synth, wire, capi
+    g = synth.make_config("c3", scale=0.03, seed=7)
+    plain = wire.encode_request(g["pose_id"], g["pose_xyt"], g["lm_id"], g["lm_xy"], g["od_ij"], g["od_Z"], g["od_w"], g["lm_ij"], g["lm_meas"],
+                                g["lm_w"], g["fixed_ids"])
+    P, L = len(g["pose_id"]), len(g["lm_id"])
+    head = [struct.pack("<I", P + L)]
+    head += [struct.pack("<IIfff", int(g["pose_id"][i]), 0, *map(float, g["pose_xyt"][i])) for i in range(P)]
+    head += [struct.pack("<IIff", int(g["lm_id"][i]), 1, *map(float, g["lm_xy"][i])) for i in range(L)]
+    od = []
+    for k, (a, b) in enumerate(g["od_ij"].tolist()):
+        Z, w = np.asarray(g["od_Z"][k], "<f4").tobytes(), [float(v) for v in g["od_w"][k]]
+        if k % 7 == 3:
+            od.append(struct.pack("<IIIII", 0, a, b, 0, 3) + struct.pack("<fff", 0.5, 0.1, 0.01) + struct.pack("<II", 0, 3) + struct.pack("<fff", *w))
+        elif k % 11 == 5:
+            od.append(struct.pack("<IIIII", 0, a, b, 3, 3) + Z + struct.pack("<II", 0, 1) + struct.pack("<f", w[0]))
+        else:
+            od.append(struct.pack("<IIIII", 0, a, b, 3, 3) + Z + struct.pack("<II", 0, 3) + struct.pack("<fff", *w))
+    lm = [struct.pack("<IIIII", 1, a, b, 0, 2) + struct.pack("<ff", *map(float, g["lm_meas"][k])) + struct.pack("<II", 0, 2)
+          + struct.pack("<ff", *map(float, g["lm_w"][k])) for k, (a, b) in enumerate(g["lm_ij"].tolist())]
+    recs, i, j = [], 0, 0
+    while i < len(lm) or j < len(od):
+        recs += lm[i:i + 3000]; i += 3000
+        recs += od[j:j + 500]; j += 500
+    fx = np.asarray(g["fixed_ids"], "<u4")
+    mixed = b"".join(head + [struct.pack("<I", len(recs))] + recs + [struct.pack("<I", len(fx)), fx.tobytes()])
+    c0, s0 = capi.host_structure(plain, 0, 1)
+    c1, s1 = capi.host_structure(mixed, 0, 1)
+    assert (c0.n_pose, c0.n_lm, c0.n_odom, c0.n_lmedge, c0.n_chunks, c0.n_slots) == (c1.n_pose, c1.n_lm, c1.n_odom, c1.n_lmedge, c1.n_chunks, c1.n_slots)
+    # lm_perm holds request-order LM indices: the same in both payloads because LM edges keep their relative order
+    for k in ("lm_perm", "pose_ptr", "chunk_desc", "slot_lm", "lm_packed"):
+        assert np.array_equal(s0[k], s1[k]), k
+    for cut in (len(mixed) - 30001, len(mixed) - 4 * len(fx) - 4 - 13):      # inside a run near the end / inside the last record
+        with pytest.raises(capi.TsbError) as ei:
+            capi.host_plan(mixed[:cut], 0, 1)
+        assert ei.value.code == 2 and "truncated payload" in str(ei.value), str(ei.value)

@@ -38,5 +38,10 @@ int main(int argc, char** argv) {
     mv(st.fixed_pose_count); mv(st.fixed_lm_count); mv(st.edge_pose); mv(st.ghost_pose); mv(st.boundary); mv(st.x_exp); mv(st.lm_mask); mv(st.top_nodes);
     for (const auto& lv : st.ml) { mv(lv.node_ptr); mv(lv.edge_lm); mv(lv.ref_ptr); mv(lv.ref); }
     std::printf("structure checksum %016llx\n", (unsigned long long)h);
+    // ... and of the parsed graph (offsets, per-type indices, decoded values, topology hash)
+    h = 1469598103934665603ull;
+    mv(g.edge_off); mv(g.edge_slot); mv(g.od_i); mv(g.od_j); mv(g.od_zinv); mv(g.od_w); mv(g.le_i); mv(g.le_l); mv(g.le_z); mv(g.le_w); mv(g.fixed); mv(g.req_vertex);
+    mix(&g.topo_hash, 8); mix(&g.reply_bytes, 4);
+    std::printf("parse checksum %016llx (Eo %u El %u hash %016llx)\n", (unsigned long long)h, g.Eo, g.El, (unsigned long long)g.topo_hash);
     return 0;
 }

@@ -9,6 +9,7 @@
 #include <unistd.h>
 
 #include <algorithm>
+#include <chrono>
 #include <cmath>
 #include <cstdio>
 #include <cstdlib>
@@ -755,7 +756,13 @@ int tsb_load_wire(tsb_ctx* c, const void* payload, uint32_t nbytes) {
     const uint32_t ml_top = ((c->world <= 1 || c->use_p2p) && c->use_coarse && !c->force_phased && !(ns && ns[0] == '1')) ? top_default : 0;
     build_structure(c->g, (uint32_t)c->rank, (uint32_t)c->world, c->st, c->world <= 1 ? res_nb : 0, &c->rp, ml_top);
     c->st_world = c->world; c->st_rank = c->rank;
-    { const int rc = upload_graph(c); c->topo_valid = rc == TSB_OK; return rc; }
+    {   const bool tm = std::getenv("TSB_HOST_TIMING") != nullptr;        // parse_wire and build_structure print their own sections
+        const auto t0 = std::chrono::steady_clock::now();
+        const int rc = upload_graph(c); c->topo_valid = rc == TSB_OK;
+        if (tm) { cudaStreamSynchronize(c->stream);
+            std::fprintf(stderr, "[tsb] upload_graph (gathers + host-to-device copies, synchronised) %8.1f ms\n",
+                         std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count()); }
+        return rc; }
 }
 
 int tsb_load_soa(tsb_ctx* c, const tsb_graph_soa* s) {

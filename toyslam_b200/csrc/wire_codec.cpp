@@ -4,6 +4,9 @@
 // (SerializeGraphFuncCpu.h:10-65).  Unlike the reference parser this one is bounds-checked and
 // never throws: a malformed payload is a returned error.
 #include "host_graph.h"
+#include <chrono>
+#include <cstdio>
+#include <cstdlib>
 
 #include <algorithm>
 #include <cmath>
@@ -48,6 +51,10 @@ struct IdMap {
 }  // namespace
 
 bool parse_wire(const uint8_t* buf, uint32_t nbytes, HostGraph& g, std::string& err) {
+    const bool tm_on = std::getenv("TSB_HOST_TIMING") != nullptr;
+    auto tm_t = std::chrono::steady_clock::now();
+    auto lap = [&](const char* what) { if (!tm_on) return; const auto n = std::chrono::steady_clock::now();
+        std::fprintf(stderr, "[tsb] parse_wire %-28s %8.1f ms\n", what, std::chrono::duration<double, std::milli>(n - tm_t).count()); tm_t = n; };
     g.reset();
     Reader r{buf, buf + nbytes};
     auto fail = [&](const char* m) { err = m; return false; };
@@ -103,6 +110,7 @@ bool parse_wire(const uint8_t* buf, uint32_t nbytes, HostGraph& g, std::string& 
     // a dropped duplicate must not reuse a survivor's slot in the reply
     for (uint32_t i = 0; i < V; ++i) if (g.req_vertex[i] != 0xFFFFFFFFu && m.find(vid[i]) != g.req_vertex[i]) g.req_vertex[i] = 0xFFFFFFFFu;
 
+    lap("vertices");
     g.edges_offset = (uint32_t)(r.p - buf);
     if (!r.have(4)) return fail("truncated payload: edge count");
     const uint32_t E = r.u32();
@@ -112,7 +120,42 @@ bool parse_wire(const uint8_t* buf, uint32_t nbytes, HostGraph& g, std::string& 
     // up to the edge dimension), so the offsets come from one cheap scan; the values are then decoded in parallel.
     g.edge_off.resize(E); g.edge_slot.resize(E);
     uint32_t nO = 0, nL = 0;
-    for (uint32_t i = 0; i < E; ++i) {
+    // Runs of records in the layout the reference client writes (graph_to_bytes.py:44-63: ODOM as a 3x3 matrix + 3 information
+    // values = 76 B, LM as (range, bearing) + 2 = 44 B) are recognised at a fixed stride: the header words of a whole block of
+    // records are compared in parallel (no pointer chasing from record to record, which is what bounds the scan below at ~10 ns
+    // per record), and the block's offsets are written by the same loop.  Anything else -- and the first record that breaks a
+    // run -- goes through the record-by-record scan, which also produces the error messages.
+    auto std_size = [&](const uint8_t* q, size_t left, uint32_t& type) -> uint32_t {
+        if (left < 76) return 0;
+        uint32_t w[5]; std::memcpy(w, q, 4); std::memcpy(w + 1, q + 12, 8);
+        type = w[0];
+        if (w[0] == 0 && w[1] == 3 && w[2] == 3) { std::memcpy(w + 3, q + 56, 8); return (w[3] == 0 && w[4] == 3) ? 76u : 0u; }
+        if (w[0] == 1 && w[1] == 0 && w[2] == 2) { std::memcpy(w + 3, q + 28, 8); return (w[3] == 0 && w[4] == 2) ? 44u : 0u; }
+        return 0;
+    };
+    constexpr uint32_t kRunBlock = 1u << 16;
+    for (uint32_t i = 0; i < E;) {
+        {   // fast path: a block of same-layout records
+            uint32_t type = 0;
+            const size_t left = (size_t)(r.end - r.p);
+            const uint32_t S = std_size(r.p, left, type);
+            const uint32_t cnt = S ? (uint32_t)std::min<uint64_t>(std::min<uint64_t>(kRunBlock, E - i), (left - 76 + S) / S) : 0;   // every record of the block has 76 readable bytes
+            if (cnt >= 1024) {
+                const uint8_t* base = r.p;
+                uint32_t first_bad = cnt;
+#pragma omp parallel for schedule(static) reduction(min : first_bad)
+                for (long long k = 0; k < (long long)cnt; ++k) {
+                    uint32_t t2 = 0;
+                    if (std_size(base + (size_t)k * S, 76, t2) != S || t2 != type) { first_bad = std::min(first_bad, (uint32_t)k); continue; }
+                    g.edge_off[i + k] = (uint32_t)(base - buf) + (uint32_t)k * S;
+                    g.edge_slot[i + k] = (type == 0 ? nO : nL) + (uint32_t)k;
+                }
+                if (first_bad > 0) {
+                    (type == 0 ? nO : nL) += first_bad; i += first_bad; r.p += (size_t)first_bad * S;
+                    continue;
+                }
+            }
+        }
         if (!r.have(20)) return fail("truncated payload: edge header");
         g.edge_off[i] = (uint32_t)(r.p - buf);
         const uint32_t type = r.u32(); r.p += 8; const uint32_t rows = r.u32(), cols = r.u32();
@@ -132,8 +175,10 @@ bool parse_wire(const uint8_t* buf, uint32_t nbytes, HostGraph& g, std::string& 
         if (!r.have(4ull * ci)) return fail("truncated payload: information");
         r.p += 4ull * ci;
         g.edge_slot[i] = type == 0 ? nO++ : nL++;
+        ++i;
     }
     g.Eo = nO; g.El = nL;
+    lap("edge offset scan");
     g.od_i.resize(nO); g.od_j.resize(nO); g.od_zinv.resize(6ull * nO); g.od_w.resize(3ull * nO);
     g.le_i.resize(nL); g.le_l.resize(nL); g.le_z.resize(2ull * nL); g.le_w.resize(2ull * nL);
     // ---- pass 2 (parallel over edges): ids -> canonical indices, values, topology hash ------------------------------------
@@ -200,6 +245,7 @@ bool parse_wire(const uint8_t* buf, uint32_t nbytes, HostGraph& g, std::string& 
         const uint64_t rb = 4 + 20ull * g.P + 16ull * g.L + 4 + 76ull * nO + 44ull * nL + 4 + 4ull * F;
         g.reply_bytes = rb > 0xFFFFFFFFull ? 0xFFFFFFFFu : (uint32_t)rb;
     }
+    lap("decode + copy + reply size");
     return true;
 }
 
